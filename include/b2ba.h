@@ -1,0 +1,112 @@
+/* b2ba -- B200-native bundle-adjustment engine: C ABI (the drop-in boundary).
+ *
+ * The reference (cteufel13/VisualOdometry) has NO optimiser API; the seam this
+ * library plugs into is the tail of VisualOdometry._create_keyframe (src/modules/vo.py:252-288,
+ * insertion point vo.py:286-288), and the data it exchanges is the state the reference holds:
+ *   - camera pose  self.T_wc / keyframe["T_wc"] 4x4 f64 (vo.py:19,57,286); BA optimises
+ *     T_cw = inv(T_wc) = [R|t] as used for projection (vo.py:260-261, frontend.py:128-139)
+ *   - landmarks    self.map_points: id -> xyz f64 (vo.py:17,281)
+ *   - observations keyframe["feats"]["keypoints"] (1,N,2) f32 + keyframe["ids"] (N,) (vo.py:53,57)
+ *   - intrinsics   self.K 3x3 f64, zero distortion (vo.py:11,139; dataset_loader.py:52-54)
+ * The Python binding a maintainer adds on the reference side is shown in INTEGRATION.md.
+ *
+ * Plain pointers and sizes only; no torch / C++ types.  All functions return 0 on success,
+ * <0 on error (see B2BA_E_*); b2ba_solve returns >0 solver outcomes.  A handle owns one problem
+ * (single or batched) with all iteration state resident on its device.  One handle <-> one CUDA
+ * stream at a time; a handle is not thread-safe; distinct handles are independent.
+ */
+#ifndef B2BA_H_
+#define B2BA_H_
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct b2ba b2ba_t;
+
+enum { B2BA_OK = 0, B2BA_E_INVALID = -1, B2BA_E_CUDA = -2, B2BA_E_NCCL = -3, B2BA_E_DUPLICATE = -4,
+       B2BA_E_STATE = -5, B2BA_E_UNSUPPORTED = -6 };
+/* solver outcomes (b2ba_summary.status; b2ba_solve returns the max over windows) */
+enum { B2BA_MAX_ITERS = 1, B2BA_CONVERGED = 2, B2BA_NUMERICAL_FAILURE = 3 };
+enum { B2BA_LOSS_TRIVIAL = 0, B2BA_LOSS_HUBER = 1 };
+enum { B2BA_SOLVER_AUTO = 0, B2BA_SOLVER_WINDOW = 1, B2BA_SOLVER_PCG = 2 };
+enum { B2BA_MEM_HOST = 0, B2BA_MEM_DEVICE = 1 };
+
+/* Spec a0 parameters. Zero tolerances disable the test (parity / bench mode). */
+typedef struct b2ba_options {
+  int32_t max_iters;      /* default 10 */
+  int32_t loss;           /* B2BA_LOSS_* */
+  double loss_scale;      /* Huber a, pixels (config.py:32,35 scale) */
+  double z_min;           /* cheirality gate, config.py:31 min_depth = 1e-3 */
+  double init_mu;         /* initial trust-region radius, 1e4 */
+  double ftol, gtol, ptol;
+  int32_t solver;         /* B2BA_SOLVER_* */
+  int32_t pcg_max_iters;  /* 200 */
+  double pcg_tol;         /* 1e-10 */
+  int32_t flags;          /* bit0: record per-iteration history (b2ba_dump B2BA_D_HIST_*) */
+  int32_t pad_;
+} b2ba_options;
+
+typedef struct b2ba_summary {
+  int32_t status, iterations, accepted, rejected, n_invalid, pcg_iters;
+  double initial_cost, final_cost, final_mu;
+} b2ba_summary;
+
+void b2ba_default_options(b2ba_options* o);
+
+int b2ba_create(b2ba_t** out, int device, const b2ba_options* opts);
+void b2ba_destroy(b2ba_t* h);
+const char* b2ba_last_error(const b2ba_t* h);
+
+/* One problem.  poses_cw: Nc x 12 row-major [R(9) | t(3)] (world->camera); points: Np x 3;
+ * obs_cam / obs_pt: No int32; obs_uv: No x 2 float32 (u,v pixels); fixed_cam: Nc bytes (1 = gauge-
+ * fixed); intr: fx, fy, cx, cy.  mem: B2BA_MEM_HOST or B2BA_MEM_DEVICE for ALL array arguments.
+ * Inputs are copied into engine-owned SoA device arrays; caller pointers are not retained. */
+int b2ba_set_problem(b2ba_t* h, int32_t Nc, int32_t Np, int64_t No, const double* poses_cw,
+                     const double* points, const int32_t* obs_cam, const int32_t* obs_pt,
+                     const float* obs_uv, const uint8_t* fixed_cam, const double intr[4], int mem);
+
+/* B independent problems (C4), CSR-packed: cam_off/pt_off (B+1 int32), obs_off (B+1 int64) are
+ * always HOST arrays; obs_cam/obs_pt are window-LOCAL indices. */
+int b2ba_set_problem_batch(b2ba_t* h, int32_t B, const int32_t* cam_off, const int32_t* pt_off,
+                           const int64_t* obs_off, const double* poses_cw, const double* points,
+                           const int32_t* obs_cam, const int32_t* obs_pt, const float* obs_uv,
+                           const uint8_t* fixed_cam, const double intr[4], int mem);
+
+/* Replace poses / points (same sizes) without rebuilding the index; NULL keeps the current. */
+int b2ba_set_state(b2ba_t* h, const double* poses_cw, const double* points, int mem);
+/* Restore the state given at set_problem / set_state (device-to-device). */
+int b2ba_reset(b2ba_t* h);
+
+/* Run LM for max_iters (<=0: options.max_iters) on `cuda_stream` (cudaStream_t, NULL = default).
+ * summaries: HOST array of B entries (1 for a single problem) or NULL.  With NULL the call only
+ * enqueues work (no synchronisation); otherwise it synchronises the stream and fills them. */
+int b2ba_solve(b2ba_t* h, int32_t max_iters, b2ba_summary* summaries, void* cuda_stream);
+int b2ba_get_summaries(b2ba_t* h, b2ba_summary* summaries);
+
+int b2ba_get(b2ba_t* h, double* poses_cw, double* points, int mem);
+
+/* Per-stage intermediates for parity tests.  `what` selects the array; `bytes` is the size of dst
+ * (HOST memory); returns the number of bytes written or <0. */
+enum {
+  B2BA_D_PM_PERM = 1, B2BA_D_PT_PTR, B2BA_D_CM_PERM, B2BA_D_CAM_PTR, B2BA_D_FIDX, B2BA_D_BLK_PTR,
+  B2BA_D_BLK_COL,                       /* a8 index arrays (int32) */
+  B2BA_D_RESIDUALS = 16, B2BA_D_WEIGHTS, B2BA_D_JC, B2BA_D_JP,   /* a1, original obs order */
+  B2BA_D_B = 32, B2BA_D_GC, B2BA_D_C, B2BA_D_GP, B2BA_D_S, B2BA_D_GRED, B2BA_D_DC, B2BA_D_DP,
+  B2BA_D_SCALARS,                       /* one LM iteration at init_mu from the CURRENT state */
+  B2BA_D_HIST_COST = 64, B2BA_D_HIST_MU, B2BA_D_HIST_ACCEPT      /* B x 64 */
+};
+int64_t b2ba_dump(b2ba_t* h, int what, void* dst, int64_t bytes);
+
+/* Multi-GPU (C5 observation sharding): nccl_unique_id = the 128 bytes of an ncclUniqueId created by
+ * rank 0 and broadcast by the caller (e.g. torch.distributed); must be called before set_problem.
+ * Every rank passes the FULL problem to set_problem; the engine keeps its point range. */
+int b2ba_create_comm(b2ba_t* h, const void* nccl_unique_id, int rank, int nranks);
+
+int b2ba_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,228 @@
+"""Host-side mirror of the optimiser interface (SURVEY §8 row b).
+
+The reference has no optimiser API; modules are plain classes taking ``(K, config)``
+(`src/modules/vo.py:10`, `src/modules/frontend.py:10`) and functions take / return numpy f64
+arrays plus a config dataclass (`frontend.py:115-122`, `src/config/config.py:4-46`).
+``BundleAdjuster(K, BAConfig)`` follows that style.  All arithmetic happens in libb2ba.so
+(CUDA, sm_100a) through the C ABI in include/b2ba.h; this file only packs arrays.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass, field
+
+import numpy as np
+
+from . import _lib
+
+try:  # torch is plumbing (device memory / streams); numpy inputs work without it
+    import torch
+except Exception:  # pragma: no cover
+    torch = None
+
+
+@dataclass
+class BAConfig:
+    """BA options, same dataclass style as the reference's VOConfig (config.py:4-46)."""
+
+    window: int = 10               # keyframes kept by the adapter's deque
+    max_iters: int = 10
+    loss: str = "trivial"          # "trivial" | "huber"
+    loss_scale: float = 1.0        # Huber a, pixels (cf. config.py:32,35 pixel thresholds)
+    z_min: float = 1e-3            # = VOConfig.min_depth (config.py:31)
+    init_radius: float = 1e4
+    ftol: float = 0.0
+    gtol: float = 0.0
+    ptol: float = 0.0
+    solver: str = "auto"           # "auto" | "chol" (window kernel) | "pcg" (large path)
+    pcg_max_iters: int = 200
+    pcg_tol: float = 1e-10
+    device: int = 0
+    record_history: bool = False
+
+    def to_options(self) -> _lib.Options:
+        return _lib.Options(self.max_iters, {"trivial": 0, "huber": 1}[self.loss], self.loss_scale,
+                            self.z_min, self.init_radius, self.ftol, self.gtol, self.ptol,
+                            {"auto": 0, "chol": 1, "pcg": 2}[self.solver], self.pcg_max_iters,
+                            self.pcg_tol, 1 if self.record_history else 0, 0)
+
+
+@dataclass
+class BASummary:
+    status: int
+    iterations: int
+    accepted: int
+    rejected: int
+    n_invalid: int
+    pcg_iters: int
+    initial_cost: float
+    final_cost: float
+    final_mu: float
+
+    @property
+    def ok(self):  # numerical failure -> the VO adapter skips the write-back
+        return self.status in (_lib.MAX_ITERS, _lib.CONVERGED)
+
+
+@dataclass
+class BAResult:
+    T_cw: np.ndarray            # (Nc,4,4) f64
+    points: np.ndarray          # (Np,3) f64
+    summary: BASummary
+    summaries: list = field(default_factory=list)   # per window (batched problems)
+
+
+def poses_from_T(T_cw) -> np.ndarray:
+    """(Nc,4,4) world->camera matrices -> (Nc,12) [R row-major | t]."""
+    T = np.asarray(T_cw, np.float64).reshape(-1, 4, 4)
+    return np.ascontiguousarray(np.concatenate([T[:, :3, :3].reshape(-1, 9), T[:, :3, 3]], axis=1))
+
+
+def T_from_poses(poses) -> np.ndarray:
+    P = np.asarray(poses, np.float64).reshape(-1, 12)
+    T = np.tile(np.eye(4), (P.shape[0], 1, 1))
+    T[:, :3, :3] = P[:, :9].reshape(-1, 3, 3)
+    T[:, :3, 3] = P[:, 9:]
+    return T
+
+
+def _is_cuda_tensor(a):
+    return torch is not None and isinstance(a, torch.Tensor) and a.is_cuda
+
+
+class _Arg:
+    """Pointer + keep-alive for one array argument, host (numpy) or device (torch CUDA)."""
+
+    def __init__(self, a, np_dtype, torch_dtype, device_mode):
+        if device_mode:
+            t = a if isinstance(a, torch.Tensor) else torch.as_tensor(np.asarray(a))
+            t = t.to(device="cuda", dtype=getattr(torch, torch_dtype)).contiguous()
+            self.keep, self.ptr = t, C.c_void_p(t.data_ptr())
+        else:
+            if torch is not None and isinstance(a, torch.Tensor):
+                a = a.detach().cpu().numpy()
+            n = np.ascontiguousarray(a, dtype=np_dtype)
+            self.keep, self.ptr = n, C.c_void_p(n.ctypes.data)
+
+
+class BundleAdjuster:
+    """Windowed / batched / large-scale BA on one B200.  Drop-in for the (missing) optimiser
+    stage at the tail of VisualOdometry._create_keyframe (vo.py:286-288)."""
+
+    def __init__(self, K: np.ndarray, config: BAConfig | None = None):
+        self.config = config or BAConfig()
+        K = np.asarray(K, np.float64)
+        self.intr = np.array([K[0, 0], K[1, 1], K[0, 2], K[1, 2]], np.float64)   # zero skew/distortion (vo.py:139)
+        self._lib = _lib.load()
+        self._h = C.c_void_p()
+        opts = self.config.to_options()
+        rc = self._lib.b2ba_create(C.byref(self._h), self.config.device, C.byref(opts))
+        if rc != _lib.OK:
+            raise RuntimeError(f"b2ba_create failed ({rc}): a CUDA device is required (no CPU fallback)")
+        self._nb = 0
+        self._shape = None
+
+    def close(self):
+        if getattr(self, "_h", None) and self._h.value:
+            self._lib.b2ba_destroy(self._h)
+            self._h = C.c_void_p()
+
+    __del__ = close
+
+    # ------------------------------------------------------------------ low level
+    def _check(self, rc, what):
+        if rc < 0:
+            msg = self._lib.b2ba_last_error(self._h)
+            raise RuntimeError(f"{what} failed ({rc}): {msg.decode() if msg else ''}")
+        return rc
+
+    def set_problem(self, poses, points, obs_cam, obs_pt, obs_uv, fixed_cam, cam_off=None, pt_off=None,
+                    obs_off=None):
+        """poses (Nc,12) [R|t] world->camera; batched when the CSR offsets are given."""
+        dev = any(_is_cuda_tensor(a) for a in (poses, points, obs_cam, obs_pt, obs_uv))
+        a = [_Arg(poses, np.float64, "float64", dev), _Arg(points, np.float64, "float64", dev),
+             _Arg(obs_cam, np.int32, "int32", dev), _Arg(obs_pt, np.int32, "int32", dev),
+             _Arg(obs_uv, np.float32, "float32", dev), _Arg(fixed_cam, np.uint8, "uint8", dev)]
+        nc = int(np.prod(a[0].keep.shape)) // 12
+        npts = int(np.prod(a[1].keep.shape)) // 3
+        no = int(np.prod(a[2].keep.shape))
+        intr = self.intr.ctypes.data_as(C.POINTER(C.c_double))
+        mem = _lib.MEM_DEVICE if dev else _lib.MEM_HOST
+        if cam_off is None:
+            rc = self._lib.b2ba_set_problem(self._h, nc, npts, no, *[x.ptr for x in a], intr, mem)
+            self._nb = 1
+        else:
+            co = np.ascontiguousarray(cam_off, np.int32)
+            po = np.ascontiguousarray(pt_off, np.int32)
+            oo = np.ascontiguousarray(obs_off, np.int64)
+            rc = self._lib.b2ba_set_problem_batch(self._h, len(co) - 1, co.ctypes.data, po.ctypes.data,
+                                                  oo.ctypes.data, *[x.ptr for x in a], intr, mem)
+            self._nb = len(co) - 1
+        self._check(rc, "b2ba_set_problem")
+        self._shape = (nc, npts, no)
+        return self
+
+    def reset(self):
+        self._check(self._lib.b2ba_reset(self._h), "b2ba_reset")
+
+    def solve(self, max_iters=0, stream=None, wait=True):
+        """Run LM. wait=False only enqueues (summaries via .summaries())."""
+        sp = C.c_void_p(stream) if stream else None
+        if not wait:
+            self._check(self._lib.b2ba_solve(self._h, max_iters, None, sp), "b2ba_solve")
+            return None
+        sm = (_lib.Summary * self._nb)()
+        self._check(self._lib.b2ba_solve(self._h, max_iters, sm, sp), "b2ba_solve")
+        return [self._summary(s) for s in sm]
+
+    def summaries(self):
+        sm = (_lib.Summary * self._nb)()
+        self._check(self._lib.b2ba_get_summaries(self._h, sm), "b2ba_get_summaries")
+        return [self._summary(s) for s in sm]
+
+    @staticmethod
+    def _summary(s):
+        return BASummary(s.status, s.iterations, s.accepted, s.rejected, s.n_invalid, s.pcg_iters,
+                         s.initial_cost, s.final_cost, s.final_mu)
+
+    def get(self, device=False):
+        nc, npts, _ = self._shape
+        if device:
+            poses = torch.empty((nc, 12), dtype=torch.float64, device="cuda")
+            pts = torch.empty((npts, 3), dtype=torch.float64, device="cuda")
+            self._check(self._lib.b2ba_get(self._h, poses.data_ptr(), pts.data_ptr(), _lib.MEM_DEVICE), "b2ba_get")
+        else:
+            poses, pts = np.empty((nc, 12)), np.empty((npts, 3))
+            self._check(self._lib.b2ba_get(self._h, poses.ctypes.data, pts.ctypes.data, _lib.MEM_HOST), "b2ba_get")
+        return poses, pts
+
+    def dump(self, what: str, shape, dtype=np.float64):
+        out = np.zeros(shape, dtype)
+        n = self._lib.b2ba_dump(self._h, _lib.D[what], out.ctypes.data, out.nbytes)
+        self._check(n, f"b2ba_dump({what})")
+        if n != out.nbytes:
+            raise RuntimeError(f"b2ba_dump({what}): wrote {n} bytes, expected {out.nbytes}")
+        return out
+
+    # ------------------------------------------------------------------ the drop-in call
+    def optimize(self, T_cw, points, obs_cam, obs_pt, obs_uv, fixed_cam) -> BAResult:
+        """T_cw (Nc,4,4) f64, points (Np,3) f64, obs_cam/obs_pt (No,) i32, obs_uv (No,2) f32,
+        fixed_cam (Nc,) bool -> refined T_cw / points + summary.  numpy (host) or torch CUDA."""
+        if _is_cuda_tensor(T_cw):
+            poses = torch.cat([T_cw[:, :3, :3].reshape(-1, 9), T_cw[:, :3, 3]], dim=1).contiguous()
+        else:
+            poses = poses_from_T(T_cw)
+        fixed = fixed_cam if _is_cuda_tensor(fixed_cam) else np.asarray(fixed_cam).astype(np.uint8)
+        self.set_problem(poses, points, obs_cam, obs_pt, obs_uv, fixed)
+        sm = self.solve()
+        poses_o, pts_o = self.get()
+        return BAResult(T_from_poses(poses_o), pts_o, sm[0], sm)
+
+    def optimize_batch(self, batch) -> BAResult:
+        """C4: a synth.BABatch-like object with CSR offsets; poses in (Nc,12) layout."""
+        self.set_problem(batch.poses, batch.points, batch.obs_cam, batch.obs_pt, batch.obs_uv,
+                         batch.fixed_cam, batch.cam_off, batch.pt_off, batch.obs_off)
+        sm = self.solve()
+        poses_o, pts_o = self.get()
+        worst = max(sm, key=lambda s: s.status)
+        return BAResult(T_from_poses(poses_o), pts_o, worst, sm)

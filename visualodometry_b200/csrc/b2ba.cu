@@ -1,0 +1,421 @@
+// C ABI of the b2ba engine (include/b2ba.h): handle, problem upload, solve, read-back, dumps.
+// All compute is CUDA (sm_100a); there is NO CPU fallback -- every entry point that needs the
+// device fails with B2BA_E_CUDA when it is missing.
+#include "../../include/b2ba.h"
+
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "ba_index.cuh"
+#include "ba_large.cuh"
+#include "ba_window.cuh"
+
+using namespace b2;
+
+namespace {
+
+template <class T>
+struct DevBuf {
+  T* p = nullptr;
+  size_t n = 0;
+  cudaError_t alloc(size_t count) {
+    if (count <= n && p) return cudaSuccess;
+    release();
+    cudaError_t e = cudaMalloc((void**)&p, (count ? count : 1) * sizeof(T));
+    if (e == cudaSuccess) n = count;
+    else p = nullptr;
+    return e;
+  }
+  void release() { if (p) cudaFree(p); p = nullptr; n = 0; }
+  ~DevBuf() { release(); }
+};
+
+enum Path { PATH_NONE = 0, PATH_WIN_SMALL, PATH_WIN_BIG, PATH_LARGE };
+
+}  // namespace
+
+struct b2ba {
+  int device = 0;
+  b2ba_options opt;
+  std::string err;
+  int B = 0, nc_tot = 0, np_tot = 0;
+  long long no = 0;
+  int max_nfree = 0, max_nc = 0;
+  Path path = PATH_NONE;
+  double intr[4] = {0, 0, 0, 0};
+  std::vector<int> h_cam_off, h_pt_off;
+  std::vector<long long> h_obs_off;
+  std::vector<unsigned char> h_fixed;
+  DevBuf<int> d_cam_off, d_pt_off, d_obs_cam, d_obs_pt, d_pt_ptr, d_cam_ptr, d_flags, d_hist_accept;
+  DevBuf<long long> d_obs_off;
+  DevBuf<float2> d_uv;
+  DevBuf<unsigned char> d_fixed;
+  DevBuf<double> d_poses, d_poses0, d_pts0, d_pts1, d_ptsinit, d_scratch, d_hist_cost, d_hist_mu, d_dbg;
+  DevBuf<ObsRec> d_pm, d_cm;
+  DevBuf<b2ba_summary> d_summ;
+  LargeState large;
+  cudaStream_t last_stream = nullptr;
+  bool solved = false;
+  // multi-GPU
+  int rank = 0, nranks = 1;
+  void* nccl_comm = nullptr;
+};
+
+namespace {
+
+int fail(b2ba* h, int code, const std::string& msg) {
+  if (h) h->err = msg;
+  return code;
+}
+int cuda_fail(b2ba* h, cudaError_t e, const char* where) {
+  return fail(h, B2BA_E_CUDA, std::string(where) + ": " + cudaGetErrorString(e));
+}
+#define CU(x, where) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) return cuda_fail(h, e_, where); } while (0)
+
+Params make_params(const b2ba* h, int max_iters) {
+  Params P;
+  P.fx = h->intr[0]; P.fy = h->intr[1]; P.cx = h->intr[2]; P.cy = h->intr[3];
+  P.z_min = h->opt.z_min; P.huber_a = h->opt.loss_scale; P.init_mu = h->opt.init_mu;
+  P.ftol = h->opt.ftol; P.gtol = h->opt.gtol; P.ptol = h->opt.ptol;
+  P.loss = h->opt.loss; P.max_iters = max_iters > 0 ? max_iters : h->opt.max_iters;
+  return P;
+}
+
+IndexIn make_index_in(const b2ba* h) {
+  IndexIn in;
+  in.nb = h->B; in.nc_tot = h->nc_tot; in.np_tot = h->np_tot; in.no = h->no;
+  in.cam_off = h->d_cam_off.p; in.pt_off = h->d_pt_off.p; in.obs_off = h->d_obs_off.p;
+  in.obs_cam = h->d_obs_cam.p; in.obs_pt = h->d_obs_pt.p; in.obs_uv = h->d_uv.p;
+  return in;
+}
+
+WinData make_win(b2ba* h, bool hist, double* dbg) {
+  WinData d;
+  d.nb = h->B; d.cam_off = h->d_cam_off.p; d.pt_off = h->d_pt_off.p;
+  d.pm = h->d_pm.p; d.pt_ptr = h->d_pt_ptr.p; d.cm = h->d_cm.p; d.cam_ptr = h->d_cam_ptr.p;
+  d.fixed = h->d_fixed.p; d.poses = h->d_poses.p; d.pts[0] = h->d_pts0.p; d.pts[1] = h->d_pts1.p;
+  d.pt_scratch = h->d_scratch.p; d.summaries = h->d_summ.p;
+  d.hist_cost = hist ? h->d_hist_cost.p : nullptr;
+  d.hist_mu = hist ? h->d_hist_mu.p : nullptr;
+  d.hist_accept = hist ? h->d_hist_accept.p : nullptr;
+  d.dbg = dbg;
+  return d;
+}
+
+cudaMemcpyKind in_kind(int mem) { return mem == B2BA_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice; }
+cudaMemcpyKind out_kind(int mem) { return mem == B2BA_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost; }
+
+}  // namespace
+
+extern "C" {
+
+int b2ba_version(void) { return 100; }
+
+void b2ba_default_options(b2ba_options* o) {
+  std::memset(o, 0, sizeof(*o));
+  o->max_iters = 10; o->loss = B2BA_LOSS_TRIVIAL; o->loss_scale = 1.0; o->z_min = 1e-3;
+  o->init_mu = 1e4; o->solver = B2BA_SOLVER_AUTO; o->pcg_max_iters = 200; o->pcg_tol = 1e-10;
+}
+
+int b2ba_create(b2ba_t** out, int device, const b2ba_options* opts) {
+  if (!out) return B2BA_E_INVALID;
+  *out = nullptr;
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || device < 0 || device >= ndev) return B2BA_E_CUDA;   // no CPU fallback
+  e = cudaSetDevice(device);
+  if (e != cudaSuccess) return B2BA_E_CUDA;
+  b2ba* h = new b2ba();
+  h->device = device;
+  if (opts) h->opt = *opts; else b2ba_default_options(&h->opt);
+  *out = h;
+  return B2BA_OK;
+}
+
+void b2ba_destroy(b2ba_t* h) {
+  if (!h) return;
+  cudaSetDevice(h->device);
+  delete h;
+}
+
+const char* b2ba_last_error(const b2ba_t* h) { return h ? h->err.c_str() : "null handle"; }
+
+int b2ba_set_problem_batch(b2ba_t* h, int32_t B, const int32_t* cam_off, const int32_t* pt_off,
+                           const int64_t* obs_off, const double* poses_cw, const double* points,
+                           const int32_t* obs_cam, const int32_t* obs_pt, const float* obs_uv,
+                           const uint8_t* fixed_cam, const double intr[4], int mem) {
+  if (!h) return B2BA_E_INVALID;
+  if (B < 1 || !cam_off || !pt_off || !obs_off || !poses_cw || !points || !fixed_cam || !intr)
+    return fail(h, B2BA_E_INVALID, "set_problem: null argument or B < 1");
+  if (cam_off[0] != 0 || pt_off[0] != 0 || obs_off[0] != 0) return fail(h, B2BA_E_INVALID, "offsets must start at 0");
+  for (int b = 0; b < B; ++b)
+    if (cam_off[b + 1] < cam_off[b] || pt_off[b + 1] < pt_off[b] || obs_off[b + 1] < obs_off[b])
+      return fail(h, B2BA_E_INVALID, "offsets must be non-decreasing");
+  const long long no = obs_off[B];
+  if (no > 0 && (!obs_cam || !obs_pt || !obs_uv)) return fail(h, B2BA_E_INVALID, "null observation arrays");
+  if (no >= (1ll << 31)) return fail(h, B2BA_E_UNSUPPORTED, "more than 2^31 observations per handle");
+  CU(cudaSetDevice(h->device), "cudaSetDevice");
+  h->B = B; h->nc_tot = cam_off[B]; h->np_tot = pt_off[B]; h->no = no;
+  h->solved = false;
+  std::memcpy(h->intr, intr, 4 * sizeof(double));
+  h->h_cam_off.assign(cam_off, cam_off + B + 1);
+  h->h_pt_off.assign(pt_off, pt_off + B + 1);
+  h->h_obs_off.assign(obs_off, obs_off + B + 1);
+  const cudaMemcpyKind k = in_kind(mem);
+  const size_t nc = h->nc_tot, np = h->np_tot;
+  CU(h->d_cam_off.alloc(B + 1), "alloc"); CU(h->d_pt_off.alloc(B + 1), "alloc"); CU(h->d_obs_off.alloc(B + 1), "alloc");
+  CU(h->d_fixed.alloc(nc), "alloc"); CU(h->d_poses.alloc(nc * 12), "alloc"); CU(h->d_poses0.alloc(nc * 12), "alloc");
+  CU(h->d_pts0.alloc(np * 3), "alloc"); CU(h->d_pts1.alloc(np * 3), "alloc"); CU(h->d_ptsinit.alloc(np * 3), "alloc");
+  CU(h->d_scratch.alloc(np * kPtScratch), "alloc");
+  CU(h->d_obs_cam.alloc(no), "alloc"); CU(h->d_obs_pt.alloc(no), "alloc"); CU(h->d_uv.alloc(no), "alloc");
+  CU(h->d_pm.alloc(no), "alloc"); CU(h->d_cm.alloc(no), "alloc");
+  CU(h->d_pt_ptr.alloc(np + 1), "alloc"); CU(h->d_cam_ptr.alloc(nc + 1), "alloc"); CU(h->d_flags.alloc(2), "alloc");
+  CU(h->d_summ.alloc(B), "alloc");
+  CU(cudaMemcpy(h->d_cam_off.p, cam_off, (B + 1) * sizeof(int), cudaMemcpyHostToDevice), "copy offsets");
+  CU(cudaMemcpy(h->d_pt_off.p, pt_off, (B + 1) * sizeof(int), cudaMemcpyHostToDevice), "copy offsets");
+  CU(cudaMemcpy(h->d_obs_off.p, obs_off, (B + 1) * sizeof(long long), cudaMemcpyHostToDevice), "copy offsets");
+  CU(cudaMemcpy(h->d_fixed.p, fixed_cam, nc, k), "copy fixed");
+  CU(cudaMemcpy(h->d_poses.p, poses_cw, nc * 12 * sizeof(double), k), "copy poses");
+  CU(cudaMemcpy(h->d_pts0.p, points, np * 3 * sizeof(double), k), "copy points");
+  if (no) {
+    CU(cudaMemcpy(h->d_obs_cam.p, obs_cam, no * sizeof(int), k), "copy obs_cam");
+    CU(cudaMemcpy(h->d_obs_pt.p, obs_pt, no * sizeof(int), k), "copy obs_pt");
+    CU(cudaMemcpy(h->d_uv.p, obs_uv, no * sizeof(float2), k), "copy obs_uv");
+  }
+  CU(cudaMemcpy(h->d_poses0.p, h->d_poses.p, nc * 12 * sizeof(double), cudaMemcpyDeviceToDevice), "keep poses");
+  CU(cudaMemcpy(h->d_ptsinit.p, h->d_pts0.p, np * 3 * sizeof(double), cudaMemcpyDeviceToDevice), "keep points");
+  // gauge / path selection needs the fixed mask on the host
+  h->h_fixed.resize(nc);
+  CU(cudaMemcpy(h->h_fixed.data(), h->d_fixed.p, nc, cudaMemcpyDeviceToHost), "read fixed");
+  h->max_nfree = 0; h->max_nc = 0;
+  for (int b = 0; b < B; ++b) {
+    int nf = 0;
+    for (int c = cam_off[b]; c < cam_off[b + 1]; ++c) nf += h->h_fixed[c] ? 0 : 1;
+    if (nf > h->max_nfree) h->max_nfree = nf;
+    if (cam_off[b + 1] - cam_off[b] > h->max_nc) h->max_nc = cam_off[b + 1] - cam_off[b];
+  }
+  // a8: index
+  IndexOut io{h->d_pm.p, h->d_pt_ptr.p, h->d_cm.p, h->d_cam_ptr.p, h->d_flags.p};
+  int rc = build_index(make_index_in(h), io, nullptr);
+  if (rc) return cuda_fail(h, (cudaError_t)rc, "build_index");
+  int flags[2] = {0, 0};
+  CU(cudaMemcpy(flags, h->d_flags.p, sizeof(flags), cudaMemcpyDeviceToHost), "read index flags");
+  if (flags[0]) { h->path = PATH_NONE; return fail(h, B2BA_E_INVALID, "observation index out of range"); }
+  if (flags[1]) { h->path = PATH_NONE; return fail(h, B2BA_E_DUPLICATE, "duplicate (camera, point) observation"); }
+  const bool want_pcg = h->opt.solver == B2BA_SOLVER_PCG;
+  if (!want_pcg && h->max_nc <= kMaxCam && h->max_nfree <= 9) h->path = PATH_WIN_SMALL;
+  else if (!want_pcg && h->max_nc <= kMaxCam && h->max_nfree <= 21) h->path = PATH_WIN_BIG;
+  else if (h->opt.solver == B2BA_SOLVER_WINDOW)
+    return fail(h, B2BA_E_UNSUPPORTED, "window solver supports at most 21 free / 24 total cameras per window");
+  else h->path = PATH_LARGE;
+  if (h->path == PATH_LARGE) {
+    h->path = PATH_NONE;
+    return fail(h, B2BA_E_UNSUPPORTED, "large (PCG) path not built yet");
+  }
+  return B2BA_OK;
+}
+
+int b2ba_set_problem(b2ba_t* h, int32_t Nc, int32_t Np, int64_t No, const double* poses_cw,
+                     const double* points, const int32_t* obs_cam, const int32_t* obs_pt,
+                     const float* obs_uv, const uint8_t* fixed_cam, const double intr[4], int mem) {
+  if (Nc < 0 || Np < 0 || No < 0) return fail(h, B2BA_E_INVALID, "negative size");
+  const int32_t co[2] = {0, Nc}, po[2] = {0, Np};
+  const int64_t oo[2] = {0, No};
+  return b2ba_set_problem_batch(h, 1, co, po, oo, poses_cw, points, obs_cam, obs_pt, obs_uv, fixed_cam, intr, mem);
+}
+
+int b2ba_set_state(b2ba_t* h, const double* poses_cw, const double* points, int mem) {
+  if (!h || h->path == PATH_NONE) return fail(h, B2BA_E_STATE, "no problem set");
+  CU(cudaSetDevice(h->device), "cudaSetDevice");
+  const cudaMemcpyKind k = in_kind(mem);
+  if (poses_cw) {
+    CU(cudaMemcpy(h->d_poses.p, poses_cw, (size_t)h->nc_tot * 12 * sizeof(double), k), "copy poses");
+    CU(cudaMemcpy(h->d_poses0.p, h->d_poses.p, (size_t)h->nc_tot * 12 * sizeof(double), cudaMemcpyDeviceToDevice), "keep poses");
+  }
+  if (points) {
+    CU(cudaMemcpy(h->d_pts0.p, points, (size_t)h->np_tot * 3 * sizeof(double), k), "copy points");
+    CU(cudaMemcpy(h->d_ptsinit.p, h->d_pts0.p, (size_t)h->np_tot * 3 * sizeof(double), cudaMemcpyDeviceToDevice), "keep points");
+  }
+  return B2BA_OK;
+}
+
+int b2ba_reset(b2ba_t* h) {
+  if (!h || h->path == PATH_NONE) return fail(h, B2BA_E_STATE, "no problem set");
+  CU(cudaSetDevice(h->device), "cudaSetDevice");
+  cudaStream_t s = h->last_stream;
+  CU(cudaMemcpyAsync(h->d_poses.p, h->d_poses0.p, (size_t)h->nc_tot * 12 * sizeof(double), cudaMemcpyDeviceToDevice, s), "reset poses");
+  CU(cudaMemcpyAsync(h->d_pts0.p, h->d_ptsinit.p, (size_t)h->np_tot * 3 * sizeof(double), cudaMemcpyDeviceToDevice, s), "reset points");
+  return B2BA_OK;
+}
+
+int b2ba_get_summaries(b2ba_t* h, b2ba_summary* summaries) {
+  if (!h || !h->solved || !summaries) return fail(h, B2BA_E_STATE, "no solve to report");
+  CU(cudaSetDevice(h->device), "cudaSetDevice");
+  CU(cudaMemcpyAsync(summaries, h->d_summ.p, (size_t)h->B * sizeof(b2ba_summary), cudaMemcpyDeviceToHost, h->last_stream), "read summaries");
+  CU(cudaStreamSynchronize(h->last_stream), "solve");
+  return B2BA_OK;
+}
+
+int b2ba_solve(b2ba_t* h, int32_t max_iters, b2ba_summary* summaries, void* cuda_stream) {
+  if (!h || h->path == PATH_NONE) return fail(h, B2BA_E_STATE, "no problem set");
+  CU(cudaSetDevice(h->device), "cudaSetDevice");
+  cudaStream_t s = (cudaStream_t)cuda_stream;
+  h->last_stream = s;
+  const Params P = make_params(h, max_iters);
+  const bool hist = (h->opt.flags & 1) != 0;
+  if (hist) {
+    CU(h->d_hist_cost.alloc((size_t)h->B * kHist), "alloc"); CU(h->d_hist_mu.alloc((size_t)h->B * kHist), "alloc");
+    CU(h->d_hist_accept.alloc((size_t)h->B * kHist), "alloc");
+    CU(cudaMemsetAsync(h->d_hist_cost.p, 0, (size_t)h->B * kHist * 8, s), "memset");
+    CU(cudaMemsetAsync(h->d_hist_mu.p, 0, (size_t)h->B * kHist * 8, s), "memset");
+    CU(cudaMemsetAsync(h->d_hist_accept.p, 0, (size_t)h->B * kHist * 4, s), "memset");
+  }
+  int rc = 0;
+  if (h->path == PATH_WIN_SMALL) rc = launch_window_small(make_win(h, hist, nullptr), P, s);
+  else if (h->path == PATH_WIN_BIG) rc = launch_window_big(make_win(h, hist, nullptr), P, s);
+  else return fail(h, B2BA_E_UNSUPPORTED, "path not available");
+  if (rc) return cuda_fail(h, (cudaError_t)rc, "launch");
+  h->solved = true;
+  if (!summaries) return B2BA_OK;
+  rc = b2ba_get_summaries(h, summaries);
+  if (rc) return rc;
+  int worst = 0;
+  for (int b = 0; b < h->B; ++b) if (summaries[b].status > worst) worst = summaries[b].status;
+  return worst;
+}
+
+int b2ba_get(b2ba_t* h, double* poses_cw, double* points, int mem) {
+  if (!h || h->path == PATH_NONE) return fail(h, B2BA_E_STATE, "no problem set");
+  CU(cudaSetDevice(h->device), "cudaSetDevice");
+  cudaStream_t s = h->last_stream;
+  const cudaMemcpyKind k = out_kind(mem);
+  if (poses_cw) CU(cudaMemcpyAsync(poses_cw, h->d_poses.p, (size_t)h->nc_tot * 12 * sizeof(double), k, s), "read poses");
+  if (points) CU(cudaMemcpyAsync(points, h->d_pts0.p, (size_t)h->np_tot * 3 * sizeof(double), k, s), "read points");
+  CU(cudaStreamSynchronize(s), "get");
+  return B2BA_OK;
+}
+
+int b2ba_create_comm(b2ba_t* h, const void* nccl_unique_id, int rank, int nranks) {
+  (void)nccl_unique_id; (void)rank; (void)nranks;
+  return fail(h, B2BA_E_UNSUPPORTED, "multi-GPU observation sharding needs the large (PCG) path");
+}
+
+namespace {
+
+// one LM iteration at init_mu from the current state with the stage dump attached; state restored
+int run_stage(b2ba* h, std::vector<double>& out, WinDbg& L) {
+  if (h->B != 1 || (h->path != PATH_WIN_SMALL && h->path != PATH_WIN_BIG))
+    return fail(h, B2BA_E_UNSUPPORTED, "stage dumps need a single-window problem on the window path");
+  int nfree = 0;
+  for (int c = 0; c < h->nc_tot; ++c) nfree += h->h_fixed[c] ? 0 : 1;
+  L = WinDbg{h->nc_tot, h->np_tot, 6 * nfree};
+  CU(h->d_dbg.alloc(L.total()), "alloc dbg");
+  CU(cudaMemset(h->d_dbg.p, 0, L.total() * sizeof(double)), "memset dbg");
+  DevBuf<double> sp, sx;
+  DevBuf<b2ba_summary> ss;
+  CU(sp.alloc((size_t)h->nc_tot * 12), "alloc"); CU(sx.alloc((size_t)h->np_tot * 3), "alloc"); CU(ss.alloc(1), "alloc");
+  CU(cudaMemcpy(sp.p, h->d_poses.p, (size_t)h->nc_tot * 12 * 8, cudaMemcpyDeviceToDevice), "save");
+  CU(cudaMemcpy(sx.p, h->d_pts0.p, (size_t)h->np_tot * 3 * 8, cudaMemcpyDeviceToDevice), "save");
+  CU(cudaMemcpy(ss.p, h->d_summ.p, sizeof(b2ba_summary), cudaMemcpyDeviceToDevice), "save");
+  const Params P = make_params(h, 1);
+  const WinData d = make_win(h, false, h->d_dbg.p);
+  int rc = h->path == PATH_WIN_SMALL ? launch_window_small(d, P, nullptr) : launch_window_big(d, P, nullptr);
+  if (rc) return cuda_fail(h, (cudaError_t)rc, "stage launch");
+  CU(cudaDeviceSynchronize(), "stage kernel");
+  out.resize(L.total());
+  CU(cudaMemcpy(out.data(), h->d_dbg.p, L.total() * 8, cudaMemcpyDeviceToHost), "read dbg");
+  CU(cudaMemcpy(h->d_poses.p, sp.p, (size_t)h->nc_tot * 12 * 8, cudaMemcpyDeviceToDevice), "restore");
+  CU(cudaMemcpy(h->d_pts0.p, sx.p, (size_t)h->np_tot * 3 * 8, cudaMemcpyDeviceToDevice), "restore");
+  CU(cudaMemcpy(h->d_summ.p, ss.p, sizeof(b2ba_summary), cudaMemcpyDeviceToDevice), "restore");
+  return B2BA_OK;
+}
+
+int64_t put(b2ba* h, const void* src, size_t bytes, void* dst, int64_t cap) {
+  if ((int64_t)bytes > cap) return fail(h, B2BA_E_INVALID, "dump: destination too small");
+  std::memcpy(dst, src, bytes);
+  return (int64_t)bytes;
+}
+
+}  // namespace
+
+int64_t b2ba_dump(b2ba_t* h, int what, void* dst, int64_t bytes) {
+  if (!h || h->path == PATH_NONE || !dst) return fail(h, B2BA_E_STATE, "no problem set");
+  CU(cudaSetDevice(h->device), "cudaSetDevice");
+  CU(cudaDeviceSynchronize(), "sync");
+  const size_t no = (size_t)h->no;
+  switch (what) {
+    case B2BA_D_PM_PERM:
+    case B2BA_D_CM_PERM: {
+      std::vector<ObsRec> rec(no);
+      CU(cudaMemcpy(rec.data(), what == B2BA_D_PM_PERM ? h->d_pm.p : h->d_cm.p, no * sizeof(ObsRec), cudaMemcpyDeviceToHost), "read");
+      std::vector<int> perm(no);
+      int b = 0;
+      for (size_t a = 0; a < no; ++a) {
+        while ((long long)a >= h->h_obs_off[b + 1]) ++b;
+        perm[a] = rec[a].orig - (int)h->h_obs_off[b];
+      }
+      return put(h, perm.data(), no * 4, dst, bytes);
+    }
+    case B2BA_D_PT_PTR:
+    case B2BA_D_CAM_PTR: {
+      const size_t n = (what == B2BA_D_PT_PTR ? h->np_tot : h->nc_tot) + 1;
+      std::vector<int> v(n);
+      CU(cudaMemcpy(v.data(), what == B2BA_D_PT_PTR ? h->d_pt_ptr.p : h->d_cam_ptr.p, n * 4, cudaMemcpyDeviceToHost), "read");
+      return put(h, v.data(), n * 4, dst, bytes);
+    }
+    case B2BA_D_FIDX: {
+      std::vector<int> v(h->nc_tot);
+      for (int b = 0; b < h->B; ++b) {
+        int nf = 0;
+        for (int c = h->h_cam_off[b]; c < h->h_cam_off[b + 1]; ++c) v[c] = h->h_fixed[c] ? -1 : nf++;
+      }
+      return put(h, v.data(), v.size() * 4, dst, bytes);
+    }
+    case B2BA_D_RESIDUALS: case B2BA_D_WEIGHTS: case B2BA_D_JC: case B2BA_D_JP: {
+      const size_t per = what == B2BA_D_RESIDUALS ? 2 : what == B2BA_D_WEIGHTS ? 1 : what == B2BA_D_JC ? 12 : 6;
+      DevBuf<double> tmp;
+      CU(tmp.alloc(no * per), "alloc");
+      int rc = dump_obs_terms(make_index_in(h), make_params(h, 1), h->d_poses.p, h->d_pts0.p,
+                              what == B2BA_D_RESIDUALS ? tmp.p : nullptr, what == B2BA_D_WEIGHTS ? tmp.p : nullptr,
+                              what == B2BA_D_JC ? tmp.p : nullptr, what == B2BA_D_JP ? tmp.p : nullptr, nullptr);
+      if (rc) return cuda_fail(h, (cudaError_t)rc, "dump_obs_terms");
+      if ((int64_t)(no * per * 8) > bytes) return fail(h, B2BA_E_INVALID, "dump: destination too small");
+      CU(cudaMemcpy(dst, tmp.p, no * per * 8, cudaMemcpyDeviceToHost), "read");
+      return (int64_t)(no * per * 8);
+    }
+    case B2BA_D_B: case B2BA_D_GC: case B2BA_D_C: case B2BA_D_GP: case B2BA_D_S: case B2BA_D_GRED:
+    case B2BA_D_DC: case B2BA_D_DP: case B2BA_D_SCALARS: {
+      std::vector<double> o;
+      WinDbg L;
+      int rc = run_stage(h, o, L);
+      if (rc) return rc;
+      const size_t n = L.n, nc = L.nc, np = L.np;
+      switch (what) {
+        case B2BA_D_B: return put(h, &o[L.off_B()], nc * 36 * 8, dst, bytes);
+        case B2BA_D_GC: return put(h, &o[L.off_gc()], nc * 6 * 8, dst, bytes);
+        case B2BA_D_C: return put(h, &o[L.off_C()], np * 6 * 8, dst, bytes);
+        case B2BA_D_GP: return put(h, &o[L.off_gp()], np * 3 * 8, dst, bytes);
+        case B2BA_D_S: return put(h, &o[L.off_S()], n * n * 8, dst, bytes);
+        case B2BA_D_GRED: return put(h, &o[L.off_gred()], n * 8, dst, bytes);
+        case B2BA_D_DC: return put(h, &o[L.off_dc()], n * 8, dst, bytes);
+        case B2BA_D_DP: return put(h, &o[L.off_dp()], np * 3 * 8, dst, bytes);
+        default: return put(h, &o[L.off_scal()], 4 * 8, dst, bytes);
+      }
+    }
+    case B2BA_D_HIST_COST: case B2BA_D_HIST_MU: case B2BA_D_HIST_ACCEPT: {
+      if (!h->solved || !(h->opt.flags & 1)) return fail(h, B2BA_E_STATE, "history not recorded (options.flags bit 0)");
+      const size_t n = (size_t)h->B * kHist, sz = what == B2BA_D_HIST_ACCEPT ? 4 : 8;
+      if ((int64_t)(n * sz) > bytes) return fail(h, B2BA_E_INVALID, "dump: destination too small");
+      const void* src = what == B2BA_D_HIST_COST ? (void*)h->d_hist_cost.p
+                        : what == B2BA_D_HIST_MU ? (void*)h->d_hist_mu.p : (void*)h->d_hist_accept.p;
+      CU(cudaMemcpy(dst, src, n * sz, cudaMemcpyDeviceToHost), "read");
+      return (int64_t)(n * sz);
+    }
+    default:
+      return fail(h, B2BA_E_UNSUPPORTED, "dump: unknown or unavailable array");
+  }
+}
+
+}  // extern "C"

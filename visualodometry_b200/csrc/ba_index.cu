@@ -1,0 +1,149 @@
+// a8 index builder (see ba_index.cuh).  Two stable LSD radix sorts (CUB, part of the CUDA
+// toolkit) + three small kernels.  Runs once per problem, not in the LM loop.
+#include "ba_index.cuh"
+
+#include <cub/device/device_radix_sort.cuh>
+
+namespace b2 {
+
+namespace {
+
+__device__ __forceinline__ int find_window(const long long* __restrict__ obs_off, int nb, long long i) {
+  int lo = 0, hi = nb;   // obs_off[lo] <= i < obs_off[hi]
+  while (hi - lo > 1) {
+    const int mid = (lo + hi) >> 1;
+    if (obs_off[mid] <= i) lo = mid; else hi = mid;
+  }
+  return lo;
+}
+
+__global__ void make_pm_keys(IndexIn in, unsigned long long* keys, int* vals, int* flags) {
+  const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (i >= in.no) return;
+  const int b = find_window(in.obs_off, in.nb, i);
+  const int nc = in.cam_off[b + 1] - in.cam_off[b], np = in.pt_off[b + 1] - in.pt_off[b];
+  int c = in.obs_cam[i], p = in.obs_pt[i];
+  if (c < 0 || c >= nc || p < 0 || p >= np) { flags[0] = 1; c = 0; p = 0; }
+  keys[i] = ((unsigned long long)(unsigned)(in.pt_off[b] + p) << 32) | (unsigned)c;
+  vals[i] = (int)i;
+}
+
+// sorted (key, original index) -> point-major records, pt_ptr boundaries, camera keys for pass 2
+__global__ void build_pm(IndexIn in, const unsigned long long* __restrict__ keys,
+                         const int* __restrict__ vals, ObsRec* pm, int* pt_ptr, unsigned* cam_keys,
+                         int* pos, int* flags) {
+  const long long a = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (a >= in.no) return;
+  const unsigned long long k = keys[a];
+  const int gp = (int)(k >> 32), c = (int)(k & 0xffffffffu), i = vals[a];
+  const float2 uv = in.obs_uv[i];
+  ObsRec r; r.u = uv.x; r.v = uv.y; r.idx = c; r.orig = i;
+  pm[a] = r;
+  const int b = find_window(in.obs_off, in.nb, i);
+  cam_keys[a] = (unsigned)(in.cam_off[b] + c);
+  pos[a] = (int)a;
+  const int prev = a == 0 ? -1 : (int)(keys[a - 1] >> 32);
+  if (a > 0 && keys[a - 1] == k) flags[1] = 1;
+  for (int q = prev + 1; q <= gp; ++q) pt_ptr[q] = (int)a;
+  if (a == in.no - 1)
+    for (int q = gp + 1; q <= in.np_tot; ++q) pt_ptr[q] = (int)in.no;
+}
+
+__global__ void build_cm(IndexIn in, const unsigned* __restrict__ cam_keys, const int* __restrict__ pos,
+                         const ObsRec* __restrict__ pm, const unsigned long long* __restrict__ pm_keys,
+                         ObsRec* cm, int* cam_ptr) {
+  const long long a = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (a >= in.no) return;
+  const int gc = (int)cam_keys[a];
+  const int src = pos[a];
+  ObsRec r = pm[src];
+  const int gp = (int)(pm_keys[src] >> 32);
+  const int b = find_window(in.obs_off, in.nb, r.orig);
+  r.idx = gp - in.pt_off[b];
+  cm[a] = r;
+  const int prev = a == 0 ? -1 : (int)cam_keys[a - 1];
+  for (int q = prev + 1; q <= gc; ++q) cam_ptr[q] = (int)a;
+  if (a == in.no - 1)
+    for (int q = gc + 1; q <= in.nc_tot; ++q) cam_ptr[q] = (int)in.no;
+}
+
+__global__ void fill_ptr(int* p, int n, int v) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) p[i] = v;
+}
+
+inline int bits_for(long long n) { int b = 1; while ((1ll << b) < n && b < 32) ++b; return b; }
+
+}  // namespace
+
+int build_index(const IndexIn& in, const IndexOut& out, cudaStream_t s) {
+  cudaError_t e;
+  e = cudaMemsetAsync(out.flags, 0, 2 * sizeof(int), s);
+  if (e != cudaSuccess) return (int)e;
+  const long long no = in.no;
+  if (no == 0) {
+    fill_ptr<<<(in.np_tot + 256) / 256, 256, 0, s>>>(out.pt_ptr, in.np_tot + 1, 0);
+    fill_ptr<<<(in.nc_tot + 256) / 256, 256, 0, s>>>(out.cam_ptr, in.nc_tot + 1, 0);
+    return (int)cudaGetLastError();
+  }
+  unsigned long long *k0 = nullptr, *k1 = nullptr;
+  int *v0 = nullptr, *v1 = nullptr, *p1 = nullptr;
+  unsigned *ck0 = nullptr, *ck1 = nullptr;
+  void* tmp = nullptr;
+  size_t tmp_bytes = 0, t2 = 0;
+  const int pbits = 32 + bits_for(in.np_tot), cbits = bits_for(in.nc_tot);
+  cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, k0, k1, v0, v1, no, 0, pbits, s);
+  cub::DeviceRadixSort::SortPairs(nullptr, t2, ck0, ck1, v0, v1, no, 0, cbits, s);
+  if (t2 > tmp_bytes) tmp_bytes = t2;
+#define B2_TRY(x) do { e = (x); if (e != cudaSuccess) goto done; } while (0)
+  B2_TRY(cudaMallocAsync(&k0, no * 8, s)); B2_TRY(cudaMallocAsync(&k1, no * 8, s));
+  B2_TRY(cudaMallocAsync(&v0, no * 4, s)); B2_TRY(cudaMallocAsync(&v1, no * 4, s));
+  B2_TRY(cudaMallocAsync(&p1, no * 4, s));
+  B2_TRY(cudaMallocAsync(&ck0, no * 4, s)); B2_TRY(cudaMallocAsync(&ck1, no * 4, s));
+  B2_TRY(cudaMallocAsync(&tmp, tmp_bytes, s));
+  {
+    const int nblk = (int)((no + 255) / 256);
+    make_pm_keys<<<nblk, 256, 0, s>>>(in, k0, v0, out.flags);
+    B2_TRY(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, k0, k1, v0, v1, no, 0, pbits, s));
+    build_pm<<<nblk, 256, 0, s>>>(in, k1, v1, out.pm, out.pt_ptr, ck0, v0, out.flags);
+    B2_TRY(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, ck0, ck1, v0, p1, no, 0, cbits, s));
+    build_cm<<<nblk, 256, 0, s>>>(in, ck1, p1, out.pm, k1, out.cm, out.cam_ptr);
+    B2_TRY(cudaGetLastError());
+  }
+done:
+#undef B2_TRY
+  cudaFreeAsync(k0, s); cudaFreeAsync(k1, s); cudaFreeAsync(v0, s); cudaFreeAsync(v1, s);
+  cudaFreeAsync(p1, s); cudaFreeAsync(ck0, s); cudaFreeAsync(ck1, s); cudaFreeAsync(tmp, s);
+  return (int)e;
+}
+
+namespace {
+__global__ void obs_terms_kernel(IndexIn in, Params P, const double* __restrict__ poses,
+                                 const double* __restrict__ pts, double* r, double* w, double* jc,
+                                 double* jp) {
+  const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (i >= in.no) return;
+  const int b = find_window(in.obs_off, in.nb, i);
+  const double* pose = poses + 12 * (size_t)(in.cam_off[b] + in.obs_cam[i]);
+  const double* X = pts + 3 * (size_t)(in.pt_off[b] + in.obs_pt[i]);
+  const float2 uv = in.obs_uv[i];
+  Proj o;
+  project(P, pose, X[0], X[1], X[2], uv.x, uv.y, o);
+  double a[12], c[6];
+  jac_cam(P, o, a);
+  jac_point(P, pose, o, c);
+  if (r) { r[2 * i] = o.r0; r[2 * i + 1] = o.r1; }
+  if (w) w[i] = o.w;
+  if (jc) for (int k = 0; k < 12; ++k) jc[12 * i + k] = a[k];
+  if (jp) for (int k = 0; k < 6; ++k) jp[6 * i + k] = c[k];
+}
+}  // namespace
+
+int dump_obs_terms(const IndexIn& in, const Params& P, const double* poses, const double* pts,
+                   double* r, double* w, double* jc, double* jp, cudaStream_t s) {
+  if (in.no == 0) return 0;
+  obs_terms_kernel<<<(int)((in.no + 127) / 128), 128, 0, s>>>(in, P, poses, pts, r, w, jc, jp);
+  return (int)cudaGetLastError();
+}
+
+}  // namespace b2

@@ -1,0 +1,37 @@
+// a8: observation-to-block index builder, on the device, once per problem.
+// Canonical orders (bit-exact contract with the oracle, oracle/ba_cpu.cpp build_index):
+//   point-major : observations sorted by (window, pt, cam, original index)
+//   camera-major: observations sorted by (window, cam, pt, original index)
+#pragma once
+#include "ba_math.cuh"
+
+namespace b2 {
+
+struct IndexIn {
+  int nb, nc_tot, np_tot;
+  long long no;
+  const int* cam_off;        // device, nb+1
+  const int* pt_off;         // device, nb+1
+  const long long* obs_off;  // device, nb+1
+  const int* obs_cam;        // device, window-local
+  const int* obs_pt;         // device, window-local
+  const float2* obs_uv;      // device
+};
+
+struct IndexOut {
+  ObsRec* pm;      // no
+  int* pt_ptr;     // np_tot+1
+  ObsRec* cm;      // no
+  int* cam_ptr;    // nc_tot+1
+  int* flags;      // [0] out-of-range index, [1] duplicate (cam,pt) observation
+};
+
+// Builds both streams. Returns cudaError_t as int. Temporary storage is allocated and freed
+// internally (stream-ordered); the call is asynchronous on `s`.
+int build_index(const IndexIn& in, const IndexOut& out, cudaStream_t s);
+
+// a1 dump in ORIGINAL observation order (parity tests): r (no x 2), w (no), Jc (no x 12), Jp (no x 6)
+int dump_obs_terms(const IndexIn& in, const Params& P, const double* poses, const double* pts,
+                   double* r, double* w, double* jc, double* jp, cudaStream_t s);
+
+}  // namespace b2

@@ -1,0 +1,76 @@
+// Window path (C1 / C3 / C4): ONE CTA runs the whole Levenberg-Marquardt loop of ONE window,
+// all iteration state in shared memory / registers, zero host synchronisation per iteration.
+// See DESIGN.md "Window kernel".  Kernel body: ba_window.cu.
+#pragma once
+#include "ba_math.cuh"
+#include "../../include/b2ba.h"
+
+namespace b2 {
+
+constexpr int kMaxCam = 24;       // cameras per window on this path (free + fixed)
+constexpr int kPtScratch = 12;    // per point: F(6) gp(3) D(3)
+constexpr int kHist = 64;
+
+struct WinData {
+  int nb;
+  const int* cam_off;          // nb+1
+  const int* pt_off;           // nb+1
+  const ObsRec* pm;            // point-major stream (idx = local camera)
+  const int* pt_ptr;           // NpTot+1, absolute offsets into pm
+  const ObsRec* cm;            // camera-major stream (idx = local point)
+  const int* cam_ptr;          // NcTot+1, absolute offsets into cm
+  const unsigned char* fixed;  // NcTot
+  double* poses;               // NcTot x 12 (in/out)
+  double* pts[2];              // NpTot x 3 ping-pong; pts[0] holds the result at exit
+  double* pt_scratch;          // NpTot x kPtScratch
+  b2ba_summary* summaries;     // nb
+  double* hist_cost;           // nb x kHist or null
+  double* hist_mu;
+  int* hist_accept;
+  double* dbg;                 // single-window stage dump or null (layout: WinDbg)
+};
+
+// layout of the stage dump (doubles), n = 6*nfree
+struct WinDbg {
+  int nc, np, n;
+  __host__ __device__ size_t off_B() const { return 0; }
+  __host__ __device__ size_t off_gc() const { return off_B() + (size_t)nc * 36; }
+  __host__ __device__ size_t off_C() const { return off_gc() + (size_t)nc * 6; }
+  __host__ __device__ size_t off_gp() const { return off_C() + (size_t)np * 6; }
+  __host__ __device__ size_t off_S() const { return off_gp() + (size_t)np * 3; }
+  __host__ __device__ size_t off_gred() const { return off_S() + (size_t)n * n; }
+  __host__ __device__ size_t off_dc() const { return off_gred() + n; }
+  __host__ __device__ size_t off_dp() const { return off_dc() + n; }
+  __host__ __device__ size_t off_scal() const { return off_dp() + (size_t)np * 3; }
+  __host__ __device__ size_t total() const { return off_scal() + 4; }
+};
+
+template <int NT_, int NWARPS_, int G_, int PB_>
+struct WinCfg {
+  static constexpr int NT = NT_, NWARPS = NWARPS_, G = G_, PB = PB_;
+  static constexpr int NTHREADS = NWARPS * 32;
+  static constexpr int KS = NWARPS / G;            // k-splits of the SYRK
+  static constexpr int T = NT * (NT + 1) / 2;      // upper 8x8 tiles
+  static constexpr int TPW = (T + G - 1) / G;      // tiles per warp
+  static constexpr int TPP = NTHREADS / PB;        // lanes per point
+  static constexpr int NR = 8 * NT;                // rows of the Z tile (6*nfree + 1 padded)
+  static constexpr int LD = 3 * PB + 4;            // == 4 mod 16 -> conflict-free fragment loads
+  static constexpr int KSTEPS = 3 * PB / 4;        // k-steps (of 4) per batch
+  static constexpr int LDS = NR + 1;               // leading dim of S (odd)
+  static constexpr int ZS = (NR * LD > NR * LDS) ? NR * LD : NR * LDS;
+  static constexpr int NRED = NWARPS * 32;
+  // doubles: pose_cur, pose_tri, B(21), gc, Dc, dvec, gred, red, scal, Z/S
+  static constexpr int SM_DOUBLES = kMaxCam * (12 + 12 + 21 + 6 + 6) + 128 + 128 + NRED + 16 + ZS;
+  static constexpr size_t SMEM = (size_t)SM_DOUBLES * 8 + (2 * kMaxCam + 8) * 4;
+  static_assert(KS * G == NWARPS, "warps = groups x k-splits");
+  static_assert(KSTEPS % KS == 0, "k-steps split evenly");
+  static_assert(TPP >= 1 && TPP <= 32 && (TPP & (TPP - 1)) == 0, "lanes per point: power of two");
+  static_assert((3 * PB) % 16 == 0, "LD == 4 mod 16");
+};
+
+// launchers (ba_window.cu). Return cudaError_t as int.
+int launch_window_small(const WinData& d, const Params& p, cudaStream_t s);   // n+1 <= 56 (<= 9 free cams)
+int launch_window_big(const WinData& d, const Params& p, cudaStream_t s);     // n+1 <= 128 (<= 21 free cams)
+int window_kernel_attrs(int which, int* regs, int* smem_bytes, int* ctas_per_sm);
+
+}  // namespace b2
