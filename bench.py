@@ -1,0 +1,281 @@
+#!/usr/bin/env python
+"""bench.py -- BA observations*iterations / second (BASELINE.json metric) on N B200s.
+
+Default workload (N=1): C4 = 4096 KITTI-05-shaped windows (10 keyframes, 2000 landmarks, ~15000
+observations each) x 10 LM iterations per step, one window per CTA, no data-path collective
+(independent windows; weak scaling: 4096 windows per GPU).  `--workload c5` runs the sharded
+BAL-style problem.  One JSON line on stdout (rank 0).  See DESIGN.md "Measurement".
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+FP64_PEAK_TFLOPS = 37.1   # tools/fp64_peak.cu on this pool's B200 (DMMA m8n8k4 37.1, DFMA 33.9);
+                          # MEASURED_PEAKS.json carries no fp64 figure
+
+
+def algorithmic_flops_per_iter(pt_ptr_counts):
+    """a1+a2+a7 = 570 flop/obs, Schur a4 = 108 k + 216 k(k+1)/2 per landmark."""
+    k = np.asarray(pt_ptr_counts, np.float64)
+    return float(570.0 * k.sum() + (108.0 * k + 108.0 * k * (k + 1)).sum())
+
+
+def algorithmic_bytes_per_iter(no, npts, nc, nblk):
+    """2*16*No + 72*Np + 2*96*Nc + 288*nnzblk(S)."""
+    return 2.0 * 16 * no + 72.0 * npts + 2.0 * 96 * nc + 288.0 * nblk
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return json.load(open(p)), "measured"
+    return {"hbm_gbs": 6650.0}, "fallback"
+
+
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, dev):
+        self.p, self.dev = None, dev
+
+    def start(self):
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(self.dev), f"--query-gpu={self.Q}",
+                                       "--format=csv,noheader,nounits", "-lms", "100"],
+                                      stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except Exception:
+            self.p = None
+
+    def stop(self):
+        if self.p is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.p.terminate()
+        out = self.p.communicate()[0]
+        sm, mx, reasons = [], [], set()
+        for line in out.splitlines():
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        busy = [s for s in sm if s > 0.5 * max(sm)] or sm
+        return {"sm_mhz": float(np.median(busy)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def make_workload(args, rank):
+    from visualodometry_b200 import synth
+    if args.workload == "c4":
+        b = synth.make_batch(args.windows, seed0=rank * args.windows, distinct=args.distinct)
+        name = (f"C4: {args.windows} independent KITTI-05-shaped windows per GPU (10 keyframes, 2000 landmarks, "
+                f"~15000 observations), {args.iters} LM iterations per step")
+    elif args.workload == "c1":
+        b = synth.pack_batch([synth.make_window(rank)])
+        name = f"C1: one KITTI-05-shaped window, {args.iters} LM iterations per step"
+    elif args.workload == "c3":
+        b = synth.pack_batch([synth.make_window(rank, n_cams=20, cam=synth.MALAGA, outlier_frac=0.1, n_obs=30000)])
+        name = f"C3: one Malaga-shaped 20-keyframe window, Huber, {args.iters} LM iterations per step"
+    else:
+        raise SystemExit(f"workload {args.workload} not available in this build")
+    return b, name
+
+
+def K_of(intr):
+    return np.array([[intr[0], 0, intr[2]], [0, intr[1], intr[3]], [0, 0, 1]])
+
+
+def cpu_baseline(batch, iters, loss, budget_windows, threads=0):
+    """Oracle (C++ fp64 port of Spec a0) on a bounded sample of the same workload."""
+    from oracle import ba_cpu
+    from visualodometry_b200 import synth
+    nw = min(batch.nb, budget_windows)
+    sample = synth.pack_batch([batch.window(i) for i in range(nw)])
+    cores = ba_cpu.num_procs() if threads <= 0 else threads
+    t0 = time.perf_counter()
+    ba_cpu.solve_batch(sample, max_iters=iters, loss=loss, threads=cores)
+    dt = time.perf_counter() - t0
+    return {"value": sample.no * iters / dt, "unit": "obs*iter/s", "cores": cores, "kind": "port",
+            "sample": f"first {nw} windows of the workload ({sample.no} observations), {iters} LM iterations, "
+                      f"oracle/ba_cpu.cpp OpenMP across windows, {dt:.2f} s"}
+
+
+def run_reference(args, rank, world):
+    """--impl reference: the reference has no BA; the CPU arm is the oracle port on
+    the host cores, all threads, on a bounded sample of the same workload."""
+    if rank != 0:
+        return
+    b, name = make_workload(argparse.Namespace(**{**vars(args), "windows": min(args.windows, args.cpu_windows),
+                                                  "distinct": None}), 0)
+    loss = "huber" if args.workload == "c3" else "trivial"
+    vals = []
+    for i in range(args.warmup + args.steps):
+        cb = cpu_baseline(b, args.iters, loss, args.cpu_windows)
+        if i >= args.warmup:
+            vals.append(cb)
+    v = float(np.mean([c["value"] for c in vals]))
+    ms = 1e3 * b.no * args.iters / v
+    cb = dict(vals[-1], value=v)
+    print(json.dumps({"impl": "reference", "metric": "BA observations*iterations/sec", "value": v,
+                      "unit": "obs*iter/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+                      "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                      "dtype": "f64", "data": "synthetic", "config": {"workload": name, "sample": cb["sample"]},
+                      "cpu_baseline": cb,
+                      "e2e": {"value": v, "unit": "obs*iter/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="c4", choices=["c1", "c3", "c4", "c5"])
+    ap.add_argument("--windows", type=int, default=4096)
+    ap.add_argument("--distinct", type=int, default=256, help="distinct geometries generated (set-up time bound)")
+    ap.add_argument("--iters", type=int, default=10)
+    ap.add_argument("--cpu-windows", type=int, default=128)
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        return run_reference(args, rank, world)
+
+    import torch
+    import torch.distributed as dist
+    from visualodometry_b200 import BAConfig, BundleAdjuster
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the b2ba engine has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    b, name = make_workload(args, rank)
+    loss = "huber" if args.workload == "c3" else "trivial"
+    ba = BundleAdjuster(K_of(b.intr), BAConfig(max_iters=args.iters, loss=loss, device=local))
+    ba.set_problem(b.poses, b.points, b.obs_cam, b.obs_pt, b.obs_uv, b.fixed_cam, b.cam_off, b.pt_off, b.obs_off)
+    stream = torch.cuda.current_stream().cuda_stream
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda") if b.no * 32 < (256 << 20) else None
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step():
+        ba.reset()
+        ba.solve(stream=stream, wait=False)
+
+    for _ in range(args.warmup):
+        step()
+    # ---- timed region: device-resident inputs, CUDA events on the launching stream
+    sampler = ClockSampler(local)
+    barrier()
+    sampler.start()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    t_wall = time.perf_counter()
+    for i in range(args.steps):
+        if flush is not None:
+            flush.fill_(i)          # L2 flush between timed iterations (small workloads)
+        ev[i][0].record()
+        step()
+        ev[i][1].record()
+    barrier()
+    t_wall = time.perf_counter() - t_wall
+    clocks = sampler.stop()
+    ms_steps = [a.elapsed_time(c) for a, c in ev]
+    ms_total = float(sum(ms_steps))
+    sms = ba.summaries()
+    iters_done = sum(s.iterations for s in sms)
+
+    # ---- e2e: host buffers in, host results out, through the public API, copies inside the timing
+    pin = lambda a: torch.from_numpy(np.ascontiguousarray(a)).pin_memory().numpy()
+    hb = dict(poses=pin(b.poses), points=pin(b.points), obs_cam=pin(b.obs_cam), obs_pt=pin(b.obs_pt),
+              obs_uv=pin(b.obs_uv), fixed=pin(b.fixed_cam))
+    h2d = sum(v.nbytes for v in hb.values()) + b.cam_off.nbytes + b.pt_off.nbytes + b.obs_off.nbytes
+    d2h = hb["poses"].nbytes + hb["points"].nbytes + 48 * b.nb
+    e2e_steps = max(2, min(args.steps, 3))
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        ba.set_problem(hb["poses"], hb["points"], hb["obs_cam"], hb["obs_pt"], hb["obs_uv"], hb["fixed"],
+                       b.cam_off, b.pt_off, b.obs_off)
+        ba.solve(stream=stream)
+        ba.get()
+    barrier()
+    t_e2e = (time.perf_counter() - t0) / e2e_steps
+
+    units = float(b.no) * args.iters          # obs*iter per step per rank
+    tt = torch.tensor([ms_total, t_e2e * 1e3], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        un = torch.tensor([units], dtype=torch.float64, device="cuda")
+        dist.all_reduce(un, op=dist.ReduceOp.SUM)
+        units_all = float(un.item())
+    else:
+        units_all = units
+    ms_total, ms_e2e = float(tt[0].item()), float(tt[1].item())
+    if rank == 0:
+        pk, pk_kind = peaks()
+        counts = np.diff(np.concatenate([[0], np.cumsum(np.bincount(
+            (b.obs_pt.astype(np.int64) + np.repeat(b.pt_off[:-1].astype(np.int64), np.diff(b.obs_off))),
+            minlength=int(b.pt_off[-1])))]))
+        flops_iter = algorithmic_flops_per_iter(counts)
+        nblk = sum(int(n * (n + 1) // 2) for n in (np.diff(b.cam_off) - 1))
+        bytes_iter = algorithmic_bytes_per_iter(b.no, int(b.pt_off[-1]), int(b.cam_off[-1]), nblk)
+        ms_kernel = ms_total / args.steps       # one window_lm_kernel launch per step
+        tf = flops_iter * args.iters / (ms_kernel * 1e-3) / 1e12
+        gbs = bytes_iter * args.iters / (ms_kernel * 1e-3) / 1e9
+        prof = os.path.join(ROOT, "profiles", "traffic.json")
+        traffic = json.load(open(prof)).get(args.workload) if os.path.exists(prof) else None
+        out = {"metric": "BA observations*iterations/sec", "value": units_all * args.steps / (ms_total * 1e-3),
+               "unit": "obs*iter/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+               "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak",
+               "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+               "config": {"workload": name, "windows_per_gpu": b.nb, "observations_per_gpu": int(b.no),
+                          "lm_iterations": args.iters, "lm_iterations_executed": int(iters_done),
+                          "distinct_geometries": args.distinct if args.workload == "c4" else 1,
+                          "partition": f"{world} x independent window shards, no collective",
+                          "l2": "inputs larger than L2" if flush is None else "L2 flushed between timed steps"},
+               "roofline": {"bound": "tensor", "kernel": "window_lm_kernel", "achieved": tf, "peak": FP64_PEAK_TFLOPS,
+                            "unit": "TFLOP/s", "frac": tf / FP64_PEAK_TFLOPS, "traffic": traffic,
+                            "note": "fp64 pipe (DMMA+DFMA) bound; peak = tools/fp64_peak.cu DMMA on this pool "
+                                    "(MEASURED_PEAKS.json has no fp64 entry); algorithmic flops per SURVEY 8(d)",
+                            "hbm_view": {"achieved": gbs, "peak": pk["hbm_gbs"], "unit": "GB/s",
+                                         "frac": gbs / pk["hbm_gbs"], "peak_kind": pk_kind}},
+               "clocks": clocks, "gpu_launches": args.steps,
+               "e2e": {"value": units_all / (ms_e2e * 1e-3), "unit": "obs*iter/s", "h2d_bytes_per_step": int(h2d),
+                       "d2h_bytes_per_step": int(d2h), "ms_per_step": ms_e2e},
+               "wall_s_timed_region": t_wall}
+        if not args.no_cpu and world == 1:
+            out["cpu_baseline"] = cpu_baseline(b, args.iters, loss, args.cpu_windows)
+        print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

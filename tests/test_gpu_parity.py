@@ -1,0 +1,198 @@
+"""GPU parity tests (-m gpu): the CUDA path, called through the C ABI (ctypes binding of
+include/b2ba.h), against the CPU oracle on the same seeded inputs.
+
+Tolerances (BASELINE.json north_star): index arrays bit-exact; final reprojection RMSE within 1e-6
+relative; poses within 1e-5; landmarks within 1e-5 RELATIVE to max(1, |X|) -- forward-motion windows
+contain landmarks near the focus of expansion whose depth is unobservable (they drift to 1e4..1e5 m);
+the oracle itself moves those by ~1e-2 m under a 1e-15 input perturbation, so an absolute 1e-5 is
+not a meaningful bar for them (DESIGN.md "Parity")."""
+import numpy as np
+import pytest
+
+from visualodometry_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+
+def K_of(p):
+    return np.array([[p.intr[0], 0, p.intr[2]], [0, p.intr[1], p.intr[3]], [0, 0, 1]])
+
+
+def rel(a, b):
+    a, b = np.asarray(a, np.float64), np.asarray(b, np.float64)
+    return float(np.abs(a - b).max() / max(np.abs(b).max(), 1e-300)) if a.size else 0.0
+
+
+def pts_err(x, xo):
+    return float((np.linalg.norm(x - xo, axis=1) / np.maximum(1.0, np.linalg.norm(xo, axis=1))).max())
+
+
+@pytest.fixture(scope="module")
+def engine():
+    import torch
+    assert torch.cuda.is_available(), "GPU tests need a CUDA device"
+    from visualodometry_b200 import BAConfig, BundleAdjuster
+
+    def make(p, **kw):
+        ba = BundleAdjuster(K_of(p), BAConfig(**kw))
+        return ba
+    return make
+
+
+PROBLEMS = {
+    "tiny": (lambda: synth.make_window(3, n_cams=4, n_pts=50, n_obs=150), "trivial"),
+    "c1": (lambda: synth.make_window(0), "trivial"),
+    "c1_seed4": (lambda: synth.make_window(4), "trivial"),
+    "c3_malaga": (lambda: synth.make_window(1, n_cams=20, cam=synth.MALAGA, outlier_frac=0.1, n_obs=30000), "huber"),
+    "c3_parking": (lambda: synth.make_window(2, n_cams=20, cam=synth.PARKING, outlier_frac=0.1, n_obs=30000), "huber"),
+    "two_fixed": (lambda: _two_fixed(), "trivial"),
+}
+
+
+def _two_fixed():
+    p = synth.make_window(9, n_cams=8, n_pts=500, n_obs=3000)
+    p.fixed_cam[3] = 1       # a fixed camera in the middle of the window
+    return p
+
+
+@pytest.mark.parametrize("name", list(PROBLEMS))
+def test_index_bit_exact(engine, oracle, name):
+    p = PROBLEMS[name][0]()
+    ba = engine(p).set_problem(p.poses, p.points, p.obs_cam, p.obs_pt, p.obs_uv, p.fixed_cam)
+    ix = oracle.index(p)
+    for k, ref in (("PM_PERM", ix.pm_perm), ("PT_PTR", ix.pt_ptr), ("CM_PERM", ix.cm_perm),
+                   ("CAM_PTR", ix.cam_ptr), ("FIDX", ix.fidx)):
+        assert np.array_equal(ba.dump(k, ref.shape, np.int32), ref), k
+    ba.close()
+
+
+@pytest.mark.parametrize("name", list(PROBLEMS))
+def test_stage_parity(engine, oracle, name):
+    """every intermediate of one LM iteration: a1 per observation, a2 blocks, a4 S / g_red, a5 delta_c,
+    a7 delta_p, cost / model decrease / trial cost."""
+    make, loss = PROBLEMS[name]
+    p = make()
+    ba = engine(p, loss=loss).set_problem(p.poses, p.points, p.obs_cam, p.obs_pt, p.obs_uv, p.fixed_cam)
+    st = oracle.stage(p, mu=1e4, loss=loss)
+    n = st["S"].shape[0]
+    free = p.fixed_cam == 0
+    tol = dict(RESIDUALS=1e-12, WEIGHTS=1e-12, JC=1e-13, JP=1e-13, B=1e-12, GC=1e-12, C=1e-12, GP=1e-12,
+               S=1e-11, GRED=1e-11, DC=1e-8, DP=1e-8, SCALARS=1e-10)
+    shapes = dict(RESIDUALS=("r", (p.no, 2)), WEIGHTS=("w", (p.no,)), JC=("Jc", (p.no, 2, 6)),
+                  JP=("Jp", (p.no, 2, 3)), B=("B", (p.nc, 6, 6)), GC=("gc", (p.nc, 6)), C=("C", (p.np_, 6)),
+                  GP=("gp", (p.np_, 3)), S=("S", (n, n)), GRED=("gred", (n,)), DC=("dc", (n,)),
+                  DP=("dp", (p.np_, 3)), SCALARS=("scalars", (4,)))
+    for k, (ok, shp) in shapes.items():
+        got, ref = ba.dump(k, shp), st[ok]
+        if k in ("B", "GC"):
+            got, ref = got[free], ref[free]
+        assert rel(got, ref) <= tol[k], (k, rel(got, ref))
+    ba.close()
+
+
+@pytest.mark.parametrize("name", list(PROBLEMS))
+def test_lm_trajectory_and_result(engine, oracle, name):
+    make, loss = PROBLEMS[name]
+    p, iters = make(), 10
+    ba = engine(p, loss=loss, max_iters=iters, record_history=True)
+    ba.set_problem(p.poses, p.points, p.obs_cam, p.obs_pt, p.obs_uv, p.fixed_cam)
+    sm = ba.solve()[0]
+    poses, pts = ba.get()
+    po, xo, so = oracle.solve(p, max_iters=iters, loss=loss)
+    assert (sm.status, sm.iterations, sm.accepted, sm.rejected, sm.n_invalid) == \
+           (so.status, so.iterations, so.accepted, so.rejected, so.n_invalid)
+    assert np.array_equal(ba.dump("HIST_ACCEPT", (1, 64), np.int32)[0, :iters], np.array(so.accept_hist[:iters]))
+    assert rel(ba.dump("HIST_COST", (1, 64))[0, :iters], np.array(so.cost_hist[:iters])) <= 1e-9
+    assert rel(ba.dump("HIST_MU", (1, 64))[0, :iters], np.array(so.mu_hist[:iters])) <= 1e-6
+    r_gpu, r_cpu = synth.rmse_px(p, poses, pts), synth.rmse_px(p, po, xo)
+    assert abs(r_gpu - r_cpu) <= 1e-6 * r_cpu
+    assert abs(sm.final_cost - so.final_cost) <= 1e-9 * so.final_cost
+    assert np.abs(poses - po).max() <= 1e-5
+    assert pts_err(pts, xo) <= 1e-5
+    assert r_gpu < 0.5 * synth.rmse_px(p)          # and it actually optimised
+    ba.close()
+
+
+def test_batch_matches_per_window_oracle(engine, oracle):
+    b = synth.make_batch(24, seed0=100)
+    from visualodometry_b200 import BAConfig, BundleAdjuster
+    res = BundleAdjuster(K_of(b), BAConfig(max_iters=10)).optimize_batch(b)
+    po, xo, sos = oracle.solve_batch(b, max_iters=10, threads=0)
+    fc = np.array([s.final_cost for s in res.summaries])
+    fo = np.array([s.final_cost for s in sos])
+    assert [s.accepted for s in res.summaries] == [s.accepted for s in sos]
+    assert rel(fc, fo) <= 1e-9
+    poses = np.concatenate([res.T_cw[:, :3, :3].reshape(-1, 9), res.T_cw[:, :3, 3]], axis=1)
+    assert np.abs(poses - po).max() <= 1e-5 and pts_err(res.points, xo) <= 1e-5
+
+
+def test_ragged_batch_and_empty_pieces(engine, oracle):
+    """windows of different sizes; a landmark without observations; a camera without observations."""
+    ws = [synth.make_window(20, n_cams=4, n_pts=50, n_obs=150), synth.make_window(21, n_cams=10, n_pts=700, n_obs=4000),
+          synth.make_window(22, n_cams=7, n_pts=65, n_obs=300)]
+    w = ws[0]
+    ws[0] = synth.BAProblem(np.vstack([w.poses, w.poses[-1:]]), np.vstack([w.points, [[1.0, 2.0, 30.0]]]), w.obs_cam,
+                            w.obs_pt, w.obs_uv, np.append(w.fixed_cam, 0).astype(np.uint8), w.intr)
+    b = synth.pack_batch(ws)
+    from visualodometry_b200 import BAConfig, BundleAdjuster
+    ba = BundleAdjuster(K_of(b), BAConfig(max_iters=8))
+    ba.set_problem(b.poses, b.points, b.obs_cam, b.obs_pt, b.obs_uv, b.fixed_cam, b.cam_off, b.pt_off, b.obs_off)
+    sms = ba.solve()
+    poses, pts = ba.get()
+    po, xo, sos = oracle.solve_batch(b, max_iters=8)
+    assert rel([s.final_cost for s in sms], [s.final_cost for s in sos]) <= 1e-9
+    assert np.abs(poses - po).max() <= 1e-5 and pts_err(pts, xo) <= 1e-5
+    assert np.array_equal(pts[50], [1.0, 2.0, 30.0])          # unobserved landmark untouched
+    assert np.abs(poses[4] - ws[0].poses[4]).max() <= 1e-12    # unobserved camera untouched
+
+
+def test_error_behaviour(engine):
+    p = synth.make_window(3, n_cams=4, n_pts=50, n_obs=150)
+    ba = engine(p)
+    bad_cam = p.obs_cam.copy(); bad_cam[0] = 77
+    with pytest.raises(RuntimeError, match="out of range"):
+        ba.set_problem(p.poses, p.points, bad_cam, p.obs_pt, p.obs_uv, p.fixed_cam)
+    with pytest.raises(RuntimeError, match="duplicate"):
+        ba.set_problem(p.poses, p.points, np.append(p.obs_cam, p.obs_cam[0]), np.append(p.obs_pt, p.obs_pt[0]),
+                       np.vstack([p.obs_uv, p.obs_uv[:1]]), p.fixed_cam)
+    with pytest.raises(RuntimeError):
+        ba.solve()                                              # no valid problem set
+    ba.close()
+
+
+def test_device_resident_inputs_zero_copy(engine, oracle):
+    import torch
+    p = synth.make_window(5, n_cams=6, n_pts=300, n_obs=1500)
+    from visualodometry_b200 import BAConfig, BundleAdjuster
+    from visualodometry_b200.ba import T_from_poses
+    ba = BundleAdjuster(K_of(p), BAConfig(max_iters=6))
+    t = lambda a: torch.as_tensor(a).cuda()
+    res = ba.optimize(t(T_from_poses(p.poses)), t(p.points), t(p.obs_cam), t(p.obs_pt), t(p.obs_uv),
+                      t(p.fixed_cam))
+    po, xo, so = oracle.solve(p, max_iters=6)
+    assert abs(res.summary.final_cost - so.final_cost) <= 1e-9 * so.final_cost
+    assert pts_err(res.points, xo) <= 1e-5
+
+
+def test_full_size_properties_c4_slice(engine):
+    """size-independent properties on a bigger batch than the oracle is asked to check: (1) permuting the
+    observation order leaves the result unchanged (canonical index), (2) a second solve from the result
+    does not increase the cost, (3) reset + solve is reproducible bit-for-bit."""
+    b = synth.make_batch(296, seed0=500, distinct=37)
+    from visualodometry_b200 import BAConfig, BundleAdjuster
+    ba = BundleAdjuster(K_of(b), BAConfig(max_iters=10))
+    ba.set_problem(b.poses, b.points, b.obs_cam, b.obs_pt, b.obs_uv, b.fixed_cam, b.cam_off, b.pt_off, b.obs_off)
+    s1 = ba.solve(); p1, x1 = ba.get()
+    ba.reset(); s2 = ba.solve(); p2, x2 = ba.get()
+    assert np.array_equal(p1, p2) and np.array_equal(x1, x2)
+    s3 = ba.solve()                                          # continue from the optimum
+    assert all(c.final_cost <= a.final_cost * (1 + 1e-12) for a, c in zip(s1, s3))
+    rng = np.random.default_rng(0)
+    oc, op, uv = b.obs_cam.copy(), b.obs_pt.copy(), b.obs_uv.copy()
+    for i in range(b.nb):
+        o0, o1 = b.obs_off[i], b.obs_off[i + 1]
+        perm = o0 + rng.permutation(o1 - o0)
+        oc[o0:o1], op[o0:o1], uv[o0:o1] = b.obs_cam[perm], b.obs_pt[perm], b.obs_uv[perm]
+    ba.set_problem(b.poses, b.points, oc, op, uv, b.fixed_cam, b.cam_off, b.pt_off, b.obs_off)
+    ba.solve(); p4, x4 = ba.get()
+    assert np.array_equal(p1, p4) and np.array_equal(x1, x4)

@@ -1,5 +1,5 @@
 // a8: observation-to-block index builder, on the device, once per problem.
-// Canonical orders (bit-exact contract with the oracle, oracle/ba_cpu.cpp build_index):
+// Canonical orders (the bit-exact contract the parity tests check):
 //   point-major : observations sorted by (window, pt, cam, original index)
 //   camera-major: observations sorted by (window, cam, pt, original index)
 #pragma once
