@@ -103,7 +103,12 @@ def test_lm_trajectory_and_result(engine, oracle, name):
            (so.status, so.iterations, so.accepted, so.rejected, so.n_invalid)
     assert np.array_equal(ba.dump("HIST_ACCEPT", (1, 64), np.int32)[0, :iters], np.array(so.accept_hist[:iters]))
     assert rel(ba.dump("HIST_COST", (1, 64))[0, :iters], np.array(so.cost_hist[:iters])) <= 1e-9
-    assert rel(ba.dump("HIST_MU", (1, 64))[0, :iters], np.array(so.mu_hist[:iters])) <= 1e-6
+    # mu depends on rho = (cost - trial)/model: once the cost decrease is ~1e-9 of the cost the
+    # numerator is cancellation noise, so compare mu only while the step still moves the cost
+    ch = np.array([so.initial_cost] + list(so.cost_hist[:iters]))
+    moving = np.concatenate([[True], (ch[:-1] - ch[1:])[:-1] > 1e-7 * ch[:-2]]) if iters > 1 else np.array([True])
+    hm, om = ba.dump("HIST_MU", (1, 64))[0, :iters], np.array(so.mu_hist[:iters])
+    assert rel(hm[moving], om[moving]) <= 1e-6
     r_gpu, r_cpu = synth.rmse_px(p, poses, pts), synth.rmse_px(p, po, xo)
     assert abs(r_gpu - r_cpu) <= 1e-6 * r_cpu
     assert abs(sm.final_cost - so.final_cost) <= 1e-9 * so.final_cost
