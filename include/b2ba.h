@@ -103,6 +103,11 @@ int64_t b2ba_dump(b2ba_t* h, int what, void* dst, int64_t bytes);
  * rank 0 and broadcast by the caller (e.g. torch.distributed); must be called before set_problem.
  * Every rank passes the FULL problem to set_problem; the engine keeps its point range. */
 int b2ba_create_comm(b2ba_t* h, const void* nccl_unique_id, int rank, int nranks);
+/* Fills 128 bytes with a fresh ncclUniqueId (call on rank 0, broadcast, pass to b2ba_create_comm). */
+int b2ba_nccl_unique_id(void* out128);
+/* This rank's landmark range [p_lo, p_hi) of the NEXT set_problem (required when nranks > 1; ranges
+ * of all ranks must tile [0, Np)).  The host side balances them by observation count. */
+int b2ba_set_point_range(b2ba_t* h, int32_t p_lo, int32_t p_hi);
 
 int b2ba_version(void);
 

@@ -121,6 +121,26 @@ class BundleAdjuster:
             raise RuntimeError(f"b2ba_create failed ({rc}): a CUDA device is required (no CPU fallback)")
         self._nb = 0
         self._shape = None
+        self.rank, self.nranks = 0, 1
+
+    def init_distributed(self, group=None):
+        """Observation-sharded solves (C5) across the ranks of a torch.distributed process group:
+        rank 0 creates an ncclUniqueId, it is broadcast through the group, and every rank builds the
+        engine's own NCCL communicator (NVLink / NVSwitch) from it."""
+        import torch.distributed as dist
+        from . import shard  # noqa: F401
+        self.rank, self.nranks = dist.get_rank(group), dist.get_world_size(group)
+        if self.nranks == 1:
+            return self
+        uid = np.zeros(128, np.uint8)
+        if self.rank == 0:
+            self._check(self._lib.b2ba_nccl_unique_id(uid.ctypes.data), "b2ba_nccl_unique_id")
+        dev = "cuda" if dist.get_backend(group) == "nccl" else "cpu"
+        t = torch.from_numpy(uid).to(dev)
+        dist.broadcast(t, src=0, group=group)
+        uid = t.cpu().numpy().copy()
+        self._check(self._lib.b2ba_create_comm(self._h, uid.ctypes.data, self.rank, self.nranks), "b2ba_create_comm")
+        return self
 
     def close(self):
         if getattr(self, "_h", None) and self._h.value:
@@ -149,6 +169,11 @@ class BundleAdjuster:
         intr = self.intr.ctypes.data_as(C.POINTER(C.c_double))
         mem = _lib.MEM_DEVICE if dev else _lib.MEM_HOST
         if cam_off is None:
+            if self.nranks > 1:
+                from .shard import point_ranges
+                op = obs_pt.detach().cpu().numpy() if _is_cuda_tensor(obs_pt) else np.asarray(obs_pt)
+                lo, hi = point_ranges(op, npts, self.nranks)[self.rank]
+                self._check(self._lib.b2ba_set_point_range(self._h, lo, hi), "b2ba_set_point_range")
             rc = self._lib.b2ba_set_problem(self._h, nc, npts, no, *[x.ptr for x in a], intr, mem)
             self._nb = 1
         else:

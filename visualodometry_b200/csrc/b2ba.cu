@@ -4,33 +4,19 @@
 #include "../../include/b2ba.h"
 
 #include <cstdio>
+#include <dlfcn.h>
 #include <cstring>
 #include <string>
 #include <vector>
 
 #include "ba_index.cuh"
+#include "devbuf.cuh"
 #include "ba_large.cuh"
 #include "ba_window.cuh"
 
 using namespace b2;
 
 namespace {
-
-template <class T>
-struct DevBuf {
-  T* p = nullptr;
-  size_t n = 0;
-  cudaError_t alloc(size_t count) {
-    if (count <= n && p) return cudaSuccess;
-    release();
-    cudaError_t e = cudaMalloc((void**)&p, (count ? count : 1) * sizeof(T));
-    if (e == cudaSuccess) n = count;
-    else p = nullptr;
-    return e;
-  }
-  void release() { if (p) cudaFree(p); p = nullptr; n = 0; }
-  ~DevBuf() { release(); }
-};
 
 enum Path { PATH_NONE = 0, PATH_WIN_SMALL, PATH_WIN_BIG, PATH_LARGE };
 
@@ -55,7 +41,14 @@ struct b2ba {
   DevBuf<double> d_poses, d_poses0, d_pts0, d_pts1, d_ptsinit, d_scratch, d_hist_cost, d_hist_mu, d_dbg;
   DevBuf<ObsRec> d_pm, d_cm;
   DevBuf<b2ba_summary> d_summ;
-  LargeState large;
+  // large path
+  LargeIndex lix;
+  DevBuf<ObsRec> l_cm;
+  DevBuf<int> l_cam_ptr;
+  DevBuf<double> l_poses_tri, l_lin_part, l_lin, l_Dc, l_Sg, l_dc, l_r, l_z, l_q, l_Minv, l_part, l_sums;
+  DevBuf<LargeCtrl> l_ctrl;
+  int p_lo = 0, p_hi = 0;
+  bool range_set = false;
   cudaStream_t last_stream = nullptr;
   bool solved = false;
   // multi-GPU
@@ -107,6 +100,121 @@ WinData make_win(b2ba* h, bool hist, double* dbg) {
 cudaMemcpyKind in_kind(int mem) { return mem == B2BA_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice; }
 cudaMemcpyKind out_kind(int mem) { return mem == B2BA_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost; }
 
+
+// ---------------------------------------------------------------------------------------------
+// NCCL through dlopen: no link-time dependency, single-GPU use never touches it.  In a torch
+// process the already-loaded libnccl.so.2 (torch's bundled 2.28.x) is the one that resolves.
+struct NcclApi {
+  typedef struct { char internal[128]; } UniqueId;
+  int (*GetUniqueId)(UniqueId*) = nullptr;
+  int (*CommInitRank)(void**, int, UniqueId, int) = nullptr;
+  int (*AllReduce)(const void*, void*, size_t, int, int, void*, cudaStream_t) = nullptr;
+  int (*CommDestroy)(void*) = nullptr;
+  const char* (*GetErrorString)(int) = nullptr;
+  bool ok = false;
+};
+NcclApi& nccl_api() {
+  static NcclApi api;
+  static bool tried = false;
+  if (!tried) {
+    tried = true;
+    void* lib = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+    if (!lib) lib = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+    if (lib) {
+      api.GetUniqueId = (int (*)(NcclApi::UniqueId*))dlsym(lib, "ncclGetUniqueId");
+      api.CommInitRank = (int (*)(void**, int, NcclApi::UniqueId, int))dlsym(lib, "ncclCommInitRank");
+      api.AllReduce = (int (*)(const void*, void*, size_t, int, int, void*, cudaStream_t))dlsym(lib, "ncclAllReduce");
+      api.CommDestroy = (int (*)(void*))dlsym(lib, "ncclCommDestroy");
+      api.GetErrorString = (const char* (*)(int))dlsym(lib, "ncclGetErrorString");
+      api.ok = api.GetUniqueId && api.CommInitRank && api.AllReduce && api.CommDestroy;
+    }
+  }
+  return api;
+}
+int nccl_allreduce_f64(void* user, const double* send, double* recv, size_t count, cudaStream_t s) {
+  b2ba* h = (b2ba*)user;
+  const int rc = nccl_api().AllReduce(send, recv, count, /*ncclFloat64*/ 8, /*ncclSum*/ 0, h->nccl_comm, s);
+  if (rc != 0) {
+    h->err = std::string("ncclAllReduce: ") + (nccl_api().GetErrorString ? nccl_api().GetErrorString(rc) : "error");
+    return B2BA_E_NCCL;
+  }
+  return 0;
+}
+
+LargeData make_large(b2ba* h, bool hist) {
+  LargeData d;
+  d.nc = h->nc_tot; d.np = h->np_tot; d.nfree = h->lix.nfree; d.n = 6 * h->lix.nfree;
+  d.p_lo = h->p_lo; d.p_hi = h->p_hi; d.rank = h->rank; d.nranks = h->nranks;
+  d.pm = h->d_pm.p; d.pt_ptr = h->d_pt_ptr.p; d.cm = h->l_cm.p; d.cam_ptr = h->l_cam_ptr.p;
+  d.fidx = h->lix.fidx.p; d.blk_ptr = h->lix.blk_ptr.p; d.blk_col = h->lix.blk_col.p; d.nblk = h->lix.nblk;
+  d.frow_ptr = h->lix.frow_ptr.p; d.fcol = h->lix.fcol.p; d.fsrc = h->lix.fsrc.p;
+  d.poses = h->d_poses.p; d.poses_tri = h->l_poses_tri.p; d.pts = h->d_pts0.p; d.pts_tri = h->d_pts1.p;
+  d.lin_part = h->l_lin_part.p; d.lin = h->nranks > 1 ? h->l_lin.p : h->l_lin_part.p;
+  d.Dc = h->l_Dc.p; d.pt_scratch = h->d_scratch.p; d.Sg = h->l_Sg.p; d.dc = h->l_dc.p;
+  d.r = h->l_r.p; d.z = h->l_z.p; d.q = h->l_q.p; d.Minv = h->l_Minv.p; d.part = h->l_part.p;
+  d.sums_part = h->l_sums.p; d.ctrl = h->l_ctrl.p; d.summary = h->d_summ.p;
+  d.hist_cost = hist ? h->d_hist_cost.p : nullptr; d.hist_mu = hist ? h->d_hist_mu.p : nullptr;
+  d.hist_accept = hist ? h->d_hist_accept.p : nullptr;
+  return d;
+}
+
+// a8 for the large path: S block structure, this rank's landmark range and its camera-major stream
+int setup_large(b2ba* h) {
+  if (h->B != 1) return fail(h, B2BA_E_UNSUPPORTED, "the large (PCG) path takes one problem, not a batch");
+  if (h->nranks > 1 && !h->range_set) return fail(h, B2BA_E_STATE, "nranks > 1: call b2ba_set_point_range first");
+  if (!h->range_set) { h->p_lo = 0; h->p_hi = h->np_tot; }
+  if (h->p_lo < 0 || h->p_hi > h->np_tot || h->p_lo > h->p_hi) return fail(h, B2BA_E_INVALID, "bad point range");
+  int rc = large_build_structure(h->nc_tot, h->np_tot, h->no, h->d_pm.p, h->d_pt_ptr.p, h->h_fixed.data(), h->lix, nullptr);
+  if (rc) return cuda_fail(h, (cudaError_t)rc, "large_build_structure");
+  const size_t nc = h->nc_tot, n = 6 * (size_t)h->lix.nfree, nblk = h->lix.nblk;
+  if (n * sizeof(double) > 200 * 1024) return fail(h, B2BA_E_UNSUPPORTED, "PCG keeps the search direction in shared memory: at most 4266 free cameras");
+  CU(h->l_cm.alloc(h->no), "alloc"); CU(h->l_cam_ptr.alloc(nc + 1), "alloc");
+  rc = large_build_cm_slice(h->nc_tot, h->p_lo, h->p_hi, h->d_pm.p, h->d_pt_ptr.p, h->l_cm.p, h->l_cam_ptr.p, nullptr);
+  if (rc) return cuda_fail(h, (cudaError_t)rc, "large_build_cm_slice");
+  int blocks = 0;
+  size_t smem = 0;
+  rc = large_pcg_grid((int)n, &blocks, &smem);
+  if (rc) return cuda_fail(h, (cudaError_t)rc, "large_pcg_grid");
+  const size_t nparts = ((size_t)(h->p_hi - h->p_lo) + 127) / 128;
+  size_t part = 2 * nc;
+  if ((size_t)blocks * 4 > part) part = (size_t)blocks * 4;
+  if (nparts * 8 > part) part = nparts * 8;
+  CU(h->l_poses_tri.alloc(nc * 12), "alloc"); CU(h->l_lin_part.alloc(nc * 27 + 2), "alloc");
+  CU(h->l_lin.alloc(nc * 27 + 2), "alloc"); CU(h->l_Dc.alloc(nc * 6), "alloc");
+  CU(h->l_Sg.alloc(nblk * 36 + n), "alloc"); CU(h->l_dc.alloc(n), "alloc"); CU(h->l_r.alloc(n), "alloc");
+  CU(h->l_z.alloc(n), "alloc"); CU(h->l_q.alloc(n), "alloc"); CU(h->l_Minv.alloc(6 * n), "alloc");
+  CU(h->l_part.alloc(part + 8), "alloc"); CU(h->l_sums.alloc(16), "alloc"); CU(h->l_ctrl.alloc(1), "alloc");
+  CU(cudaMemset(h->l_lin_part.p, 0, (nc * 27 + 2) * sizeof(double)), "memset");
+  CU(cudaMemset(h->l_sums.p, 0, 16 * sizeof(double)), "memset");
+  CU(cudaDeviceSynchronize(), "setup_large");
+  return B2BA_OK;
+}
+
+__global__ void zero_outside_range(double* pts, int np, int p_lo, int p_hi) {
+  const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  if (i < (size_t)np * 3 && (i < (size_t)p_lo * 3 || i >= (size_t)p_hi * 3)) pts[i] = 0.0;
+}
+
+int solve_large(b2ba* h, const Params& P, bool hist, cudaStream_t s) {
+  const LargeData d = make_large(h, hist);
+  AllReduceFn ar = h->nranks > 1 ? nccl_allreduce_f64 : nullptr;
+  int rc = large_init_ctrl(d, P, s);
+  if (rc) return cuda_fail(h, (cudaError_t)rc, "large_init_ctrl");
+  for (int it = 0; it < P.max_iters; ++it) {
+    rc = large_iteration(d, P, h->opt.pcg_max_iters, h->opt.pcg_tol, ar, h, s);
+    if (rc == B2BA_E_NCCL) return rc;
+    if (rc) return cuda_fail(h, (cudaError_t)rc, "large_iteration");
+  }
+  rc = large_finish(d, s);
+  if (rc) return cuda_fail(h, (cudaError_t)rc, "large_finish");
+  if (h->nranks > 1) {   // every rank ends with all landmarks: sum of range-masked copies
+    zero_outside_range<<<(h->np_tot * 3 + 255) / 256, 256, 0, s>>>(h->d_pts0.p, h->np_tot, h->p_lo, h->p_hi);
+    rc = nccl_allreduce_f64(h, h->d_pts0.p, h->d_pts0.p, (size_t)h->np_tot * 3, s);
+    if (rc) return rc;
+  }
+  return B2BA_OK;
+}
+
 }  // namespace
 
 extern "C" {
@@ -137,6 +245,7 @@ int b2ba_create(b2ba_t** out, int device, const b2ba_options* opts) {
 void b2ba_destroy(b2ba_t* h) {
   if (!h) return;
   cudaSetDevice(h->device);
+  if (h->nccl_comm && nccl_api().ok) nccl_api().CommDestroy(h->nccl_comm);
   delete h;
 }
 
@@ -210,9 +319,11 @@ int b2ba_set_problem_batch(b2ba_t* h, int32_t B, const int32_t* cam_off, const i
   else if (h->opt.solver == B2BA_SOLVER_WINDOW)
     return fail(h, B2BA_E_UNSUPPORTED, "window solver supports at most 21 free / 24 total cameras per window");
   else h->path = PATH_LARGE;
+  if (h->nranks > 1 && h->path != PATH_LARGE)
+    return fail(h, B2BA_E_UNSUPPORTED, "observation sharding (nranks > 1) needs solver = B2BA_SOLVER_PCG");
   if (h->path == PATH_LARGE) {
-    h->path = PATH_NONE;
-    return fail(h, B2BA_E_UNSUPPORTED, "large (PCG) path not built yet");
+    const int rc2 = setup_large(h);
+    if (rc2) { h->path = PATH_NONE; return rc2; }
   }
   return B2BA_OK;
 }
@@ -275,7 +386,11 @@ int b2ba_solve(b2ba_t* h, int32_t max_iters, b2ba_summary* summaries, void* cuda
   int rc = 0;
   if (h->path == PATH_WIN_SMALL) rc = launch_window_small(make_win(h, hist, nullptr), P, s);
   else if (h->path == PATH_WIN_BIG) rc = launch_window_big(make_win(h, hist, nullptr), P, s);
-  else return fail(h, B2BA_E_UNSUPPORTED, "path not available");
+  else if (h->path == PATH_LARGE) {
+    if (hist) { CU(h->d_hist_cost.alloc(kHist), "alloc"); }
+    rc = solve_large(h, P, hist, s);
+    if (rc) return rc;
+  } else return fail(h, B2BA_E_UNSUPPORTED, "path not available");
   if (rc) return cuda_fail(h, (cudaError_t)rc, "launch");
   h->solved = true;
   if (!summaries) return B2BA_OK;
@@ -298,8 +413,32 @@ int b2ba_get(b2ba_t* h, double* poses_cw, double* points, int mem) {
 }
 
 int b2ba_create_comm(b2ba_t* h, const void* nccl_unique_id, int rank, int nranks) {
-  (void)nccl_unique_id; (void)rank; (void)nranks;
-  return fail(h, B2BA_E_UNSUPPORTED, "multi-GPU observation sharding needs the large (PCG) path");
+  if (!h || !nccl_unique_id || nranks < 1 || rank < 0 || rank >= nranks) return fail(h, B2BA_E_INVALID, "create_comm: bad arguments");
+  NcclApi& api = nccl_api();
+  if (!api.ok) return fail(h, B2BA_E_NCCL, "libnccl.so.2 could not be loaded");
+  CU(cudaSetDevice(h->device), "cudaSetDevice");
+  if (h->nccl_comm) { api.CommDestroy(h->nccl_comm); h->nccl_comm = nullptr; }
+  NcclApi::UniqueId id;
+  std::memcpy(&id, nccl_unique_id, sizeof(id));
+  const int rc = api.CommInitRank(&h->nccl_comm, nranks, id, rank);
+  if (rc != 0) return fail(h, B2BA_E_NCCL, std::string("ncclCommInitRank: ") + (api.GetErrorString ? api.GetErrorString(rc) : "error"));
+  h->rank = rank; h->nranks = nranks;
+  return B2BA_OK;
+}
+
+int b2ba_nccl_unique_id(void* out128) {
+  NcclApi& api = nccl_api();
+  if (!api.ok || !out128) return B2BA_E_NCCL;
+  NcclApi::UniqueId id;
+  if (api.GetUniqueId(&id) != 0) return B2BA_E_NCCL;
+  std::memcpy(out128, &id, sizeof(id));
+  return B2BA_OK;
+}
+
+int b2ba_set_point_range(b2ba_t* h, int32_t p_lo, int32_t p_hi) {
+  if (!h || p_lo < 0 || p_hi < p_lo) return fail(h, B2BA_E_INVALID, "set_point_range: bad range");
+  h->p_lo = p_lo; h->p_hi = p_hi; h->range_set = true;
+  return B2BA_OK;
 }
 
 namespace {
@@ -385,8 +524,61 @@ int64_t b2ba_dump(b2ba_t* h, int what, void* dst, int64_t bytes) {
       CU(cudaMemcpy(dst, tmp.p, no * per * 8, cudaMemcpyDeviceToHost), "read");
       return (int64_t)(no * per * 8);
     }
+    case B2BA_D_BLK_PTR:
+    case B2BA_D_BLK_COL: {
+      if (h->path != PATH_LARGE) return fail(h, B2BA_E_UNSUPPORTED, "S block structure exists on the large (PCG) path only");
+      const size_t n = what == B2BA_D_BLK_PTR ? (size_t)h->lix.nfree + 1 : (size_t)h->lix.nblk;
+      std::vector<int> v(n);
+      CU(cudaMemcpy(v.data(), what == B2BA_D_BLK_PTR ? h->lix.blk_ptr.p : h->lix.blk_col.p, n * 4, cudaMemcpyDeviceToHost), "read");
+      return put(h, v.data(), n * 4, dst, bytes);
+    }
     case B2BA_D_B: case B2BA_D_GC: case B2BA_D_C: case B2BA_D_GP: case B2BA_D_S: case B2BA_D_GRED:
     case B2BA_D_DC: case B2BA_D_DP: case B2BA_D_SCALARS: {
+      if (h->path == PATH_LARGE) {
+        if (what != B2BA_D_S && what != B2BA_D_GRED && what != B2BA_D_DC && what != B2BA_D_SCALARS)
+          return fail(h, B2BA_E_UNSUPPORTED, "large path dumps S, g_red, delta_c and the scalars only");
+        if (h->nranks > 1) return fail(h, B2BA_E_UNSUPPORTED, "stage dumps are single-GPU");
+        DevBuf<double> sp, sx;
+        DevBuf<b2ba_summary> ss;
+        const size_t nc12 = (size_t)h->nc_tot * 12, np3 = (size_t)h->np_tot * 3, n = 6 * (size_t)h->lix.nfree;
+        CU(sp.alloc(nc12), "alloc"); CU(sx.alloc(np3), "alloc"); CU(ss.alloc(1), "alloc");
+        CU(cudaMemcpy(sp.p, h->d_poses.p, nc12 * 8, cudaMemcpyDeviceToDevice), "save");
+        CU(cudaMemcpy(sx.p, h->d_pts0.p, np3 * 8, cudaMemcpyDeviceToDevice), "save");
+        CU(cudaMemcpy(ss.p, h->d_summ.p, sizeof(b2ba_summary), cudaMemcpyDeviceToDevice), "save");
+        int rc = solve_large(h, make_params(h, 1), false, nullptr);
+        if (rc) return rc;
+        CU(cudaDeviceSynchronize(), "stage");
+        std::vector<double> sg((size_t)h->lix.nblk * 36 + n), dcv(n);
+        std::vector<int> bp(h->lix.nfree + 1), bc(h->lix.nblk);
+        LargeCtrl ctrl;
+        CU(cudaMemcpy(sg.data(), h->l_Sg.p, sg.size() * 8, cudaMemcpyDeviceToHost), "read");
+        CU(cudaMemcpy(dcv.data(), h->l_dc.p, n * 8, cudaMemcpyDeviceToHost), "read");
+        CU(cudaMemcpy(bp.data(), h->lix.blk_ptr.p, bp.size() * 4, cudaMemcpyDeviceToHost), "read");
+        CU(cudaMemcpy(bc.data(), h->lix.blk_col.p, bc.size() * 4, cudaMemcpyDeviceToHost), "read");
+        CU(cudaMemcpy(&ctrl, h->l_ctrl.p, sizeof(ctrl), cudaMemcpyDeviceToHost), "read");
+        CU(cudaMemcpy(h->d_poses.p, sp.p, nc12 * 8, cudaMemcpyDeviceToDevice), "restore");
+        CU(cudaMemcpy(h->d_pts0.p, sx.p, np3 * 8, cudaMemcpyDeviceToDevice), "restore");
+        CU(cudaMemcpy(h->d_summ.p, ss.p, sizeof(b2ba_summary), cudaMemcpyDeviceToDevice), "restore");
+        if (what == B2BA_D_GRED) return put(h, &sg[(size_t)h->lix.nblk * 36], n * 8, dst, bytes);
+        if (what == B2BA_D_DC) return put(h, dcv.data(), n * 8, dst, bytes);
+        if (what == B2BA_D_SCALARS) {
+          const double sc[4] = {ctrl.initial_cost, 0.0, ctrl.accept ? ctrl.cost : 0.0, (double)ctrl.pcg_last};
+          return put(h, sc, sizeof(sc), dst, bytes);
+        }
+        std::vector<double> S(n * n, 0.0);
+        for (int fi = 0; fi < h->lix.nfree; ++fi)
+          for (int b = bp[fi]; b < bp[fi + 1]; ++b) {
+            const int fj = bc[b];
+            for (int r = 0; r < 6; ++r)
+              for (int c = 0; c < 6; ++c) {
+                if (fi == fj && c < r) continue;
+                const double v = sg[(size_t)b * 36 + 6 * r + c];
+                S[(size_t)(6 * fi + r) * n + 6 * fj + c] = v;
+                S[(size_t)(6 * fj + c) * n + 6 * fi + r] = v;
+              }
+          }
+        return put(h, S.data(), n * n * 8, dst, bytes);
+      }
       std::vector<double> o;
       WinDbg L;
       int rc = run_stage(h, o, L);

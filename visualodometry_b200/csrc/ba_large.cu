@@ -1,2 +1,892 @@
-// Large path (C5) kernels -- see ba_large.cuh.
+// Large path kernels -- see ba_large.cuh.
 #include "ba_large.cuh"
+
+#include <cooperative_groups.h>
+#include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_scan.cuh>
+#include <cub/device/device_select.cuh>
+
+#include <vector>
+
+namespace cg = cooperative_groups;
+
+namespace b2 {
+
+namespace {
+
+#define B2_TRY(x) do { e = (x); if (e != cudaSuccess) goto done; } while (0)
+
+inline int bits_for(long long n) { int b = 1; while ((1ll << b) < n && b < 62) ++b; return b; }
+
+// ------------------------------------------------------------------------------------------
+// S structure (a8): upper block pairs (fi <= fj) that share a landmark, plus all diagonals.
+__global__ void count_pairs(int np, const ObsRec* __restrict__ pm, const int* __restrict__ pt_ptr,
+                            const int* __restrict__ fidx, int* cnt) {
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= np) return;
+  int k = 0;
+  for (int a = pt_ptr[p]; a < pt_ptr[p + 1]; ++a) k += fidx[pm[a].idx] >= 0 ? 1 : 0;
+  cnt[p] = k * (k - 1) / 2;
+}
+
+__global__ void emit_pairs(int np, int nfree, const ObsRec* __restrict__ pm, const int* __restrict__ pt_ptr,
+                           const int* __restrict__ fidx, const int* __restrict__ off,
+                           unsigned long long* keys) {
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= np) return;
+  int o = off[p];
+  const int a1 = pt_ptr[p + 1];
+  for (int a = pt_ptr[p]; a < a1; ++a) {
+    const int fa = fidx[pm[a].idx];
+    if (fa < 0) continue;
+    for (int b = a + 1; b < a1; ++b) {
+      const int fb = fidx[pm[b].idx];
+      if (fb < 0) continue;
+      keys[o++] = (unsigned long long)fa * nfree + fb;    // cameras ascend within a landmark
+    }
+  }
+}
+
+__global__ void emit_diag(int nfree, unsigned long long* keys) {
+  const int f = blockIdx.x * blockDim.x + threadIdx.x;
+  if (f < nfree) keys[f] = (unsigned long long)f * nfree + f;
+}
+
+// sorted unique keys -> CSR (row_ptr, col); optional payload copy
+__global__ void keys_to_csr(int nkeys, int nrows, int ncols, const unsigned long long* __restrict__ keys,
+                            int* row_ptr, int* col) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= nkeys) return;
+  const int row = (int)(keys[i] / ncols);
+  col[i] = (int)(keys[i] % ncols);
+  const int prev = i == 0 ? -1 : (int)(keys[i - 1] / ncols);
+  for (int q = prev + 1; q <= row; ++q) row_ptr[q] = i;
+  if (i == nkeys - 1)
+    for (int q = row + 1; q <= nrows; ++q) row_ptr[q] = nkeys;
+}
+
+// upper blocks -> entries of the full symmetric structure
+__global__ void emit_full(int nfree, const int* __restrict__ blk_ptr, const int* __restrict__ blk_col,
+                          unsigned long long* keys, int* vals) {
+  const int fi = blockIdx.x * blockDim.x + threadIdx.x;
+  if (fi >= nfree) return;
+  for (int b = blk_ptr[fi]; b < blk_ptr[fi + 1]; ++b) {
+    const int fj = blk_col[b];
+    // entry positions: upper block b -> slot 2b-(#diagonals before) is awkward; use two arrays halves
+    keys[2 * b] = (unsigned long long)fi * nfree + fj;
+    vals[2 * b] = b;
+    if (fi != fj) { keys[2 * b + 1] = (unsigned long long)fj * nfree + fi; vals[2 * b + 1] = b | (1 << 31); }
+    else { keys[2 * b + 1] = ~0ull; vals[2 * b + 1] = -1; }   // padding, sorts last
+  }
+}
+
+__global__ void pt_of_obs(int p_lo, int p_hi, const int* __restrict__ pt_ptr, int base, int* pt) {
+  const int p = p_lo + blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= p_hi) return;
+  for (int a = pt_ptr[p]; a < pt_ptr[p + 1]; ++a) pt[a - base] = p;
+}
+
+__global__ void cam_keys_of_slice(int n, const ObsRec* __restrict__ pm, unsigned* keys, int* pos) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  keys[i] = (unsigned)pm[i].idx;
+  pos[i] = i;
+}
+
+__global__ void build_cm_slice(int n, int nc, const unsigned* __restrict__ keys, const int* __restrict__ pos,
+                               const ObsRec* __restrict__ pm, const int* __restrict__ pt, ObsRec* cm,
+                               int* cam_ptr) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  ObsRec r = pm[pos[i]];
+  r.idx = pt[pos[i]];
+  cm[i] = r;
+  const int c = (int)keys[i], prev = i == 0 ? -1 : (int)keys[i - 1];
+  for (int q = prev + 1; q <= c; ++q) cam_ptr[q] = i;
+  if (i == n - 1)
+    for (int q = c + 1; q <= nc; ++q) cam_ptr[q] = n;
+}
+
+__global__ void fill_int(int* p, int n, int v) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) p[i] = v;
+}
+
+}  // namespace
+
+int large_build_structure(int nc, int np, long long no, const ObsRec* pm, const int* pt_ptr,
+                          const unsigned char* h_fixed, LargeIndex& ix, cudaStream_t s) {
+  (void)no;
+  cudaError_t e = cudaSuccess;
+  std::vector<int> hf(nc);
+  int nfree = 0;
+  for (int c = 0; c < nc; ++c) hf[c] = h_fixed[c] ? -1 : nfree++;
+  ix.nfree = nfree;
+  int *cnt = nullptr, *off = nullptr, *vals = nullptr, *vals2 = nullptr, *dnum = nullptr;
+  unsigned long long *keys = nullptr, *keys2 = nullptr;
+  void* tmp = nullptr;
+  size_t tb = 0, t2 = 0;
+  int last_cnt = 0, last_off = 0, nuniq = 0;
+  long long total = 0;
+  const int kb = bits_for((long long)nfree * nfree + 1);
+  B2_TRY(ix.fidx.alloc(nc));
+  B2_TRY(cudaMemcpyAsync(ix.fidx.p, hf.data(), nc * sizeof(int), cudaMemcpyHostToDevice, s));
+  B2_TRY(cudaStreamSynchronize(s));   // hf goes out of scope at return; keep it simple
+  B2_TRY(cudaMallocAsync(&cnt, (np + 1) * sizeof(int), s));
+  B2_TRY(cudaMallocAsync(&off, (np + 1) * sizeof(int), s));
+  B2_TRY(cudaMallocAsync(&dnum, sizeof(int), s));
+  if (np > 0) {
+    count_pairs<<<(np + 255) / 256, 256, 0, s>>>(np, pm, pt_ptr, ix.fidx.p, cnt);
+    cub::DeviceScan::ExclusiveSum(nullptr, tb, cnt, off, np, s);
+    B2_TRY(cudaMallocAsync(&tmp, tb, s));
+    B2_TRY(cub::DeviceScan::ExclusiveSum(tmp, tb, cnt, off, np, s));
+    B2_TRY(cudaMemcpyAsync(&last_cnt, cnt + np - 1, sizeof(int), cudaMemcpyDeviceToHost, s));
+    B2_TRY(cudaMemcpyAsync(&last_off, off + np - 1, sizeof(int), cudaMemcpyDeviceToHost, s));
+    B2_TRY(cudaStreamSynchronize(s));
+    B2_TRY(cudaFreeAsync(tmp, s));
+    tmp = nullptr;
+  }
+  total = (long long)last_cnt + last_off + nfree;
+  if (total >= (1ll << 31)) { e = cudaErrorInvalidValue; goto done; }
+  B2_TRY(cudaMallocAsync(&keys, (total + 1) * 8, s));
+  B2_TRY(cudaMallocAsync(&keys2, (total + 1) * 8, s));
+  if (nfree > 0) emit_diag<<<(nfree + 255) / 256, 256, 0, s>>>(nfree, keys);
+  if (np > 0) emit_pairs<<<(np + 255) / 256, 256, 0, s>>>(np, nfree, pm, pt_ptr, ix.fidx.p, off, keys + nfree);
+  if (total > 0) {
+    cub::DeviceRadixSort::SortKeys(nullptr, tb, keys, keys2, (int)total, 0, kb, s);
+    cub::DeviceSelect::Unique(nullptr, t2, keys2, keys, dnum, (int)total, s);
+    if (t2 > tb) tb = t2;
+    B2_TRY(cudaMallocAsync(&tmp, tb, s));
+    B2_TRY(cub::DeviceRadixSort::SortKeys(tmp, tb, keys, keys2, (int)total, 0, kb, s));
+    B2_TRY(cub::DeviceSelect::Unique(tmp, tb, keys2, keys, dnum, (int)total, s));
+    B2_TRY(cudaMemcpyAsync(&nuniq, dnum, sizeof(int), cudaMemcpyDeviceToHost, s));
+    B2_TRY(cudaStreamSynchronize(s));
+    B2_TRY(cudaFreeAsync(tmp, s));
+    tmp = nullptr;
+  }
+  ix.nblk = nuniq;
+  ix.nfull = 2 * nuniq - nfree;
+  B2_TRY(ix.blk_ptr.alloc(nfree + 1)); B2_TRY(ix.blk_col.alloc(nuniq));
+  B2_TRY(ix.frow_ptr.alloc(nfree + 1)); B2_TRY(ix.fcol.alloc(2 * (size_t)nuniq)); B2_TRY(ix.fsrc.alloc(2 * (size_t)nuniq));
+  if (nuniq == 0) {
+    fill_int<<<1, 32, 0, s>>>(ix.blk_ptr.p, nfree + 1, 0);
+    fill_int<<<1, 32, 0, s>>>(ix.frow_ptr.p, nfree + 1, 0);
+    goto done;
+  }
+  keys_to_csr<<<(nuniq + 255) / 256, 256, 0, s>>>(nuniq, nfree, nfree, keys, ix.blk_ptr.p, ix.blk_col.p);
+  // full symmetric structure: 2*nblk candidate entries (diagonal duplicates padded out), sorted by (row, col)
+  B2_TRY(cudaMallocAsync(&vals, 2 * (size_t)nuniq * sizeof(int), s));
+  B2_TRY(cudaMallocAsync(&vals2, 2 * (size_t)nuniq * sizeof(int), s));
+  B2_TRY(cudaFreeAsync(keys2, s)); keys2 = nullptr;
+  B2_TRY(cudaMallocAsync(&keys2, 2 * (size_t)nuniq * 8, s));
+  {
+    unsigned long long* fk = nullptr;
+    B2_TRY(cudaMallocAsync(&fk, 2 * (size_t)nuniq * 8, s));
+    emit_full<<<(nfree + 255) / 256, 256, 0, s>>>(nfree, ix.blk_ptr.p, ix.blk_col.p, fk, vals);
+    cub::DeviceRadixSort::SortPairs(nullptr, tb, fk, keys2, vals, vals2, 2 * nuniq, 0, 64, s);
+    e = cudaMallocAsync(&tmp, tb, s);
+    if (e == cudaSuccess) e = cub::DeviceRadixSort::SortPairs(tmp, tb, fk, keys2, vals, vals2, 2 * nuniq, 0, 64, s);
+    cudaFreeAsync(fk, s);
+    if (e != cudaSuccess) goto done;
+  }
+  keys_to_csr<<<(ix.nfull + 255) / 256, 256, 0, s>>>(ix.nfull, nfree, nfree, keys2, ix.frow_ptr.p, ix.fcol.p);
+  B2_TRY(cudaMemcpyAsync(ix.fsrc.p, vals2, (size_t)ix.nfull * sizeof(int), cudaMemcpyDeviceToDevice, s));
+  B2_TRY(cudaGetLastError());
+done:
+  cudaFreeAsync(cnt, s); cudaFreeAsync(off, s); cudaFreeAsync(dnum, s); cudaFreeAsync(keys, s);
+  cudaFreeAsync(keys2, s); cudaFreeAsync(vals, s); cudaFreeAsync(vals2, s); cudaFreeAsync(tmp, s);
+  cudaStreamSynchronize(s);
+  return (int)e;
+}
+
+int large_build_cm_slice(int nc, int p_lo, int p_hi, const ObsRec* pm, const int* pt_ptr, ObsRec* cm,
+                         int* cam_ptr, cudaStream_t s) {
+  cudaError_t e = cudaSuccess;
+  int lo = 0, hi = 0;
+  unsigned *k0 = nullptr, *k1 = nullptr;
+  int *v0 = nullptr, *v1 = nullptr, *pt = nullptr;
+  void* tmp = nullptr;
+  size_t tb = 0;
+  int n = 0;
+  B2_TRY(cudaMemcpyAsync(&lo, pt_ptr + p_lo, sizeof(int), cudaMemcpyDeviceToHost, s));
+  B2_TRY(cudaMemcpyAsync(&hi, pt_ptr + p_hi, sizeof(int), cudaMemcpyDeviceToHost, s));
+  B2_TRY(cudaStreamSynchronize(s));
+  n = hi - lo;
+  if (n == 0) {
+    fill_int<<<(nc + 256) / 256, 256, 0, s>>>(cam_ptr, nc + 1, 0);
+    return (int)cudaGetLastError();
+  }
+  B2_TRY(cudaMallocAsync(&k0, n * 4, s)); B2_TRY(cudaMallocAsync(&k1, n * 4, s));
+  B2_TRY(cudaMallocAsync(&v0, n * 4, s)); B2_TRY(cudaMallocAsync(&v1, n * 4, s));
+  B2_TRY(cudaMallocAsync(&pt, n * 4, s));
+  pt_of_obs<<<(p_hi - p_lo + 255) / 256, 256, 0, s>>>(p_lo, p_hi, pt_ptr, lo, pt);
+  cam_keys_of_slice<<<(n + 255) / 256, 256, 0, s>>>(n, pm + lo, k0, v0);
+  cub::DeviceRadixSort::SortPairs(nullptr, tb, k0, k1, v0, v1, n, 0, bits_for(nc), s);
+  B2_TRY(cudaMallocAsync(&tmp, tb, s));
+  B2_TRY(cub::DeviceRadixSort::SortPairs(tmp, tb, k0, k1, v0, v1, n, 0, bits_for(nc), s));
+  build_cm_slice<<<(n + 255) / 256, 256, 0, s>>>(n, nc, k1, v1, pm + lo, pt, cm, cam_ptr);
+  B2_TRY(cudaGetLastError());
+done:
+  cudaFreeAsync(k0, s); cudaFreeAsync(k1, s); cudaFreeAsync(v0, s); cudaFreeAsync(v1, s);
+  cudaFreeAsync(pt, s); cudaFreeAsync(tmp, s);
+  return (int)e;
+}
+
+}  // namespace b2
+
+// =============================================================================================
+// LM iteration kernels.  Every kernel returns immediately once ctrl->stop is set, so the host can
+// enqueue a fixed number of iterations without reading anything back.
+namespace b2 {
+namespace {
+
+__device__ __forceinline__ int packed21(int r, int s) { return r * 6 - r * (r - 1) / 2 + (s - r); }
+
+__device__ __forceinline__ int find_blk(const int* __restrict__ blk_ptr, const int* __restrict__ blk_col, int fi, int fj) {
+  int lo = blk_ptr[fi], hi = blk_ptr[fi + 1] - 1;
+  while (lo < hi) {
+    const int mid = (lo + hi) >> 1;
+    if (blk_col[mid] < fj) lo = mid + 1; else hi = mid;
+  }
+  return lo;
+}
+
+// a1+a2, camera-major: one CTA per camera -> B_c (21), g_c (6); fixed-order CTA reduction.
+// Camera c also owns slot c of the cost / invalid partials; thread 0 of CTA 0 sums them last.
+constexpr int kCamThreads = 128;
+__global__ void __launch_bounds__(kCamThreads) large_cam_kernel(LargeData d, Params P) {
+  const LargeCtrl* ctrl = d.ctrl;
+  if (ctrl->stop || ctrl->have_lin) return;
+  __shared__ double red[kCamThreads / 32][32];
+  const int c = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const double* pose = d.poses + 12 * (size_t)c;
+  const bool isfree = d.fidx[c] >= 0;
+  double acc[29];
+#pragma unroll
+  for (int k = 0; k < 29; ++k) acc[k] = 0.0;
+  for (int a = d.cam_ptr[c] + tid; a < d.cam_ptr[c + 1]; a += kCamThreads) {
+    const ObsRec rec = d.cm[a];
+    const double* X = d.pts + 3 * (size_t)rec.idx;
+    Proj o;
+    project(P, pose, X[0], X[1], X[2], rec.u, rec.v, o);
+    if (!o.valid) { acc[28] += 1.0; continue; }
+    acc[27] += 0.5 * o.rho;
+    if (isfree) {
+      double jc[12];
+      jac_cam(P, o, jc);
+      int k = 0;
+#pragma unroll
+      for (int r = 0; r < 6; ++r) {
+        const double j0 = o.w * jc[r], j1 = o.w * jc[6 + r];
+#pragma unroll
+        for (int s = r; s < 6; ++s) acc[k++] += j0 * jc[s] + j1 * jc[6 + s];
+        acc[21 + r] += j0 * o.r0 + j1 * o.r1;
+      }
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < 29; ++k) {
+    const double v = warp_sum(acc[k]);
+    if (lane == 0) red[warp][k] = v;
+  }
+  __syncthreads();
+  if (tid < 29) {
+    double v = 0.0;
+    for (int w = 0; w < kCamThreads / 32; ++w) v += red[w][tid];
+    if (tid < 21) d.lin_part[(size_t)c * 21 + tid] = v;
+    else if (tid < 27) d.lin_part[(size_t)d.nc * 21 + (size_t)c * 6 + tid - 21] = v;
+    else d.part[(tid - 27) * d.nc + c] = v;      // per-camera cost / invalid count
+  }
+}
+
+// fixed-order sum of the per-camera cost partials -> lin_part tail
+__global__ void large_cam_finish_kernel(LargeData d) {
+  const LargeCtrl* ctrl = d.ctrl;
+  if (ctrl->stop || ctrl->have_lin) return;
+  if (threadIdx.x < 2) {
+    double v = 0.0;
+    for (int c = 0; c < d.nc; ++c) v += d.part[threadIdx.x * d.nc + c];
+    d.lin_part[(size_t)d.nc * 27 + threadIdx.x] = v;
+  }
+}
+
+// after the {B, g_c, cost} reduction: D_c, cost bookkeeping, S := blockdiag(B') (rank 0), g_red := g_c
+__global__ void large_init_S_kernel(LargeData d) {
+  LargeCtrl* ctrl = d.ctrl;
+  if (ctrl->stop) return;
+  const size_t gid = blockIdx.x * (size_t)blockDim.x + threadIdx.x, gsz = (size_t)gridDim.x * blockDim.x;
+  const double* B = d.lin;
+  for (size_t i = gid; i < (size_t)d.nc * 6; i += gsz) d.Dc[i] = clampd(B[(i / 6) * 21 + packed21((int)(i % 6), (int)(i % 6))]);
+  for (size_t i = gid; i < d.sg_count(); i += gsz) d.Sg[i] = 0.0;
+  // the grid-wide zero fill must finish before the diagonal blocks are written: second kernel below
+}
+
+__global__ void large_init_diag_kernel(LargeData d) {
+  LargeCtrl* ctrl = d.ctrl;
+  if (ctrl->stop) return;
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c == 0) {
+    if (!ctrl->have_lin) {
+      ctrl->cost = d.lin[(size_t)d.nc * 27];
+      ctrl->cur_ninv = d.lin[(size_t)d.nc * 27 + 1];
+      if (ctrl->it == 0) ctrl->initial_cost = ctrl->cost;
+      ctrl->fresh_lin = 1;
+    } else ctrl->fresh_lin = 0;
+    ctrl->have_lin = 1;
+    ctrl->step_bad = 0;
+    ctrl->sums[6] = 0.0;
+  }
+  if (c >= d.nc || d.rank != 0) return;
+  const int f = d.fidx[c];
+  if (f < 0) return;
+  const double imu = 1.0 / ctrl->mu;
+  const double* B = d.lin + (size_t)c * 21;
+  double* S = d.Sg + (size_t)d.blk_ptr[f] * 36;      // the diagonal block is the first of its row
+  for (int r = 0; r < 6; ++r)
+    for (int s = 0; s < 6; ++s) {
+      double v = B[packed21(min(r, s), max(r, s))];
+      if (r == s) v += clampd(v) * imu;
+      S[6 * r + s] = v;
+    }
+  double* gred = d.Sg + (size_t)d.nblk * 36;
+  for (int r = 0; r < 6; ++r) gred[6 * f + r] = d.lin[(size_t)d.nc * 21 + (size_t)c * 6 + r];
+}
+
+__device__ __forceinline__ void atomic_max_pos(double* addr, double v) {   // v >= 0
+  atomicMax(reinterpret_cast<unsigned long long*>(addr), (unsigned long long)__double_as_longlong(v));
+}
+
+// a1-a4, point-major: one thread per landmark of this rank's range.  C_p, g_p -> F (C'^-1 = F F^T),
+// then S(fi,fj) -= Y_a E_b^T, g_red(fi) -= Y_a g_p with fp64 RED atomics on the block-sparse S
+// (contributions of one landmark go to k(k+1)/2 distinct blocks; cameras are not "hot" here).
+__global__ void __launch_bounds__(128) large_schur_kernel(LargeData d, Params P) {
+  LargeCtrl* ctrl = d.ctrl;
+  if (ctrl->stop) return;
+  const int p = d.p_lo + blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= d.p_hi) return;
+  const double imu = 1.0 / ctrl->mu;
+  const int a0 = d.pt_ptr[p], a1 = d.pt_ptr[p + 1];
+  const double X0 = d.pts[3 * (size_t)p], X1 = d.pts[3 * (size_t)p + 1], X2 = d.pts[3 * (size_t)p + 2];
+  double C[6] = {0, 0, 0, 0, 0, 0}, g[3] = {0, 0, 0};
+  for (int a = a0; a < a1; ++a) {
+    const ObsRec rec = d.pm[a];
+    const double* pose = d.poses + 12 * (size_t)rec.idx;
+    Proj o;
+    project(P, pose, X0, X1, X2, rec.u, rec.v, o);
+    double jp[6];
+    jac_point(P, pose, o, jp);
+    const double w = o.w;
+    C[0] += w * (jp[0] * jp[0] + jp[3] * jp[3]); C[1] += w * (jp[0] * jp[1] + jp[3] * jp[4]);
+    C[2] += w * (jp[0] * jp[2] + jp[3] * jp[5]); C[3] += w * (jp[1] * jp[1] + jp[4] * jp[4]);
+    C[4] += w * (jp[1] * jp[2] + jp[4] * jp[5]); C[5] += w * (jp[2] * jp[2] + jp[5] * jp[5]);
+#pragma unroll
+    for (int j = 0; j < 3; ++j) g[j] += w * (jp[j] * o.r0 + jp[3 + j] * o.r1);
+  }
+  const double D0 = clampd(C[0]), D1 = clampd(C[3]), D2 = clampd(C[5]);
+  double F[6];
+  {
+    const double Cd[6] = {C[0] + D0 * imu, C[1], C[2], C[3] + D1 * imu, C[4], C[5] + D2 * imu};
+    if (!sym3_inv_factor(Cd, F)) {
+#pragma unroll
+      for (int k = 0; k < 6; ++k) F[k] = 0.0;
+      ctrl->step_bad = 1;
+    }
+  }
+  double* sc = d.pt_scratch + (size_t)p * 12;
+#pragma unroll
+  for (int k = 0; k < 6; ++k) sc[k] = F[k];
+  sc[6] = g[0]; sc[7] = g[1]; sc[8] = g[2]; sc[9] = D0; sc[10] = D1; sc[11] = D2;
+  atomic_max_pos(&ctrl->sums[6], fmax(fabs(g[0]), fmax(fabs(g[1]), fabs(g[2]))));
+  // C'^-1 = F F^T (symmetric, upper)
+  const double I0 = F[0] * F[0] + F[1] * F[1] + F[2] * F[2], I1 = F[1] * F[3] + F[2] * F[4], I2 = F[2] * F[5];
+  const double I3 = F[3] * F[3] + F[4] * F[4], I4 = F[4] * F[5], I5 = F[5] * F[5];
+  double* gred = d.Sg + (size_t)d.nblk * 36;
+  for (int a = a0; a < a1; ++a) {
+    const ObsRec ra = d.pm[a];
+    const int fa = d.fidx[ra.idx];
+    if (fa < 0) continue;
+    const double* pose = d.poses + 12 * (size_t)ra.idx;
+    Proj o;
+    project(P, pose, X0, X1, X2, ra.u, ra.v, o);
+    if (!o.valid) continue;
+    double jp[6], jc[12], E[18], Y[18];
+    jac_point(P, pose, o, jp);
+    jac_cam(P, o, jc);
+    make_E(o.w, jc, jp, E);
+#pragma unroll
+    for (int r = 0; r < 6; ++r) {
+      const double e0 = E[3 * r], e1 = E[3 * r + 1], e2 = E[3 * r + 2];
+      Y[3 * r] = e0 * I0 + e1 * I1 + e2 * I2;
+      Y[3 * r + 1] = e0 * I1 + e1 * I3 + e2 * I4;
+      Y[3 * r + 2] = e0 * I2 + e1 * I4 + e2 * I5;
+      atomicAdd(&gred[6 * fa + r], -(Y[3 * r] * g[0] + Y[3 * r + 1] * g[1] + Y[3 * r + 2] * g[2]));
+    }
+    for (int b = a; b < a1; ++b) {
+      const ObsRec rb = d.pm[b];
+      const int fb = d.fidx[rb.idx];
+      if (fb < 0) continue;
+      double Eb[18];
+      if (b == a) {
+#pragma unroll
+        for (int k = 0; k < 18; ++k) Eb[k] = E[k];
+      } else {
+        const double* pb = d.poses + 12 * (size_t)rb.idx;
+        Proj ob;
+        project(P, pb, X0, X1, X2, rb.u, rb.v, ob);
+        if (!ob.valid) continue;
+        double jpb[6], jcb[12];
+        jac_point(P, pb, ob, jpb);
+        jac_cam(P, ob, jcb);
+        make_E(ob.w, jcb, jpb, Eb);
+      }
+      double* S = d.Sg + (size_t)find_blk(d.blk_ptr, d.blk_col, fa, fb) * 36;
+#pragma unroll
+      for (int r = 0; r < 6; ++r)
+#pragma unroll
+        for (int s = 0; s < 6; ++s)
+          atomicAdd(&S[6 * r + s], -(Y[3 * r] * Eb[3 * s] + Y[3 * r + 1] * Eb[3 * s + 1] + Y[3 * r + 2] * Eb[3 * s + 2]));
+    }
+  }
+}
+
+}  // namespace
+}  // namespace b2
+
+// =============================================================================================
+// a6: PCG on the block-sparse S with a block-Jacobi (6x6) preconditioner, ONE cooperative launch.
+// Each CTA keeps the whole search direction p in shared memory, so an iteration needs two grid
+// syncs: [p update (redundant per CTA) + q = S p on own rows + p.q]  |  [x, r, z on own rows + r.z, r.r].
+// All dot products are summed in a fixed order (per-CTA partials, then one ordered pass) so the
+// iteration is deterministic for a given grid size.
+namespace b2 {
+namespace {
+
+constexpr int kPcgThreads = 256;
+
+__device__ __forceinline__ bool inv6_spd(const double* M, double* Inv) {   // M row-major, upper used
+  double L[21];   // packed lower: L[i*(i+1)/2 + j]
+  for (int j = 0; j < 6; ++j) {
+    double dj = M[6 * j + j];
+    for (int k = 0; k < j; ++k) dj -= L[j * (j + 1) / 2 + k] * L[j * (j + 1) / 2 + k];
+    if (!(dj > 0.0) || !isfinite(dj)) return false;
+    dj = sqrt(dj);
+    L[j * (j + 1) / 2 + j] = dj;
+    for (int i = j + 1; i < 6; ++i) {
+      double v = M[6 * j + i];
+      for (int k = 0; k < j; ++k) v -= L[i * (i + 1) / 2 + k] * L[j * (j + 1) / 2 + k];
+      L[i * (i + 1) / 2 + j] = v / dj;
+    }
+  }
+  for (int c = 0; c < 6; ++c) {
+    double e[6];
+    for (int i = 0; i < 6; ++i) {
+      double v = i == c ? 1.0 : 0.0;
+      for (int k = 0; k < i; ++k) v -= L[i * (i + 1) / 2 + k] * e[k];
+      e[i] = v / L[i * (i + 1) / 2 + i];
+    }
+    for (int i = 5; i >= 0; --i) {
+      double v = e[i];
+      for (int k = i + 1; k < 6; ++k) v -= L[k * (k + 1) / 2 + i] * e[k];
+      e[i] = v / L[i * (i + 1) / 2 + i];
+    }
+    for (int i = 0; i < 6; ++i) Inv[6 * i + c] = e[i];
+  }
+  return true;
+}
+
+// ordered sum of `count` partials (stride `stride`) by one warp; result broadcast through smem
+__device__ __forceinline__ double ordered_sum(const double* part, int count, int stride, double* slot) {
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    double v = 0.0;
+    for (int i = threadIdx.x; i < count; i += 32) v += part[(size_t)i * stride];
+    v = warp_sum(v);
+    if (threadIdx.x == 0) *slot = v;
+  }
+  __syncthreads();
+  return *slot;
+}
+
+__global__ void __launch_bounds__(kPcgThreads) large_pcg_kernel(LargeData d, int max_it, double tol) {
+  cg::grid_group grid = cg::this_grid();
+  LargeCtrl* ctrl = d.ctrl;
+  if (ctrl->stop || ctrl->step_bad) return;       // uniform across the grid
+  extern __shared__ double psh[];                  // p (n doubles)
+  __shared__ double red[kPcgThreads / 32][4];
+  __shared__ double bcast[4];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int nwarp_cta = kPcgThreads / 32;
+  const int gwarp = blockIdx.x * nwarp_cta + warp, nwarps = gridDim.x * nwarp_cta;
+  const int n = d.n, nfree = d.nfree;
+  const double* S = d.Sg;
+  const double* gred = d.Sg + (size_t)d.nblk * 36;
+  double* part = d.part;                           // [gridDim.x * 4]
+  const int bl = lane / 6, rr = lane % 6;          // lanes 0..29: (block slot, row); 30, 31 idle
+
+  // ---- setup: block-Jacobi inverse, r = b = -g_red, x = 0, z = M^-1 r, partial r.z and b.b
+  double s_rz = 0.0, s_bb = 0.0;
+  for (int f = blockIdx.x * kPcgThreads + tid; f < nfree; f += gridDim.x * kPcgThreads) {
+    double Inv[36];
+    if (!inv6_spd(S + (size_t)d.blk_ptr[f] * 36, Inv)) {
+      ctrl->step_bad = 1;
+      for (int k = 0; k < 36; ++k) Inv[k] = 0.0;
+    }
+    double rv[6];
+    for (int k = 0; k < 36; ++k) d.Minv[(size_t)f * 36 + k] = Inv[k];
+    for (int r_ = 0; r_ < 6; ++r_) { rv[r_] = -gred[6 * f + r_]; d.r[6 * f + r_] = rv[r_]; d.dc[6 * f + r_] = 0.0; }
+    for (int r_ = 0; r_ < 6; ++r_) {
+      double v = 0.0;
+      for (int s_ = 0; s_ < 6; ++s_) v += Inv[6 * r_ + s_] * rv[s_];
+      d.z[6 * f + r_] = v;
+      s_rz += rv[r_] * v;
+      s_bb += rv[r_] * rv[r_];
+    }
+  }
+  s_rz = warp_sum(s_rz); s_bb = warp_sum(s_bb);
+  if (lane == 0) { red[warp][0] = s_rz; red[warp][1] = s_bb; }
+  __syncthreads();
+  if (tid == 0) {
+    double a = 0, b = 0;
+    for (int w = 0; w < nwarp_cta; ++w) { a += red[w][0]; b += red[w][1]; }
+    part[blockIdx.x * 4] = a; part[blockIdx.x * 4 + 1] = b;
+  }
+  grid.sync();
+  if (ctrl->step_bad) return;                      // uniform: written before the sync
+  double rz = ordered_sum(part, gridDim.x, 4, &bcast[0]);
+  const double bb = ordered_sum(part + 1, gridDim.x, 4, &bcast[1]);
+  double rnorm2 = bb, beta = 0.0;
+  int it = 0;
+  grid.sync();                                     // partials are reused below
+  for (int i = tid; i < n; i += kPcgThreads) psh[i] = 0.0;
+  __syncthreads();
+  if (bb > 0.0) {
+    for (; it < max_it; ++it) {
+      if (rnorm2 <= tol * tol * bb) break;
+      // ---- phase A: p = z + beta p (whole vector, every CTA), q = S p on own rows, p.q
+      for (int i = tid; i < n; i += kPcgThreads) psh[i] = d.z[i] + beta * psh[i];
+      __syncthreads();
+      double s_pq = 0.0;
+      for (int f = gwarp; f < nfree; f += nwarps) {
+        double v = 0.0;
+        if (lane < 30) {
+          for (int b = d.frow_ptr[f] + bl; b < d.frow_ptr[f + 1]; b += 5) {
+            const int src = d.fsrc[b];
+            const double* M = S + (size_t)(src & 0x7fffffff) * 36;
+            const double* x = psh + 6 * d.fcol[b];
+            if (src < 0) {
+#pragma unroll
+              for (int s_ = 0; s_ < 6; ++s_) v += M[6 * s_ + rr] * x[s_];
+            } else {
+#pragma unroll
+              for (int s_ = 0; s_ < 6; ++s_) v += M[6 * rr + s_] * x[s_];
+            }
+          }
+        }
+        v += __shfl_down_sync(0xffffffffu, v, 6) + __shfl_down_sync(0xffffffffu, v, 12) +
+             __shfl_down_sync(0xffffffffu, v, 18) + __shfl_down_sync(0xffffffffu, v, 24);
+        if (lane < 6) { d.q[6 * f + lane] = v; s_pq += v * psh[6 * f + lane]; }
+      }
+      s_pq = warp_sum(s_pq);
+      if (lane == 0) red[warp][0] = s_pq;
+      __syncthreads();
+      if (tid == 0) { double a = 0; for (int w = 0; w < nwarp_cta; ++w) a += red[w][0]; part[blockIdx.x * 4] = a; }
+      grid.sync();
+      const double pq = ordered_sum(part, gridDim.x, 4, &bcast[0]);
+      if (!(pq > 0.0) || !isfinite(pq)) { if (blockIdx.x == 0 && tid == 0) ctrl->step_bad = 1; break; }
+      const double alpha = rz / pq;
+      // ---- phase B: x += alpha p, r -= alpha q, z = M^-1 r on own rows; r.z, r.r
+      double s_a = 0.0, s_b = 0.0;
+      for (int f = gwarp; f < nfree; f += nwarps) {
+        double rn = 0.0;
+        if (lane < 6) {
+          d.dc[6 * f + lane] += alpha * psh[6 * f + lane];
+          rn = d.r[6 * f + lane] - alpha * d.q[6 * f + lane];
+          d.r[6 * f + lane] = rn;
+        }
+        double zv = 0.0;
+#pragma unroll
+        for (int s_ = 0; s_ < 6; ++s_) {
+          const double rs = __shfl_sync(0xffffffffu, rn, s_);
+          if (lane < 6) zv += d.Minv[(size_t)f * 36 + 6 * lane + s_] * rs;
+        }
+        if (lane < 6) { d.z[6 * f + lane] = zv; s_a += rn * zv; s_b += rn * rn; }
+      }
+      s_a = warp_sum(s_a); s_b = warp_sum(s_b);
+      if (lane == 0) { red[warp][2] = s_a; red[warp][3] = s_b; }
+      __syncthreads();
+      if (tid == 0) {
+        double a = 0, b = 0;
+        for (int w = 0; w < nwarp_cta; ++w) { a += red[w][2]; b += red[w][3]; }
+        part[blockIdx.x * 4 + 2] = a; part[blockIdx.x * 4 + 3] = b;
+      }
+      grid.sync();
+      const double rz2 = ordered_sum(part + 2, gridDim.x, 4, &bcast[2]);
+      rnorm2 = ordered_sum(part + 3, gridDim.x, 4, &bcast[3]);
+      beta = rz2 / rz;
+      rz = rz2;
+    }
+  }
+  if (blockIdx.x == 0 && tid == 0) { ctrl->pcg_last = it; ctrl->pcg_iters += it; }
+}
+
+}  // namespace
+}  // namespace b2
+
+namespace b2 {
+namespace {
+
+// trial cameras + camera part of the model decrease (one CTA)
+__global__ void large_cam_update_kernel(LargeData d) {
+  LargeCtrl* ctrl = d.ctrl;
+  if (ctrl->stop) return;
+  __shared__ double red[8][4];
+  __shared__ int bad;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid == 0) bad = 0;
+  __syncthreads();
+  double s0 = 0, s1 = 0, s2 = 0;
+  if (!ctrl->step_bad) {
+    for (int c = tid; c < d.nc; c += blockDim.x) {
+      const int f = d.fidx[c];
+      double* out = d.poses_tri + 12 * (size_t)c;
+      const double* in = d.poses + 12 * (size_t)c;
+      if (f < 0) { for (int k = 0; k < 12; ++k) out[k] = in[k]; continue; }
+      double dl[6];
+      for (int r = 0; r < 6; ++r) {
+        dl[r] = d.dc[6 * f + r];
+        if (!isfinite(dl[r])) bad = 1;
+        s0 += dl[r] * dl[r] * d.Dc[6 * (size_t)c + r];
+        s1 += dl[r] * d.lin[(size_t)d.nc * 21 + 6 * (size_t)c + r];
+        s2 += dl[r] * dl[r];
+      }
+      retract_pose(in, dl, out);
+    }
+  }
+  s0 = warp_sum(s0); s1 = warp_sum(s1); s2 = warp_sum(s2);
+  if (lane == 0) { red[warp][0] = s0; red[warp][1] = s1; red[warp][2] = s2; }
+  __syncthreads();
+  if (tid == 0) {
+    double a = 0, b = 0, c = 0;
+    for (int w = 0; w < (int)blockDim.x / 32; ++w) { a += red[w][0]; b += red[w][1]; c += red[w][2]; }
+    ctrl->cam_sums[0] = a; ctrl->cam_sums[1] = b; ctrl->cam_sums[2] = c;
+    if (bad) ctrl->step_bad = 1;
+  }
+}
+
+// a7: back-substitution, trial landmark, trial cost; per-CTA partials (fixed-order sums later)
+constexpr int kBsThreads = 128;
+__global__ void __launch_bounds__(kBsThreads) large_backsub_kernel(LargeData d, Params P) {
+  LargeCtrl* ctrl = d.ctrl;
+  if (ctrl->stop) return;
+  __shared__ double red[kBsThreads / 32][6];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int p = d.p_lo + blockIdx.x * kBsThreads + tid;
+  double s[6] = {0, 0, 0, 0, 0, 0};   // trial cost, dDd, gd, dn2, xn2, invalid
+  if (!ctrl->step_bad && p < d.p_hi) {
+    const int a0 = d.pt_ptr[p], a1 = d.pt_ptr[p + 1];
+    const double X0 = d.pts[3 * (size_t)p], X1 = d.pts[3 * (size_t)p + 1], X2 = d.pts[3 * (size_t)p + 2];
+    double v[3] = {0, 0, 0};
+    for (int a = a0; a < a1; ++a) {
+      const ObsRec rec = d.pm[a];
+      const int f = d.fidx[rec.idx];
+      if (f < 0) continue;
+      const double* pose = d.poses + 12 * (size_t)rec.idx;
+      Proj o;
+      project(P, pose, X0, X1, X2, rec.u, rec.v, o);
+      double jp[6], jc[12];
+      jac_point(P, pose, o, jp);
+      jac_cam(P, o, jc);
+      const double* dc = d.dc + 6 * f;
+      double t0 = 0.0, t1 = 0.0;
+#pragma unroll
+      for (int r = 0; r < 6; ++r) { t0 += jc[r] * dc[r]; t1 += jc[6 + r] * dc[r]; }
+#pragma unroll
+      for (int j = 0; j < 3; ++j) v[j] += o.w * (jp[j] * t0 + jp[3 + j] * t1);
+    }
+    const double* sc = d.pt_scratch + (size_t)p * 12;
+    const double F0 = sc[0], F1 = sc[1], F2 = sc[2], F3 = sc[3], F4 = sc[4], F5 = sc[5];
+    const double g0 = sc[6], g1 = sc[7], g2 = sc[8];
+    const double t0 = g0 + v[0], t1 = g1 + v[1], t2 = g2 + v[2];
+    const double u0 = F0 * t0, u1 = F1 * t0 + F3 * t1, u2 = F2 * t0 + F4 * t1 + F5 * t2;
+    const double d0 = -(F0 * u0 + F1 * u1 + F2 * u2), d1 = -(F3 * u1 + F4 * u2), d2 = -(F5 * u2);
+    const double Xn0 = X0 + d0, Xn1 = X1 + d1, Xn2 = X2 + d2;
+    d.pts_tri[3 * (size_t)p] = Xn0; d.pts_tri[3 * (size_t)p + 1] = Xn1; d.pts_tri[3 * (size_t)p + 2] = Xn2;
+    s[1] = d0 * d0 * sc[9] + d1 * d1 * sc[10] + d2 * d2 * sc[11];
+    s[2] = d0 * g0 + d1 * g1 + d2 * g2;
+    s[3] = d0 * d0 + d1 * d1 + d2 * d2;
+    s[4] = X0 * X0 + X1 * X1 + X2 * X2;
+    for (int a = a0; a < a1; ++a) {
+      const ObsRec rec = d.pm[a];
+      Proj o;
+      project(P, d.poses_tri + 12 * (size_t)rec.idx, Xn0, Xn1, Xn2, rec.u, rec.v, o);
+      if (o.valid) s[0] += 0.5 * o.rho; else s[5] += 1.0;
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < 6; ++k) {
+    const double v = warp_sum(s[k]);
+    if (lane == 0) red[warp][k] = v;
+  }
+  __syncthreads();
+  if (tid < 6) {
+    double v = 0.0;
+    for (int w = 0; w < kBsThreads / 32; ++w) v += red[w][tid];
+    d.part[(size_t)blockIdx.x * 8 + tid] = v;
+  }
+}
+
+// ordered sum of the back-substitution partials -> sums_part[0..5] (+ local gmax in [6])
+__global__ void large_reduce_kernel(LargeData d, int nparts) {
+  LargeCtrl* ctrl = d.ctrl;
+  if (ctrl->stop) return;
+  const int k = threadIdx.x / 32, lane = threadIdx.x & 31;   // 6 warps, one per sum
+  if (k < 6) {
+    double v = 0.0;
+    for (int i = lane; i < nparts; i += 32) v += d.part[(size_t)i * 8 + k];
+    v = warp_sum(v);
+    if (lane == 0) d.sums_part[k] = v;
+  }
+  if (threadIdx.x == 0) { d.sums_part[6] = ctrl->sums[6]; d.sums_part[7] = ctrl->step_bad ? 1.0 : 0.0; }
+}
+
+// LM control (Spec a0), one thread; identical on every rank (inputs are allreduced)
+__global__ void large_control_kernel(LargeData d, Params P, const double* sums) {
+  LargeCtrl* c = d.ctrl;
+  if (c->stop || threadIdx.x != 0) return;
+  const bool step_ok = sums[7] == 0.0 && !c->step_bad;
+  const double tc = sums[0];
+  const double dDd = sums[1] + c->cam_sums[0], gd = sums[2] + c->cam_sums[1], dn2 = sums[3] + c->cam_sums[2];
+  const double xn2 = sums[4];
+  double gm = sums[6];
+  if (P.gtol > 0.0)
+    for (int i = 0; i < d.nc * 6; ++i)
+      if (d.fidx[i / 6] >= 0) gm = fmax(gm, fabs(d.lin[(size_t)d.nc * 21 + i]));
+  const double mu = c->mu;
+  const double model = 0.5 * (dDd / mu - gd);
+  int accept = 0, stop = 0;
+  double rho = 0.0;
+  if (step_ok && model > 0.0) {
+    rho = (c->cost - tc) / model;
+    accept = (isfinite(tc) && rho > kMinRatio) ? 1 : 0;
+  }
+  if (P.gtol > 0.0 && c->fresh_lin && gm <= P.gtol) { c->status = B2BA_CONVERGED; c->stop = 1; c->accept = 0; return; }
+  if (accept) {
+    if (P.ftol > 0.0 && fabs(c->cost - tc) <= P.ftol * c->cost) stop = B2BA_CONVERGED;
+    if (P.ptol > 0.0 && sqrt(dn2) <= P.ptol * (sqrt(xn2) + P.ptol)) stop = B2BA_CONVERGED;
+    const double t = 2.0 * rho - 1.0;
+    c->mu = fmin(kMuMax, mu / fmax(1.0 / 3.0, 1.0 - t * t * t));
+    c->nu = 2.0;
+    c->cost = tc;
+    c->cur_ninv = sums[5];
+    c->have_lin = 0;
+    c->n_acc++;
+  } else {
+    c->mu = mu / c->nu;
+    c->nu *= 2.0;
+    c->n_rej++;
+  }
+  c->accept = accept;
+  if (d.hist_cost != nullptr && c->it < 64) {
+    d.hist_cost[c->it] = c->cost; d.hist_mu[c->it] = mu; d.hist_accept[c->it] = accept;
+  }
+  c->it++;
+  if (!stop && !(c->mu > kMuMin)) stop = B2BA_NUMERICAL_FAILURE;
+  if (!stop && c->it >= P.max_iters) { stop = B2BA_MAX_ITERS; }
+  if (stop) { c->status = stop; c->stop = 1; }
+}
+
+// accepted step: trial state becomes the current state (every rank keeps ALL landmarks current
+// only inside its own range; the final gather happens on the host side of b2ba_get)
+__global__ void large_commit_kernel(LargeData d) {
+  const LargeCtrl* c = d.ctrl;
+  if (!c->accept) return;
+  const size_t gid = blockIdx.x * (size_t)blockDim.x + threadIdx.x, gsz = (size_t)gridDim.x * blockDim.x;
+  for (size_t i = gid; i < (size_t)d.nc * 12; i += gsz) d.poses[i] = d.poses_tri[i];
+  for (size_t i = (size_t)d.p_lo * 3 + gid; i < (size_t)d.p_hi * 3; i += gsz) d.pts[i] = d.pts_tri[i];
+}
+
+__global__ void large_clear_accept_kernel(LargeData d) { d.ctrl->accept = 0; }
+
+__global__ void large_init_ctrl_kernel(LargeData d, Params P) {
+  LargeCtrl* c = d.ctrl;
+  c->mu = P.init_mu; c->nu = 2.0; c->cost = 0.0; c->initial_cost = 0.0;
+  for (int k = 0; k < 8; ++k) c->sums[k] = 0.0;
+  for (int k = 0; k < 4; ++k) c->cam_sums[k] = 0.0;
+  c->cur_ninv = 0.0;
+  c->it = 0; c->n_acc = 0; c->n_rej = 0; c->status = B2BA_MAX_ITERS; c->stop = 0; c->step_bad = 0;
+  c->have_lin = 0; c->accept = 0; c->pcg_iters = 0; c->pcg_last = 0; c->fresh_lin = 0; c->pad = 0;
+}
+
+__global__ void large_finish_kernel(LargeData d) {
+  const LargeCtrl* c = d.ctrl;
+  b2ba_summary s;
+  s.status = c->status; s.iterations = c->it; s.accepted = c->n_acc; s.rejected = c->n_rej;
+  s.n_invalid = (int)c->cur_ninv; s.pcg_iters = c->pcg_iters;
+  s.initial_cost = c->initial_cost; s.final_cost = c->cost; s.final_mu = c->mu;
+  *d.summary = s;
+}
+
+}  // namespace
+
+int large_pcg_grid(int n, int* blocks, size_t* smem) {
+  *smem = (size_t)n * sizeof(double);
+  cudaError_t e = cudaFuncSetAttribute(large_pcg_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)*smem);
+  if (e != cudaSuccess) return (int)e;
+  int per_sm = 0, dev = 0, sms = 0;
+  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, large_pcg_kernel, kPcgThreads, *smem);
+  if (e != cudaSuccess) return (int)e;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  if (per_sm < 1) return (int)cudaErrorInvalidConfiguration;
+  *blocks = sms * (per_sm > 2 ? 2 : per_sm);
+  return 0;
+}
+
+int large_init_ctrl(const LargeData& d, const Params& P, cudaStream_t s) {
+  large_init_ctrl_kernel<<<1, 1, 0, s>>>(d, P);
+  return (int)cudaGetLastError();
+}
+
+int large_iteration(const LargeData& d, const Params& P, int pcg_max_iters, double pcg_tol,
+                    AllReduceFn ar, void* ar_user, cudaStream_t s) {
+  int rc;
+  large_clear_accept_kernel<<<1, 1, 0, s>>>(d);
+  if (d.nc > 0) large_cam_kernel<<<d.nc, kCamThreads, 0, s>>>(d, P);
+  large_cam_finish_kernel<<<1, 32, 0, s>>>(d);
+  if (ar && (rc = ar(ar_user, d.lin_part, d.lin, d.lin_count(), s)) != 0) return rc;
+  large_init_S_kernel<<<296, 256, 0, s>>>(d);
+  large_init_diag_kernel<<<(d.nc + 127) / 128 + 1, 128, 0, s>>>(d);
+  const int npl = d.p_hi - d.p_lo;
+  if (npl > 0) large_schur_kernel<<<(npl + 127) / 128, 128, 0, s>>>(d, P);
+  if (ar && (rc = ar(ar_user, d.Sg, d.Sg, d.sg_count(), s)) != 0) return rc;
+  {
+    int blocks = 0;
+    size_t smem = 0;
+    if ((rc = large_pcg_grid(d.n, &blocks, &smem)) != 0) return rc;
+    LargeData dd = d;
+    int mi = pcg_max_iters;
+    double tol = pcg_tol;
+    void* args[] = {&dd, &mi, &tol};
+    cudaError_t e = cudaLaunchCooperativeKernel((void*)large_pcg_kernel, dim3(blocks), dim3(kPcgThreads), args, smem, s);
+    if (e != cudaSuccess) return (int)e;
+  }
+  large_cam_update_kernel<<<1, 256, 0, s>>>(d);
+  const int nparts = (npl + kBsThreads - 1) / kBsThreads;
+  if (nparts > 0) large_backsub_kernel<<<nparts, kBsThreads, 0, s>>>(d, P);
+  large_reduce_kernel<<<1, 192, 0, s>>>(d, nparts);
+  const double* sums = d.sums_part;
+  if (ar) {
+    if ((rc = ar(ar_user, d.sums_part, d.sums_part + 8, 8, s)) != 0) return rc;
+    sums = d.sums_part + 8;
+  }
+  large_control_kernel<<<1, 32, 0, s>>>(d, P, sums);
+  large_commit_kernel<<<148, 256, 0, s>>>(d);
+  return (int)cudaGetLastError();
+}
+
+int large_finish(const LargeData& d, cudaStream_t s) {
+  large_finish_kernel<<<1, 1, 0, s>>>(d);
+  return (int)cudaGetLastError();
+}
+
+}  // namespace b2

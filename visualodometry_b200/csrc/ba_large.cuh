@@ -1,12 +1,80 @@
-// Large path (C5, BAL-style): multi-kernel LM with a block-sparse reduced camera system and PCG.
+// Large path (C5, BAL-style; any camera count): multi-kernel Levenberg-Marquardt with a
+// block-sparse reduced camera system and block-Jacobi PCG, all control on the device (the host
+// only enqueues a fixed kernel sequence per LM iteration; no host synchronisation in the loop).
+//
+// Multi-GPU (SURVEY §8 row e): landmarks are sharded by contiguous point ranges balanced by
+// observation count; poses are replicated; per LM iteration three ncclAllReduce(sum, f64):
+//   {B_c, g_c, cost}  ->  {S blocks, g_red}  ->  {trial cost, model-decrease terms}
+// and the PCG + LM control run replicated (bit-identical inputs on every rank).
 #pragma once
 #include "ba_math.cuh"
+#include "devbuf.cuh"
 #include "../../include/b2ba.h"
 
 namespace b2 {
 
-struct LargeState {
-  bool ready = false;
+struct LargeCtrl {          // device-resident LM state
+  double mu, nu, cost, initial_cost;
+  double sums[8];           // reduced: trial cost, dDd, gd, dn2, xn2, n_invalid(trial), gmax, -
+  double cam_sums[4];       // camera part of dDd, gd, dn2
+  double cur_ninv;
+  int it, n_acc, n_rej, status, stop, step_bad, have_lin, accept, pcg_iters, pcg_last, fresh_lin, pad;
 };
+
+struct LargeData {
+  int nc, np, nfree, n;
+  int p_lo, p_hi;                  // this rank's landmark range (whole problem on one GPU)
+  int rank, nranks;
+  const ObsRec* pm;                // point-major stream of the WHOLE problem (idx = camera)
+  const int* pt_ptr;               // np+1
+  const ObsRec* cm;                // camera-major stream of the LOCAL observations (idx = point)
+  const int* cam_ptr;              // nc+1
+  const int* fidx;                 // nc
+  const int* blk_ptr;              // nfree+1   upper block structure of S (fi <= fj)
+  const int* blk_col;
+  int nblk;
+  const int* frow_ptr;             // nfree+1   full symmetric structure for the mat-vec
+  const int* fcol;
+  const int* fsrc;                 // upper slot | (transposed << 31)
+  double* poses;                   // nc x 12 current
+  double* poses_tri;               // nc x 12 trial
+  double* pts;                     // np x 3 current
+  double* pts_tri;                 // np x 3 trial
+  double* lin_part;                // local partial [nc*21 B | nc*6 g_c | cost | n_invalid]
+  double* lin;                     // reduced (same layout)
+  double* Dc;                      // nc x 6
+  double* pt_scratch;              // np x 12 (F, g_p, D_p)
+  double* Sg;                      // [nblk*36 S blocks | n g_red]   (one buffer: one allreduce)
+  double* dc;                      // n   delta_c (PCG x)
+  double* r; double* z; double* q; // n each
+  double* Minv;                    // nfree x 36
+  double* part;                    // partial-sum scratch (grid partials)
+  double* sums_part;               // 8 local partial sums (before the allreduce)
+  LargeCtrl* ctrl;
+  b2ba_summary* summary;
+  double* hist_cost; double* hist_mu; int* hist_accept;
+  __host__ __device__ size_t lin_count() const { return (size_t)nc * 27 + 2; }
+  __host__ __device__ size_t sg_count() const { return (size_t)nblk * 36 + n; }
+};
+
+typedef int (*AllReduceFn)(void* user, const double* send, double* recv, size_t count, cudaStream_t s);
+
+// S block structure from the point-major stream (a8, device). Fills the DevBufs; returns cudaError.
+struct LargeIndex {
+  DevBuf<int> fidx, blk_ptr, blk_col, frow_ptr, fcol, fsrc;
+  int nblk = 0, nfull = 0, nfree = 0;
+};
+int large_build_structure(int nc, int np, long long no, const ObsRec* pm, const int* pt_ptr,
+                          const unsigned char* h_fixed, LargeIndex& ix, cudaStream_t s);
+// camera-major stream of the observations of landmarks [p_lo, p_hi)
+int large_build_cm_slice(int nc, int p_lo, int p_hi, const ObsRec* pm, const int* pt_ptr, ObsRec* cm,
+                         int* cam_ptr, cudaStream_t s);
+
+int large_init_ctrl(const LargeData& d, const Params& P, cudaStream_t s);
+// enqueue one LM iteration (all kernels + the three allreduces when ar != null)
+int large_iteration(const LargeData& d, const Params& P, int pcg_max_iters, double pcg_tol,
+                    AllReduceFn ar, void* ar_user, cudaStream_t s);
+int large_finish(const LargeData& d, cudaStream_t s);
+int large_pcg_grid(int n, int* blocks, size_t* smem);   // cooperative launch geometry
 
 }  // namespace b2

@@ -203,41 +203,54 @@ def make_batch(n_windows=4096, seed0=0, distinct=None, **kw) -> BABatch:
 
 
 def make_large(seed=0, n_cams=1000, n_pts=200_000, k=5, mode="local", cam=KITTI, noise_px=0.5,
-               path_len=1000.0):
-    """C5: BAL-style problem. Cameras on a straight path along +x looking sideways (+z),
-    exactly k observations per point. mode 'local': the k cameras nearest the point along the
-    path (+- jitter) -> block-banded S; 'random': any k cameras (frustum ignored) -> dense S."""
+               path_len=None):
+    """C5: BAL-style problem, exactly k observations per point, observation order shuffled.
+    mode 'local' : cameras on a straight path along +x (1 m spacing unless path_len is given) looking
+                   sideways (+z); each point is seen by the k cameras nearest to it along the path
+                   (+- jitter) -> block-banded reduced camera system S.
+    mode 'random': cameras on a ring of radius 40 m looking at the centre, points in a 16 m cube at
+                   the centre, each point seen by ANY k cameras -> dense S (BAL-style stress)."""
     rng = np.random.default_rng(seed)
     fx, fy, cx, cy, W, H = cam
     intr = np.array([fx, fy, cx, cy])
-    step = path_len / n_cams
     gt_poses = np.empty((n_cams, 12))
-    cam_x = np.arange(n_cams) * step
-    for c in range(n_cams):
-        yaw = 0.0 if c == 0 else rng.normal(0, 0.02)
-        gt_poses[c] = _pose_cw(rot_y(yaw), np.array([cam_x[c], 0.0, 0.0]))
-    X = np.stack([rng.uniform(0, path_len, n_pts), rng.uniform(-3, 2, n_pts),
-                  rng.uniform(5, 60, n_pts)], axis=1)
     if mode == "local":
+        path_len = float(n_cams) if path_len is None else float(path_len)
+        step = path_len / n_cams
+        for c in range(n_cams):
+            yaw = 0.0 if c == 0 else rng.normal(0, 0.02)
+            gt_poses[c] = _pose_cw(rot_y(yaw), np.array([c * step, 0.0, 0.0]))
+        X = np.stack([rng.uniform(0, path_len, n_pts), rng.uniform(-3, 2, n_pts),
+                      rng.uniform(5, 60, n_pts)], axis=1)
         centre = np.rint(X[:, 0] / step).astype(np.int64) + rng.integers(-2, 3, n_pts)
         centre = np.clip(centre, k // 2, n_cams - 1 - (k - k // 2 - 1))
         cams = centre[:, None] + (np.arange(k) - k // 2)[None, :]
+        depth_ref = X[:, 2]
     elif mode == "random":
+        radius = 40.0
+        for c in range(n_cams):
+            th = 2 * np.pi * c / n_cams
+            C = np.array([radius * np.sin(th), 0.0, -radius * np.cos(th)])
+            # camera z axis points at the origin: R_wc = rot_y(-th) has z_cam = (-sin th, 0, cos th)
+            gt_poses[c] = _pose_cw(rot_y(-th) @ rot_y(0.0 if c == 0 else rng.normal(0, 0.02)), C)
+        X = rng.uniform(-8, 8, (n_pts, 3)) * np.array([1.0, 0.25, 1.0])
         # k distinct cameras per point: random keys, take the k smallest
         cams = np.argsort(rng.random((n_pts, n_cams), dtype=np.float32), axis=1)[:, :k]
         cams.sort(axis=1)
+        depth_ref = np.full(n_pts, radius)
     else:
         raise ValueError(mode)
     pt_i = np.repeat(np.arange(n_pts), k)
     cam_i = cams.reshape(-1)
     R = gt_poses[cam_i, :9].reshape(-1, 3, 3)
     xc = np.einsum("nij,nj->ni", R, X[pt_i]) + gt_poses[cam_i, 9:]
+    assert (xc[:, 2] > 1.0).all()
     uv = np.stack([fx * xc[:, 0] / xc[:, 2] + cx, fy * xc[:, 1] / xc[:, 2] + cy], axis=1)
     uv += rng.normal(0, noise_px, uv.shape)
     # shuffle observation order: the engine's index builder must restore point-major order
     perm = rng.permutation(cam_i.size)
-    poses, points = _perturb(rng, gt_poses, X, np.zeros(3), sig_pt=0.0)
-    points = X + rng.normal(0, 1, X.shape) * (0.02 * X[:, 2])[:, None]
+    poses, _ = _perturb(rng, gt_poses, X, np.zeros(3), sig_pt=0.0)
+    points = X + rng.normal(0, 1, X.shape) * (0.02 * depth_ref)[:, None]
     fixed = np.zeros(n_cams, np.uint8)
     fixed[0] = 1
     return BAProblem(poses, points, cam_i[perm].astype(np.int32), pt_i[perm].astype(np.int32),
