@@ -95,8 +95,12 @@ def make_workload(args, rank):
     elif args.workload == "c3":
         b = synth.pack_batch([synth.make_window(rank, n_cams=20, cam=synth.MALAGA, outlier_frac=0.1, n_obs=30000)])
         name = f"C3: one Malaga-shaped 20-keyframe window, Huber, {args.iters} LM iterations per step"
+    elif args.workload == "c5":
+        b = synth.pack_batch([synth.make_large(0, mode=args.c5_mode)])     # same problem on every rank
+        name = (f"C5: BAL-style, 1000 cameras, 200k landmarks, 1M observations, visibility '{args.c5_mode}', "
+                f"{args.iters} LM iterations per step, landmarks sharded across ranks")
     else:
-        raise SystemExit(f"workload {args.workload} not available in this build")
+        raise SystemExit(f"unknown workload {args.workload}")
     return b, name
 
 
@@ -112,7 +116,10 @@ def cpu_baseline(batch, iters, loss, budget_windows, threads=0):
     sample = synth.pack_batch([batch.window(i) for i in range(nw)])
     cores = ba_cpu.num_procs() if threads <= 0 else threads
     t0 = time.perf_counter()
-    ba_cpu.solve_batch(sample, max_iters=iters, loss=loss, threads=cores)
+    if sample.nb == 1 and sample.cam_off[-1] > 24:      # C5: one large problem, PCG, OpenMP inside the solve
+        ba_cpu.solve(sample.window(0), max_iters=iters, loss=loss, solver="pcg", threads=cores)
+    else:
+        ba_cpu.solve_batch(sample, max_iters=iters, loss=loss, threads=cores)
     dt = time.perf_counter() - t0
     return {"value": sample.no * iters / dt, "unit": "obs*iter/s", "cores": cores, "kind": "port",
             "sample": f"first {nw} windows of the workload ({sample.no} observations), {iters} LM iterations, "
@@ -152,10 +159,13 @@ def main():
     ap.add_argument("--workload", default="c4", choices=["c1", "c3", "c4", "c5"])
     ap.add_argument("--windows", type=int, default=4096)
     ap.add_argument("--distinct", type=int, default=256, help="distinct geometries generated (set-up time bound)")
-    ap.add_argument("--iters", type=int, default=10)
+    ap.add_argument("--iters", type=int, default=None, help="LM iterations per step (10 windows, 20 C5)")
+    ap.add_argument("--c5-mode", default="local", choices=["local", "random"])
     ap.add_argument("--cpu-windows", type=int, default=128)
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()
+    if args.iters is None:
+        args.iters = 20 if args.workload == "c5" else 10
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -174,8 +184,13 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     b, name = make_workload(args, rank)
     loss = "huber" if args.workload == "c3" else "trivial"
-    ba = BundleAdjuster(K_of(b.intr), BAConfig(max_iters=args.iters, loss=loss, device=local))
-    ba.set_problem(b.poses, b.points, b.obs_cam, b.obs_pt, b.obs_uv, b.fixed_cam, b.cam_off, b.pt_off, b.obs_off)
+    c5 = args.workload == "c5"
+    ba = BundleAdjuster(K_of(b.intr), BAConfig(max_iters=args.iters, loss=loss, device=local,
+                                               solver="pcg" if c5 else "auto"))
+    if c5 and world > 1:
+        ba.init_distributed()
+    offs = (None, None, None) if c5 else (b.cam_off, b.pt_off, b.obs_off)
+    ba.set_problem(b.poses, b.points, b.obs_cam, b.obs_pt, b.obs_uv, b.fixed_cam, *offs)
     stream = torch.cuda.current_stream().cuda_stream
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda") if b.no * 32 < (256 << 20) else None
 
@@ -221,14 +236,15 @@ def main():
     barrier()
     t0 = time.perf_counter()
     for _ in range(e2e_steps):
-        ba.set_problem(hb["poses"], hb["points"], hb["obs_cam"], hb["obs_pt"], hb["obs_uv"], hb["fixed"],
-                       b.cam_off, b.pt_off, b.obs_off)
+        ba.set_problem(hb["poses"], hb["points"], hb["obs_cam"], hb["obs_pt"], hb["obs_uv"], hb["fixed"], *offs)
         ba.solve(stream=stream)
         ba.get()
     barrier()
     t_e2e = (time.perf_counter() - t0) / e2e_steps
 
     units = float(b.no) * args.iters          # obs*iter per step per rank
+    if c5:
+        units = units / world                  # ONE problem shared by all ranks (strong scaling)
     tt = torch.tensor([ms_total, t_e2e * 1e3], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
@@ -253,12 +269,14 @@ def main():
         traffic = json.load(open(prof)).get(args.workload) if os.path.exists(prof) else None
         out = {"metric": "BA observations*iterations/sec", "value": units_all * args.steps / (ms_total * 1e-3),
                "unit": "obs*iter/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-               "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak",
-               "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+               "ms_per_step": ms_total / args.steps, "higher_is_better": True,
+               "scaling": "strong" if c5 else "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
                "config": {"workload": name, "windows_per_gpu": b.nb, "observations_per_gpu": int(b.no),
                           "lm_iterations": args.iters, "lm_iterations_executed": int(iters_done),
                           "distinct_geometries": args.distinct if args.workload == "c4" else 1,
-                          "partition": f"{world} x independent window shards, no collective",
+                          "partition": (f"landmarks sharded over {world} rank(s) by observation count; 3 ncclAllReduce "
+                                        f"(f64 sum) per LM iteration; PCG + LM control replicated") if c5 else
+                                       f"{world} x independent window shards, no collective",
                           "l2": "inputs larger than L2" if flush is None else "L2 flushed between timed steps"},
                "roofline": {"bound": "tensor", "kernel": "window_lm_kernel", "achieved": tf, "peak": FP64_PEAK_TFLOPS,
                             "unit": "TFLOP/s", "frac": tf / FP64_PEAK_TFLOPS, "traffic": traffic,
@@ -270,8 +288,43 @@ def main():
                "e2e": {"value": units_all / (ms_e2e * 1e-3), "unit": "obs*iter/s", "h2d_bytes_per_step": int(h2d),
                        "d2h_bytes_per_step": int(d2h), "ms_per_step": ms_e2e},
                "wall_s_timed_region": t_wall}
+        if c5:
+            # dominant kernel: the cooperative PCG (block-sparse mat-vec, HBM/L2 bound).  Algorithmic bytes of
+            # the step: 46.4 B per observation*iteration + 288 B per S block read per CG iteration
+            # (upper blocks are read twice: row and transposed row) + 7 vectors of 6*Nfree doubles.
+            pcg_its = sum(s_.pcg_iters for s_ in sms)
+            ncam = int(b.cam_off[-1])
+            pairs = set()
+            # nnzblk(S) from the visibility: only needed here, on the host, for the byte count
+            order = np.lexsort((b.obs_cam, b.obs_pt))
+            oc, op = b.obs_cam[order], b.obs_pt[order]
+            k = np.bincount(op)
+            if (k == k[0]).all():
+                cams = oc.reshape(-1, int(k[0]))
+                for i in range(cams.shape[1]):
+                    for j in range(i, cams.shape[1]):
+                        pairs.update((cams[:, i].astype(np.int64) * ncam + cams[:, j]).tolist())
+            nfull = 2 * len(pairs) - ncam
+            byt = (46.4 * b.no * iters_done + pcg_its * (288.0 * nfull + 7 * 48.0 * ncam))
+            gbs5 = byt / (ms_total / args.steps * 1e-3) / 1e9
+            out["roofline"] = {"bound": "hbm", "kernel": "large_pcg_kernel (+ schur/backsub passes)", "achieved": gbs5,
+                               "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": gbs5 / pk["hbm_gbs"], "traffic": None,
+                               "note": f"whole-step algorithmic bytes / step time; {pcg_its} CG iterations per step; "
+                                       f"peak {pk_kind}"}
+            out["gpu_launches"] = args.steps * (int(iters_done) * 13 + 2)
+            out["config"].pop("windows_per_gpu"); out["config"].pop("distinct_geometries")
+            out["config"]["pcg_iterations_per_step"] = int(pcg_its)
         if not args.no_cpu and world == 1:
-            out["cpu_baseline"] = cpu_baseline(b, args.iters, loss, args.cpu_windows)
+            if c5:
+                from oracle import ba_cpu
+                t0 = time.perf_counter()
+                _, _, so = ba_cpu.solve(b.window(0), max_iters=args.iters, solver="pcg", threads=0)
+                dt = time.perf_counter() - t0
+                out["cpu_baseline"] = {"value": b.no * so.iterations / dt, "unit": "obs*iter/s", "cores": ba_cpu.num_procs(),
+                                       "kind": "port", "sample": f"the whole C5 problem, {so.iterations} LM iterations, "
+                                       f"oracle/ba_cpu.cpp OpenMP, {dt:.2f} s"}
+            else:
+                out["cpu_baseline"] = cpu_baseline(b, args.iters, loss, args.cpu_windows)
         print(json.dumps(out))
     if world > 1:
         dist.destroy_process_group()

@@ -1,0 +1,83 @@
+"""GPU parity of the large (PCG) path against the oracle (same PCG rule), through the C ABI."""
+import numpy as np
+import pytest
+
+from visualodometry_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+
+def K_of(p):
+    return np.array([[p.intr[0], 0, p.intr[2]], [0, p.intr[1], p.intr[3]], [0, 0, 1]])
+
+
+def rel(a, b):
+    a, b = np.asarray(a, np.float64), np.asarray(b, np.float64)
+    return float(np.abs(a - b).max() / max(np.abs(b).max(), 1e-300)) if a.size else 0.0
+
+
+def _engine(p, **kw):
+    from visualodometry_b200 import BAConfig, BundleAdjuster
+    ba = BundleAdjuster(K_of(p), BAConfig(solver="pcg", **kw))
+    return ba.set_problem(p.poses, p.points, p.obs_cam, p.obs_pt, p.obs_uv, p.fixed_cam)
+
+
+@pytest.mark.parametrize("mode,nc,npts", [("random", 40, 2000), ("local", 40, 2000), ("random", 200, 20000)])
+def test_structure_and_stage(oracle, mode, nc, npts):
+    p = synth.make_large(2, n_cams=nc, n_pts=npts, mode=mode)
+    ba = _engine(p)
+    ix = oracle.index(p)
+    for k, ref in (("PM_PERM", ix.pm_perm), ("PT_PTR", ix.pt_ptr), ("FIDX", ix.fidx), ("BLK_PTR", ix.blk_ptr),
+                   ("BLK_COL", ix.blk_col)):
+        assert np.array_equal(ba.dump(k, ref.shape, np.int32), ref), k
+    st = oracle.stage(p, mu=1e4, solver="pcg")
+    n = st["S"].shape[0]
+    assert rel(ba.dump("S", (n, n)), st["S"]) <= 1e-11          # fp64 RED order differs, values agree
+    assert rel(ba.dump("GRED", (n,)), st["gred"]) <= 1e-11
+    if mode == "random":                                         # PCG converges: the step agrees too
+        assert rel(ba.dump("DC", (n,)), st["dc"]) <= 1e-8
+    ba.close()
+
+
+@pytest.mark.parametrize("nc,npts", [(40, 2000), (200, 20000)])
+def test_lm_result_random_visibility(oracle, nc, npts):
+    p = synth.make_large(3, n_cams=nc, n_pts=npts, mode="random")
+    ba = _engine(p, max_iters=8, record_history=True)
+    sm = ba.solve()[0]
+    poses, pts = ba.get()
+    po, xo, so = oracle.solve(p, max_iters=8, solver="pcg")
+    assert (sm.iterations, sm.accepted, sm.rejected) == (so.iterations, so.accepted, so.rejected)
+    assert rel(ba.dump("HIST_COST", (1, 64))[0, :8], np.array(so.cost_hist[:8])) <= 1e-9
+    r_gpu, r_cpu = synth.rmse_px(p, poses, pts), synth.rmse_px(p, po, xo)
+    assert abs(r_gpu - r_cpu) <= 1e-6 * r_cpu and r_gpu < 0.1 * synth.rmse_px(p)
+    assert np.abs(poses - po).max() <= 1e-5
+    assert (np.linalg.norm(pts - xo, axis=1) / np.maximum(1, np.linalg.norm(xo, axis=1))).max() <= 1e-5
+    ba.close()
+
+
+def test_lm_result_chain_rmse_only(oracle):
+    """local visibility: block-Jacobi PCG is capped at 200 iterations in oracle AND engine;
+    the cost / RMSE agree, the unconverged drift mode of the chain does not."""
+    p = synth.make_large(3, n_cams=100, n_pts=10000, mode="local")
+    ba = _engine(p, max_iters=8)
+    sm = ba.solve()[0]
+    poses, pts = ba.get()
+    po, xo, so = oracle.solve(p, max_iters=8, solver="pcg")
+    assert sm.accepted == so.accepted
+    r_gpu, r_cpu = synth.rmse_px(p, poses, pts), synth.rmse_px(p, po, xo)
+    assert abs(r_gpu - r_cpu) <= 1e-5 * r_cpu and r_gpu < 0.1 * synth.rmse_px(p)
+    ba.close()
+
+
+def test_window_problem_on_large_path_matches_window_kernel():
+    """the two CUDA paths solve the same small problem to the same answer (Cholesky vs converged PCG)."""
+    from visualodometry_b200 import BAConfig, BundleAdjuster
+    p = synth.make_window(11, n_cams=8, n_pts=400, n_obs=2500)
+    a = BundleAdjuster(K_of(p), BAConfig(max_iters=6, solver="chol"))
+    a.set_problem(p.poses, p.points, p.obs_cam, p.obs_pt, p.obs_uv, p.fixed_cam)
+    sa = a.solve()[0]; pa, xa = a.get()
+    b = BundleAdjuster(K_of(p), BAConfig(max_iters=6, solver="pcg", pcg_max_iters=500))
+    b.set_problem(p.poses, p.points, p.obs_cam, p.obs_pt, p.obs_uv, p.fixed_cam)
+    sb = b.solve()[0]; pb, xb = b.get()
+    assert sa.accepted == sb.accepted and abs(sa.final_cost - sb.final_cost) <= 1e-7 * sa.final_cost
+    assert np.abs(pa - pb).max() <= 1e-5
