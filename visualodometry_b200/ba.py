@@ -210,8 +210,17 @@ class BundleAdjuster:
         return BASummary(s.status, s.iterations, s.accepted, s.rejected, s.n_invalid, s.pcg_iters,
                          s.initial_cost, s.final_cost, s.final_mu)
 
-    def get(self, device=False):
+    def get(self, device=False, out=None):
+        """Current poses (Nc,12) / landmarks (Np,3).  `out=(poses, points)`: caller-owned C-contiguous f64
+        numpy arrays (e.g. pinned host memory) to fill instead of allocating new ones."""
         nc, npts, _ = self._shape
+        if out is not None:
+            poses, pts = out
+            for a, shp in ((poses, nc * 12), (pts, npts * 3)):
+                if a.dtype != np.float64 or a.size != shp or not a.flags.c_contiguous:
+                    raise ValueError("get(out=...): C-contiguous float64 arrays of the problem's size required")
+            self._check(self._lib.b2ba_get(self._h, poses.ctypes.data, pts.ctypes.data, _lib.MEM_HOST), "b2ba_get")
+            return poses, pts
         if device:
             poses = torch.empty((nc, 12), dtype=torch.float64, device="cuda")
             pts = torch.empty((npts, 3), dtype=torch.float64, device="cuda")

@@ -235,6 +235,15 @@ int b2ba_create(b2ba_t** out, int device, const b2ba_options* opts) {
   if (e != cudaSuccess || device < 0 || device >= ndev) return B2BA_E_CUDA;   // no CPU fallback
   e = cudaSetDevice(device);
   if (e != cudaSuccess) return B2BA_E_CUDA;
+  {
+    // the index builder's temporaries are stream-ordered allocations: keep them cached in the pool
+    // between set_problem calls instead of returning them to the driver at every synchronisation
+    cudaMemPool_t pool;
+    if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
+      unsigned long long thr = ~0ull;
+      cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr);
+    }
+  }
   b2ba* h = new b2ba();
   h->device = device;
   if (opts) h->opt = *opts; else b2ba_default_options(&h->opt);
