@@ -114,18 +114,25 @@ def test_lm_trajectory_and_result(engine, oracle, name):
     assert abs(sm.final_cost - so.final_cost) <= 1e-9 * so.final_cost
     assert np.abs(poses - po).max() <= 1e-5
     assert pts_err(pts, xo) <= 1e-5
-    assert r_gpu < 0.5 * synth.rmse_px(p)          # and it actually optimised
+    # and it actually optimised (robust cost: the plain RMSE of the Huber problems is dominated by the 20 px outliers)
+    assert sm.final_cost < 0.5 * sm.initial_cost
     ba.close()
 
 
 def test_batch_matches_per_window_oracle(engine, oracle):
     b = synth.make_batch(24, seed0=100)
     from visualodometry_b200 import BAConfig, BundleAdjuster
-    res = BundleAdjuster(K_of(b), BAConfig(max_iters=10)).optimize_batch(b)
+    ba = BundleAdjuster(K_of(b), BAConfig(max_iters=10, record_history=True))
+    res = ba.optimize_batch(b)
     po, xo, sos = oracle.solve_batch(b, max_iters=10, threads=0)
     fc = np.array([s.final_cost for s in res.summaries])
     fo = np.array([s.final_cost for s in sos])
-    assert [s.accepted for s in res.summaries] == [s.accepted for s in sos]
+    # accept / reject per window, over the iterations that still move the cost (afterwards rho is noise)
+    ha = ba.dump("HIST_ACCEPT", (b.nb, 64), np.int32)[:, :10]
+    for w, so in enumerate(sos):
+        ch = np.array([so.initial_cost] + list(so.cost_hist[:10]))
+        moving = np.concatenate([[True], (ch[:-1] - ch[1:])[:-1] > 1e-7 * ch[:-2]])
+        assert np.array_equal(ha[w][moving], np.array(so.accept_hist[:10])[moving]), w
     assert rel(fc, fo) <= 1e-9
     poses = np.concatenate([res.T_cw[:, :3, :3].reshape(-1, 9), res.T_cw[:, :3, 3]], axis=1)
     assert np.abs(poses - po).max() <= 1e-5 and pts_err(res.points, xo) <= 1e-5

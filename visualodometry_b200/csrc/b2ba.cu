@@ -323,8 +323,8 @@ int b2ba_set_problem_batch(b2ba_t* h, int32_t B, const int32_t* cam_off, const i
   if (flags[0]) { h->path = PATH_NONE; return fail(h, B2BA_E_INVALID, "observation index out of range"); }
   if (flags[1]) { h->path = PATH_NONE; return fail(h, B2BA_E_DUPLICATE, "duplicate (camera, point) observation"); }
   const bool want_pcg = h->opt.solver == B2BA_SOLVER_PCG;
-  if (!want_pcg && h->max_nc <= kMaxCam && h->max_nfree <= 9) h->path = PATH_WIN_SMALL;
-  else if (!want_pcg && h->max_nc <= kMaxCam && h->max_nfree <= 21) h->path = PATH_WIN_BIG;
+  if (!want_pcg && h->max_nc <= kSmallMaxCam && h->max_nfree <= kSmallMaxFree) h->path = PATH_WIN_SMALL;
+  else if (!want_pcg && h->max_nc <= kMaxCam && h->max_nfree <= kBigMaxFree) h->path = PATH_WIN_BIG;
   else if (h->opt.solver == B2BA_SOLVER_WINDOW)
     return fail(h, B2BA_E_UNSUPPORTED, "window solver supports at most 21 free / 24 total cameras per window");
   else h->path = PATH_LARGE;

@@ -121,6 +121,64 @@ __device__ __forceinline__ void retract_pose(const double* pose, const double* d
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Lean forms used by the window kernel's hot loops.  Same quantities as project / jac_cam /
+// jac_point / make_E above, written as explicit FMA chains that skip the structural zeros of
+// J_c (J_c[0][4] = J_c[1][3] = 0); differences to the forms above are pure rounding (~1e-16).
+struct Pose12 { double r[12]; };   // [R row-major | t] in registers
+
+__device__ __forceinline__ void load_pose(const double* __restrict__ p, Pose12& q) {   // p: 16-byte aligned
+  const double2* v = reinterpret_cast<const double2*>(p);
+#pragma unroll
+  for (int i = 0; i < 6; ++i) { const double2 t = v[i]; q.r[2 * i] = t.x; q.r[2 * i + 1] = t.y; }
+}
+
+struct Geo {       // one observation: camera-frame point, residual, weight, dr/dx = [[a0,0,a2],[0,b1,b2]]
+  double x, y, z, r0, r1, w, rho, a0, a2, b1, b2;
+  bool valid;
+};
+
+__device__ __forceinline__ void geo_project(const Params& P, const Pose12& q, double X0, double X1, double X2,
+                                            float u, float v, Geo& o) {
+  o.x = fma(q.r[0], X0, fma(q.r[1], X1, fma(q.r[2], X2, q.r[9])));
+  o.y = fma(q.r[3], X0, fma(q.r[4], X1, fma(q.r[5], X2, q.r[10])));
+  o.z = fma(q.r[6], X0, fma(q.r[7], X1, fma(q.r[8], X2, q.r[11])));
+  o.valid = o.z >= P.z_min;
+  const double iz = o.valid ? 1.0 / o.z : 0.0;
+  o.a0 = P.fx * iz;
+  o.b1 = P.fy * iz;
+  o.r0 = fma(o.a0, o.x, P.cx - (double)u);
+  o.r1 = fma(o.b1, o.y, P.cy - (double)v);
+  o.a2 = -(o.a0 * o.x) * iz;
+  o.b2 = -(o.b1 * o.y) * iz;
+  const double s = fma(o.r0, o.r0, o.r1 * o.r1);
+  o.w = 1.0;
+  o.rho = s;
+  if (P.loss == 1 && s > P.huber_a * P.huber_a) {
+    const double rs = sqrt(s);
+    o.rho = 2.0 * P.huber_a * rs - P.huber_a * P.huber_a;
+    o.w = P.huber_a / rs;
+  }
+  if (!o.valid) { o.r0 = 0; o.r1 = 0; o.w = 0; o.rho = 0; }
+}
+
+// J_p rows: jp[0..2] = a0 R0 + a2 R2, jp[3..5] = b1 R1 + b2 R2
+__device__ __forceinline__ void geo_jp(const Pose12& q, const Geo& o, double* jp) {
+#pragma unroll
+  for (int j = 0; j < 3; ++j) {
+    jp[j] = fma(o.a0, q.r[j], o.a2 * q.r[6 + j]);
+    jp[3 + j] = fma(o.b1, q.r[3 + j], o.b2 * q.r[6 + j]);
+  }
+}
+
+// J_c rows (left perturbation [dw, dt]); c0[4] and c1[3] are structurally zero and never read
+__device__ __forceinline__ void geo_jc(const Geo& o, double* c0, double* c1) {
+  c0[0] = o.a2 * o.y;                 c0[1] = fma(o.a0, o.z, -(o.a2 * o.x)); c0[2] = -(o.a0 * o.y);
+  c0[3] = o.a0;                       c0[4] = 0.0;                            c0[5] = o.a2;
+  c1[0] = fma(o.b2, o.y, -(o.b1 * o.z)); c1[1] = -(o.b2 * o.x);               c1[2] = o.b1 * o.x;
+  c1[3] = 0.0;                        c1[4] = o.b1;                           c1[5] = o.b2;
+}
+
 __device__ __forceinline__ double warp_sum(double v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

@@ -4,38 +4,94 @@
 //   camera pass   (a1+a2)  camera-major stream -> B_c (6x6 sym), g_c, cost; CTA-wide fixed-order
 //                           reduction, no atomics.
 //   point pass    (a1-a4)  point-major stream, TPP lanes per landmark: C_p, g_p -> damped 3x3
-//                           factor F (C'^-1 = F F^T) -> Z_p = E_k F staged in shared memory; the
-//                           Schur complement  sum_p W_p C'^-1 W_p^T = Z Z^T  is accumulated by
-//                           FP64 tensor-core MMA (DMMA m8n8k4) with the sum over landmarks as the
-//                           K dimension: no atomics, no shuffles, fixed summation order.  An extra
+//                           factor F (C'^-1 = F F^T) -> Z_p = E_k F staged in shared memory
+//                           (transposed: one contiguous column block per landmark); the Schur
+//                           complement  sum_p W_p C'^-1 W_p^T = Z Z^T  is accumulated by FP64
+//                           tensor-core MMA (DMMA m8n8k4) with the sum over landmarks as the K
+//                           dimension: no atomics, no shuffles, fixed summation order.  An extra
 //                           row y_p = F^T g_p makes  Z y = sum E C'^-1 g_p  fall out of the same MMA.
+//                           The tile schedule is compile-time per warp group (fragments of a tile
+//                           row are loaded once and reused across its tiles).
 //   solve         (a5)     S = B' - Z Z^T, in-CTA Cholesky + triangular solves.
 //   back-subst    (a7)     delta_p, retraction, trial cost, gain ratio, accept/reject, mu update.
 #include "ba_window.cuh"
+
+#include <cstdlib>
+#include <utility>
 
 namespace b2 {
 
 __device__ __forceinline__ int packed21(int r, int s) { return r * 6 - r * (r - 1) / 2 + (s - r); }
 
+// ---- compile-time loop: f(integral_constant<int, I>) for I in [0, N)
+template <int I, int N, class F>
+__device__ __forceinline__ void static_for(F&& f) {
+  if constexpr (I < N) {
+    f(std::integral_constant<int, I>{});
+    static_for<I + 1, N>(f);
+  }
+}
+
+template <class Cfg, int GRP, int R>
+constexpr bool row_used() {
+  for (int q = 0; q < Cfg::TPW; ++q) {
+    const int t = GRP * Cfg::TPW + q;
+    if (t < Cfg::T && (Tri<Cfg::NT>::mi(t) == R || Tri<Cfg::NT>::ni(t) == R)) return true;
+  }
+  return false;
+}
+
+// acc += Zt-slice * Zt-slice^T for the tiles of warp group GRP over k-steps [kb, kb + KPER).
+// zf = Zt + (lane & 3) * LDT + (lane >> 2): fragment (a and b alike) of tile row r at k-step k is
+// zf[(4 k) * LDT + 8 r].  All offsets are immediates after unrolling.
+template <class Cfg, int GRP>
+__device__ __forceinline__ void syrk_group(const double* __restrict__ zf, int kb, double (&acc)[Cfg::TPW][2]) {
+  constexpr int KPER = Cfg::KSTEPS / Cfg::KS;
+  const double* zk = zf + (size_t)kb * 4 * Cfg::LDT;
+#pragma unroll 2
+  for (int ks = 0; ks < KPER; ++ks) {
+    double fr[Cfg::NT];
+    static_for<0, Cfg::NT>([&](auto r) {
+      constexpr int R = decltype(r)::value;
+      if constexpr (row_used<Cfg, GRP, R>()) fr[R] = zk[8 * R];
+    });
+    static_for<0, Cfg::TPW>([&](auto q) {
+      constexpr int Q = decltype(q)::value;
+      constexpr int t = GRP * Cfg::TPW + Q;
+      if constexpr (t < Cfg::T) dmma884(acc[Q][0], acc[Q][1], fr[Tri<Cfg::NT>::mi(t)], fr[Tri<Cfg::NT>::ni(t)]);
+    });
+    zk += 4 * Cfg::LDT;
+  }
+}
+
+template <class Cfg, int GRP = 0>
+__device__ __forceinline__ void syrk_dispatch(int grp, const double* __restrict__ zf, int kb,
+                                              double (&acc)[Cfg::TPW][2]) {
+  if constexpr (GRP < Cfg::G) {
+    if (grp == GRP) syrk_group<Cfg, GRP>(zf, kb, acc);
+    else syrk_dispatch<Cfg, GRP + 1>(grp, zf, kb, acc);
+  }
+}
+
 template <class Cfg>
-__global__ void __launch_bounds__(Cfg::NTHREADS, (Cfg::SMEM <= 110 * 1024) ? 2 : 1)
+__global__ void __launch_bounds__(Cfg::NTHREADS, Cfg::MINB)
 window_lm_kernel(const WinData d, const Params P) {
-  constexpr int NTHREADS = Cfg::NTHREADS, NWARPS = Cfg::NWARPS, G = Cfg::G, KS = Cfg::KS;
-  constexpr int TPW = Cfg::TPW, TPP = Cfg::TPP, PB = Cfg::PB, LD = Cfg::LD, LDS = Cfg::LDS;
+  constexpr int NTHREADS = Cfg::NTHREADS, NWARPS = Cfg::NWARPS, G = Cfg::G, KS = Cfg::KS, NT = Cfg::NT;
+  constexpr int TPW = Cfg::TPW, TPP = Cfg::TPP, PB = Cfg::PB, LDT = Cfg::LDT, LDS = Cfg::LDS, MAXCAM = Cfg::MAXCAM;
   extern __shared__ __align__(16) double smem[];
   double* pose_cur = smem;
-  double* pose_tri = pose_cur + kMaxCam * 12;
-  double* Bc = pose_tri + kMaxCam * 12;      // kMaxCam x 21 (upper, packed)
-  double* gc = Bc + kMaxCam * 21;            // kMaxCam x 6
-  double* Dc = gc + kMaxCam * 6;
-  double* dvec = Dc + kMaxCam * 6;           // delta_c (6*nfree)
+  double* pose_tri = pose_cur + MAXCAM * 12;
+  double* Bc = pose_tri + MAXCAM * 12;      // MAXCAM x 21 (upper, packed)
+  double* gc = Bc + MAXCAM * 21;            // MAXCAM x 6
+  double* Dc = gc + MAXCAM * 6;
+  double* dvec = Dc + MAXCAM * 6;           // delta_c (6*nfree)
   double* gred = dvec + 128;
-  double* red = gred + 128;                  // NWARPS x 32 reduction scratch
-  double* scal = red + Cfg::NRED;            // 16 control scalars
-  double* Z = scal + 16;                     // Z tile, later S
+  double* red = gred + 128;                 // NWARPS x 32 reduction scratch
+  double* scal = red + Cfg::NRED;           // 16 control scalars
+  double* Z = scal + 16;                    // Zt tile (transposed), later S
   int* fidx = reinterpret_cast<int*>(Z + Cfg::ZS);   // free index or -1
-  int* lo = fidx + kMaxCam;                  // # free cameras with index < c  (kMaxCam+1)
-  int* iflag = lo + kMaxCam + 1;             // [0] step_bad  [1] accept  [2] stop
+  int* lo = fidx + MAXCAM;                  // # free cameras with index < c  (MAXCAM+1)
+  int* iflag = lo + MAXCAM + 1;             // [0] step_bad  [1] accept  [2] stop
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int win = blockIdx.x;
@@ -55,25 +111,7 @@ window_lm_kernel(const WinData d, const Params P) {
   __syncthreads();
   const int nfree = lo[nc];
   const int n = 6 * nfree;              // reduced system size; row n of Z is the y row
-  const int nt = (n + 1 + 7) >> 3;      // 8x8 tile rows in use
-  const int T = nt * (nt + 1) / 2;
-  const int tpw = (T + G - 1) / G;
-
-  // tiles of this warp: group g owns upper tiles [g*tpw, (g+1)*tpw) in row-major upper order
   const int grp = warp % G, ksp = warp / G;
-  int tmi[TPW], tni[TPW];
-  {
-    int t = grp * tpw, mi = 0, rowlen = nt, base = 0;
-    while (mi < nt && t >= base + rowlen) { base += rowlen; --rowlen; ++mi; }
-    int ni = mi + (t - base);
-#pragma unroll
-    for (int q = 0; q < TPW; ++q) {
-      bool ok = q < tpw && mi < nt;
-      tmi[q] = ok ? mi : -1;
-      tni[q] = ok ? ni : 0;
-      if (++ni >= nt) { ++mi; ni = mi; }
-    }
-  }
 
   double mu = P.init_mu, nu = 2.0, cost = 0.0, initial_cost = 0.0;
   int cur = 0, have_lin = 0, it = 0, n_acc = 0, n_rej = 0, status = B2BA_MAX_ITERS, ninv_cur = 0;
@@ -93,7 +131,8 @@ window_lm_kernel(const WinData d, const Params P) {
       double cst_tot = 0.0, ninv_tot = 0.0;   // live in thread 27 / 28
       for (int c = 0; c < nc; ++c) {
         const int b = d.cam_ptr[c0 + c], e = d.cam_ptr[c0 + c + 1];
-        const double* pose = pose_cur + 12 * c;
+        Pose12 q;
+        load_pose(pose_cur + 12 * c, q);
         const bool isfree = fidx[c] >= 0;
         double acc[29];
 #pragma unroll
@@ -101,20 +140,24 @@ window_lm_kernel(const WinData d, const Params P) {
         for (int a = b + tid; a < e; a += NTHREADS) {
           const ObsRec rec = d.cm[a];
           const double* Xp = X + 3 * rec.idx;
-          Proj o;
-          project(P, pose, Xp[0], Xp[1], Xp[2], rec.u, rec.v, o);
+          Geo o;
+          geo_project(P, q, Xp[0], Xp[1], Xp[2], rec.u, rec.v, o);
           if (!o.valid) { acc[28] += 1.0; continue; }
-          acc[27] += 0.5 * o.rho;
+          acc[27] = fma(0.5, o.rho, acc[27]);
           if (isfree) {
-            double jc[12];
-            jac_cam(P, o, jc);
+            double j0[6], j1[6];
+            geo_jc(o, j0, j1);
             int k = 0;
 #pragma unroll
             for (int r = 0; r < 6; ++r) {
-              const double j0 = o.w * jc[r], j1 = o.w * jc[6 + r];
+              const double w0 = o.w * j0[r], w1 = o.w * j1[r];
 #pragma unroll
-              for (int s = r; s < 6; ++s) acc[k++] += j0 * jc[s] + j1 * jc[6 + s];
-              acc[21 + r] += j0 * o.r0 + j1 * o.r1;
+              for (int s = r; s < 6; ++s, ++k) {
+                if (r != 4 && s != 4) acc[k] = fma(w0, j0[s], acc[k]);
+                if (r != 3 && s != 3) acc[k] = fma(w1, j1[s], acc[k]);
+              }
+              if (r != 4) acc[21 + r] = fma(w0, o.r0, acc[21 + r]);
+              if (r != 3) acc[21 + r] = fma(w1, o.r1, acc[21 + r]);
             }
           }
         }
@@ -155,36 +198,48 @@ window_lm_kernel(const WinData d, const Params P) {
     double acc[TPW][2];
 #pragma unroll
     for (int q = 0; q < TPW; ++q) acc[q][0] = acc[q][1] = 0.0;
-    // rows above the y row are never written by the point pass: keep them zero
-    for (int i = tid; i < (8 * nt - n - 1) * (3 * PB); i += NTHREADS)
-      Z[(n + 1 + i / (3 * PB)) * LD + i % (3 * PB)] = 0.0;
     double gmax = 0.0;
     const double imu = 1.0 / mu;
+    const double* zf = Z + (lane & 3) * LDT + (lane >> 2);   // DMMA fragment base of this lane
+    double* const zcol = Z + (size_t)3 * slot * LDT;          // this landmark's 3 columns: 3*LDT contiguous doubles
+    int a0n = 0, a1n = 0;
+    double Xn0 = 0, Xn1 = 0, Xn2 = 0;
+    if (slot < npw) {
+      a0n = d.pt_ptr[p0 + slot]; a1n = d.pt_ptr[p0 + slot + 1];
+      Xn0 = X[3 * slot]; Xn1 = X[3 * slot + 1]; Xn2 = X[3 * slot + 2];
+    }
 
     for (int b0 = 0; b0 < npw; b0 += PB) {
       const int p = b0 + slot;
       const bool act = p < npw;
-      int a0 = 0, a1 = 0;
-      double X0 = 0, X1 = 0, X2 = 0;
-      if (act) {
-        a0 = d.pt_ptr[p0 + p]; a1 = d.pt_ptr[p0 + p + 1];
-        X0 = X[3 * p]; X1 = X[3 * p + 1]; X2 = X[3 * p + 2];
+      const int a0 = a0n, a1 = a1n;
+      const double X0 = Xn0, X1 = Xn1, X2 = Xn2;
+      // clear the column block (rows of cameras that do not see the landmark must be zero; the
+      // block is contiguous, so this is TPP lanes x STS.128)
+      {
+        double2* zc2 = reinterpret_cast<double2*>(zcol);
+        const double2 zz = make_double2(0.0, 0.0);
+#pragma unroll 4
+        for (int i = sub; i < 3 * LDT / 2; i += TPP) zc2[i] = zz;
       }
       // loop 1: C_p, g_p
       double C[6] = {0, 0, 0, 0, 0, 0}, g[3] = {0, 0, 0};
       for (int a = a0 + sub; a < a1; a += TPP) {
         const ObsRec rec = d.pm[a];
-        const double* pose = pose_cur + 12 * rec.idx;
-        Proj o;
-        project(P, pose, X0, X1, X2, rec.u, rec.v, o);
+        Pose12 q;
+        load_pose(pose_cur + 12 * rec.idx, q);
+        Geo o;
+        geo_project(P, q, X0, X1, X2, rec.u, rec.v, o);
         double jp[6];
-        jac_point(P, pose, o, jp);
-        const double w = o.w;
-        C[0] += w * (jp[0] * jp[0] + jp[3] * jp[3]); C[1] += w * (jp[0] * jp[1] + jp[3] * jp[4]);
-        C[2] += w * (jp[0] * jp[2] + jp[3] * jp[5]); C[3] += w * (jp[1] * jp[1] + jp[4] * jp[4]);
-        C[4] += w * (jp[1] * jp[2] + jp[4] * jp[5]); C[5] += w * (jp[2] * jp[2] + jp[5] * jp[5]);
-#pragma unroll
-        for (int j = 0; j < 3; ++j) g[j] += w * (jp[j] * o.r0 + jp[3 + j] * o.r1);
+        geo_jp(q, o, jp);
+        const double u0 = o.w * jp[0], u1 = o.w * jp[1], u2 = o.w * jp[2];
+        const double v0 = o.w * jp[3], v1 = o.w * jp[4], v2 = o.w * jp[5];
+        C[0] = fma(u0, jp[0], fma(v0, jp[3], C[0])); C[1] = fma(u0, jp[1], fma(v0, jp[4], C[1]));
+        C[2] = fma(u0, jp[2], fma(v0, jp[5], C[2])); C[3] = fma(u1, jp[1], fma(v1, jp[4], C[3]));
+        C[4] = fma(u1, jp[2], fma(v1, jp[5], C[4])); C[5] = fma(u2, jp[2], fma(v2, jp[5], C[5]));
+        g[0] = fma(u0, o.r0, fma(v0, o.r1, g[0]));
+        g[1] = fma(u1, o.r0, fma(v1, o.r1, g[1]));
+        g[2] = fma(u2, o.r0, fma(v2, o.r1, g[2]));
       }
 #pragma unroll
       for (int m = TPP >> 1; m > 0; m >>= 1) {
@@ -196,7 +251,7 @@ window_lm_kernel(const WinData d, const Params P) {
       const double D0 = clampd(C[0]), D1 = clampd(C[3]), D2 = clampd(C[5]);
       double F[6];
       {
-        const double Cd[6] = {C[0] + D0 * imu, C[1], C[2], C[3] + D1 * imu, C[4], C[5] + D2 * imu};
+        const double Cd[6] = {fma(D0, imu, C[0]), C[1], C[2], fma(D1, imu, C[3]), C[4], fma(D2, imu, C[5])};
         if (!sym3_inv_factor(Cd, F)) {
 #pragma unroll
           for (int k = 0; k < 6; ++k) F[k] = 0.0;
@@ -204,70 +259,61 @@ window_lm_kernel(const WinData d, const Params P) {
         }
       }
       gmax = fmax(gmax, fmax(fabs(g[0]), fmax(fabs(g[1]), fabs(g[2]))));
-      double* zc = Z + 3 * slot;   // this point's 3 columns
-      if (sub == 0) {
-        zc[n * LD + 0] = F[0] * g[0];
-        zc[n * LD + 1] = F[1] * g[0] + F[3] * g[1];
-        zc[n * LD + 2] = F[2] * g[0] + F[4] * g[1] + F[5] * g[2];
-        if (act) {
-          double* sc = scratch + (size_t)p * kPtScratch;
+      __syncwarp();   // column block cleared by all TPP lanes before anyone writes into it
+      if (sub == 0 && act) {
+        zcol[n] = F[0] * g[0];
+        zcol[LDT + n] = fma(F[1], g[0], F[3] * g[1]);
+        zcol[2 * LDT + n] = fma(F[2], g[0], fma(F[4], g[1], F[5] * g[2]));
+        double2* sc = reinterpret_cast<double2*>(scratch + (size_t)p * kPtScratch);
+        sc[0] = make_double2(F[0], F[1]); sc[1] = make_double2(F[2], F[3]); sc[2] = make_double2(F[4], F[5]);
+        sc[3] = make_double2(g[0], g[1]); sc[4] = make_double2(g[2], D0); sc[5] = make_double2(D1, D2);
+        if (dbg) {
 #pragma unroll
-          for (int k = 0; k < 6; ++k) sc[k] = F[k];
-          sc[6] = g[0]; sc[7] = g[1]; sc[8] = g[2]; sc[9] = D0; sc[10] = D1; sc[11] = D2;
-          if (dbg) {
+          for (int k = 0; k < 6; ++k) d.dbg[dbgL.off_C() + (size_t)p * 6 + k] = C[k];
 #pragma unroll
-            for (int k = 0; k < 6; ++k) d.dbg[dbgL.off_C() + (size_t)p * 6 + k] = C[k];
-#pragma unroll
-            for (int k = 0; k < 3; ++k) d.dbg[dbgL.off_gp() + (size_t)p * 3 + k] = g[k];
-          }
+          for (int k = 0; k < 3; ++k) d.dbg[dbgL.off_gp() + (size_t)p * 3 + k] = g[k];
         }
       }
-      // loop 2: Z rows of this point = E_k F at the rows of camera k; zero rows of unseen cameras
-      if (a1 == a0) {
-        if (sub == 0)
-          for (int r = 0; r < n; ++r) { zc[r * LD] = 0.0; zc[r * LD + 1] = 0.0; zc[r * LD + 2] = 0.0; }
-      }
+      // loop 2: Z rows of camera k = E_k F = w J_c^T (J_p F), 6 x 3, into the column block
       for (int a = a0 + sub; a < a1; a += TPP) {
         const ObsRec rec = d.pm[a];
-        const int c = rec.idx, f = fidx[c];
-        int zlo = 0;
-        if (a > a0) { const int cp = d.pm[a - 1].idx; zlo = lo[cp] + (fidx[cp] >= 0 ? 1 : 0); }
-        for (int r = 6 * zlo; r < 6 * lo[c]; ++r) { zc[r * LD] = 0.0; zc[r * LD + 1] = 0.0; zc[r * LD + 2] = 0.0; }
-        if (a == a1 - 1)
-          for (int r = 6 * (lo[c] + (f >= 0 ? 1 : 0)); r < n; ++r) { zc[r * LD] = 0.0; zc[r * LD + 1] = 0.0; zc[r * LD + 2] = 0.0; }
+        const int f = fidx[rec.idx];
         if (f < 0) continue;
-        const double* pose = pose_cur + 12 * c;
-        Proj o;
-        project(P, pose, X0, X1, X2, rec.u, rec.v, o);
-        double jp[6], jc[12], E[18];
-        jac_point(P, pose, o, jp);
-        jac_cam(P, o, jc);
-        make_E(o.w, jc, jp, E);
-        double* zr = zc + 6 * f * LD;
+        Pose12 q;
+        load_pose(pose_cur + 12 * rec.idx, q);
+        Geo o;
+        geo_project(P, q, X0, X1, X2, rec.u, rec.v, o);
+        double jp[6];
+        geo_jp(q, o, jp);
+        // G = w J_p F  (2 x 3; F upper triangular)
+        const double w0 = o.w * jp[0], w3 = o.w * jp[3];
+        const double G0[3] = {w0 * F[0], fma(w0, F[1], o.w * jp[1] * F[3]),
+                              fma(w0, F[2], fma(o.w * jp[1], F[4], o.w * jp[2] * F[5]))};
+        const double G1[3] = {w3 * F[0], fma(w3, F[1], o.w * jp[4] * F[3]),
+                              fma(w3, F[2], fma(o.w * jp[4], F[4], o.w * jp[5] * F[5]))};
+        double j0[6], j1[6];
+        geo_jc(o, j0, j1);
+        double* zr = zcol + 6 * f;
 #pragma unroll
-        for (int r = 0; r < 6; ++r) {
-          zr[r * LD + 0] = E[3 * r] * F[0];
-          zr[r * LD + 1] = E[3 * r] * F[1] + E[3 * r + 1] * F[3];
-          zr[r * LD + 2] = E[3 * r] * F[2] + E[3 * r + 1] * F[4] + E[3 * r + 2] * F[5];
+        for (int j = 0; j < 3; ++j) {
+          double2* dst = reinterpret_cast<double2*>(zr + j * LDT);
+          dst[0] = make_double2(fma(j0[0], G0[j], j1[0] * G1[j]), fma(j0[1], G0[j], j1[1] * G1[j]));
+          dst[1] = make_double2(fma(j0[2], G0[j], j1[2] * G1[j]), j0[3] * G0[j]);
+          dst[2] = make_double2(j1[4] * G1[j], fma(j0[5], G0[j], j1[5] * G1[j]));
         }
       }
       __syncthreads();
-      // Z Z^T accumulate: DMMA over this batch's 3*PB columns (this warp's k-slice)
+      // prefetch the next batch's landmark while the tensor pipe works
       {
-        const int krow = lane >> 2, kcol = lane & 3;
-        const int k_begin = ksp * (Cfg::KSTEPS / KS) * 4, k_end = k_begin + (Cfg::KSTEPS / KS) * 4;
-#pragma unroll 2
-        for (int k0 = k_begin; k0 < k_end; k0 += 4) {
-#pragma unroll
-          for (int q = 0; q < TPW; ++q) {
-            if (tmi[q] >= 0) {
-              const double a = Z[(8 * tmi[q] + krow) * LD + k0 + kcol];
-              const double b = Z[(8 * tni[q] + krow) * LD + k0 + kcol];
-              dmma884(acc[q][0], acc[q][1], a, b);
-            }
-          }
+        const int pn = p + PB;
+        a0n = 0; a1n = 0;
+        if (pn < npw) {
+          a0n = d.pt_ptr[p0 + pn]; a1n = d.pt_ptr[p0 + pn + 1];
+          Xn0 = X[3 * pn]; Xn1 = X[3 * pn + 1]; Xn2 = X[3 * pn + 2];
         }
       }
+      // Z Z^T accumulate: DMMA over this batch's 3*PB columns (this warp's k-slice)
+      syrk_dispatch<Cfg>(grp, zf, ksp * (Cfg::KSTEPS / KS), acc);
       __syncthreads();
     }
 
@@ -278,8 +324,10 @@ window_lm_kernel(const WinData d, const Params P) {
       if (ksp == s) {
 #pragma unroll
         for (int q = 0; q < TPW; ++q) {
-          if (tmi[q] >= 0) {
-            double* dst = S + (8 * tmi[q] + (lane >> 2)) * LDS + 8 * tni[q] + 2 * (lane & 3);
+          const int t = grp * TPW + q;
+          if (t < Cfg::T) {
+            const int mi = Tri<NT>::mi(t), ni = Tri<NT>::ni(t);
+            double* dst = S + (8 * mi + (lane >> 2)) * LDS + 8 * ni + 2 * (lane & 3);
             if (s == 0) { dst[0] = acc[q][0]; dst[1] = acc[q][1]; }
             else { dst[0] += acc[q][0]; dst[1] += acc[q][1]; }
           }
@@ -383,6 +431,7 @@ window_lm_kernel(const WinData d, const Params P) {
     if (dbg)
       for (int i = tid; i < n; i += NTHREADS) d.dbg[dbgL.off_dc() + i] = dvec[i];
 
+
     // ------------------------------------------------------------------ back-substitution + trial cost (a7)
     double s_tc = 0.0, s_dDd = 0.0, s_gd = 0.0, s_dn2 = 0.0, s_xn2 = 0.0, s_inv = 0.0;
     if (step_ok) {
@@ -399,19 +448,19 @@ window_lm_kernel(const WinData d, const Params P) {
           const ObsRec rec = d.pm[a];
           const int f = fidx[rec.idx];
           if (f < 0) continue;
-          const double* pose = pose_cur + 12 * rec.idx;
-          Proj o;
-          project(P, pose, X0, X1, X2, rec.u, rec.v, o);
-          double jp[6], jc[12];
-          jac_point(P, pose, o, jp);
-          jac_cam(P, o, jc);
+          Pose12 q;
+          load_pose(pose_cur + 12 * rec.idx, q);
+          Geo o;
+          geo_project(P, q, X0, X1, X2, rec.u, rec.v, o);
+          double jp[6], j0[6], j1[6];
+          geo_jp(q, o, jp);
+          geo_jc(o, j0, j1);
           // E^T dc = w J_p^T (J_c dc)
           const double* dc = dvec + 6 * f;
-          double t0 = 0.0, t1 = 0.0;
+          const double t0 = o.w * fma(j0[0], dc[0], fma(j0[1], dc[1], fma(j0[2], dc[2], fma(j0[3], dc[3], j0[5] * dc[5]))));
+          const double t1 = o.w * fma(j1[0], dc[0], fma(j1[1], dc[1], fma(j1[2], dc[2], fma(j1[4], dc[4], j1[5] * dc[5]))));
 #pragma unroll
-          for (int r = 0; r < 6; ++r) { t0 += jc[r] * dc[r]; t1 += jc[6 + r] * dc[r]; }
-#pragma unroll
-          for (int j = 0; j < 3; ++j) v[j] += o.w * (jp[j] * t0 + jp[3 + j] * t1);
+          for (int j = 0; j < 3; ++j) v[j] = fma(jp[j], t0, fma(jp[3 + j], t1, v[j]));
         }
 #pragma unroll
         for (int m = TPP >> 1; m > 0; m >>= 1) {
@@ -420,17 +469,18 @@ window_lm_kernel(const WinData d, const Params P) {
         }
         double Xn0 = X0, Xn1 = X1, Xn2 = X2;
         if (act) {
-          const double* sc = scratch + (size_t)p * kPtScratch;
-          const double F0 = sc[0], F1 = sc[1], F2 = sc[2], F3 = sc[3], F4 = sc[4], F5 = sc[5];
-          const double g0 = sc[6], g1 = sc[7], g2 = sc[8];
+          const double2* sc = reinterpret_cast<const double2*>(scratch + (size_t)p * kPtScratch);
+          const double2 s0 = sc[0], s1 = sc[1], s2 = sc[2], s3 = sc[3], s4 = sc[4], s5 = sc[5];
+          const double F0 = s0.x, F1 = s0.y, F2 = s1.x, F3 = s1.y, F4 = s2.x, F5 = s2.y;
+          const double g0 = s3.x, g1 = s3.y, g2 = s4.x;
           const double t0 = g0 + v[0], t1 = g1 + v[1], t2 = g2 + v[2];
           // delta_p = -F F^T t
-          const double u0 = F0 * t0, u1 = F1 * t0 + F3 * t1, u2 = F2 * t0 + F4 * t1 + F5 * t2;
-          const double d0 = -(F0 * u0 + F1 * u1 + F2 * u2), d1 = -(F3 * u1 + F4 * u2), d2 = -(F5 * u2);
+          const double u0 = F0 * t0, u1 = fma(F1, t0, F3 * t1), u2 = fma(F2, t0, fma(F4, t1, F5 * t2));
+          const double d0 = -fma(F0, u0, fma(F1, u1, F2 * u2)), d1 = -fma(F3, u1, F4 * u2), d2 = -(F5 * u2);
           Xn0 = X0 + d0; Xn1 = X1 + d1; Xn2 = X2 + d2;
           if (sub == 0) {
             Xt[3 * p] = Xn0; Xt[3 * p + 1] = Xn1; Xt[3 * p + 2] = Xn2;
-            s_dDd += d0 * d0 * sc[9] + d1 * d1 * sc[10] + d2 * d2 * sc[11];
+            s_dDd += d0 * d0 * s4.y + d1 * d1 * s5.x + d2 * d2 * s5.y;
             s_gd += d0 * g0 + d1 * g1 + d2 * g2;
             s_dn2 += d0 * d0 + d1 * d1 + d2 * d2;
             s_xn2 += X0 * X0 + X1 * X1 + X2 * X2;
@@ -439,9 +489,11 @@ window_lm_kernel(const WinData d, const Params P) {
         }
         for (int a = a0 + sub; a < a1; a += TPP) {
           const ObsRec rec = d.pm[a];
-          Proj o;
-          project(P, pose_tri + 12 * rec.idx, Xn0, Xn1, Xn2, rec.u, rec.v, o);
-          if (o.valid) s_tc += 0.5 * o.rho; else s_inv += 1.0;
+          Pose12 q;
+          load_pose(pose_tri + 12 * rec.idx, q);
+          Geo o;
+          geo_project(P, q, Xn0, Xn1, Xn2, rec.u, rec.v, o);
+          if (o.valid) s_tc = fma(0.5, o.rho, s_tc); else s_inv += 1.0;
         }
       }
     }
@@ -536,8 +588,9 @@ window_lm_kernel(const WinData d, const Params P) {
   }
 }
 
-using CfgSmall = WinCfg<7, 8, 4, 64>;     // n+1 <= 56: up to 9 free cameras (C1 / C4)
-using CfgBig = WinCfg<16, 16, 16, 32>;    // n+1 <= 128: up to 21 free cameras (C3)
+using CfgSmall = WinCfg<7, 8, 4, 64, kSmallMaxCam, 2>;    // 256 threads, 2 CTAs / SM
+using CfgSmall4 = WinCfg<7, 4, 4, 32, kSmallMaxCam, 4>;   // 128 threads, 4 CTAs / SM
+using CfgBig = WinCfg<16, 16, 16, 32, kMaxCam, 1>;        // n+1 <= 128: up to 21 free cameras (C3)
 
 template <class Cfg>
 static int launch(const WinData& d, const Params& p, cudaStream_t s) {
@@ -552,32 +605,39 @@ static int launch(const WinData& d, const Params& p, cudaStream_t s) {
   return (int)cudaGetLastError();
 }
 
-int launch_window_small(const WinData& d, const Params& p, cudaStream_t s) { return launch<CfgSmall>(d, p, s); }
+// B2BA_WIN_VARIANT (developer knob, read once): 0 = 256-thread CTAs, 1 = 128-thread CTAs
+static int small_variant() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = std::getenv("B2BA_WIN_VARIANT");
+    v = e ? std::atoi(e) : 0;
+  }
+  return v;
+}
+
+int launch_window_small(const WinData& d, const Params& p, cudaStream_t s) {
+  return small_variant() == 1 ? launch<CfgSmall4>(d, p, s) : launch<CfgSmall>(d, p, s);
+}
 int launch_window_big(const WinData& d, const Params& p, cudaStream_t s) { return launch<CfgBig>(d, p, s); }
 
-int window_kernel_attrs(int which, int* regs, int* smem_bytes, int* ctas_per_sm) {
+template <class Cfg>
+static int attrs_of(int* regs, int* smem_bytes, int* ctas_per_sm) {
   cudaFuncAttributes a;
-  cudaError_t e;
   int nb = 0;
-  if (which == 0) {
-    e = cudaFuncGetAttributes(&a, window_lm_kernel<CfgSmall>);
-    if (e == cudaSuccess) {
-      cudaFuncSetAttribute(window_lm_kernel<CfgSmall>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)CfgSmall::SMEM);
-      e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, window_lm_kernel<CfgSmall>, CfgSmall::NTHREADS, CfgSmall::SMEM);
-    }
-    *smem_bytes = (int)CfgSmall::SMEM;
-  } else {
-    e = cudaFuncGetAttributes(&a, window_lm_kernel<CfgBig>);
-    if (e == cudaSuccess) {
-      cudaFuncSetAttribute(window_lm_kernel<CfgBig>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)CfgBig::SMEM);
-      e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, window_lm_kernel<CfgBig>, CfgBig::NTHREADS, CfgBig::SMEM);
-    }
-    *smem_bytes = (int)CfgBig::SMEM;
+  cudaError_t e = cudaFuncGetAttributes(&a, window_lm_kernel<Cfg>);
+  if (e == cudaSuccess) {
+    cudaFuncSetAttribute(window_lm_kernel<Cfg>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM);
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, window_lm_kernel<Cfg>, Cfg::NTHREADS, Cfg::SMEM);
   }
   if (e != cudaSuccess) return (int)e;
-  *regs = a.numRegs;
-  *ctas_per_sm = nb;
+  *regs = a.numRegs; *smem_bytes = (int)Cfg::SMEM; *ctas_per_sm = nb;
   return 0;
+}
+
+int window_kernel_attrs(int which, int* regs, int* smem_bytes, int* ctas_per_sm) {
+  if (which == 0) return small_variant() == 1 ? attrs_of<CfgSmall4>(regs, smem_bytes, ctas_per_sm)
+                                              : attrs_of<CfgSmall>(regs, smem_bytes, ctas_per_sm);
+  return attrs_of<CfgBig>(regs, smem_bytes, ctas_per_sm);
 }
 
 }  // namespace b2

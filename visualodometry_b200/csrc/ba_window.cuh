@@ -45,31 +45,47 @@ struct WinDbg {
   __host__ __device__ size_t total() const { return off_scal() + 4; }
 };
 
-template <int NT_, int NWARPS_, int G_, int PB_>
+// Upper-triangle tile enumeration (row-major over NT tile rows), usable in constant expressions.
+template <int NT>
+struct Tri {
+  static constexpr int T = NT * (NT + 1) / 2;
+  static constexpr __host__ __device__ int mi(int t) { int m = 0, len = NT; while (t >= len) { t -= len; --len; ++m; } return m; }
+  static constexpr __host__ __device__ int ni(int t) { int m = 0, len = NT; while (t >= len) { t -= len; --len; ++m; } return m + t; }
+};
+
+// NT tile rows (8 each) of the reduced system incl. the y row; NWARPS = G tile groups x KS k-splits;
+// PB landmarks per batch; MAXCAM cameras per window held in shared memory; MINB CTAs per SM.
+template <int NT_, int NWARPS_, int G_, int PB_, int MAXCAM_, int MINB_>
 struct WinCfg {
-  static constexpr int NT = NT_, NWARPS = NWARPS_, G = G_, PB = PB_;
+  static constexpr int NT = NT_, NWARPS = NWARPS_, G = G_, PB = PB_, MAXCAM = MAXCAM_, MINB = MINB_;
   static constexpr int NTHREADS = NWARPS * 32;
   static constexpr int KS = NWARPS / G;            // k-splits of the SYRK
   static constexpr int T = NT * (NT + 1) / 2;      // upper 8x8 tiles
   static constexpr int TPW = (T + G - 1) / G;      // tiles per warp
   static constexpr int TPP = NTHREADS / PB;        // lanes per point
-  static constexpr int NR = 8 * NT;                // rows of the Z tile (6*nfree + 1 padded)
-  static constexpr int LD = 3 * PB + 4;            // == 4 mod 16 -> conflict-free fragment loads
-  static constexpr int KSTEPS = 3 * PB / 4;        // k-steps (of 4) per batch
+  static constexpr int NR = 8 * NT;                // rows of Z (6*nfree + 1, padded)
+  static constexpr int NCOL = 3 * PB;              // columns of Z per batch (3 per landmark)
+  static constexpr int LDT = NR + 4;               // Z is stored TRANSPOSED: Zt[col * LDT + row];
+                                                   // LDT == 4 or 12 mod 16 -> conflict-free DMMA fragment loads
+  static constexpr int KSTEPS = NCOL / 4;          // k-steps (of 4 columns) per batch
   static constexpr int LDS = NR + 1;               // leading dim of S (odd)
-  static constexpr int ZS = (NR * LD > NR * LDS) ? NR * LD : NR * LDS;
+  static constexpr int ZS = (NCOL * LDT > NR * LDS) ? NCOL * LDT : NR * LDS;
   static constexpr int NRED = NWARPS * 32;
-  // doubles: pose_cur, pose_tri, B(21), gc, Dc, dvec, gred, red, scal, Z/S
-  static constexpr int SM_DOUBLES = kMaxCam * (12 + 12 + 21 + 6 + 6) + 128 + 128 + NRED + 16 + ZS;
-  static constexpr size_t SMEM = (size_t)SM_DOUBLES * 8 + (2 * kMaxCam + 8) * 4;
+  // doubles: pose_cur, pose_tri, B(21), gc, Dc, dvec, gred, red, scal, Zt/S
+  static constexpr int SM_DOUBLES = MAXCAM * (12 + 12 + 21 + 6 + 6) + 128 + 128 + NRED + 16 + ZS;
+  static constexpr size_t SMEM = (size_t)SM_DOUBLES * 8 + (2 * MAXCAM + 8) * 4;
   static_assert(KS * G == NWARPS, "warps = groups x k-splits");
   static_assert(KSTEPS % KS == 0, "k-steps split evenly");
   static_assert(TPP >= 1 && TPP <= 32 && (TPP & (TPP - 1)) == 0, "lanes per point: power of two");
-  static_assert((3 * PB) % 16 == 0, "LD == 4 mod 16");
+  static_assert(NCOL % 4 == 0 && (MAXCAM % 2) == 0, "alignment");
+  static_assert(6 * (MAXCAM - 1) + 1 <= NR || true, "n+1 <= NR is checked at path selection");
 };
 
+constexpr int kSmallMaxCam = 12, kSmallMaxFree = 9;    // window_small: n+1 <= 56
+constexpr int kBigMaxFree = 21;                        // window_big:   n+1 <= 128
+
 // launchers (ba_window.cu). Return cudaError_t as int.
-int launch_window_small(const WinData& d, const Params& p, cudaStream_t s);   // n+1 <= 56 (<= 9 free cams)
+int launch_window_small(const WinData& d, const Params& p, cudaStream_t s);   // <= 12 cameras, <= 9 free (n+1 <= 56)
 int launch_window_big(const WinData& d, const Params& p, cudaStream_t s);     // n+1 <= 128 (<= 21 free cams)
 int window_kernel_attrs(int which, int* regs, int* smem_bytes, int* ctas_per_sm);
 
