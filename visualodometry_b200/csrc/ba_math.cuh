@@ -138,13 +138,25 @@ struct Geo {       // one observation: camera-frame point, residual, weight, dr/
   bool valid;
 };
 
+// 1/z without the slow-path branch of the IEEE division: float reciprocal seed (2^-23) + two Newton
+// steps in fp64 (-> ~2^-52 relative; not correctly rounded, 1-2 ulp).  z is a depth >= z_min here.
+__device__ __forceinline__ double rcp_depth(double z) {
+  double y = (double)__frcp_rn((float)z);
+  y = y * fma(-z, y, 2.0);
+  y = y * fma(-z, y, 2.0);
+  return y;
+}
+
+// LOSS is compile-time in the window kernel (0 trivial, 1 Huber): the trivial path is branch-free, so
+// two observations handled by one lane interleave in the instruction stream.
+template <int LOSS>
 __device__ __forceinline__ void geo_project(const Params& P, const Pose12& q, double X0, double X1, double X2,
                                             float u, float v, Geo& o) {
   o.x = fma(q.r[0], X0, fma(q.r[1], X1, fma(q.r[2], X2, q.r[9])));
   o.y = fma(q.r[3], X0, fma(q.r[4], X1, fma(q.r[5], X2, q.r[10])));
   o.z = fma(q.r[6], X0, fma(q.r[7], X1, fma(q.r[8], X2, q.r[11])));
   o.valid = o.z >= P.z_min;
-  const double iz = o.valid ? 1.0 / o.z : 0.0;
+  const double iz = o.valid ? rcp_depth(o.z) : 0.0;
   o.a0 = P.fx * iz;
   o.b1 = P.fy * iz;
   o.r0 = fma(o.a0, o.x, P.cx - (double)u);
@@ -154,12 +166,14 @@ __device__ __forceinline__ void geo_project(const Params& P, const Pose12& q, do
   const double s = fma(o.r0, o.r0, o.r1 * o.r1);
   o.w = 1.0;
   o.rho = s;
-  if (P.loss == 1 && s > P.huber_a * P.huber_a) {
-    const double rs = sqrt(s);
-    o.rho = 2.0 * P.huber_a * rs - P.huber_a * P.huber_a;
-    o.w = P.huber_a / rs;
+  if (LOSS == 1) {
+    if (s > P.huber_a * P.huber_a) {
+      const double rs = sqrt(s);
+      o.rho = 2.0 * P.huber_a * rs - P.huber_a * P.huber_a;
+      o.w = P.huber_a / rs;
+    }
   }
-  if (!o.valid) { o.r0 = 0; o.r1 = 0; o.w = 0; o.rho = 0; }
+  if (!o.valid) { o.r0 = 0; o.r1 = 0; o.rho = 0; o.w = 0; }
 }
 
 // J_p rows: jp[0..2] = a0 R0 + a2 R2, jp[3..5] = b1 R1 + b2 R2

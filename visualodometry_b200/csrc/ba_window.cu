@@ -73,7 +73,7 @@ __device__ __forceinline__ void syrk_dispatch(int grp, const double* __restrict_
   }
 }
 
-template <class Cfg>
+template <class Cfg, int LOSS>
 __global__ void __launch_bounds__(Cfg::NTHREADS, Cfg::MINB)
 window_lm_kernel(const WinData d, const Params P) {
   constexpr int NTHREADS = Cfg::NTHREADS, NWARPS = Cfg::NWARPS, G = Cfg::G, KS = Cfg::KS, NT = Cfg::NT;
@@ -141,7 +141,7 @@ window_lm_kernel(const WinData d, const Params P) {
           const ObsRec rec = d.cm[a];
           const double* Xp = X + 3 * rec.idx;
           Geo o;
-          geo_project(P, q, Xp[0], Xp[1], Xp[2], rec.u, rec.v, o);
+          geo_project<LOSS>(P, q, Xp[0], Xp[1], Xp[2], rec.u, rec.v, o);
           if (!o.valid) { acc[28] += 1.0; continue; }
           acc[27] = fma(0.5, o.rho, acc[27]);
           if (isfree) {
@@ -222,24 +222,40 @@ window_lm_kernel(const WinData d, const Params P) {
 #pragma unroll 4
         for (int i = sub; i < 3 * LDT / 2; i += TPP) zc2[i] = zz;
       }
-      // loop 1: C_p, g_p
+      // loop 1: C_p, g_p.  A lane takes observations a0+sub, a0+sub+TPP, ...; they are handled two at a
+      // time in one basic block (independent dependency chains interleave); `rounds` is warp-uniform.
+      const int rounds = (int)((__reduce_max_sync(0xffffffffu, (unsigned)(a1 - a0)) + TPP - 1) / TPP);
+      const ObsRec zrec{0.f, 0.f, 0, 0};
       double C[6] = {0, 0, 0, 0, 0, 0}, g[3] = {0, 0, 0};
-      for (int a = a0 + sub; a < a1; a += TPP) {
-        const ObsRec rec = d.pm[a];
+      auto accum = [&](const ObsRec& rec, bool lv) {
         Pose12 q;
         load_pose(pose_cur + 12 * rec.idx, q);
         Geo o;
-        geo_project(P, q, X0, X1, X2, rec.u, rec.v, o);
+        geo_project<LOSS>(P, q, X0, X1, X2, rec.u, rec.v, o);
+        const double w = lv ? o.w : 0.0;
         double jp[6];
         geo_jp(q, o, jp);
-        const double u0 = o.w * jp[0], u1 = o.w * jp[1], u2 = o.w * jp[2];
-        const double v0 = o.w * jp[3], v1 = o.w * jp[4], v2 = o.w * jp[5];
+        const double u0 = w * jp[0], u1 = w * jp[1], u2 = w * jp[2];
+        const double v0 = w * jp[3], v1 = w * jp[4], v2 = w * jp[5];
         C[0] = fma(u0, jp[0], fma(v0, jp[3], C[0])); C[1] = fma(u0, jp[1], fma(v0, jp[4], C[1]));
         C[2] = fma(u0, jp[2], fma(v0, jp[5], C[2])); C[3] = fma(u1, jp[1], fma(v1, jp[4], C[3]));
         C[4] = fma(u1, jp[2], fma(v1, jp[5], C[4])); C[5] = fma(u2, jp[2], fma(v2, jp[5], C[5]));
         g[0] = fma(u0, o.r0, fma(v0, o.r1, g[0]));
         g[1] = fma(u1, o.r0, fma(v1, o.r1, g[1]));
         g[2] = fma(u2, o.r0, fma(v2, o.r1, g[2]));
+      };
+      for (int r = 0; r < rounds; r += 2) {
+        const int aA = a0 + sub + r * TPP, aB = aA + TPP;
+        const bool lvA = aA < a1, lvB = aB < a1;
+        ObsRec recA = zrec, recB = zrec;
+        if (lvA) recA = d.pm[aA];
+        if (r + 1 < rounds) {
+          if (lvB) recB = d.pm[aB];
+          accum(recA, lvA);
+          accum(recB, lvB);
+        } else {
+          accum(recA, lvA);
+        }
       }
 #pragma unroll
       for (int m = TPP >> 1; m > 0; m >>= 1) {
@@ -275,31 +291,44 @@ window_lm_kernel(const WinData d, const Params P) {
         }
       }
       // loop 2: Z rows of camera k = E_k F = w J_c^T (J_p F), 6 x 3, into the column block
-      for (int a = a0 + sub; a < a1; a += TPP) {
-        const ObsRec rec = d.pm[a];
+      auto emit = [&](const ObsRec& rec, bool lv) {
         const int f = fidx[rec.idx];
-        if (f < 0) continue;
+        const bool st = lv && f >= 0;
         Pose12 q;
         load_pose(pose_cur + 12 * rec.idx, q);
         Geo o;
-        geo_project(P, q, X0, X1, X2, rec.u, rec.v, o);
+        geo_project<LOSS>(P, q, X0, X1, X2, rec.u, rec.v, o);
         double jp[6];
         geo_jp(q, o, jp);
         // G = w J_p F  (2 x 3; F upper triangular)
-        const double w0 = o.w * jp[0], w3 = o.w * jp[3];
-        const double G0[3] = {w0 * F[0], fma(w0, F[1], o.w * jp[1] * F[3]),
-                              fma(w0, F[2], fma(o.w * jp[1], F[4], o.w * jp[2] * F[5]))};
-        const double G1[3] = {w3 * F[0], fma(w3, F[1], o.w * jp[4] * F[3]),
-                              fma(w3, F[2], fma(o.w * jp[4], F[4], o.w * jp[5] * F[5]))};
+        const double w0 = o.w * jp[0], w1 = o.w * jp[1], w2 = o.w * jp[2];
+        const double w3 = o.w * jp[3], w4 = o.w * jp[4], w5 = o.w * jp[5];
+        const double G0[3] = {w0 * F[0], fma(w0, F[1], w1 * F[3]), fma(w0, F[2], fma(w1, F[4], w2 * F[5]))};
+        const double G1[3] = {w3 * F[0], fma(w3, F[1], w4 * F[3]), fma(w3, F[2], fma(w4, F[4], w5 * F[5]))};
         double j0[6], j1[6];
         geo_jc(o, j0, j1);
-        double* zr = zcol + 6 * f;
+        if (st) {
+          double* zr = zcol + 6 * f;
 #pragma unroll
-        for (int j = 0; j < 3; ++j) {
-          double2* dst = reinterpret_cast<double2*>(zr + j * LDT);
-          dst[0] = make_double2(fma(j0[0], G0[j], j1[0] * G1[j]), fma(j0[1], G0[j], j1[1] * G1[j]));
-          dst[1] = make_double2(fma(j0[2], G0[j], j1[2] * G1[j]), j0[3] * G0[j]);
-          dst[2] = make_double2(j1[4] * G1[j], fma(j0[5], G0[j], j1[5] * G1[j]));
+          for (int j = 0; j < 3; ++j) {
+            double2* dst = reinterpret_cast<double2*>(zr + j * LDT);
+            dst[0] = make_double2(fma(j0[0], G0[j], j1[0] * G1[j]), fma(j0[1], G0[j], j1[1] * G1[j]));
+            dst[1] = make_double2(fma(j0[2], G0[j], j1[2] * G1[j]), j0[3] * G0[j]);
+            dst[2] = make_double2(j1[4] * G1[j], fma(j0[5], G0[j], j1[5] * G1[j]));
+          }
+        }
+      };
+      for (int r = 0; r < rounds; r += 2) {
+        const int aA = a0 + sub + r * TPP, aB = aA + TPP;
+        const bool lvA = aA < a1, lvB = aB < a1;
+        ObsRec recA = zrec, recB = zrec;
+        if (lvA) recA = d.pm[aA];
+        if (r + 1 < rounds) {
+          if (lvB) recB = d.pm[aB];
+          emit(recA, lvA);
+          emit(recB, lvB);
+        } else {
+          emit(recA, lvA);
         }
       }
       __syncthreads();
@@ -366,20 +395,83 @@ window_lm_kernel(const WinData d, const Params P) {
     }
 
     // ------------------------------------------------------------------ Cholesky + solve (a5)
-    for (int j = 0; j < n; ++j) {
-      if (tid == 0) {
-        double dj = S[j * LDS + j];
-        if (!(dj > 0.0) || !isfinite(dj)) { iflag[0] = 1; dj = 1.0; }
-        S[j * LDS + j] = sqrt(dj);
+    // right-looking Cholesky in 6-column (camera) blocks, lower triangle of S, 2 barriers per block
+    for (int j0 = 0; j0 < n; j0 += 6) {
+      // every thread factors the 6x6 diagonal block redundantly in registers: L (packed lower, row-major)
+      double L[6][6], inv[6];
+      bool bad = false;
+#pragma unroll
+      for (int r = 0; r < 6; ++r)
+#pragma unroll
+        for (int c = 0; c < 6; ++c)
+          if (c <= r) L[r][c] = S[(j0 + r) * LDS + j0 + c];
+#pragma unroll
+      for (int c = 0; c < 6; ++c) {
+        double dj = L[c][c];
+#pragma unroll
+        for (int k = 0; k < 6; ++k)
+          if (k < c) dj = fma(-L[c][k], L[c][k], dj);
+        if (!(dj > 0.0) || !isfinite(dj)) { bad = true; dj = 1.0; }
+        const double lcc = sqrt(dj);
+        inv[c] = 1.0 / lcc;
+        L[c][c] = lcc;
+#pragma unroll
+        for (int r = 0; r < 6; ++r) {
+          if (r > c) {
+            double v = L[r][c];
+#pragma unroll
+            for (int k = 0; k < 6; ++k)
+              if (k < c) v = fma(-L[r][k], L[c][k], v);
+            L[r][c] = v * inv[c];
+          }
+        }
+      }
+      if (bad && tid == 0) iflag[0] = 1;
+      const int m = n - j0 - 6;
+      // panel: row i of L21 = A21 row * L11^-T, one thread per row
+      for (int t = tid; t < m; t += NTHREADS) {
+        double* row = S + (j0 + 6 + t) * LDS + j0;
+        double x[6];
+#pragma unroll
+        for (int c = 0; c < 6; ++c) {
+          double v = row[c];
+#pragma unroll
+          for (int k = 0; k < 6; ++k)
+            if (k < c) v = fma(-x[k], L[c][k], v);
+          x[c] = v * inv[c];
+        }
+#pragma unroll
+        for (int c = 0; c < 6; ++c) row[c] = x[c];
       }
       __syncthreads();
-      const double inv = 1.0 / S[j * LDS + j];
-      for (int i = j + 1 + tid; i < n; i += NTHREADS) S[i * LDS + j] *= inv;
-      __syncthreads();
-      const int m = n - j - 1;
-      for (int idx = tid; idx < m * m; idx += NTHREADS) {
-        const int ii = idx / m, kk = idx - ii * m;
-        if (kk <= ii) S[(j + 1 + ii) * LDS + j + 1 + kk] -= S[(j + 1 + ii) * LDS + j] * S[(j + 1 + kk) * LDS + j];
+      if (tid == 0) {
+#pragma unroll
+        for (int r = 0; r < 6; ++r)
+#pragma unroll
+          for (int c = 0; c < 6; ++c)
+            if (c <= r) S[(j0 + r) * LDS + j0 + c] = L[r][c];
+      }
+      // trailing update A22 -= L21 L21^T (lower triangle), work items = (row, 6-column block) pairs
+      const int npairs = (m / 6) * (m + 6) / 2;      // sum over column blocks cb of (m - cb)
+      for (int id = tid; id < npairs; id += NTHREADS) {
+        int cb = 0, rem = id, len = m;
+        while (rem >= len) { rem -= len; len -= 6; cb += 6; }
+        const int ii = cb + rem;
+        double* ri = S + (j0 + 6 + ii) * LDS + j0;
+        double li[6];
+#pragma unroll
+        for (int c = 0; c < 6; ++c) li[c] = ri[c];
+#pragma unroll
+        for (int cc = 0; cc < 6; ++cc) {
+          const int kc = cb + cc;
+          if (kc <= ii) {
+            const double* lk = S + (j0 + 6 + kc) * LDS + j0;
+            double v = ri[6 + kc];
+#pragma unroll
+            for (int c = 0; c < 6; ++c) v = fma(-li[c], lk[c], v);
+            ri[6 + kc] = v;
+          }
+        }
       }
       __syncthreads();
     }
@@ -443,24 +535,39 @@ window_lm_kernel(const WinData d, const Params P) {
           a0 = d.pt_ptr[p0 + p]; a1 = d.pt_ptr[p0 + p + 1];
           X0 = X[3 * p]; X1 = X[3 * p + 1]; X2 = X[3 * p + 2];
         }
+        const int rounds = (int)((__reduce_max_sync(0xffffffffu, (unsigned)(a1 - a0)) + TPP - 1) / TPP);
+        const ObsRec zrec{0.f, 0.f, 0, 0};
         double v[3] = {0, 0, 0};
-        for (int a = a0 + sub; a < a1; a += TPP) {
-          const ObsRec rec = d.pm[a];
+        auto etd = [&](const ObsRec& rec, bool lv) {
           const int f = fidx[rec.idx];
-          if (f < 0) continue;
+          const bool use = lv && f >= 0;
           Pose12 q;
           load_pose(pose_cur + 12 * rec.idx, q);
           Geo o;
-          geo_project(P, q, X0, X1, X2, rec.u, rec.v, o);
+          geo_project<LOSS>(P, q, X0, X1, X2, rec.u, rec.v, o);
           double jp[6], j0[6], j1[6];
           geo_jp(q, o, jp);
           geo_jc(o, j0, j1);
           // E^T dc = w J_p^T (J_c dc)
-          const double* dc = dvec + 6 * f;
-          const double t0 = o.w * fma(j0[0], dc[0], fma(j0[1], dc[1], fma(j0[2], dc[2], fma(j0[3], dc[3], j0[5] * dc[5]))));
-          const double t1 = o.w * fma(j1[0], dc[0], fma(j1[1], dc[1], fma(j1[2], dc[2], fma(j1[4], dc[4], j1[5] * dc[5]))));
+          const double* dc = dvec + 6 * (f < 0 ? 0 : f);
+          const double w = use ? o.w : 0.0;
+          const double t0 = w * fma(j0[0], dc[0], fma(j0[1], dc[1], fma(j0[2], dc[2], fma(j0[3], dc[3], j0[5] * dc[5]))));
+          const double t1 = w * fma(j1[0], dc[0], fma(j1[1], dc[1], fma(j1[2], dc[2], fma(j1[4], dc[4], j1[5] * dc[5]))));
 #pragma unroll
           for (int j = 0; j < 3; ++j) v[j] = fma(jp[j], t0, fma(jp[3 + j], t1, v[j]));
+        };
+        for (int r = 0; r < rounds; r += 2) {
+          const int aA = a0 + sub + r * TPP, aB = aA + TPP;
+          const bool lvA = aA < a1, lvB = aB < a1;
+          ObsRec recA = zrec, recB = zrec;
+          if (lvA) recA = d.pm[aA];
+          if (r + 1 < rounds) {
+            if (lvB) recB = d.pm[aB];
+            etd(recA, lvA);
+            etd(recB, lvB);
+          } else {
+            etd(recA, lvA);
+          }
         }
 #pragma unroll
         for (int m = TPP >> 1; m > 0; m >>= 1) {
@@ -487,13 +594,26 @@ window_lm_kernel(const WinData d, const Params P) {
             if (dbg) { double* dp = d.dbg + dbgL.off_dp() + (size_t)p * 3; dp[0] = d0; dp[1] = d1; dp[2] = d2; }
           }
         }
-        for (int a = a0 + sub; a < a1; a += TPP) {
-          const ObsRec rec = d.pm[a];
+        auto trial = [&](const ObsRec& rec, bool lv) {
           Pose12 q;
           load_pose(pose_tri + 12 * rec.idx, q);
           Geo o;
-          geo_project(P, q, Xn0, Xn1, Xn2, rec.u, rec.v, o);
-          if (o.valid) s_tc = fma(0.5, o.rho, s_tc); else s_inv += 1.0;
+          geo_project<LOSS>(P, q, Xn0, Xn1, Xn2, rec.u, rec.v, o);
+          s_tc = fma(0.5, lv ? o.rho : 0.0, s_tc);
+          s_inv += (lv && !o.valid) ? 1.0 : 0.0;
+        };
+        for (int r = 0; r < rounds; r += 2) {
+          const int aA = a0 + sub + r * TPP, aB = aA + TPP;
+          const bool lvA = aA < a1, lvB = aB < a1;
+          ObsRec recA = zrec, recB = zrec;
+          if (lvA) recA = d.pm[aA];
+          if (r + 1 < rounds) {
+            if (lvB) recB = d.pm[aB];
+            trial(recA, lvA);
+            trial(recB, lvB);
+          } else {
+            trial(recA, lvA);
+          }
         }
       }
     }
@@ -592,17 +712,21 @@ using CfgSmall = WinCfg<7, 8, 4, 64, kSmallMaxCam, 2>;    // 256 threads, 2 CTAs
 using CfgSmall4 = WinCfg<7, 4, 4, 32, kSmallMaxCam, 4>;   // 128 threads, 4 CTAs / SM
 using CfgBig = WinCfg<16, 16, 16, 32, kMaxCam, 1>;        // n+1 <= 128: up to 21 free cameras (C3)
 
-template <class Cfg>
-static int launch(const WinData& d, const Params& p, cudaStream_t s) {
+template <class Cfg, int LOSS>
+static int launch_l(const WinData& d, const Params& p, cudaStream_t s) {
   static bool configured = false;
   if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(window_lm_kernel<Cfg>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    cudaError_t e = cudaFuncSetAttribute(window_lm_kernel<Cfg, LOSS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          (int)Cfg::SMEM);
     if (e != cudaSuccess) return (int)e;
     configured = true;
   }
-  window_lm_kernel<Cfg><<<d.nb, Cfg::NTHREADS, Cfg::SMEM, s>>>(d, p);
+  window_lm_kernel<Cfg, LOSS><<<d.nb, Cfg::NTHREADS, Cfg::SMEM, s>>>(d, p);
   return (int)cudaGetLastError();
+}
+template <class Cfg>
+static int launch(const WinData& d, const Params& p, cudaStream_t s) {
+  return p.loss == B2BA_LOSS_HUBER ? launch_l<Cfg, 1>(d, p, s) : launch_l<Cfg, 0>(d, p, s);
 }
 
 // B2BA_WIN_VARIANT (developer knob, read once): 0 = 256-thread CTAs, 1 = 128-thread CTAs
@@ -624,10 +748,10 @@ template <class Cfg>
 static int attrs_of(int* regs, int* smem_bytes, int* ctas_per_sm) {
   cudaFuncAttributes a;
   int nb = 0;
-  cudaError_t e = cudaFuncGetAttributes(&a, window_lm_kernel<Cfg>);
+  cudaError_t e = cudaFuncGetAttributes(&a, window_lm_kernel<Cfg, 0>);
   if (e == cudaSuccess) {
-    cudaFuncSetAttribute(window_lm_kernel<Cfg>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM);
-    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, window_lm_kernel<Cfg>, Cfg::NTHREADS, Cfg::SMEM);
+    cudaFuncSetAttribute(window_lm_kernel<Cfg, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM);
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, window_lm_kernel<Cfg, 0>, Cfg::NTHREADS, Cfg::SMEM);
   }
   if (e != cudaSuccess) return (int)e;
   *regs = a.numRegs; *smem_bytes = (int)Cfg::SMEM; *ctas_per_sm = nb;
