@@ -138,14 +138,18 @@ struct Geo {       // one observation: camera-frame point, residual, weight, dr/
   bool valid;
 };
 
-// 1/z without the slow-path branch of the IEEE division: float reciprocal seed (2^-23) + two Newton
-// steps in fp64 (-> ~2^-52 relative; not correctly rounded, 1-2 ulp).  z is a depth >= z_min here.
+// 1/z without the slow-path branch of the IEEE division: rcp.approx.ftz.f64 seed (MUFU.RCP64H, ~2^-20)
+// + two Newton steps in fp64 (-> below 2^-52 relative; not correctly rounded, 1-2 ulp).  z >= z_min here.
 __device__ __forceinline__ double rcp_depth(double z) {
-  double y = (double)__frcp_rn((float)z);
+  double y;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(z));
   y = y * fma(-z, y, 2.0);
   y = y * fma(-z, y, 2.0);
   return y;
 }
+
+// fire-and-forget L1 prefetch of the 128-byte line holding p (no register cost)
+__device__ __forceinline__ void prefetch_l1(const void* p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
 
 // LOSS is compile-time in the window kernel (0 trivial, 1 Huber): the trivial path is branch-free, so
 // two observations handled by one lane interleave in the instruction stream.

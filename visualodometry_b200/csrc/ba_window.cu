@@ -137,8 +137,16 @@ window_lm_kernel(const WinData d, const Params P) {
         double acc[29];
 #pragma unroll
         for (int k = 0; k < 29; ++k) acc[k] = 0.0;
+        // records two iterations ahead in registers; the landmark of the next iteration is L1-prefetched
+        const ObsRec zrec{0.f, 0.f, 0, 0};
+        ObsRec rec_n = zrec, rec_nn = zrec;
+        if (b + tid < e) rec_n = d.cm[b + tid];
+        if (b + tid + NTHREADS < e) rec_nn = d.cm[b + tid + NTHREADS];
         for (int a = b + tid; a < e; a += NTHREADS) {
-          const ObsRec rec = d.cm[a];
+          const ObsRec rec = rec_n;
+          rec_n = rec_nn;
+          if (a + 2 * NTHREADS < e) rec_nn = d.cm[a + 2 * NTHREADS];
+          if (a + NTHREADS < e) { prefetch_l1(X + 3 * rec_n.idx); prefetch_l1(X + 3 * rec_n.idx + 2); }
           const double* Xp = X + 3 * rec.idx;
           Geo o;
           geo_project<LOSS>(P, q, Xp[0], Xp[1], Xp[2], rec.u, rec.v, o);
@@ -208,6 +216,9 @@ window_lm_kernel(const WinData d, const Params P) {
       a0n = d.pt_ptr[p0 + slot]; a1n = d.pt_ptr[p0 + slot + 1];
       Xn0 = X[3 * slot]; Xn1 = X[3 * slot + 1]; Xn2 = X[3 * slot + 2];
     }
+    // record range (contiguous in the point-major stream) of the batch AFTER the current one: it is
+    // L1-prefetched while the current batch's DMMA runs; the range itself is loaded one batch earlier
+    int pf_s = d.pt_ptr[p0 + min(PB, npw)], pf_e = d.pt_ptr[p0 + min(2 * PB, npw)];
 
     for (int b0 = 0; b0 < npw; b0 += PB) {
       const int p = b0 + slot;
@@ -332,7 +343,7 @@ window_lm_kernel(const WinData d, const Params P) {
         }
       }
       __syncthreads();
-      // prefetch the next batch's landmark while the tensor pipe works
+      // prefetch the next batch's landmark (registers) and records (L1) while the tensor pipe works
       {
         const int pn = p + PB;
         a0n = 0; a1n = 0;
@@ -340,6 +351,9 @@ window_lm_kernel(const WinData d, const Params P) {
           a0n = d.pt_ptr[p0 + pn]; a1n = d.pt_ptr[p0 + pn + 1];
           Xn0 = X[3 * pn]; Xn1 = X[3 * pn + 1]; Xn2 = X[3 * pn + 2];
         }
+        for (int a = (pf_s & ~7) + tid * 8; a < pf_e; a += NTHREADS * 8) prefetch_l1(d.pm + a);
+        pf_s = d.pt_ptr[p0 + min(b0 + 2 * PB, npw)];
+        pf_e = d.pt_ptr[p0 + min(b0 + 3 * PB, npw)];
       }
       // Z Z^T accumulate: DMMA over this batch's 3*PB columns (this warp's k-slice)
       syrk_dispatch<Cfg>(grp, zf, ksp * (Cfg::KSTEPS / KS), acc);
@@ -529,6 +543,17 @@ window_lm_kernel(const WinData d, const Params P) {
     if (step_ok) {
       for (int p = slot; p < np_round; p += PB) {
         const bool act = p < npw;
+        {   // L1-prefetch the next batch: landmark offsets, landmarks, scratch rows, records
+          const int bn = p - slot + PB, bnn = min(bn + PB, npw);
+          if (bn < npw) {
+            const int* pp = d.pt_ptr + p0 + bn;
+            if (tid * 32 <= bnn - bn) prefetch_l1(pp + tid * 32);
+            if (tid * 16 < 3 * (bnn - bn)) prefetch_l1(X + 3 * bn + tid * 16);
+            if (tid * 16 < kPtScratch * (bnn - bn)) prefetch_l1(scratch + (size_t)bn * kPtScratch + tid * 16);
+            const int rs = d.pt_ptr[p0 + bn], re = d.pt_ptr[p0 + bnn];
+            for (int a = (rs & ~7) + tid * 8; a < re; a += NTHREADS * 8) prefetch_l1(d.pm + a);
+          }
+        }
         int a0 = 0, a1 = 0;
         double X0 = 0, X1 = 0, X2 = 0;
         if (act) {
@@ -729,12 +754,12 @@ static int launch(const WinData& d, const Params& p, cudaStream_t s) {
   return p.loss == B2BA_LOSS_HUBER ? launch_l<Cfg, 1>(d, p, s) : launch_l<Cfg, 0>(d, p, s);
 }
 
-// B2BA_WIN_VARIANT (developer knob, read once): 0 = 256-thread CTAs, 1 = 128-thread CTAs
+// B2BA_WIN_VARIANT (developer knob, read once): 1 = 128-thread CTAs, 4 per SM (default), 0 = 256-thread CTAs, 2 per SM
 static int small_variant() {
   static int v = -1;
   if (v < 0) {
     const char* e = std::getenv("B2BA_WIN_VARIANT");
-    v = e ? std::atoi(e) : 0;
+    v = e ? std::atoi(e) : 1;
   }
   return v;
 }
