@@ -1,0 +1,98 @@
+"""VO keyframe-window adapter (visualodometry_b200/adapter.py): packing from / writing back to the state the
+reference holds (keyframe dicts vo.py:57,286; map_points vo.py:17; T_wc vo.py:19), id back-fill, error
+behaviour; and the adapter hooked onto the frame loop with the CPU oracle as the solver."""
+import numpy as np
+import pytest
+
+cv2 = pytest.importorskip("cv2")
+
+from visualodometry_b200 import BAConfig, adapter, vo_loop, vo_synth  # noqa: E402
+from visualodometry_b200.ba import BAResult, BASummary  # noqa: E402
+
+
+class FakeVO:
+    def __init__(self):
+        self.K = vo_synth.KITTI_K
+        self.map_points = {}
+        self.T_wc = np.eye(4)
+        self.last_pos = np.zeros(3)
+
+
+def kf(uv, ids, x):
+    T = np.eye(4); T[0, 3] = x
+    return {"feats": {"keypoints": np.asarray(uv, np.float32)[None]}, "ids": np.asarray(ids, dtype=int), "T_wc": T}
+
+
+def test_pack_window_layout_and_filters():
+    vo = FakeVO()
+    vo.map_points = {5: np.array([0.0, 0, 10]), 7: np.array([1.0, 0, 12]), 9: np.array([2.0, 0, 9])}
+    w = [kf([[1, 1], [2, 2], [3, 3], [4, 4]], [5, 7, -1, 5], 0.0),       # id 5 twice: first keypoint kept
+         kf([[5, 5], [6, 6], [7, 7]], [7, 5, 33], 1.0),                  # id 33 not in the map
+         kf([[8, 8], [9, 9]], [9, 5], 2.0)]                              # id 9 seen once -> dropped
+    p = adapter.pack_window(w, vo.map_points, n_fixed=1)
+    assert p.pids.tolist() == [5, 7] and p.points.shape == (2, 3) and p.points.dtype == np.float64
+    assert p.obs_cam.dtype == np.int32 and p.obs_pt.dtype == np.int32 and p.obs_uv.dtype == np.float32
+    got = sorted(zip(p.obs_cam.tolist(), p.obs_pt.tolist(), p.obs_uv[:, 0].tolist()))
+    assert got == [(0, 0, 1.0), (0, 1, 2.0), (1, 0, 6.0), (1, 1, 5.0), (2, 0, 9.0)]
+    assert p.fixed_cam.tolist() == [True, False, False]
+    assert np.allclose(p.T_cw[2], np.linalg.inv(w[2]["T_wc"]))
+    assert len(set(zip(p.obs_cam.tolist(), p.obs_pt.tolist()))) == len(p.obs_cam)     # no duplicate (cam, point)
+    assert adapter.pack_window(w[:1], vo.map_points) is None                            # one keyframe: nothing to do
+    assert adapter.pack_window(w, {}) is None
+
+
+def test_backfill_and_write_back_and_failure_skip():
+    vo = FakeVO()
+    vo.map_points = {0: np.array([0.0, 0, 10]), 1: np.array([1.0, 0, 12])}
+    a, b = kf([[1, 1], [2, 2]], [-1, -1], 0.0), kf([[3, 3], [4, 4]], [1, 0], 1.0)
+    assert adapter.backfill_ids(a, b, np.array([0, 1]), np.array([1, 0])) == 2 and a["ids"].tolist() == [0, 1]
+    w = [a, b]
+
+    class Shift:
+        def __init__(self, status): self.status = status
+        def optimize(self, T_cw, points, *rest):
+            T = T_cw.copy(); T[:, 0, 3] += 0.5
+            sm = BASummary(self.status, 1, 1, 0, 0, 0, 2.0, 1.0, 1e4)
+            return BAResult(T, points + 1.0, sm, [sm])
+
+    before = (b["T_wc"].copy(), vo.map_points[0].copy())
+    assert adapter.refine_window(vo, w, Shift(3), n_fixed=1).status == 3                           # numerical failure: no write-back
+    assert np.array_equal(b["T_wc"], before[0]) and np.array_equal(vo.map_points[0], before[1])
+    adapter.refine_window(vo, w, Shift(1), n_fixed=1)
+    assert np.array_equal(a["T_wc"], np.eye(4))                                          # gauge-fixed keyframe untouched
+    assert np.allclose(np.linalg.inv(b["T_wc"])[0, 3], np.linalg.inv(before[0])[0, 3] + 0.5)
+    assert np.array_equal(vo.T_wc, b["T_wc"]) and np.array_equal(vo.last_pos, b["T_wc"][:3, 3])
+    assert np.allclose(vo.map_points[0], before[1] + 1.0)
+
+
+@pytest.fixture(scope="module")
+def loop_runs(oracle):
+    from oracle_ba import OracleBA
+    seq = vo_synth.SynthSequence(n_frames=160, seed=5)
+    out = {}
+    for name in ("plain", "ba"):
+        cv2.setRNGSeed(0)
+        vo = vo_loop.VOLoop(seq.K, vo_loop.LoopConfig(), vo_synth.SynthFrontend(seq))
+        ad = None
+        if name == "ba":
+            cfg = BAConfig(window=6, max_iters=5, loss="huber", loss_scale=2.0)
+            ad = adapter.install(vo, cfg, ba=OracleBA(seq.K, cfg))
+        for i in range(seq.n_frames):
+            vo.process_frame(seq.image(i))
+        out[name] = (vo, ad, np.array(vo.trajectory))
+    return seq, out
+
+
+def test_adapter_in_the_frame_loop_with_oracle_solver(loop_runs):
+    seq, out = loop_runs
+    vo, ad, traj = out["ba"]
+    sms = [s for s in ad.summaries if s is not None]
+    assert len(sms) >= 10 and all(s.ok for s in sms)
+    assert len(ad.window) == 6 and ad.window[-1] is vo.keyframe                         # the reference's own dict objects
+    assert np.mean([s.final_cost / s.initial_cost for s in sms]) < 0.9                  # BA lowers the window cost
+    assert vo.initialized and len(traj) == len(out["plain"][2])                          # tracking never reset
+    # landmarks of the previous keyframe carry ids (back-fill), so windows have multi-view tracks
+    assert (ad.window[-2]["ids"] >= 0).sum() > 200
+    gt = seq.T_wc[:, :3, 3]
+    e_ba, e_plain = vo_synth.ate_sim3(traj[20:], gt[20:]), vo_synth.ate_sim3(out["plain"][2][20:], gt[20:])
+    assert np.isfinite(e_ba) and e_ba < 2.0 * e_plain + 1.0                              # and does not wreck the trajectory

@@ -58,13 +58,15 @@ class PackedWindow:
         return poses_from_T(self.T_cw)
 
 
-def pack_window(window, map_points, n_fixed: int = 1, min_obs: int = 2) -> PackedWindow | None:
+def pack_window(window, map_points, n_fixed: int = 2, min_obs: int = 2) -> PackedWindow | None:
     """Keyframe dicts + landmark dict -> BA arrays.
 
     Landmarks seen by fewer than ``min_obs`` window keyframes are left out (they do not constrain
     the cameras); duplicate (keyframe, landmark) pairs keep the first keypoint (the engine rejects
     duplicates, include/b2ba.h B2BA_E_DUPLICATE).  Slots are assigned in increasing id order so the
-    packing is deterministic.  Returns None when nothing can be optimised.
+    packing is deterministic.  The `n_fixed` oldest keyframes are gauge-fixed (default 2: a monocular window
+    has 7 gauge freedoms, two fixed poses pin all of them incl. the scale; at least one camera stays free).
+    Returns None when nothing can be optimised.
     """
     kfs = list(window)
     nc = len(kfs)
@@ -125,7 +127,7 @@ def write_back(vo, window, packed: PackedWindow, T_cw: np.ndarray, points: np.nd
             mp[p] = x.copy()
 
 
-def refine_window(vo, window, ba: BundleAdjuster, n_fixed: int = 1):
+def refine_window(vo, window, ba: BundleAdjuster, n_fixed: int = 2):
     """Pack -> BundleAdjuster.optimize -> write back.  Returns the BASummary (or None if skipped)."""
     packed = pack_window(window, vo.map_points, n_fixed=n_fixed)
     if packed is None:
@@ -140,7 +142,7 @@ def refine_window(vo, window, ba: BundleAdjuster, n_fixed: int = 1):
 class WindowAdapter:
     """Keyframe window + BA call, hooked onto one VisualOdometry instance."""
 
-    def __init__(self, vo, config: BAConfig | None = None, ba=None, n_fixed: int = 1):
+    def __init__(self, vo, config: BAConfig | None = None, ba=None, n_fixed: int = 2):
         self.vo = vo
         self.config = config or BAConfig()
         self.ba = ba if ba is not None else BundleAdjuster(vo.K, self.config)
@@ -188,6 +190,6 @@ def backfill_ids(prev_kf, new_kf, ref_indices, curr_indices) -> int:
     return int(m.sum())
 
 
-def install(vo, config: BAConfig | None = None, ba=None, n_fixed: int = 1) -> WindowAdapter:
+def install(vo, config: BAConfig | None = None, ba=None, n_fixed: int = 2) -> WindowAdapter:
     """The one call a maintainer adds after constructing VisualOdometry."""
     return WindowAdapter(vo, config, ba, n_fixed).install()
