@@ -126,11 +126,79 @@ def cpu_baseline(batch, iters, loss, budget_windows, threads=0):
                       f"oracle/ba_cpu.cpp OpenMP across windows, {dt:.2f} s"}
 
 
+def run_c2(args, impl):
+    """BASELINE config 2: end-to-end VO on the synthetic KITTI-05-shaped sequence, frames/sec.  The frame loop is
+    visualodometry_b200/vo_loop.py (the reference's loop restated and pinned to it, tests/test_vo_loop.py), the
+    frontend is synthetic (id-matched keypoints), BA runs once per keyframe through adapter.install():
+    impl "b200" -> BundleAdjuster on the GPU (host buffers in/out every call), "reference" -> the CPU oracle."""
+    import cv2
+    from visualodometry_b200 import BAConfig, adapter, vo_loop, vo_synth
+    seq = vo_synth.SynthSequence(n_frames=args.frames, seed=0)
+    cfg = BAConfig(window=10, max_iters=args.iters, loss="huber", loss_scale=2.0)
+
+    def one_run(kind):
+        cv2.setRNGSeed(0)
+        vo = vo_loop.VOLoop(seq.K, vo_loop.LoopConfig(), vo_synth.SynthFrontend(seq))
+        ad, t_ba, n_obs = None, [0.0], [0]
+        if kind != "none":
+            if kind == "gpu":
+                from visualodometry_b200 import BundleAdjuster
+                solver = BundleAdjuster(seq.K, cfg)
+            else:
+                sys.path.insert(0, os.path.join(ROOT, "tests"))
+                from oracle_ba import OracleBA
+                solver = OracleBA(seq.K, cfg)
+            inner = solver.optimize
+
+            def timed(*a):
+                t = time.perf_counter()
+                r = inner(*a)
+                t_ba[0] += time.perf_counter() - t
+                n_obs[0] += len(a[2]) * r.summary.iterations
+                return r
+            solver.optimize = timed
+            ad = adapter.install(vo, cfg, ba=solver)
+        t0 = time.perf_counter()
+        for i in range(seq.n_frames):
+            vo.process_frame(seq.image(i))
+        dt = time.perf_counter() - t0
+        nkf = len([s_ for s_ in ad.summaries if s_ is not None]) if ad else 0
+        ate = vo_synth.ate_sim3(np.array(vo.trajectory), seq.T_wc[-len(vo.trajectory):, :3, 3]) if len(vo.trajectory) > 10 else None
+        return {"fps": seq.n_frames / dt, "s": dt, "ba_s": t_ba[0], "ba_calls": nkf, "ba_obs_iters": n_obs[0],
+                "frames_since_last_reset": len(vo.trajectory), "ate_sim3_m": ate}
+
+    plain = one_run("none")
+    if impl == "reference":
+        r = one_run("cpu")
+    else:
+        one_run("gpu")                       # warm-up (module load, allocations)
+        r = one_run("gpu")
+    name = (f"C2: end-to-end VO, synthetic KITTI-05-shaped sequence ({args.frames} frames, 1241x376 K, <=2048 keypoints "
+            f"per frame, 5% wrong matches), 10-keyframe window BA ({args.iters} LM iterations, Huber) once per keyframe")
+    out = {"metric": "VO frames/sec", "value": r["fps"], "unit": "frames/s", "n_gpus": 1, "steps": 1, "warmup": 1,
+           "ms_per_step": 1e3 * r["s"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+           "data": "synthetic", "config": {"workload": name},
+           "vo": {"with_ba": r, "without_ba": plain,
+                  "ba_ms_per_keyframe": 1e3 * r["ba_s"] / max(1, r["ba_calls"]),
+                  "ba_obs_iters_per_s": r["ba_obs_iters"] / r["ba_s"] if r["ba_s"] > 0 else None},
+           "e2e": {"value": r["fps"], "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    if impl == "reference":
+        from oracle import ba_cpu
+        out["impl"] = "reference"
+        out["cpu_baseline"] = {"value": r["fps"], "unit": "frames/s", "cores": 1, "kind": "port",
+                               "sample": f"whole sequence; BA = oracle/ba_cpu.cpp single thread per window ({ba_cpu.num_procs()} cores on the box)"}
+    else:
+        out["gpu_launches"] = r["ba_calls"]
+    print(json.dumps(out))
+
+
 def run_reference(args, rank, world):
     """--impl reference: the reference has no BA; the CPU arm is the oracle port on
     the host cores, all threads, on a bounded sample of the same workload."""
     if rank != 0:
         return
+    if args.workload == "c2":
+        return run_c2(args, "reference")
     b, name = make_workload(argparse.Namespace(**{**vars(args), "windows": min(args.windows, args.cpu_windows),
                                                   "distinct": None}), 0)
     loss = "huber" if args.workload == "c3" else "trivial"
@@ -156,7 +224,8 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default="c4", choices=["c1", "c3", "c4", "c5"])
+    ap.add_argument("--workload", default="c4", choices=["c1", "c2", "c3", "c4", "c5"])
+    ap.add_argument("--frames", type=int, default=2700, help="C2: frames of the synthetic sequence")
     ap.add_argument("--windows", type=int, default=4096)
     ap.add_argument("--distinct", type=int, default=256, help="distinct geometries generated (set-up time bound)")
     ap.add_argument("--iters", type=int, default=None, help="LM iterations per step (10 windows, 20 C5)")
@@ -178,6 +247,8 @@ def main():
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the b2ba engine has no CPU fallback")
+    if args.workload == "c2":
+        return run_c2(args, "b200") if rank == 0 else None
     torch.cuda.set_device(local)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
