@@ -44,7 +44,9 @@ typedef struct b2ba_options {
   int32_t solver;         /* B2BA_SOLVER_* */
   int32_t pcg_max_iters;  /* 200 */
   double pcg_tol;         /* 1e-10 */
-  int32_t flags;          /* bit0: record per-iteration history (b2ba_dump B2BA_D_HIST_*) */
+  int32_t flags;          /* bit0: record per-iteration history (b2ba_dump B2BA_D_HIST_*);
+                             bit1: never split a window over a thread-block cluster (<= 18 windows per
+                             handle are otherwise solved by one 8-CTA cluster each: the latency path) */
   int32_t pad_;
 } b2ba_options;
 

@@ -39,12 +39,13 @@ class BAConfig:
     pcg_tol: float = 1e-10
     device: int = 0
     record_history: bool = False
+    cluster: bool = True           # few windows: one 8-CTA cluster per window (latency path); False = one CTA per window
 
     def to_options(self) -> _lib.Options:
         return _lib.Options(self.max_iters, {"trivial": 0, "huber": 1}[self.loss], self.loss_scale,
                             self.z_min, self.init_radius, self.ftol, self.gtol, self.ptol,
                             {"auto": 0, "chol": 1, "pcg": 2}[self.solver], self.pcg_max_iters,
-                            self.pcg_tol, 1 if self.record_history else 0, 0)
+                            self.pcg_tol, (1 if self.record_history else 0) | (0 if self.cluster else 2), 0)
 
 
 @dataclass

@@ -4,6 +4,7 @@
 #include "../../include/b2ba.h"
 
 #include <cstdio>
+#include <cstdlib>
 #include <dlfcn.h>
 #include <cstring>
 #include <string>
@@ -393,8 +394,13 @@ int b2ba_solve(b2ba_t* h, int32_t max_iters, b2ba_summary* summaries, void* cuda
     CU(cudaMemsetAsync(h->d_hist_accept.p, 0, (size_t)h->B * kHist * 4, s), "memset");
   }
   int rc = 0;
-  if (h->path == PATH_WIN_SMALL) rc = launch_window_small(make_win(h, hist, nullptr), P, s);
-  else if (h->path == PATH_WIN_BIG) rc = launch_window_big(make_win(h, hist, nullptr), P, s);
+  // few windows: the latency path, one 8-CTA cluster per window (B2BA_CLUSTER=0 forces one CTA per window)
+  static const bool cluster_on = [] { const char* e = std::getenv("B2BA_CLUSTER"); return !e || std::atoi(e) != 0; }();
+  const bool clus = cluster_on && !(h->opt.flags & 2) && h->B <= 18;
+  if (h->path == PATH_WIN_SMALL)
+    rc = clus ? launch_window_small_cluster(make_win(h, hist, nullptr), P, s) : launch_window_small(make_win(h, hist, nullptr), P, s);
+  else if (h->path == PATH_WIN_BIG)
+    rc = clus ? launch_window_big_cluster(make_win(h, hist, nullptr), P, s) : launch_window_big(make_win(h, hist, nullptr), P, s);
   else if (h->path == PATH_LARGE) {
     if (hist) { CU(h->d_hist_cost.alloc(kHist), "alloc"); }
     rc = solve_large(h, P, hist, s);

@@ -16,10 +16,14 @@
 //   back-subst    (a7)     delta_p, retraction, trial cost, gain ratio, accept/reject, mu update.
 #include "ba_window.cuh"
 
+#include <cooperative_groups.h>
+
 #include <cstdlib>
 #include <utility>
 
 namespace b2 {
+
+namespace cg = cooperative_groups;
 
 __device__ __forceinline__ int packed21(int r, int s) { return r * 6 - r * (r - 1) / 2 + (s - r); }
 
@@ -78,6 +82,7 @@ __global__ void __launch_bounds__(Cfg::NTHREADS, Cfg::MINB)
 window_lm_kernel(const WinData d, const Params P) {
   constexpr int NTHREADS = Cfg::NTHREADS, NWARPS = Cfg::NWARPS, G = Cfg::G, KS = Cfg::KS, NT = Cfg::NT;
   constexpr int TPW = Cfg::TPW, TPP = Cfg::TPP, PB = Cfg::PB, LDT = Cfg::LDT, LDS = Cfg::LDS, MAXCAM = Cfg::MAXCAM;
+  constexpr int CS = Cfg::CS, BS = Cfg::CS * Cfg::PB;   // CTAs per window; landmark stride between this CTA's batches
   extern __shared__ __align__(16) double smem[];
   double* pose_cur = smem;
   double* pose_tri = pose_cur + MAXCAM * 12;
@@ -88,13 +93,16 @@ window_lm_kernel(const WinData d, const Params P) {
   double* gred = dvec + 128;
   double* red = gred + 128;                 // NWARPS x 32 reduction scratch
   double* scal = red + Cfg::NRED;           // 16 control scalars
-  double* Z = scal + 16;                    // Zt tile (transposed), later S
+  double* xbuf = scal + 16;                 // cluster exchange buffer (CS > 1)
+  double* Z = xbuf + Cfg::XBUF;             // Zt tile (transposed), later Z Z^T tiles + S
   int* fidx = reinterpret_cast<int*>(Z + Cfg::ZS);   // free index or -1
   int* lo = fidx + MAXCAM;                  // # free cameras with index < c  (MAXCAM+1)
   int* iflag = lo + MAXCAM + 1;             // [0] step_bad  [1] accept  [2] stop
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int win = blockIdx.x;
+  const int win = blockIdx.x / CS;
+  int crank = 0;                            // rank of this CTA in the window's cluster
+  if constexpr (CS > 1) crank = (int)cg::this_cluster().block_rank();
   const int c0 = d.cam_off[win], nc = d.cam_off[win + 1] - c0;
   const int p0 = d.pt_off[win], npw = d.pt_off[win + 1] - p0;
 
@@ -130,7 +138,12 @@ window_lm_kernel(const WinData d, const Params P) {
     if (!have_lin) {
       double cst_tot = 0.0, ninv_tot = 0.0;   // live in thread 27 / 28
       for (int c = 0; c < nc; ++c) {
-        const int b = d.cam_ptr[c0 + c], e = d.cam_ptr[c0 + c + 1];
+        int b = d.cam_ptr[c0 + c], e = d.cam_ptr[c0 + c + 1];
+        if constexpr (CS > 1) {   // this CTA's contiguous share of the camera's observations
+          const int len = e - b;
+          e = b + (int)(((long long)len * (crank + 1)) / CS);
+          b = b + (int)(((long long)len * crank) / CS);
+        }
         Pose12 q;
         load_pose(pose_cur + 12 * c, q);
         const bool isfree = fidx[c] >= 0;
@@ -187,6 +200,24 @@ window_lm_kernel(const WinData d, const Params P) {
       }
       if (tid == 27) scal[0] = cst_tot;
       if (tid == 28) scal[1] = ninv_tot;
+      if constexpr (CS > 1) {
+        // all-reduce {B_c, g_c, cost, n_invalid} over the cluster: partials go to xbuf, every CTA sums the
+        // CS remote copies in rank order (deterministic and identical on all CTAs)
+        __syncthreads();
+        constexpr int NB = MAXCAM * 27;          // Bc and gc are contiguous in shared memory
+        for (int i = tid; i < NB; i += NTHREADS) xbuf[i] = Bc[i];
+        if (tid < 2) xbuf[NB + tid] = scal[tid];
+        cg::cluster_group cl = cg::this_cluster();
+        cl.sync();
+        for (int i = tid; i < NB + 2; i += NTHREADS) {
+          double v = 0.0;
+#pragma unroll
+          for (int r = 0; r < CS; ++r) v += cl.map_shared_rank(xbuf, r)[i];
+          if (i < NB) Bc[i] = v; else scal[i - NB] = v;
+        }
+        cl.sync();                               // xbuf may be overwritten again
+      }
+      __syncthreads();
       for (int i = tid; i < nc * 6; i += NTHREADS) Dc[i] = clampd(Bc[(i / 6) * 21 + packed21(i % 6, i % 6)]);
       __syncthreads();
       cost = scal[0];
@@ -212,15 +243,17 @@ window_lm_kernel(const WinData d, const Params P) {
     double* const zcol = Z + (size_t)3 * slot * LDT;          // this landmark's 3 columns: 3*LDT contiguous doubles
     int a0n = 0, a1n = 0;
     double Xn0 = 0, Xn1 = 0, Xn2 = 0;
-    if (slot < npw) {
-      a0n = d.pt_ptr[p0 + slot]; a1n = d.pt_ptr[p0 + slot + 1];
-      Xn0 = X[3 * slot]; Xn1 = X[3 * slot + 1]; Xn2 = X[3 * slot + 2];
+    const int bfirst = crank * PB;            // this CTA takes batches bfirst, bfirst + BS, ...
+    if (bfirst + slot < npw) {
+      const int pf = bfirst + slot;
+      a0n = d.pt_ptr[p0 + pf]; a1n = d.pt_ptr[p0 + pf + 1];
+      Xn0 = X[3 * pf]; Xn1 = X[3 * pf + 1]; Xn2 = X[3 * pf + 2];
     }
     // record range (contiguous in the point-major stream) of the batch AFTER the current one: it is
     // L1-prefetched while the current batch's DMMA runs; the range itself is loaded one batch earlier
-    int pf_s = d.pt_ptr[p0 + min(PB, npw)], pf_e = d.pt_ptr[p0 + min(2 * PB, npw)];
+    int pf_s = d.pt_ptr[p0 + min(bfirst + BS, npw)], pf_e = d.pt_ptr[p0 + min(bfirst + BS + PB, npw)];
 
-    for (int b0 = 0; b0 < npw; b0 += PB) {
+    for (int b0 = bfirst; b0 < npw; b0 += BS) {
       const int p = b0 + slot;
       const bool act = p < npw;
       const int a0 = a0n, a1 = a1n;
@@ -345,15 +378,15 @@ window_lm_kernel(const WinData d, const Params P) {
       __syncthreads();
       // prefetch the next batch's landmark (registers) and records (L1) while the tensor pipe works
       {
-        const int pn = p + PB;
+        const int pn = p + BS;
         a0n = 0; a1n = 0;
         if (pn < npw) {
           a0n = d.pt_ptr[p0 + pn]; a1n = d.pt_ptr[p0 + pn + 1];
           Xn0 = X[3 * pn]; Xn1 = X[3 * pn + 1]; Xn2 = X[3 * pn + 2];
         }
         for (int a = (pf_s & ~7) + tid * 8; a < pf_e; a += NTHREADS * 8) prefetch_l1(d.pm + a);
-        pf_s = d.pt_ptr[p0 + min(b0 + 2 * PB, npw)];
-        pf_e = d.pt_ptr[p0 + min(b0 + 3 * PB, npw)];
+        pf_s = d.pt_ptr[p0 + min(b0 + 2 * BS, npw)];
+        pf_e = d.pt_ptr[p0 + min(b0 + 2 * BS + PB, npw)];
       }
       // Z Z^T accumulate: DMMA over this batch's 3*PB columns (this warp's k-slice)
       syrk_dispatch<Cfg>(grp, zf, ksp * (Cfg::KSTEPS / KS), acc);
@@ -361,7 +394,10 @@ window_lm_kernel(const WinData d, const Params P) {
     }
 
     // ------------------------------------------------------------------ S = B' - Z Z^T  (a4)
-    double* S = Z;   // the Z tile is dead now; S (n x n, leading dim LDS) aliases it
+    // the Z tile is dead now: its memory takes this CTA's Z Z^T tiles (SP, T x 64, 8x8 row-major each) and
+    // the assembled system S (n x n, leading dim LDS)
+    double* SP = Z;
+    double* S = Z + Cfg::SPART;
 #pragma unroll
     for (int s = 0; s < KS; ++s) {
       if (ksp == s) {
@@ -369,8 +405,7 @@ window_lm_kernel(const WinData d, const Params P) {
         for (int q = 0; q < TPW; ++q) {
           const int t = grp * TPW + q;
           if (t < Cfg::T) {
-            const int mi = Tri<NT>::mi(t), ni = Tri<NT>::ni(t);
-            double* dst = S + (8 * mi + (lane >> 2)) * LDS + 8 * ni + 2 * (lane & 3);
+            double* dst = SP + t * 64 + (lane >> 2) * 8 + 2 * (lane & 3);
             if (s == 0) { dst[0] = acc[q][0]; dst[1] = acc[q][1]; }
             else { dst[0] += acc[q][0]; dst[1] += acc[q][1]; }
           }
@@ -378,10 +413,35 @@ window_lm_kernel(const WinData d, const Params P) {
       }
       __syncthreads();
     }
+    if constexpr (CS > 1) {
+      // a landmark block that failed to factor in ANY CTA invalidates the step for the whole window
+      if (tid == 0) xbuf[MAXCAM * 27 + 8] = iflag[0] ? 1.0 : 0.0;
+      cg::cluster_group cl = cg::this_cluster();
+      cl.sync();                                 // all CTAs' tiles (and flags) are in place
+      if (tid == 0) {
+        bool bad = false;
+        for (int r = 0; r < CS; ++r) bad = bad || cl.map_shared_rank(xbuf, r)[MAXCAM * 27 + 8] != 0.0;
+        if (bad) iflag[0] = 1;
+      }
+    }
+    // (Z Z^T)[i][j] for i <= j: one tile entry, summed over the cluster's CTAs in rank order
+    auto zzt = [&](int i, int j) -> double {
+      const int mi = i >> 3, ni = j >> 3;
+      const int off = (mi * NT - mi * (mi - 1) / 2 + (ni - mi)) * 64 + (i & 7) * 8 + (j & 7);
+      if constexpr (CS > 1) {
+        cg::cluster_group cl = cg::this_cluster();
+        double v = 0.0;
+#pragma unroll
+        for (int r = 0; r < CS; ++r) v += cl.map_shared_rank(SP, r)[off];
+        return v;
+      } else {
+        return SP[off];
+      }
+    };
     for (int idx = tid; idx < n * n; idx += NTHREADS) {
       const int i = idx / n, j = idx - i * n;
       if (i > j) continue;
-      double v = -S[i * LDS + j];
+      double v = -zzt(i, j);
       const int fi = i / 6, fj = j / 6;
       if (fi == fj) {
         // camera index of free slot fi: lo[] is monotone, find c with fidx[c] == fi
@@ -399,7 +459,7 @@ window_lm_kernel(const WinData d, const Params P) {
       const int fi = tid / 6;
       int c = fi;
       while (fidx[c] != fi) ++c;
-      gred[tid] = gc[c * 6 + tid - 6 * fi] - S[tid * LDS + n];
+      gred[tid] = gc[c * 6 + tid - 6 * fi] - zzt(tid, n);
     }
     __syncthreads();
     if (dbg) {
@@ -541,10 +601,10 @@ window_lm_kernel(const WinData d, const Params P) {
     // ------------------------------------------------------------------ back-substitution + trial cost (a7)
     double s_tc = 0.0, s_dDd = 0.0, s_gd = 0.0, s_dn2 = 0.0, s_xn2 = 0.0, s_inv = 0.0;
     if (step_ok) {
-      for (int p = slot; p < np_round; p += PB) {
+      for (int p = crank * PB + slot; p < np_round; p += BS) {
         const bool act = p < npw;
         {   // L1-prefetch the next batch: landmark offsets, landmarks, scratch rows, records
-          const int bn = p - slot + PB, bnn = min(bn + PB, npw);
+          const int bn = p - slot + BS, bnn = min(bn + PB, npw);
           if (bn < npw) {
             const int* pp = d.pt_ptr + p0 + bn;
             if (tid * 32 <= bnn - bn) prefetch_l1(pp + tid * 32);
@@ -657,11 +717,33 @@ window_lm_kernel(const WinData d, const Params P) {
     __syncthreads();
 
     // ------------------------------------------------------------------ LM control (Spec a0)
+    if constexpr (CS > 1) {
+      // landmark-part sums of this CTA -> xbuf; every CTA then adds the CS copies in rank order
+      if (tid == 0) {
+        double t[7] = {0, 0, 0, 0, 0, 0, 0};
+        for (int w = 0; w < NWARPS; ++w) {
+#pragma unroll
+          for (int k = 0; k < 6; ++k) t[k] += red[w * 32 + k];
+          t[6] = fmax(t[6], red[w * 32 + 6]);
+        }
+#pragma unroll
+        for (int k = 0; k < 7; ++k) xbuf[k] = t[k];
+      }
+      cg::this_cluster().sync();
+    }
     if (tid == 0) {
       double tc = 0, dDd = scal[2], gd = scal[3], dn2 = scal[4], xn2 = 0, ninv = 0, gm = 0;
-      for (int w = 0; w < NWARPS; ++w) {
-        tc += red[w * 32]; dDd += red[w * 32 + 1]; gd += red[w * 32 + 2]; dn2 += red[w * 32 + 3];
-        xn2 += red[w * 32 + 4]; ninv += red[w * 32 + 5]; gm = fmax(gm, red[w * 32 + 6]);
+      if constexpr (CS > 1) {
+        cg::cluster_group cl = cg::this_cluster();
+        for (int r = 0; r < CS; ++r) {
+          const double* xr = cl.map_shared_rank(xbuf, r);
+          tc += xr[0]; dDd += xr[1]; gd += xr[2]; dn2 += xr[3]; xn2 += xr[4]; ninv += xr[5]; gm = fmax(gm, xr[6]);
+        }
+      } else {
+        for (int w = 0; w < NWARPS; ++w) {
+          tc += red[w * 32]; dDd += red[w * 32 + 1]; gd += red[w * 32 + 2]; dn2 += red[w * 32 + 3];
+          xn2 += red[w * 32 + 4]; ninv += red[w * 32 + 5]; gm = fmax(gm, red[w * 32 + 6]);
+        }
       }
       for (int i = 0; i < nc * 6; ++i) if (fidx[i / 6] >= 0) gm = fmax(gm, fabs(gc[i]));
       const double model = 0.5 * (dDd * imu - gd);
@@ -687,7 +769,8 @@ window_lm_kernel(const WinData d, const Params P) {
       }
       iflag[1] = accept; iflag[2] = stop; iflag[0] = 0;
     }
-    __syncthreads();
+    if constexpr (CS > 1) cg::this_cluster().sync();   // every CTA has read the xbufs; trial landmarks are visible
+    else __syncthreads();
     const int accept = iflag[1];
     int stop = iflag[2];
     if (stop < 0) { status = B2BA_CONVERGED; break; }
@@ -707,7 +790,7 @@ window_lm_kernel(const WinData d, const Params P) {
       nu *= 2.0;
       ++n_rej;
     }
-    if (tid == 0 && d.hist_cost != nullptr && it < kHist) {
+    if (tid == 0 && crank == 0 && d.hist_cost != nullptr && it < kHist) {
       d.hist_cost[(size_t)win * kHist + it] = cost;
       d.hist_mu[(size_t)win * kHist + it] = mu_used;
       d.hist_accept[(size_t)win * kHist + it] = accept;
@@ -721,8 +804,9 @@ window_lm_kernel(const WinData d, const Params P) {
   if (cur == 1) {
     const double* src = d.pts[1] + (size_t)p0 * 3;
     double* dst = d.pts[0] + (size_t)p0 * 3;
-    for (int i = tid; i < npw * 3; i += NTHREADS) dst[i] = src[i];
+    for (int i = crank * NTHREADS + tid; i < npw * 3; i += CS * NTHREADS) dst[i] = src[i];
   }
+  if (crank != 0) return;                  // poses and the summary are identical in every CTA of the cluster
   for (int i = tid; i < nc * 12; i += NTHREADS) d.poses[(size_t)c0 * 12 + i] = pose_cur[i];
   if (tid == 0) {
     b2ba_summary s;
@@ -736,6 +820,9 @@ window_lm_kernel(const WinData d, const Params P) {
 using CfgSmall = WinCfg<7, 8, 4, 64, kSmallMaxCam, 2>;    // 256 threads, 2 CTAs / SM
 using CfgSmall4 = WinCfg<7, 4, 4, 32, kSmallMaxCam, 4>;   // 128 threads, 4 CTAs / SM
 using CfgBig = WinCfg<16, 16, 16, 32, kMaxCam, 1>;        // n+1 <= 128: up to 21 free cameras (C3)
+constexpr int kClusterSize = 8;                           // portable cluster size
+using CfgSmallC = WinCfg<7, 8, 4, 64, kSmallMaxCam, 1, kClusterSize>;   // latency path: 8 CTAs x 256 threads per window
+using CfgBigC = WinCfg<16, 16, 16, 32, kMaxCam, 1, kClusterSize>;      // latency path, up to 21 free cameras
 
 template <class Cfg, int LOSS>
 static int launch_l(const WinData& d, const Params& p, cudaStream_t s) {
@@ -746,8 +833,21 @@ static int launch_l(const WinData& d, const Params& p, cudaStream_t s) {
     if (e != cudaSuccess) return (int)e;
     configured = true;
   }
-  window_lm_kernel<Cfg, LOSS><<<d.nb, Cfg::NTHREADS, Cfg::SMEM, s>>>(d, p);
-  return (int)cudaGetLastError();
+  if constexpr (Cfg::CS > 1) {
+    cudaLaunchConfig_t lc = {};
+    lc.gridDim = dim3((unsigned)d.nb * Cfg::CS, 1, 1);
+    lc.blockDim = dim3(Cfg::NTHREADS, 1, 1);
+    lc.dynamicSmemBytes = Cfg::SMEM;
+    lc.stream = s;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = Cfg::CS; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    lc.attrs = at; lc.numAttrs = 1;
+    return (int)cudaLaunchKernelEx(&lc, window_lm_kernel<Cfg, LOSS>, d, p);
+  } else {
+    window_lm_kernel<Cfg, LOSS><<<d.nb, Cfg::NTHREADS, Cfg::SMEM, s>>>(d, p);
+    return (int)cudaGetLastError();
+  }
 }
 template <class Cfg>
 static int launch(const WinData& d, const Params& p, cudaStream_t s) {
@@ -768,6 +868,8 @@ int launch_window_small(const WinData& d, const Params& p, cudaStream_t s) {
   return small_variant() == 1 ? launch<CfgSmall4>(d, p, s) : launch<CfgSmall>(d, p, s);
 }
 int launch_window_big(const WinData& d, const Params& p, cudaStream_t s) { return launch<CfgBig>(d, p, s); }
+int launch_window_small_cluster(const WinData& d, const Params& p, cudaStream_t s) { return launch<CfgSmallC>(d, p, s); }
+int launch_window_big_cluster(const WinData& d, const Params& p, cudaStream_t s) { return launch<CfgBigC>(d, p, s); }
 
 template <class Cfg>
 static int attrs_of(int* regs, int* smem_bytes, int* ctas_per_sm) {

@@ -54,10 +54,13 @@ struct Tri {
 };
 
 // NT tile rows (8 each) of the reduced system incl. the y row; NWARPS = G tile groups x KS k-splits;
-// PB landmarks per batch; MAXCAM cameras per window held in shared memory; MINB CTAs per SM.
-template <int NT_, int NWARPS_, int G_, int PB_, int MAXCAM_, int MINB_>
+// PB landmarks per batch; MAXCAM cameras per window held in shared memory; MINB CTAs per SM; CS = CTAs
+// (one thread-block cluster) that share ONE window: landmarks / observations are split across the
+// cluster, partial sums are all-reduced through distributed shared memory in a fixed order, and the
+// reduced camera system is solved redundantly by every CTA (CS = 1: one CTA per window, no cluster).
+template <int NT_, int NWARPS_, int G_, int PB_, int MAXCAM_, int MINB_, int CS_ = 1>
 struct WinCfg {
-  static constexpr int NT = NT_, NWARPS = NWARPS_, G = G_, PB = PB_, MAXCAM = MAXCAM_, MINB = MINB_;
+  static constexpr int NT = NT_, NWARPS = NWARPS_, G = G_, PB = PB_, MAXCAM = MAXCAM_, MINB = MINB_, CS = CS_;
   static constexpr int NTHREADS = NWARPS * 32;
   static constexpr int KS = NWARPS / G;            // k-splits of the SYRK
   static constexpr int T = NT * (NT + 1) / 2;      // upper 8x8 tiles
@@ -69,10 +72,14 @@ struct WinCfg {
                                                    // LDT == 4 or 12 mod 16 -> conflict-free DMMA fragment loads
   static constexpr int KSTEPS = NCOL / 4;          // k-steps (of 4 columns) per batch
   static constexpr int LDS = NR + 1;               // leading dim of S (odd)
-  static constexpr int ZS = (NCOL * LDT > NR * LDS) ? NCOL * LDT : NR * LDS;
+  // the tile memory is reused after the point pass: [0, SPART) this CTA's Z Z^T tiles (T x 64, as the
+  // DMMA accumulators hold them), [SPART, SPART + NR*LDS) the assembled system S
+  static constexpr int SPART = T * 64;
+  static constexpr int ZS = (NCOL * LDT > SPART + NR * LDS) ? NCOL * LDT : SPART + NR * LDS;
   static constexpr int NRED = NWARPS * 32;
-  // doubles: pose_cur, pose_tri, B(21), gc, Dc, dvec, gred, red, scal, Zt/S
-  static constexpr int SM_DOUBLES = MAXCAM * (12 + 12 + 21 + 6 + 6) + 128 + 128 + NRED + 16 + ZS;
+  static constexpr int XBUF = CS > 1 ? MAXCAM * 27 + 16 : 0;    // cluster exchange buffer: camera blocks + scalars
+  // doubles: pose_cur, pose_tri, B(21), gc, Dc, dvec, gred, red, scal, xbuf, Zt/S
+  static constexpr int SM_DOUBLES = MAXCAM * (12 + 12 + 21 + 6 + 6) + 128 + 128 + NRED + 16 + XBUF + ZS;
   static constexpr size_t SMEM = (size_t)SM_DOUBLES * 8 + (2 * MAXCAM + 8) * 4;
   static_assert(KS * G == NWARPS, "warps = groups x k-splits");
   static_assert(KSTEPS % KS == 0, "k-steps split evenly");
@@ -87,6 +94,10 @@ constexpr int kBigMaxFree = 21;                        // window_big:   n+1 <= 1
 // launchers (ba_window.cu). Return cudaError_t as int.
 int launch_window_small(const WinData& d, const Params& p, cudaStream_t s);   // <= 12 cameras, <= 9 free (n+1 <= 56)
 int launch_window_big(const WinData& d, const Params& p, cudaStream_t s);     // n+1 <= 128 (<= 21 free cams)
+// Few windows (latency path): one 8-CTA cluster per window.  Same arithmetic per observation; sums are formed
+// per CTA and then across the cluster in rank order, so results differ from the 1-CTA kernels by rounding only.
+int launch_window_small_cluster(const WinData& d, const Params& p, cudaStream_t s);
+int launch_window_big_cluster(const WinData& d, const Params& p, cudaStream_t s);
 int window_kernel_attrs(int which, int* regs, int* smem_bytes, int* ctas_per_sm);
 
 }  // namespace b2
