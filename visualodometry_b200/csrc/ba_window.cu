@@ -823,6 +823,8 @@ using CfgBig = WinCfg<16, 16, 16, 32, kMaxCam, 1>;        // n+1 <= 128: up to 2
 constexpr int kClusterSize = 8;                           // portable cluster size
 using CfgSmallC = WinCfg<7, 8, 4, 64, kSmallMaxCam, 1, kClusterSize>;   // latency path: 8 CTAs x 256 threads per window
 using CfgBigC = WinCfg<16, 16, 16, 32, kMaxCam, 1, kClusterSize>;      // latency path, up to 21 free cameras
+using CfgSmallC16 = WinCfg<7, 8, 4, 64, kSmallMaxCam, 1, 16>;          // <= 8 windows: 16 CTAs (non-portable cluster size)
+using CfgBigC16 = WinCfg<16, 16, 16, 32, kMaxCam, 1, 16>;
 
 template <class Cfg, int LOSS>
 static int launch_l(const WinData& d, const Params& p, cudaStream_t s) {
@@ -831,6 +833,10 @@ static int launch_l(const WinData& d, const Params& p, cudaStream_t s) {
     cudaError_t e = cudaFuncSetAttribute(window_lm_kernel<Cfg, LOSS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          (int)Cfg::SMEM);
     if (e != cudaSuccess) return (int)e;
+    if (Cfg::CS > 8) {
+      e = cudaFuncSetAttribute(window_lm_kernel<Cfg, LOSS>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+      if (e != cudaSuccess) return (int)e;
+    }
     configured = true;
   }
   if constexpr (Cfg::CS > 1) {
@@ -868,8 +874,18 @@ int launch_window_small(const WinData& d, const Params& p, cudaStream_t s) {
   return small_variant() == 1 ? launch<CfgSmall4>(d, p, s) : launch<CfgSmall>(d, p, s);
 }
 int launch_window_big(const WinData& d, const Params& p, cudaStream_t s) { return launch<CfgBig>(d, p, s); }
-int launch_window_small_cluster(const WinData& d, const Params& p, cudaStream_t s) { return launch<CfgSmallC>(d, p, s); }
-int launch_window_big_cluster(const WinData& d, const Params& p, cudaStream_t s) { return launch<CfgBigC>(d, p, s); }
+// B2BA_CLUSTER16=0 (developer knob) keeps the portable cluster size for every window count
+static bool cluster16() {
+  static int v = -1;
+  if (v < 0) { const char* e = std::getenv("B2BA_CLUSTER16"); v = (!e || std::atoi(e) != 0) ? 1 : 0; }
+  return v == 1;
+}
+int launch_window_small_cluster(const WinData& d, const Params& p, cudaStream_t s) {
+  return (d.nb <= 8 && cluster16()) ? launch<CfgSmallC16>(d, p, s) : launch<CfgSmallC>(d, p, s);
+}
+int launch_window_big_cluster(const WinData& d, const Params& p, cudaStream_t s) {
+  return (d.nb <= 8 && cluster16()) ? launch<CfgBigC16>(d, p, s) : launch<CfgBigC>(d, p, s);
+}
 
 template <class Cfg>
 static int attrs_of(int* regs, int* smem_bytes, int* ctas_per_sm) {
