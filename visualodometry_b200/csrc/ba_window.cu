@@ -182,10 +182,22 @@ window_lm_kernel(const WinData d, const Params P) {
             }
           }
         }
+        // transposing butterfly: 31 shuffles instead of 29 x 5; lane l ends with the warp total of acc[l]
+        {
+          double v[32];
 #pragma unroll
-        for (int k = 0; k < 29; ++k) {
-          const double v = warp_sum(acc[k]);
-          if (lane == 0) red[warp * 32 + k] = v;
+          for (int k = 0; k < 32; ++k) v[k] = k < 29 ? acc[k] : 0.0;
+#pragma unroll
+          for (int off = 16; off > 0; off >>= 1) {
+            const bool up = (lane & off) != 0;
+#pragma unroll
+            for (int j = 0; j < off; ++j) {
+              const double keep = up ? v[j + off] : v[j];
+              const double send = up ? v[j] : v[j + off];
+              v[j] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+            }
+          }
+          red[warp * 32 + lane] = v[0];
         }
         __syncthreads();
         if (tid < 29) {
@@ -415,25 +427,32 @@ window_lm_kernel(const WinData d, const Params P) {
     }
     if constexpr (CS > 1) {
       // a landmark block that failed to factor in ANY CTA invalidates the step for the whole window
-      if (tid == 0) xbuf[MAXCAM * 27 + 8] = iflag[0] ? 1.0 : 0.0;
+      if (tid == 0) xbuf[Cfg::XDATA + 8] = iflag[0] ? 1.0 : 0.0;
       cg::cluster_group cl = cg::this_cluster();
       cl.sync();                                 // all CTAs' tiles (and flags) are in place
       if (tid == 0) {
         bool bad = false;
-        for (int r = 0; r < CS; ++r) bad = bad || cl.map_shared_rank(xbuf, r)[MAXCAM * 27 + 8] != 0.0;
+        for (int r = 0; r < CS; ++r) bad = bad || cl.map_shared_rank(xbuf, r)[Cfg::XDATA + 8] != 0.0;
         if (bad) iflag[0] = 1;
       }
+      // reduce-scatter: this CTA sums its XCHUNK-entry share of the tiles over all CTAs (rank order) ...
+      for (int e = tid; e < Cfg::XCHUNK; e += NTHREADS) {
+        const int off = crank * Cfg::XCHUNK + e;
+        double v = 0.0;
+        if (off < Cfg::SPART) {
+#pragma unroll
+          for (int r = 0; r < CS; ++r) v += cl.map_shared_rank(SP, r)[off];
+        }
+        xbuf[e] = v;
+      }
+      cl.sync();                                 // ... and every CTA then gathers the sums from their owners
     }
     // (Z Z^T)[i][j] for i <= j: one tile entry, summed over the cluster's CTAs in rank order
     auto zzt = [&](int i, int j) -> double {
       const int mi = i >> 3, ni = j >> 3;
       const int off = (mi * NT - mi * (mi - 1) / 2 + (ni - mi)) * 64 + (i & 7) * 8 + (j & 7);
       if constexpr (CS > 1) {
-        cg::cluster_group cl = cg::this_cluster();
-        double v = 0.0;
-#pragma unroll
-        for (int r = 0; r < CS; ++r) v += cl.map_shared_rank(SP, r)[off];
-        return v;
+        return cg::this_cluster().map_shared_rank(xbuf, off / Cfg::XCHUNK)[off % Cfg::XCHUNK];
       } else {
         return SP[off];
       }
@@ -486,9 +505,8 @@ window_lm_kernel(const WinData d, const Params P) {
         for (int k = 0; k < 6; ++k)
           if (k < c) dj = fma(-L[c][k], L[c][k], dj);
         if (!(dj > 0.0) || !isfinite(dj)) { bad = true; dj = 1.0; }
-        const double lcc = sqrt(dj);
-        inv[c] = 1.0 / lcc;
-        L[c][c] = lcc;
+        inv[c] = rsqrt(dj);
+        L[c][c] = dj * inv[c];
 #pragma unroll
         for (int r = 0; r < 6; ++r) {
           if (r > c) {
@@ -520,10 +538,12 @@ window_lm_kernel(const WinData d, const Params P) {
       __syncthreads();
       if (tid == 0) {
 #pragma unroll
-        for (int r = 0; r < 6; ++r)
+        for (int r = 0; r < 6; ++r) {
 #pragma unroll
           for (int c = 0; c < 6; ++c)
             if (c <= r) S[(j0 + r) * LDS + j0 + c] = L[r][c];
+          red[j0 + r] = inv[r];               // 1 / L_rr for the triangular solves (red is free here)
+        }
       }
       // trailing update A22 -= L21 L21^T (lower triangle), work items = (row, 6-column block) pairs
       const int npairs = (m / 6) * (m + 6) / 2;      // sum over column blocks cb of (m - cb)
@@ -549,22 +569,43 @@ window_lm_kernel(const WinData d, const Params P) {
       }
       __syncthreads();
     }
-    if (tid < n) dvec[tid] = -gred[tid];
     __syncthreads();
     if (warp == 0) {
+      // L y = -g_red, L^T x = y with the vector in registers (row k of lane k % 32), one shuffle per step
+      constexpr int RPL = Cfg::NR / 32 + (Cfg::NR % 32 ? 1 : 0);
+      double x[RPL], di[RPL];
+#pragma unroll
+      for (int q = 0; q < RPL; ++q) {
+        const int k = lane + 32 * q;
+        x[q] = k < n ? -gred[k] : 0.0;
+        di[q] = k < n ? red[k] : 0.0;
+      }
       for (int i = 0; i < n; ++i) {
-        const double xi = dvec[i] / S[i * LDS + i];
-        __syncwarp();
-        if (lane == 0) dvec[i] = xi;
-        for (int k = i + 1 + lane; k < n; k += 32) dvec[k] -= S[k * LDS + i] * xi;
-        __syncwarp();
+        double xi = 0.0;
+#pragma unroll
+        for (int q = 0; q < RPL; ++q)
+          if ((i >> 5) == q) { x[q] = (lane == (i & 31)) ? x[q] * di[q] : x[q]; xi = __shfl_sync(0xffffffffu, x[q], i & 31); }
+#pragma unroll
+        for (int q = 0; q < RPL; ++q) {
+          const int k = lane + 32 * q;
+          if (k > i && k < n) x[q] = fma(-S[k * LDS + i], xi, x[q]);
+        }
       }
       for (int i = n - 1; i >= 0; --i) {
-        const double xi = dvec[i] / S[i * LDS + i];
-        __syncwarp();
-        if (lane == 0) dvec[i] = xi;
-        for (int k = lane; k < i; k += 32) dvec[k] -= S[i * LDS + k] * xi;
-        __syncwarp();
+        double xi = 0.0;
+#pragma unroll
+        for (int q = 0; q < RPL; ++q)
+          if ((i >> 5) == q) { x[q] = (lane == (i & 31)) ? x[q] * di[q] : x[q]; xi = __shfl_sync(0xffffffffu, x[q], i & 31); }
+#pragma unroll
+        for (int q = 0; q < RPL; ++q) {
+          const int k = lane + 32 * q;
+          if (k < i) x[q] = fma(-S[i * LDS + k], xi, x[q]);
+        }
+      }
+#pragma unroll
+      for (int q = 0; q < RPL; ++q) {
+        const int k = lane + 32 * q;
+        if (k < n) dvec[k] = x[q];
       }
     }
     __syncthreads();
@@ -727,7 +768,7 @@ window_lm_kernel(const WinData d, const Params P) {
           t[6] = fmax(t[6], red[w * 32 + 6]);
         }
 #pragma unroll
-        for (int k = 0; k < 7; ++k) xbuf[k] = t[k];
+        for (int k = 0; k < 7; ++k) xbuf[Cfg::XDATA + k] = t[k];
       }
       cg::this_cluster().sync();
     }
@@ -736,7 +777,7 @@ window_lm_kernel(const WinData d, const Params P) {
       if constexpr (CS > 1) {
         cg::cluster_group cl = cg::this_cluster();
         for (int r = 0; r < CS; ++r) {
-          const double* xr = cl.map_shared_rank(xbuf, r);
+          const double* xr = cl.map_shared_rank(xbuf, r) + Cfg::XDATA;
           tc += xr[0]; dDd += xr[1]; gd += xr[2]; dn2 += xr[3]; xn2 += xr[4]; ninv += xr[5]; gm = fmax(gm, xr[6]);
         }
       } else {

@@ -77,7 +77,11 @@ struct WinCfg {
   static constexpr int SPART = T * 64;
   static constexpr int ZS = (NCOL * LDT > SPART + NR * LDS) ? NCOL * LDT : SPART + NR * LDS;
   static constexpr int NRED = NWARPS * 32;
-  static constexpr int XBUF = CS > 1 ? MAXCAM * 27 + 16 : 0;    // cluster exchange buffer: camera blocks + scalars
+  // cluster exchange buffer: [0, XDATA) camera blocks or this CTA's share of the reduced Z Z^T tiles,
+  // [XDATA, XDATA + 8) step scalars, [XDATA + 8] step-bad flag
+  static constexpr int XCHUNK = (T * 64 + (CS > 1 ? CS : 1) - 1) / (CS > 1 ? CS : 1);
+  static constexpr int XDATA = ((MAXCAM * 27 + 2 > XCHUNK ? MAXCAM * 27 + 2 : XCHUNK) + 1) / 2 * 2;
+  static constexpr int XBUF = CS > 1 ? XDATA + 16 : 0;
   // doubles: pose_cur, pose_tri, B(21), gc, Dc, dvec, gred, red, scal, xbuf, Zt/S
   static constexpr int SM_DOUBLES = MAXCAM * (12 + 12 + 21 + 6 + 6) + 128 + 128 + NRED + 16 + XBUF + ZS;
   static constexpr size_t SMEM = (size_t)SM_DOUBLES * 8 + (2 * MAXCAM + 8) * 4;
