@@ -257,7 +257,7 @@ def main():
     loss = "huber" if args.workload == "c3" else "trivial"
     c5 = args.workload == "c5"
     ba = BundleAdjuster(K_of(b.intr), BAConfig(max_iters=args.iters, loss=loss, device=local,
-                                               solver="pcg" if c5 else "auto"))
+                                               solver="auto"))            # C5: banded Cholesky if S is block-banded, else PCG
     if c5 and world > 1:
         ba.init_distributed()
     offs = (None, None, None) if c5 else (b.cam_off, b.pt_off, b.obs_off)

@@ -62,15 +62,51 @@ def test_lm_result_random_visibility(oracle, nc, npts):
     ba.close()
 
 
-def test_lm_result_chain_rmse_only(oracle):
-    """local visibility: block-Jacobi PCG is capped at 200 iterations in oracle AND engine (DESIGN §6);
-    the cost / RMSE agree, the unconverged drift mode of the chain does not."""
+def test_lm_result_chain_banded_cholesky(oracle):
+    """local visibility: S is block-banded, the large path's default solver is the exact banded Cholesky; the
+    oracle's dense Cholesky is the comparator (same normal equations, same LM rule)."""
+    p = synth.make_large(3, n_cams=100, n_pts=10000, mode="local")
+    from visualodometry_b200 import BAConfig, BundleAdjuster
+    ba = BundleAdjuster(K_of(p), BAConfig(max_iters=8, record_history=True))      # solver="auto"
+    ba.set_problem(p.poses, p.points, p.obs_cam, p.obs_pt, p.obs_uv, p.fixed_cam)
+    sm = ba.solve()[0]
+    poses, pts = ba.get()
+    po, xo, so = oracle.solve(p, max_iters=8, solver="chol")
+    assert sm.pcg_iters == 0 and sm.iterations == so.iterations
+    ch = np.array([so.initial_cost] + list(so.cost_hist[:8]))
+    moving = np.concatenate([[True], (ch[:-1] - ch[1:])[:-1] > 1e-7 * ch[:-2]])
+    ha = ba.dump("HIST_ACCEPT", (1, 64), np.int32)[0, :8]
+    assert np.array_equal(ha[moving], np.array(so.accept_hist[:8])[moving])
+    assert rel(ba.dump("HIST_COST", (1, 64))[0, :8], np.array(so.cost_hist[:8])) <= 1e-9
+    r_gpu, r_cpu = synth.rmse_px(p, poses, pts), synth.rmse_px(p, po, xo)
+    assert abs(r_gpu - r_cpu) <= 1e-6 * r_cpu and r_gpu < 0.1 * synth.rmse_px(p)
+    assert np.abs(poses - po).max() <= 1e-5
+    assert (np.linalg.norm(pts - xo, axis=1) / np.maximum(1, np.linalg.norm(xo, axis=1))).max() <= 1e-5
+    ba.close()
+
+
+def test_banded_step_matches_oracle_cholesky_step(oracle):
+    """one LM iteration: delta_c of the banded Cholesky against the oracle's dense Cholesky."""
+    p = synth.make_large(5, n_cams=60, n_pts=4000, mode="local")
+    from visualodometry_b200 import BAConfig, BundleAdjuster
+    ba = BundleAdjuster(K_of(p), BAConfig())
+    ba.set_problem(p.poses, p.points, p.obs_cam, p.obs_pt, p.obs_uv, p.fixed_cam)
+    st = oracle.stage(p, mu=1e4, solver="chol")
+    n = st["S"].shape[0]
+    assert rel(ba.dump("S", (n, n)), st["S"]) <= 1e-11
+    assert rel(ba.dump("DC", (n,)), st["dc"]) <= 1e-8
+    ba.close()
+
+
+def test_lm_result_chain_pcg_rmse_only(oracle):
+    """the same chain with PCG forced: block-Jacobi PCG is capped at 200 iterations in oracle AND engine
+    (DESIGN §6); the cost / RMSE agree, the unconverged drift mode of the chain does not."""
     p = synth.make_large(3, n_cams=100, n_pts=10000, mode="local")
     ba = _engine(p, max_iters=8)
     sm = ba.solve()[0]
     poses, pts = ba.get()
     po, xo, so = oracle.solve(p, max_iters=8, solver="pcg")
-    assert sm.accepted == so.accepted
+    assert sm.accepted == so.accepted and sm.pcg_iters > 0
     r_gpu, r_cpu = synth.rmse_px(p, poses, pts), synth.rmse_px(p, po, xo)
     assert abs(r_gpu - r_cpu) <= 1e-5 * r_cpu and r_gpu < 0.1 * synth.rmse_px(p)
     ba.close()

@@ -46,7 +46,8 @@ struct b2ba {
   LargeIndex lix;
   DevBuf<ObsRec> l_cm;
   DevBuf<int> l_cam_ptr;
-  DevBuf<double> l_poses_tri, l_lin_part, l_lin, l_Dc, l_Sg, l_dc, l_r, l_z, l_q, l_Minv, l_part, l_sums;
+  DevBuf<double> l_poses_tri, l_lin_part, l_lin, l_Dc, l_Sg, l_dc, l_r, l_z, l_q, l_Minv, l_part, l_sums, l_band, l_binv;
+  int l_bw = -1;     // block half-bandwidth of S when the banded Cholesky is selected, else -1
   DevBuf<LargeCtrl> l_ctrl;
   int p_lo = 0, p_hi = 0;
   bool range_set = false;
@@ -153,6 +154,7 @@ LargeData make_large(b2ba* h, bool hist) {
   d.lin_part = h->l_lin_part.p; d.lin = h->nranks > 1 ? h->l_lin.p : h->l_lin_part.p;
   d.Dc = h->l_Dc.p; d.pt_scratch = h->d_scratch.p; d.Sg = h->l_Sg.p; d.dc = h->l_dc.p;
   d.r = h->l_r.p; d.z = h->l_z.p; d.q = h->l_q.p; d.Minv = h->l_Minv.p; d.part = h->l_part.p;
+  d.bw = h->l_bw; d.band = h->l_band.p; d.binv = h->l_binv.p;
   d.sums_part = h->l_sums.p; d.ctrl = h->l_ctrl.p; d.summary = h->d_summ.p;
   d.hist_cost = hist ? h->d_hist_cost.p : nullptr; d.hist_mu = hist ? h->d_hist_mu.p : nullptr;
   d.hist_accept = hist ? h->d_hist_accept.p : nullptr;
@@ -185,6 +187,21 @@ int setup_large(b2ba* h) {
   CU(h->l_Sg.alloc(nblk * 36 + n), "alloc"); CU(h->l_dc.alloc(n), "alloc"); CU(h->l_r.alloc(n), "alloc");
   CU(h->l_z.alloc(n), "alloc"); CU(h->l_q.alloc(n), "alloc"); CU(h->l_Minv.alloc(6 * n), "alloc");
   CU(h->l_part.alloc(part + 8), "alloc"); CU(h->l_sums.alloc(16), "alloc"); CU(h->l_ctrl.alloc(1), "alloc");
+  // solver choice on the large path: S block-banded (half-bandwidth <= kBandMaxBw camera blocks) -> exact banded
+  // Cholesky, unless PCG was asked for explicitly; otherwise block-Jacobi PCG
+  h->l_bw = -1;
+  if (h->opt.solver != B2BA_SOLVER_PCG && h->lix.nfree > 0) {
+    std::vector<int> bp(h->lix.nfree + 1), bc(h->lix.nblk);
+    CU(cudaMemcpy(bp.data(), h->lix.blk_ptr.p, bp.size() * 4, cudaMemcpyDeviceToHost), "read structure");
+    CU(cudaMemcpy(bc.data(), h->lix.blk_col.p, bc.size() * 4, cudaMemcpyDeviceToHost), "read structure");
+    int bw = 0;
+    for (int f = 0; f < h->lix.nfree; ++f)
+      for (int b = bp[f]; b < bp[f + 1]; ++b) if (bc[b] - f > bw) bw = bc[b] - f;
+    if (bw <= kBandMaxBw) {
+      h->l_bw = bw;
+      CU(h->l_band.alloc((size_t)h->lix.nfree * (bw + 1) * 36), "alloc"); CU(h->l_binv.alloc((size_t)h->lix.nfree * 6), "alloc");
+    }
+  }
   CU(cudaMemset(h->l_lin_part.p, 0, (nc * 27 + 2) * sizeof(double)), "memset");
   CU(cudaMemset(h->l_sums.p, 0, 16 * sizeof(double)), "memset");
   CU(cudaDeviceSynchronize(), "setup_large");

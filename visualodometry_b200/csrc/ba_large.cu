@@ -859,7 +859,9 @@ int large_iteration(const LargeData& d, const Params& P, int pcg_max_iters, doub
   const int npl = d.p_hi - d.p_lo;
   if (npl > 0) large_schur_kernel<<<(npl + 127) / 128, 128, 0, s>>>(d, P);
   if (ar && (rc = ar(ar_user, d.Sg, d.Sg, d.sg_count(), s)) != 0) return rc;
-  {
+  if (d.bw >= 0) {
+    if ((rc = large_band_solve(d, s)) != 0) return rc;
+  } else {
     int blocks = 0;
     size_t smem = 0;
     if ((rc = large_pcg_grid(d.n, &blocks, &smem)) != 0) return rc;

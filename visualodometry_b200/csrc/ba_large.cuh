@@ -48,6 +48,9 @@ struct LargeData {
   double* dc;                      // n   delta_c (PCG x)
   double* r; double* z; double* q; // n each
   double* Minv;                    // nfree x 36
+  int bw;                          // block half-bandwidth of S if the banded Cholesky is used, else -1 (PCG)
+  double* band;                    // nfree x (bw+1) x 36: lower band by block column (A, then L in place)
+  double* binv;                    // nfree x 6: 1 / diag(L)
   double* part;                    // partial-sum scratch (grid partials)
   double* sums_part;               // 8 local partial sums (before the allreduce)
   LargeCtrl* ctrl;
@@ -76,5 +79,9 @@ int large_iteration(const LargeData& d, const Params& P, int pcg_max_iters, doub
                     AllReduceFn ar, void* ar_user, cudaStream_t s);
 int large_finish(const LargeData& d, cudaStream_t s);
 int large_pcg_grid(int n, int* blocks, size_t* smem);   // cooperative launch geometry
+// exact banded Cholesky solve of S dc = -g_red (ba_band.cu); needs d.bw >= 0
+size_t large_band_smem(int bw);
+int large_band_solve(const LargeData& d, cudaStream_t s);
+constexpr int kBandMaxBw = 23;     // (bw+1)^2 blocks of shared memory: 24 x 24 x 288 B = 166 KB
 
 }  // namespace b2
