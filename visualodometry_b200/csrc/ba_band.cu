@@ -10,6 +10,7 @@ namespace b2 {
 namespace {
 
 constexpr int kBandThreads = 256;
+constexpr int kBandAhead = 3;      // block columns loaded ahead of the active window
 
 // band block (j, k), k = 0..w, is A_{j+k, j} (6 x 6 row-major): the lower band, by block column.
 // A_{j+k, j}[r][c] = S(j, j+k)[c][r] (S is stored as its upper blocks).
@@ -41,24 +42,25 @@ __global__ void __launch_bounds__(kBandThreads) large_band_chol_kernel(LargeData
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int N = d.nfree, w = d.bw, W1 = w + 1;
   const int SLOT = W1 * 36 + 6;                       // one block column (w+1 blocks) + its right-hand side
-  double* ring = bsm;                                  // W1 slots
-  double* xs = ring + (size_t)W1 * SLOT;               // backward pass: ring of the last W1 solution blocks
+  const int RS = W1 + kBandAhead;                      // ring slots: the active window + columns loaded ahead
+  double* ring = bsm;
+  double* xs = ring + (size_t)RS * SLOT;               // backward pass: ring of the last W1 solution blocks
   double* Lsm = xs + 6 * W1;                           // factor of the current diagonal block (36)
   __shared__ int bad;
   if (tid == 0) bad = 0;
   const double* gred = d.Sg + (size_t)d.nblk * 36;
 
   auto load_col = [&](int j) {                         // global band column j (+ rhs = -g_red) -> ring slot
-    double* s = ring + (size_t)(j % W1) * SLOT;
+    double* s = ring + (size_t)(j % RS) * SLOT;
     const double* g = d.band + (size_t)j * W1 * 36;
     for (int i = tid; i < W1 * 36; i += kBandThreads) s[i] = g[i];
     if (tid < 6) s[W1 * 36 + tid] = -gred[6 * j + tid];
   };
-  for (int j = 0; j < min(W1, N); ++j) load_col(j);
+  for (int j = 0; j < min(RS - 1, N); ++j) load_col(j);
   __syncthreads();
 
   for (int j = 0; j < N; ++j) {
-    double* cj = ring + (size_t)(j % W1) * SLOT;
+    double* cj = ring + (size_t)(j % RS) * SLOT;
     // ---- every thread factors the diagonal block redundantly in registers
     double L[6][6], inv[6];
     bool isbad = false;
@@ -135,7 +137,7 @@ __global__ void __launch_bounds__(kBandThreads) large_band_chol_kernel(LargeData
         const int a = b + rem, r = e / 6, c = e % 6;
         const double* la = cj + 36 * a + 6 * r;
         const double* lb = cj + 36 * b + 6 * c;
-        double* dst = ring + (size_t)((j + b) % W1) * SLOT + 36 * (a - b) + 6 * r + c;
+        double* dst = ring + (size_t)((j + b) % RS) * SLOT + 36 * (a - b) + 6 * r + c;
         double v = *dst;
 #pragma unroll
         for (int m = 0; m < 6; ++m) v = fma(-la[m], lb[m], v);
@@ -144,7 +146,7 @@ __global__ void __launch_bounds__(kBandThreads) large_band_chol_kernel(LargeData
         const int q = id - npair * 36, a = 1 + q / 6, r = q % 6;
         const double* la = cj + 36 * a + 6 * r;
         const double* y = cj + W1 * 36;
-        double* dst = ring + (size_t)((j + a) % W1) * SLOT + W1 * 36 + r;
+        double* dst = ring + (size_t)((j + a) % RS) * SLOT + W1 * 36 + r;
         double v = *dst;
 #pragma unroll
         for (int m = 0; m < 6; ++m) v = fma(-la[m], y[m], v);
@@ -157,47 +159,64 @@ __global__ void __launch_bounds__(kBandThreads) large_band_chol_kernel(LargeData
       for (int i = tid; i < W1 * 36; i += kBandThreads) g[i] = i < 36 ? Lsm[i] : cj[i];
       if (tid < 6) d.dc[6 * j + tid] = cj[W1 * 36 + tid];
     }
-    __syncthreads();
-    if (j + W1 < N) load_col(j + W1);                  // same slot as column j (all reads of it are done)
+    // the slot of column j-1 is free since the previous barrier: it takes column j-1+RS, which is first
+    // touched kBandAhead steps from now (its global load latency is off the critical path)
+    if (j + RS - 1 < N) load_col(j + RS - 1);
     __syncthreads();
   }
   if (bad) { if (tid == 0) ctrl->step_bad = 1; return; }
 
-  // ---- backward substitution L^T x = y by warp 0; x blocks of the last w columns stay in shared memory
+  // ---- backward substitution L^T x = y by warp 0; x blocks of the last w columns stay in shared memory.
+  // Lane layout: c = lane % 6 (component), sl = lane / 6 (a-slice, 5 slices; lanes 30, 31 idle).  The entries a
+  // lane needs from column j-1 (its first a-slice, the diagonal block column c, 1/diag, y) are loaded one step
+  // ahead, so the L2 latency of the band array is off the serial chain.
   if (warp == 0) {
+    const int c = lane % 6, sl = lane / 6;
+    double nb[6], nd[6], ninv = 0.0, ny = 0.0;          // prefetched for the column about to be processed
+    auto fetch = [&](int j) {
+      const double* g = d.band + (size_t)j * W1 * 36;
+      const int wj = min(w, N - 1 - j);
+#pragma unroll
+      for (int r = 0; r < 6; ++r) {
+        nb[r] = (lane < 30 && 1 + sl <= wj) ? g[36 * (1 + sl) + 6 * r + c] : 0.0;
+        nd[r] = lane < 6 ? g[6 * r + c] : 0.0;          // column c of L_jj: L[r][c], r > c used
+      }
+      ninv = lane < 6 ? d.binv[6 * (size_t)j + lane] : 0.0;
+      ny = lane < 6 ? d.dc[6 * j + lane] : 0.0;
+    };
+    if (N > 0) fetch(N - 1);
     for (int j = N - 1; j >= 0; --j) {
       const int wj = min(w, N - 1 - j);
       const double* g = d.band + (size_t)j * W1 * 36;
-      // t[c] = y_j[c] - sum_a sum_r L_{j+a,j}[r][c] x_{j+a}[r]; lanes: c = lane % 6, a-slices by lane / 6 (5 slices)
-      double t = 0.0;
-      const int c = lane % 6, sl = lane / 6;
-      if (lane < 30) {
-        for (int a = 1 + sl; a <= wj; a += 5) {
-          const double* blk = g + 36 * a;
-          const double* xa = xs + 6 * ((j + a) % W1);
+      double blk[6], dg[6];
 #pragma unroll
-          for (int r = 0; r < 6; ++r) t = fma(blk[6 * r + c], xa[r], t);
+      for (int r = 0; r < 6; ++r) { blk[r] = nb[r]; dg[r] = nd[r]; }
+      const double inv_c = ninv, yc = ny;
+      if (j > 0) fetch(j - 1);
+      // t[c] = sum_a sum_r L_{j+a,j}[r][c] x_{j+a}[r]
+      double t = 0.0;
+      if (lane < 30 && 1 + sl <= wj) {
+        const double* xa = xs + 6 * ((j + 1 + sl) % W1);
+#pragma unroll
+        for (int r = 0; r < 6; ++r) t = fma(blk[r], xa[r], t);
+        for (int a = 6 + sl; a <= wj; a += 5) {         // bandwidths > 5: further slices, loaded in place
+          const double* bl2 = g + 36 * a;
+          const double* xa2 = xs + 6 * ((j + a) % W1);
+#pragma unroll
+          for (int r = 0; r < 6; ++r) t = fma(bl2[6 * r + c], xa2[r], t);
         }
       }
       t += __shfl_down_sync(0xffffffffu, t, 6) + __shfl_down_sync(0xffffffffu, t, 12) +
            __shfl_down_sync(0xffffffffu, t, 18) + __shfl_down_sync(0xffffffffu, t, 24);
-      // lanes 0..5 hold the sums; solve L_jj^T x = y - t serially on lane 0 (6x6)
-      double rhs = lane < 6 ? d.dc[6 * j + lane] - t : 0.0;
-      double x[6];
+      // lanes 0..5: solve L_jj^T x = y - t by back substitution, one shuffle per component
+      double xc = yc - t;                               // lane c holds component c
 #pragma unroll
-      for (int i = 0; i < 6; ++i) x[i] = __shfl_sync(0xffffffffu, rhs, i);
-      if (lane == 0) {
-#pragma unroll
-        for (int i = 5; i >= 0; --i) {
-          double v = x[i];
-#pragma unroll
-          for (int k = 0; k < 6; ++k)
-            if (k > i) v = fma(-g[6 * k + i], x[k], v);
-          x[i] = v * d.binv[6 * (size_t)j + i];
-        }
-#pragma unroll
-        for (int i = 0; i < 6; ++i) { xs[6 * (j % W1) + i] = x[i]; d.dc[6 * j + i] = x[i]; }
+      for (int i = 5; i >= 0; --i) {
+        const double xi = __shfl_sync(0xffffffffu, xc * inv_c, i);   // x_i is final when its turn comes
+        if (lane == i) xc = xi;
+        else if (lane < i) xc = fma(-dg[i], xi, xc);    // L[i][c] of lane c = dg[i]
       }
+      if (lane < 6) { xs[6 * (j % W1) + lane] = xc; d.dc[6 * j + lane] = xc; }
       __syncwarp();
     }
   }
@@ -208,7 +227,7 @@ __global__ void __launch_bounds__(kBandThreads) large_band_chol_kernel(LargeData
 
 size_t large_band_smem(int bw) {
   const size_t W1 = (size_t)bw + 1;
-  return (W1 * (W1 * 36 + 6) + W1 * 6 + 36) * sizeof(double);
+  return ((W1 + kBandAhead) * (W1 * 36 + 6) + W1 * 6 + 36) * sizeof(double);
 }
 
 int large_band_solve(const LargeData& d, cudaStream_t s) {

@@ -82,6 +82,6 @@ int large_pcg_grid(int n, int* blocks, size_t* smem);   // cooperative launch ge
 // exact banded Cholesky solve of S dc = -g_red (ba_band.cu); needs d.bw >= 0
 size_t large_band_smem(int bw);
 int large_band_solve(const LargeData& d, cudaStream_t s);
-constexpr int kBandMaxBw = 23;     // (bw+1)^2 blocks of shared memory: 24 x 24 x 288 B = 166 KB
+constexpr int kBandMaxBw = 22;     // (bw+4) x (bw+1) blocks of shared memory: 26 x 23 x 288 B = 172 KB
 
 }  // namespace b2
