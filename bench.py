@@ -305,12 +305,22 @@ def main():
     d2h = hb["poses"].nbytes + hb["points"].nbytes + 48 * b.nb
     out_host = (pin(np.empty_like(b.poses, dtype=np.float64)), pin(np.empty_like(b.points, dtype=np.float64)))
     e2e_steps = max(2, min(args.steps, 3))
+    from types import SimpleNamespace
+    hbatch = SimpleNamespace(poses=hb["poses"], points=hb["points"], obs_cam=hb["obs_cam"], obs_pt=hb["obs_pt"],
+                             obs_uv=hb["obs_uv"], fixed_cam=hb["fixed"], cam_off=b.cam_off, pt_off=b.pt_off,
+                             obs_off=b.obs_off)
+    if not c5:
+        ba.optimize_batch(hbatch, out=out_host)     # warm-up of the pipelined path (child engines, streams)
     barrier()
     t0 = time.perf_counter()
     for _ in range(e2e_steps):
-        ba.set_problem(hb["poses"], hb["points"], hb["obs_cam"], hb["obs_pt"], hb["obs_uv"], hb["fixed"], *offs)
-        ba.solve(stream=stream)
-        ba.get(out=out_host)            # refined poses / landmarks into pinned host buffers
+        if c5:
+            ba.set_problem(hb["poses"], hb["points"], hb["obs_cam"], hb["obs_pt"], hb["obs_uv"], hb["fixed"], *offs)
+            ba.solve(stream=stream)
+            ba.get(out=out_host)            # refined poses / landmarks into pinned host buffers
+        else:
+            # the public batch call: chunked H2D copies / index build + solve / D2H read-back overlap on three streams
+            ba.optimize_batch(hbatch, out=out_host)
     barrier()
     t_e2e = (time.perf_counter() - t0) / e2e_steps
 

@@ -89,6 +89,18 @@ int b2ba_get_summaries(b2ba_t* h, b2ba_summary* summaries);
 
 int b2ba_get(b2ba_t* h, double* poses_cw, double* points, int mem);
 
+/* Pipelined end-to-end batch solve (BASELINE config 4): set_problem_batch + solve + get in one call, with the
+ * windows cut into `chunks` (<= 0: 8) contiguous chunks whose host->device copies, index build + solve and
+ * device->host read-back overlap on three streams.  HOST buffers only (pinned memory makes the copies
+ * asynchronous); window problems only (<= 24 cameras per window).  out_poses_cw / out_points / summaries (B
+ * entries) receive the results; the handle keeps no problem afterwards (b2ba_get / b2ba_dump need set_problem).
+ * Results are identical to set_problem_batch + solve + get (each window is solved by the same kernel). */
+int b2ba_optimize_batch(b2ba_t* h, int32_t B, const int32_t* cam_off, const int32_t* pt_off,
+                        const int64_t* obs_off, const double* poses_cw, const double* points,
+                        const int32_t* obs_cam, const int32_t* obs_pt, const float* obs_uv,
+                        const uint8_t* fixed_cam, const double intr[4], int32_t max_iters,
+                        double* out_poses_cw, double* out_points, b2ba_summary* summaries, int32_t chunks);
+
 /* Per-stage intermediates for parity tests.  `what` selects the array; `bytes` is the size of dst
  * (HOST memory); returns the number of bytes written or <0. */
 enum {

@@ -208,3 +208,23 @@ def test_full_size_properties_c4_slice(engine):
     ba.set_problem(b.poses, b.points, oc, op, uv, b.fixed_cam, b.cam_off, b.pt_off, b.obs_off)
     ba.solve(); p4, x4 = ba.get()
     assert np.array_equal(p1, p4) and np.array_equal(x1, x4)
+
+
+def test_pipelined_batch_call_equals_set_solve_get(engine):
+    """b2ba_optimize_batch (chunked copies / solves / read-backs on three streams) returns exactly what
+    set_problem_batch + solve + get return: each window is solved by the same kernel on the same data."""
+    b = synth.make_batch(60, seed0=900, distinct=12)
+    from visualodometry_b200 import BAConfig, BundleAdjuster
+    ba = BundleAdjuster(K_of(b), BAConfig(max_iters=6))
+    ba.set_problem(b.poses, b.points, b.obs_cam, b.obs_pt, b.obs_uv, b.fixed_cam, b.cam_off, b.pt_off, b.obs_off)
+    s1 = ba.solve(); p1, x1 = ba.get()
+    for chunks in (1, 7):
+        res = ba.optimize_batch(b, chunks=chunks)
+        poses = np.concatenate([res.T_cw[:, :3, :3].reshape(-1, 9), res.T_cw[:, :3, 3]], axis=1)
+        assert np.array_equal(poses, p1) and np.array_equal(res.points, x1), chunks
+        assert [(s.status, s.accepted, s.final_cost) for s in res.summaries] == [(s.status, s.accepted, s.final_cost) for s in s1]
+    bad = synth.make_batch(4, seed0=1)
+    bad.obs_cam = bad.obs_cam.copy(); bad.obs_cam[5] = 99
+    with pytest.raises(RuntimeError, match="out of range"):
+        ba.optimize_batch(bad)
+    ba.close()

@@ -253,11 +253,33 @@ class BundleAdjuster:
         poses_o, pts_o = self.get()
         return BAResult(T_from_poses(poses_o), pts_o, sm[0], sm)
 
-    def optimize_batch(self, batch) -> BAResult:
-        """C4: a synth.BABatch-like object with CSR offsets; poses in (Nc,12) layout."""
-        self.set_problem(batch.poses, batch.points, batch.obs_cam, batch.obs_pt, batch.obs_uv,
-                         batch.fixed_cam, batch.cam_off, batch.pt_off, batch.obs_off)
-        sm = self.solve()
-        poses_o, pts_o = self.get()
+    def optimize_batch(self, batch, out=None, chunks=0) -> BAResult:
+        """C4: a synth.BABatch-like object with CSR offsets; poses in (Nc,12) layout.  Host arrays go through the
+        pipelined C-ABI call (copies of one chunk of windows overlap the solve of another); `out=(poses, points)`
+        are optional caller-owned (e.g. pinned) result arrays."""
+        arrs = (batch.poses, batch.points, batch.obs_cam, batch.obs_pt, batch.obs_uv, batch.fixed_cam)
+        if self.config.record_history or any(_is_cuda_tensor(a) for a in arrs):    # history dumps need handle state
+            self.set_problem(*arrs, batch.cam_off, batch.pt_off, batch.obs_off)
+            sm = self.solve()
+            poses_o, pts_o = self.get()
+        else:
+            a = [_Arg(batch.poses, np.float64, "float64", False), _Arg(batch.points, np.float64, "float64", False),
+                 _Arg(batch.obs_cam, np.int32, "int32", False), _Arg(batch.obs_pt, np.int32, "int32", False),
+                 _Arg(batch.obs_uv, np.float32, "float32", False), _Arg(batch.fixed_cam, np.uint8, "uint8", False)]
+            co = np.ascontiguousarray(batch.cam_off, np.int32)
+            po = np.ascontiguousarray(batch.pt_off, np.int32)
+            oo = np.ascontiguousarray(batch.obs_off, np.int64)
+            nb, nc, npts = len(co) - 1, int(co[-1]), int(po[-1])
+            poses_o, pts_o = out if out is not None else (np.empty((nc, 12)), np.empty((npts, 3)))
+            for arr, size in ((poses_o, nc * 12), (pts_o, npts * 3)):
+                if arr.dtype != np.float64 or arr.size != size or not arr.flags.c_contiguous:
+                    raise ValueError("optimize_batch(out=...): C-contiguous float64 arrays of the problem's size required")
+            sms = (_lib.Summary * nb)()
+            rc = self._lib.b2ba_optimize_batch(self._h, nb, co.ctypes.data, po.ctypes.data, oo.ctypes.data,
+                                               *[x.ptr for x in a], self.intr.ctypes.data_as(C.POINTER(C.c_double)), 0,
+                                               poses_o.ctypes.data, pts_o.ctypes.data, sms, chunks)
+            self._check(rc, "b2ba_optimize_batch")
+            sm = [self._summary(x) for x in sms]
+            self._nb, self._shape = 0, None
         worst = max(sm, key=lambda s: s.status)
         return BAResult(T_from_poses(poses_o), pts_o, worst, sm)

@@ -56,6 +56,14 @@ struct b2ba {
   // multi-GPU
   int rank = 0, nranks = 1;
   void* nccl_comm = nullptr;
+  // pipelined batch call (b2ba_optimize_batch): child engines (one per chunk) and their streams / events
+  std::vector<b2ba*> kids;
+  cudaStream_t pipe_copy = nullptr, pipe_solve = nullptr, pipe_solve2 = nullptr, pipe_back = nullptr;
+  std::vector<cudaEvent_t> ev_in, ev_done;
+  int* pinned_flags = nullptr;     // 2 ints per chunk (index-builder range / duplicate flags)
+  char* pinned_stage = nullptr;    // summaries + rebased offsets (pinned: async copies never block the enqueue loop)
+  size_t pinned_stage_bytes = 0;
+  int wave_small = 0, wave_big = 0;   // windows one launch wave holds (CTAs per SM x SMs)
 };
 
 namespace {
@@ -97,6 +105,15 @@ WinData make_win(b2ba* h, bool hist, double* dbg) {
   d.hist_accept = hist ? h->d_hist_accept.p : nullptr;
   d.dbg = dbg;
   return d;
+}
+
+// few windows: the latency path, one 8/16-CTA cluster per window (B2BA_CLUSTER=0 or options.flags bit 1 force
+// one CTA per window)
+int launch_window_path(const b2ba* h, const WinData& wd, const Params& P, cudaStream_t s) {
+  static const bool cluster_on = [] { const char* e = std::getenv("B2BA_CLUSTER"); return !e || std::atoi(e) != 0; }();
+  const bool clus = cluster_on && !(h->opt.flags & 2) && h->B <= 18;
+  if (h->path == PATH_WIN_SMALL) return clus ? launch_window_small_cluster(wd, P, s) : launch_window_small(wd, P, s);
+  return clus ? launch_window_big_cluster(wd, P, s) : launch_window_big(wd, P, s);
 }
 
 cudaMemcpyKind in_kind(int mem) { return mem == B2BA_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice; }
@@ -272,6 +289,15 @@ int b2ba_create(b2ba_t** out, int device, const b2ba_options* opts) {
 void b2ba_destroy(b2ba_t* h) {
   if (!h) return;
   cudaSetDevice(h->device);
+  for (b2ba* k : h->kids) b2ba_destroy(k);
+  for (cudaEvent_t e : h->ev_in) cudaEventDestroy(e);
+  for (cudaEvent_t e : h->ev_done) cudaEventDestroy(e);
+  if (h->pipe_copy) cudaStreamDestroy(h->pipe_copy);
+  if (h->pipe_solve) cudaStreamDestroy(h->pipe_solve);
+  if (h->pipe_solve2) cudaStreamDestroy(h->pipe_solve2);
+  if (h->pinned_stage) cudaFreeHost(h->pinned_stage);
+  if (h->pipe_back) cudaStreamDestroy(h->pipe_back);
+  if (h->pinned_flags) cudaFreeHost(h->pinned_flags);
   if (h->nccl_comm && nccl_api().ok) nccl_api().CommDestroy(h->nccl_comm);
   delete h;
 }
@@ -411,13 +437,7 @@ int b2ba_solve(b2ba_t* h, int32_t max_iters, b2ba_summary* summaries, void* cuda
     CU(cudaMemsetAsync(h->d_hist_accept.p, 0, (size_t)h->B * kHist * 4, s), "memset");
   }
   int rc = 0;
-  // few windows: the latency path, one 8-CTA cluster per window (B2BA_CLUSTER=0 forces one CTA per window)
-  static const bool cluster_on = [] { const char* e = std::getenv("B2BA_CLUSTER"); return !e || std::atoi(e) != 0; }();
-  const bool clus = cluster_on && !(h->opt.flags & 2) && h->B <= 18;
-  if (h->path == PATH_WIN_SMALL)
-    rc = clus ? launch_window_small_cluster(make_win(h, hist, nullptr), P, s) : launch_window_small(make_win(h, hist, nullptr), P, s);
-  else if (h->path == PATH_WIN_BIG)
-    rc = clus ? launch_window_big_cluster(make_win(h, hist, nullptr), P, s) : launch_window_big(make_win(h, hist, nullptr), P, s);
+  if (h->path == PATH_WIN_SMALL || h->path == PATH_WIN_BIG) rc = launch_window_path(h, make_win(h, hist, nullptr), P, s);
   else if (h->path == PATH_LARGE) {
     if (hist) { CU(h->d_hist_cost.alloc(kHist), "alloc"); }
     rc = solve_large(h, P, hist, s);
@@ -442,6 +462,147 @@ int b2ba_get(b2ba_t* h, double* poses_cw, double* points, int mem) {
   if (points) CU(cudaMemcpyAsync(points, h->d_pts0.p, (size_t)h->np_tot * 3 * sizeof(double), k, s), "read points");
   CU(cudaStreamSynchronize(s), "get");
   return B2BA_OK;
+}
+
+// Pipelined batch solve (C4 end to end): the windows are cut into `chunks` contiguous chunks; chunk i's host->device
+// copies (copy stream), index build + LM solve (solve stream) and device->host read-back (read-back stream)
+// overlap with the neighbouring chunks', so the copies hide behind the solves.  Host buffers only; pinned
+// memory makes the copies truly asynchronous.  Every chunk is an independent sub-problem (own index arrays).
+int b2ba_optimize_batch(b2ba_t* h, int32_t B, const int32_t* cam_off, const int32_t* pt_off, const int64_t* obs_off,
+                        const double* poses_cw, const double* points, const int32_t* obs_cam, const int32_t* obs_pt,
+                        const float* obs_uv, const uint8_t* fixed_cam, const double intr[4], int32_t max_iters,
+                        double* out_poses_cw, double* out_points, b2ba_summary* summaries, int32_t chunks) {
+  if (!h) return B2BA_E_INVALID;
+  if (B < 1 || !cam_off || !pt_off || !obs_off || !poses_cw || !points || !fixed_cam || !intr || !out_poses_cw ||
+      !out_points || !summaries)
+    return fail(h, B2BA_E_INVALID, "optimize_batch: null argument or B < 1");
+  if (h->nranks > 1) return fail(h, B2BA_E_UNSUPPORTED, "optimize_batch is single-GPU (windows shard across ranks on the host side)");
+  for (int b = 0; b < B; ++b)
+    if (cam_off[b + 1] < cam_off[b] || pt_off[b + 1] < pt_off[b] || obs_off[b + 1] < obs_off[b])
+      return fail(h, B2BA_E_INVALID, "offsets must be non-decreasing");
+  if (obs_off[B] > 0 && (!obs_cam || !obs_pt || !obs_uv)) return fail(h, B2BA_E_INVALID, "null observation arrays");
+  CU(cudaSetDevice(h->device), "cudaSetDevice");
+  if (!h->pipe_copy) {
+    CU(cudaStreamCreateWithFlags(&h->pipe_copy, cudaStreamNonBlocking), "stream");
+    CU(cudaStreamCreateWithFlags(&h->pipe_solve, cudaStreamNonBlocking), "stream");
+    CU(cudaStreamCreateWithFlags(&h->pipe_solve2, cudaStreamNonBlocking), "stream");
+    CU(cudaStreamCreateWithFlags(&h->pipe_back, cudaStreamNonBlocking), "stream");
+    int regs = 0, smem = 0, per_sm = 0, sms = 0;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->device);
+    if (window_kernel_attrs(0, &regs, &smem, &per_sm) == 0) h->wave_small = per_sm * sms;
+    if (window_kernel_attrs(1, &regs, &smem, &per_sm) == 0) h->wave_big = per_sm * sms;
+  }
+  // path of the whole batch (every chunk runs the same kernel family)
+  int max_nc = 0, max_nfree = 0;
+  for (int b = 0; b < B; ++b) {
+    int nf = 0;
+    for (int q = cam_off[b]; q < cam_off[b + 1]; ++q) nf += fixed_cam[q] ? 0 : 1;
+    if (nf > max_nfree) max_nfree = nf;
+    if (cam_off[b + 1] - cam_off[b] > max_nc) max_nc = cam_off[b + 1] - cam_off[b];
+  }
+  Path path;
+  if (max_nc <= kSmallMaxCam && max_nfree <= kSmallMaxFree) path = PATH_WIN_SMALL;
+  else if (max_nc <= kMaxCam && max_nfree <= kBigMaxFree) path = PATH_WIN_BIG;
+  else return fail(h, B2BA_E_UNSUPPORTED, "optimize_batch takes window problems (<= 24 cameras, <= 21 free per window)");
+  // chunk boundaries: with chunks <= 0 they fall on multiples of one launch wave (no partial waves inside the
+  // batch): a first chunk of one wave (the solve starts early), then two waves per chunk; few windows -> one
+  // chunk on the cluster (latency) path
+  std::vector<int> cut{0};
+  const int wave = path == PATH_WIN_SMALL ? h->wave_small : h->wave_big;
+  if (B <= 18) cut.push_back(B);
+  else if (chunks > 0) { const int K = chunks > B ? B : chunks; for (int c = 1; c <= K; ++c) cut.push_back((int)((long long)B * c / K)); }
+  else if (wave <= 0 || B <= 2 * wave) cut.push_back(B);
+  else { int w = wave; while (w < B) { cut.push_back(w); w += 2 * wave; } cut.push_back(B); }
+  const int K = (int)cut.size() - 1;
+  while ((int)h->kids.size() < K) {
+    b2ba* k = nullptr;
+    const int rc = b2ba_create(&k, h->device, &h->opt);
+    if (rc) return fail(h, rc, "optimize_batch: child engine");
+    h->kids.push_back(k);
+    cudaEvent_t e0, e1;
+    CU(cudaEventCreateWithFlags(&e0, cudaEventDisableTiming), "event");
+    CU(cudaEventCreateWithFlags(&e1, cudaEventDisableTiming), "event");
+    h->ev_in.push_back(e0); h->ev_done.push_back(e1);
+    if (h->pinned_flags) { cudaFreeHost(h->pinned_flags); h->pinned_flags = nullptr; }
+  }
+  if (!h->pinned_flags) CU(cudaMallocHost((void**)&h->pinned_flags, sizeof(int) * 2 * h->kids.size()), "pinned flags");
+  const size_t off_bytes = ((size_t)B + K) * (2 * sizeof(int) + sizeof(long long));
+  const size_t need = (size_t)B * sizeof(b2ba_summary) + off_bytes + 64;
+  if (need > h->pinned_stage_bytes) {
+    if (h->pinned_stage) cudaFreeHost(h->pinned_stage);
+    h->pinned_stage = nullptr; h->pinned_stage_bytes = 0;
+    CU(cudaMallocHost((void**)&h->pinned_stage, need), "pinned staging");
+    h->pinned_stage_bytes = need;
+  }
+  b2ba_summary* st_summ = reinterpret_cast<b2ba_summary*>(h->pinned_stage);
+  long long* st_obs = reinterpret_cast<long long*>(h->pinned_stage + (((size_t)B * sizeof(b2ba_summary) + 15) / 16) * 16);
+  int* st_cam = reinterpret_cast<int*>(st_obs + B + K);
+  int* st_pt = st_cam + B + K;
+  const Params P = make_params(h, max_iters);
+  h->path = PATH_NONE;                       // results live in the caller's buffers, not in this handle
+  size_t stpos = 0;
+  for (int c = 0; c < K; ++c) {
+    b2ba* k = h->kids[c];
+    k->opt = h->opt;
+    if (B > 18) k->opt.flags |= 2;           // the batch decides the kernel family, not the chunk size
+    const int w0 = cut[c], w1 = cut[c + 1], nb = w1 - w0;
+    const size_t c0 = cam_off[w0], nc = cam_off[w1] - c0, p0 = pt_off[w0], np = pt_off[w1] - p0;
+    const long long o0 = obs_off[w0], no = obs_off[w1] - o0;
+    if (no >= (1ll << 31)) return fail(h, B2BA_E_UNSUPPORTED, "more than 2^31 observations per chunk");
+    k->B = nb; k->nc_tot = (int)nc; k->np_tot = (int)np; k->no = no; k->path = path;
+    std::memcpy(k->intr, intr, 4 * sizeof(double));
+    int* sc = st_cam + stpos; int* sp = st_pt + stpos; long long* so = st_obs + stpos;
+    stpos += nb + 1;
+    for (int b = 0; b <= nb; ++b) {
+      sc[b] = cam_off[w0 + b] - (int)c0; sp[b] = pt_off[w0 + b] - (int)p0; so[b] = obs_off[w0 + b] - o0;
+    }
+    CU(k->d_cam_off.alloc(nb + 1), "alloc"); CU(k->d_pt_off.alloc(nb + 1), "alloc"); CU(k->d_obs_off.alloc(nb + 1), "alloc");
+    CU(k->d_fixed.alloc(nc), "alloc"); CU(k->d_poses.alloc(nc * 12), "alloc");
+    CU(k->d_pts0.alloc(np * 3), "alloc"); CU(k->d_pts1.alloc(np * 3), "alloc"); CU(k->d_scratch.alloc(np * kPtScratch), "alloc");
+    CU(k->d_obs_cam.alloc(no), "alloc"); CU(k->d_obs_pt.alloc(no), "alloc"); CU(k->d_uv.alloc(no), "alloc");
+    CU(k->d_pm.alloc(no), "alloc"); CU(k->d_cm.alloc(no), "alloc");
+    CU(k->d_pt_ptr.alloc(np + 1), "alloc"); CU(k->d_cam_ptr.alloc(nc + 1), "alloc"); CU(k->d_flags.alloc(2), "alloc");
+    CU(k->d_summ.alloc(nb), "alloc");
+    cudaStream_t cs = h->pipe_copy, ks = (c & 1) ? h->pipe_solve2 : h->pipe_solve, bs = h->pipe_back;
+    const cudaMemcpyKind hd = cudaMemcpyHostToDevice, dh = cudaMemcpyDeviceToHost;
+    // nothing of an earlier call is in flight: every call ends with a synchronisation of all streams
+    CU(cudaMemcpyAsync(k->d_cam_off.p, sc, (nb + 1) * sizeof(int), hd, cs), "copy");
+    CU(cudaMemcpyAsync(k->d_pt_off.p, sp, (nb + 1) * sizeof(int), hd, cs), "copy");
+    CU(cudaMemcpyAsync(k->d_obs_off.p, so, (nb + 1) * sizeof(long long), hd, cs), "copy");
+    CU(cudaMemcpyAsync(k->d_fixed.p, fixed_cam + c0, nc, hd, cs), "copy");
+    CU(cudaMemcpyAsync(k->d_poses.p, poses_cw + c0 * 12, nc * 12 * sizeof(double), hd, cs), "copy");
+    CU(cudaMemcpyAsync(k->d_pts0.p, points + p0 * 3, np * 3 * sizeof(double), hd, cs), "copy");
+    if (no) {
+      CU(cudaMemcpyAsync(k->d_obs_cam.p, obs_cam + o0, no * sizeof(int), hd, cs), "copy");
+      CU(cudaMemcpyAsync(k->d_obs_pt.p, obs_pt + o0, no * sizeof(int), hd, cs), "copy");
+      CU(cudaMemcpyAsync(k->d_uv.p, obs_uv + 2 * o0, no * sizeof(float2), hd, cs), "copy");
+    }
+    CU(cudaEventRecord(h->ev_in[c], cs), "event");
+    CU(cudaStreamWaitEvent(ks, h->ev_in[c], 0), "wait");
+    IndexOut io{k->d_pm.p, k->d_pt_ptr.p, k->d_cm.p, k->d_cam_ptr.p, k->d_flags.p};
+    int rc = build_index(make_index_in(k), io, ks);
+    if (rc) return cuda_fail(h, (cudaError_t)rc, "build_index");
+    rc = launch_window_path(k, make_win(k, false, nullptr), P, ks);
+    if (rc) return cuda_fail(h, (cudaError_t)rc, "launch");
+    CU(cudaEventRecord(h->ev_done[c], ks), "event");
+    CU(cudaStreamWaitEvent(bs, h->ev_done[c], 0), "wait");
+    CU(cudaMemcpyAsync(out_poses_cw + c0 * 12, k->d_poses.p, nc * 12 * sizeof(double), dh, bs), "read");
+    CU(cudaMemcpyAsync(out_points + p0 * 3, k->d_pts0.p, np * 3 * sizeof(double), dh, bs), "read");
+    CU(cudaMemcpyAsync(st_summ + w0, k->d_summ.p, nb * sizeof(b2ba_summary), dh, bs), "read");
+    CU(cudaMemcpyAsync(h->pinned_flags + 2 * c, k->d_flags.p, 2 * sizeof(int), dh, bs), "read");
+  }
+  CU(cudaStreamSynchronize(h->pipe_copy), "optimize_batch");
+  CU(cudaStreamSynchronize(h->pipe_solve), "optimize_batch");
+  CU(cudaStreamSynchronize(h->pipe_solve2), "optimize_batch");
+  CU(cudaStreamSynchronize(h->pipe_back), "optimize_batch");
+  for (int c = 0; c < K; ++c) {
+    if (h->pinned_flags[2 * c]) return fail(h, B2BA_E_INVALID, "observation index out of range");
+    if (h->pinned_flags[2 * c + 1]) return fail(h, B2BA_E_DUPLICATE, "duplicate (camera, point) observation");
+  }
+  std::memcpy(summaries, st_summ, (size_t)B * sizeof(b2ba_summary));
+  int worst = 0;
+  for (int b = 0; b < B; ++b) if (summaries[b].status > worst) worst = summaries[b].status;
+  return worst;
 }
 
 int b2ba_create_comm(b2ba_t* h, const void* nccl_unique_id, int rank, int nranks) {
