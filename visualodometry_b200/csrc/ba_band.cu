@@ -76,7 +76,7 @@ __global__ void __launch_bounds__(kBandThreads) large_band_chol_kernel(LargeData
       for (int k = 0; k < 6; ++k)
         if (k < c) dj = fma(-L[c][k], L[c][k], dj);
       if (!(dj > 0.0) || !isfinite(dj)) { isbad = true; dj = 1.0; }
-      inv[c] = rsqrt(dj);
+      inv[c] = rsqrt_pos(dj);
       L[c][c] = dj * inv[c];
 #pragma unroll
       for (int r = 0; r < 6; ++r) {

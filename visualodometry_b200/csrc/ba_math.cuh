@@ -148,6 +148,34 @@ __device__ __forceinline__ double rcp_depth(double z) {
   return y;
 }
 
+// 1/sqrt(x) for x > 0 without the library's slow path: rsqrt.approx.ftz.f64 seed (MUFU.RSQ64H) + two
+// Newton steps (-> below 2^-52 relative).  Branch-free.
+__device__ __forceinline__ double rsqrt_pos(double x) {
+  double y;
+  asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+  const double hx = 0.5 * x;
+  y = y * fma(-hx * y, y, 1.5);
+  y = y * fma(-hx * y, y, 1.5);
+  return y;
+}
+
+// sym3_inv_factor with reciprocal square roots only (no sqrt, no division): F = G^-T for C' = G G^T.
+__device__ __forceinline__ bool sym3_inv_factor_fast(const double* C, double* F) {
+  const double a = C[0];
+  const double ia = rsqrt_pos(a);
+  const double b = C[1] * ia, d = C[2] * ia;
+  const double c2 = fma(-b, b, C[3]);
+  const double ic = rsqrt_pos(c2);
+  const double e = fma(-b, d, C[4]) * ic;
+  const double f2 = fma(-e, e, fma(-d, d, C[5]));
+  const double ifr = rsqrt_pos(f2);
+  const double c = c2 * ic;                       // sqrt(c2)
+  F[0] = ia;  F[1] = -b * ia * ic;  F[2] = fma(b, e, -(c * d)) * ia * ic * ifr;
+  F[3] = ic;  F[4] = -e * ic * ifr;
+  F[5] = ifr;
+  return (a > 0.0) && (c2 > 0.0) && (f2 > 0.0) && isfinite(f2);
+}
+
 // fire-and-forget L1 prefetch of the 128-byte line holding p (no register cost)
 __device__ __forceinline__ void prefetch_l1(const void* p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
 

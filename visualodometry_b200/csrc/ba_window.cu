@@ -324,7 +324,7 @@ window_lm_kernel(const WinData d, const Params P) {
       double F[6];
       {
         const double Cd[6] = {fma(D0, imu, C[0]), C[1], C[2], fma(D1, imu, C[3]), C[4], fma(D2, imu, C[5])};
-        if (!sym3_inv_factor(Cd, F)) {
+        if (!sym3_inv_factor_fast(Cd, F)) {
 #pragma unroll
           for (int k = 0; k < 6; ++k) F[k] = 0.0;
           if (act) iflag[0] = 1;
@@ -505,7 +505,7 @@ window_lm_kernel(const WinData d, const Params P) {
         for (int k = 0; k < 6; ++k)
           if (k < c) dj = fma(-L[c][k], L[c][k], dj);
         if (!(dj > 0.0) || !isfinite(dj)) { bad = true; dj = 1.0; }
-        inv[c] = rsqrt(dj);
+        inv[c] = rsqrt_pos(dj);
         L[c][c] = dj * inv[c];
 #pragma unroll
         for (int r = 0; r < 6; ++r) {
