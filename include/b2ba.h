@@ -106,6 +106,7 @@ int b2ba_optimize_batch(b2ba_t* h, int32_t B, const int32_t* cam_off, const int3
 enum {
   B2BA_D_PM_PERM = 1, B2BA_D_PT_PTR, B2BA_D_CM_PERM, B2BA_D_CAM_PTR, B2BA_D_FIDX, B2BA_D_BLK_PTR,
   B2BA_D_BLK_COL,                       /* a8 index arrays (int32) */
+  B2BA_D_SCHED,                         /* landmark schedule: per window, local ids by decreasing observation count (stable) */
   B2BA_D_RESIDUALS = 16, B2BA_D_WEIGHTS, B2BA_D_JC, B2BA_D_JP,   /* a1, original obs order */
   B2BA_D_B = 32, B2BA_D_GC, B2BA_D_C, B2BA_D_GP, B2BA_D_S, B2BA_D_GRED, B2BA_D_DC, B2BA_D_DP,
   B2BA_D_SCALARS,                       /* one LM iteration at init_mu from the CURRENT state */

@@ -66,6 +66,25 @@ def test_index_bit_exact(engine, oracle, name):
     ba.close()
 
 
+def test_landmark_schedule_is_stable_count_sort(engine):
+    """The window kernel walks the landmarks of a window by decreasing observation count (ties in id order), so
+    that the landmarks sharing a warp do the same number of rounds.  Checked on a ragged batch with an
+    unobserved landmark and an empty window."""
+    ps = [synth.make_window(s, n_cams=6 + s, n_pts=150 + 40 * s, n_obs=900 + 300 * s) for s in range(3)]
+    keep = ps[1].obs_pt != 7                       # landmark 7 of window 1 loses all its observations
+    ps[1].obs_cam, ps[1].obs_pt, ps[1].obs_uv = ps[1].obs_cam[keep], ps[1].obs_pt[keep], ps[1].obs_uv[keep]
+    b = synth.pack_batch(ps)
+    ba = engine(ps[0])
+    ba.set_problem(b.poses, b.points, b.obs_cam, b.obs_pt, b.obs_uv, b.fixed_cam, b.cam_off, b.pt_off, b.obs_off)
+    sched = ba.dump("SCHED", (b.points.shape[0],), np.int32)
+    for w in range(len(ps)):
+        p0, p1 = b.pt_off[w], b.pt_off[w + 1]
+        o0, o1 = b.obs_off[w], b.obs_off[w + 1]
+        k = np.bincount(b.obs_pt[o0:o1], minlength=p1 - p0)
+        assert np.array_equal(sched[p0:p1], np.argsort(-k, kind="stable")), w
+    ba.close()
+
+
 @pytest.mark.parametrize("name", list(PROBLEMS))
 def test_stage_parity(engine, oracle, name):
     """every intermediate of one LM iteration: a1 per observation, a2 blocks, a4 S / g_red, a5 delta_c,

@@ -11,7 +11,7 @@ LIB_PATH = os.path.join(HERE, "libb2ba.so")
 OK, E_INVALID, E_CUDA, E_NCCL, E_DUPLICATE, E_STATE, E_UNSUPPORTED = 0, -1, -2, -3, -4, -5, -6
 MAX_ITERS, CONVERGED, NUMERICAL_FAILURE = 1, 2, 3
 MEM_HOST, MEM_DEVICE = 0, 1
-D = dict(PM_PERM=1, PT_PTR=2, CM_PERM=3, CAM_PTR=4, FIDX=5, BLK_PTR=6, BLK_COL=7,
+D = dict(PM_PERM=1, PT_PTR=2, CM_PERM=3, CAM_PTR=4, FIDX=5, BLK_PTR=6, BLK_COL=7, SCHED=8,
          RESIDUALS=16, WEIGHTS=17, JC=18, JP=19,
          B=32, GC=33, C=34, GP=35, S=36, GRED=37, DC=38, DP=39, SCALARS=40,
          HIST_COST=64, HIST_MU=65, HIST_ACCEPT=66)

@@ -35,7 +35,7 @@ struct b2ba {
   std::vector<int> h_cam_off, h_pt_off;
   std::vector<long long> h_obs_off;
   std::vector<unsigned char> h_fixed;
-  DevBuf<int> d_cam_off, d_pt_off, d_obs_cam, d_obs_pt, d_pt_ptr, d_cam_ptr, d_flags, d_hist_accept;
+  DevBuf<int> d_cam_off, d_pt_off, d_obs_cam, d_obs_pt, d_pt_ptr, d_cam_ptr, d_flags, d_hist_accept, d_sched;
   DevBuf<long long> d_obs_off;
   DevBuf<float2> d_uv;
   DevBuf<unsigned char> d_fixed;
@@ -97,7 +97,7 @@ IndexIn make_index_in(const b2ba* h) {
 WinData make_win(b2ba* h, bool hist, double* dbg) {
   WinData d;
   d.nb = h->B; d.cam_off = h->d_cam_off.p; d.pt_off = h->d_pt_off.p;
-  d.pm = h->d_pm.p; d.pt_ptr = h->d_pt_ptr.p; d.cm = h->d_cm.p; d.cam_ptr = h->d_cam_ptr.p;
+  d.pm = h->d_pm.p; d.pt_ptr = h->d_pt_ptr.p; d.cm = h->d_cm.p; d.cam_ptr = h->d_cam_ptr.p; d.sched = h->d_sched.p;
   d.fixed = h->d_fixed.p; d.poses = h->d_poses.p; d.pts[0] = h->d_pts0.p; d.pts[1] = h->d_pts1.p;
   d.pt_scratch = h->d_scratch.p; d.summaries = h->d_summ.p;
   d.hist_cost = hist ? h->d_hist_cost.p : nullptr;
@@ -334,6 +334,7 @@ int b2ba_set_problem_batch(b2ba_t* h, int32_t B, const int32_t* cam_off, const i
   CU(h->d_obs_cam.alloc(no), "alloc"); CU(h->d_obs_pt.alloc(no), "alloc"); CU(h->d_uv.alloc(no), "alloc");
   CU(h->d_pm.alloc(no), "alloc"); CU(h->d_cm.alloc(no), "alloc");
   CU(h->d_pt_ptr.alloc(np + 1), "alloc"); CU(h->d_cam_ptr.alloc(nc + 1), "alloc"); CU(h->d_flags.alloc(2), "alloc");
+  CU(h->d_sched.alloc(np), "alloc");
   CU(h->d_summ.alloc(B), "alloc");
   CU(cudaMemcpy(h->d_cam_off.p, cam_off, (B + 1) * sizeof(int), cudaMemcpyHostToDevice), "copy offsets");
   CU(cudaMemcpy(h->d_pt_off.p, pt_off, (B + 1) * sizeof(int), cudaMemcpyHostToDevice), "copy offsets");
@@ -359,7 +360,7 @@ int b2ba_set_problem_batch(b2ba_t* h, int32_t B, const int32_t* cam_off, const i
     if (cam_off[b + 1] - cam_off[b] > h->max_nc) h->max_nc = cam_off[b + 1] - cam_off[b];
   }
   // a8: index
-  IndexOut io{h->d_pm.p, h->d_pt_ptr.p, h->d_cm.p, h->d_cam_ptr.p, h->d_flags.p};
+  IndexOut io{h->d_pm.p, h->d_pt_ptr.p, h->d_cm.p, h->d_cam_ptr.p, h->d_flags.p, h->d_sched.p};
   int rc = build_index(make_index_in(h), io, nullptr);
   if (rc) return cuda_fail(h, (cudaError_t)rc, "build_index");
   int flags[2] = {0, 0};
@@ -562,6 +563,7 @@ int b2ba_optimize_batch(b2ba_t* h, int32_t B, const int32_t* cam_off, const int3
     CU(k->d_obs_cam.alloc(no), "alloc"); CU(k->d_obs_pt.alloc(no), "alloc"); CU(k->d_uv.alloc(no), "alloc");
     CU(k->d_pm.alloc(no), "alloc"); CU(k->d_cm.alloc(no), "alloc");
     CU(k->d_pt_ptr.alloc(np + 1), "alloc"); CU(k->d_cam_ptr.alloc(nc + 1), "alloc"); CU(k->d_flags.alloc(2), "alloc");
+    CU(k->d_sched.alloc(np), "alloc");
     CU(k->d_summ.alloc(nb), "alloc");
     cudaStream_t cs = h->pipe_copy, ks = (c & 1) ? h->pipe_solve2 : h->pipe_solve, bs = h->pipe_back;
     const cudaMemcpyKind hd = cudaMemcpyHostToDevice, dh = cudaMemcpyDeviceToHost;
@@ -579,7 +581,7 @@ int b2ba_optimize_batch(b2ba_t* h, int32_t B, const int32_t* cam_off, const int3
     }
     CU(cudaEventRecord(h->ev_in[c], cs), "event");
     CU(cudaStreamWaitEvent(ks, h->ev_in[c], 0), "wait");
-    IndexOut io{k->d_pm.p, k->d_pt_ptr.p, k->d_cm.p, k->d_cam_ptr.p, k->d_flags.p};
+    IndexOut io{k->d_pm.p, k->d_pt_ptr.p, k->d_cm.p, k->d_cam_ptr.p, k->d_flags.p, k->d_sched.p};
     int rc = build_index(make_index_in(k), io, ks);
     if (rc) return cuda_fail(h, (cudaError_t)rc, "build_index");
     rc = launch_window_path(k, make_win(k, false, nullptr), P, ks);
@@ -696,6 +698,11 @@ int64_t b2ba_dump(b2ba_t* h, int what, void* dst, int64_t bytes) {
       std::vector<int> v(n);
       CU(cudaMemcpy(v.data(), what == B2BA_D_PT_PTR ? h->d_pt_ptr.p : h->d_cam_ptr.p, n * 4, cudaMemcpyDeviceToHost), "read");
       return put(h, v.data(), n * 4, dst, bytes);
+    }
+    case B2BA_D_SCHED: {
+      std::vector<int> v(h->np_tot);
+      CU(cudaMemcpy(v.data(), h->d_sched.p, v.size() * 4, cudaMemcpyDeviceToHost), "read");
+      return put(h, v.data(), v.size() * 4, dst, bytes);
     }
     case B2BA_D_FIDX: {
       std::vector<int> v(h->nc_tot);

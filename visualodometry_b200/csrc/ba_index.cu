@@ -67,12 +67,54 @@ __global__ void build_cm(IndexIn in, const unsigned* __restrict__ cam_keys, cons
     for (int q = gc + 1; q <= in.nc_tot; ++q) cam_ptr[q] = (int)in.no;
 }
 
+__device__ __forceinline__ int find_window_pt(const int* __restrict__ pt_off, int nb, int g) {
+  int lo = 0, hi = nb;   // pt_off[lo] <= g < pt_off[hi]; empty windows are skipped by taking the LAST match
+  while (hi - lo > 1) {
+    const int mid = (lo + hi) >> 1;
+    if (pt_off[mid] <= g) lo = mid; else hi = mid;
+  }
+  return lo;
+}
+
+// landmark schedule keys: (window, 31 - min(observation count, 31)); value = window-local landmark id
+__global__ void make_sched_keys(IndexIn in, const int* __restrict__ pt_ptr, unsigned* keys, int* vals) {
+  const int g = blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= in.np_tot) return;
+  const int b = find_window_pt(in.pt_off, in.nb, g);
+  const int k = pt_ptr[g + 1] - pt_ptr[g];
+  keys[g] = ((unsigned)b << 5) | (unsigned)(31 - min(k, 31));
+  vals[g] = g - in.pt_off[b];
+}
+
 __global__ void fill_ptr(int* p, int n, int v) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) p[i] = v;
 }
 
 inline int bits_for(long long n) { int b = 1; while ((1ll << b) < n && b < 32) ++b; return b; }
+
+cudaError_t sort_sched(const IndexIn& in, const IndexOut& out, void* tmp, size_t tmp_bytes, cudaStream_t s) {
+  const int np = in.np_tot;
+  unsigned *k0 = nullptr, *k1 = nullptr;
+  int* v0 = nullptr;
+  void* t = nullptr;
+  size_t need = 0;
+  const int bits = 5 + bits_for(in.nb);
+  cudaError_t e = cub::DeviceRadixSort::SortPairs(nullptr, need, k0, k1, v0, out.sched, np, 0, bits, s);
+  if (e != cudaSuccess) return e;
+  if ((e = cudaMallocAsync(&k0, (size_t)np * 4, s)) != cudaSuccess) goto done;
+  if ((e = cudaMallocAsync(&k1, (size_t)np * 4, s)) != cudaSuccess) goto done;
+  if ((e = cudaMallocAsync(&v0, (size_t)np * 4, s)) != cudaSuccess) goto done;
+  if (need > tmp_bytes) {
+    if ((e = cudaMallocAsync(&t, need, s)) != cudaSuccess) goto done;
+    tmp = t;
+  }
+  make_sched_keys<<<(np + 255) / 256, 256, 0, s>>>(in, out.pt_ptr, k0, v0);
+  e = cub::DeviceRadixSort::SortPairs(tmp, need, k0, k1, v0, out.sched, np, 0, bits, s);
+done:
+  cudaFreeAsync(k0, s); cudaFreeAsync(k1, s); cudaFreeAsync(v0, s); cudaFreeAsync(t, s);
+  return e;
+}
 
 }  // namespace
 
@@ -84,6 +126,7 @@ int build_index(const IndexIn& in, const IndexOut& out, cudaStream_t s) {
   if (no == 0) {
     fill_ptr<<<(in.np_tot + 256) / 256, 256, 0, s>>>(out.pt_ptr, in.np_tot + 1, 0);
     fill_ptr<<<(in.nc_tot + 256) / 256, 256, 0, s>>>(out.cam_ptr, in.nc_tot + 1, 0);
+    if (out.sched && in.np_tot > 0) return (int)sort_sched(in, out, nullptr, 0, s);
     return (int)cudaGetLastError();
   }
   unsigned long long *k0 = nullptr, *k1 = nullptr;
@@ -109,6 +152,11 @@ int build_index(const IndexIn& in, const IndexOut& out, cudaStream_t s) {
     B2_TRY(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, ck0, ck1, v0, p1, no, 0, cbits, s));
     build_cm<<<nblk, 256, 0, s>>>(in, ck1, p1, out.pm, k1, out.cm, out.cam_ptr);
     B2_TRY(cudaGetLastError());
+    if (out.sched && in.np_tot > 0) {
+      // stable sort of (window, observation-count class): the temporaries above are free again
+      // (np_tot <= no is not guaranteed, so the keys/values get their own small buffers)
+      B2_TRY(sort_sched(in, out, tmp, tmp_bytes, s));
+    }
   }
 done:
 #undef B2_TRY

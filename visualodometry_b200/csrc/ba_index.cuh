@@ -24,6 +24,9 @@ struct IndexOut {
   ObsRec* cm;      // no
   int* cam_ptr;    // nc_tot+1
   int* flags;      // [0] out-of-range index, [1] duplicate (cam,pt) observation
+  int* sched;      // np_tot or nullptr: per window, the window-local landmark ids ordered by decreasing
+                   // observation count (stable).  The window kernel walks landmarks in this order so that
+                   // the landmarks sharing a warp have (nearly) the same number of observations.
 };
 
 // Builds both streams. Returns cudaError_t as int. Temporary storage is allocated and freed

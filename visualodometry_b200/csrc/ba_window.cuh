@@ -17,6 +17,7 @@ struct WinData {
   const int* pt_off;           // nb+1
   const ObsRec* pm;            // point-major stream (idx = local camera)
   const int* pt_ptr;           // NpTot+1, absolute offsets into pm
+  const int* sched;            // NpTot: per window, local landmark ids by decreasing observation count
   const ObsRec* cm;            // camera-major stream (idx = local point)
   const int* cam_ptr;          // NcTot+1, absolute offsets into cm
   const unsigned char* fixed;  // NcTot
