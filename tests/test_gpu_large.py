@@ -85,8 +85,14 @@ def test_lm_result_chain_banded_cholesky(oracle):
     ba.close()
 
 
-def test_banded_step_matches_oracle_cholesky_step(oracle):
-    """one LM iteration: delta_c of the banded Cholesky against the oracle's dense Cholesky."""
+@pytest.mark.parametrize("chunks", [None, 1, 2, 5])
+def test_banded_step_matches_oracle_cholesky_step(oracle, monkeypatch, chunks):
+    """one LM iteration: delta_c of the banded Cholesky against the oracle's dense Cholesky -- sequential
+    (1 chunk) and substructured (interiors factored concurrently + separator system; None = the engine's choice)."""
+    if chunks is None:
+        monkeypatch.delenv("B2BA_BAND_CHUNKS", raising=False)
+    else:
+        monkeypatch.setenv("B2BA_BAND_CHUNKS", str(chunks))
     p = synth.make_large(5, n_cams=60, n_pts=4000, mode="local")
     from visualodometry_b200 import BAConfig, BundleAdjuster
     ba = BundleAdjuster(K_of(p), BAConfig())

@@ -46,7 +46,8 @@ struct b2ba {
   LargeIndex lix;
   DevBuf<ObsRec> l_cm;
   DevBuf<int> l_cam_ptr;
-  DevBuf<double> l_poses_tri, l_lin_part, l_lin, l_Dc, l_Sg, l_dc, l_r, l_z, l_q, l_Minv, l_part, l_sums, l_band, l_binv;
+  DevBuf<double> l_poses_tri, l_lin_part, l_lin, l_Dc, l_Sg, l_dc, l_r, l_z, l_q, l_Minv, l_part, l_sums, l_band, l_binv, l_band_ws;
+  int l_band_P = 1;  // interiors of the substructured banded solve (1 = sequential)
   int l_bw = -1;     // block half-bandwidth of S when the banded Cholesky is selected, else -1
   DevBuf<LargeCtrl> l_ctrl;
   int p_lo = 0, p_hi = 0;
@@ -171,7 +172,7 @@ LargeData make_large(b2ba* h, bool hist) {
   d.lin_part = h->l_lin_part.p; d.lin = h->nranks > 1 ? h->l_lin.p : h->l_lin_part.p;
   d.Dc = h->l_Dc.p; d.pt_scratch = h->d_scratch.p; d.Sg = h->l_Sg.p; d.dc = h->l_dc.p;
   d.r = h->l_r.p; d.z = h->l_z.p; d.q = h->l_q.p; d.Minv = h->l_Minv.p; d.part = h->l_part.p;
-  d.bw = h->l_bw; d.band = h->l_band.p; d.binv = h->l_binv.p;
+  d.bw = h->l_bw; d.band = h->l_band.p; d.binv = h->l_binv.p; d.band_P = h->l_band_P; d.band_ws = h->l_band_ws.p;
   d.sums_part = h->l_sums.p; d.ctrl = h->l_ctrl.p; d.summary = h->d_summ.p;
   d.hist_cost = hist ? h->d_hist_cost.p : nullptr; d.hist_mu = hist ? h->d_hist_mu.p : nullptr;
   d.hist_accept = hist ? h->d_hist_accept.p : nullptr;
@@ -217,6 +218,8 @@ int setup_large(b2ba* h) {
     if (bw <= kBandMaxBw) {
       h->l_bw = bw;
       CU(h->l_band.alloc((size_t)h->lix.nfree * (bw + 1) * 36), "alloc"); CU(h->l_binv.alloc((size_t)h->lix.nfree * 6), "alloc");
+      h->l_band_P = large_band_chunks(h->lix.nfree, bw);
+      CU(h->l_band_ws.alloc(large_band_ws_count(h->lix.nfree, bw, h->l_band_P)), "alloc");
     }
   }
   CU(cudaMemset(h->l_lin_part.p, 0, (nc * 27 + 2) * sizeof(double)), "memset");

@@ -1,25 +1,65 @@
 // Exact solver of the large path for BLOCK-BANDED reduced camera systems (a5/a6): when the
 // cameras that share landmarks are close in index (VO / chain-like BAL visibility: C5 `local`), S is
 // block-banded and a banded Cholesky costs n * (6 w)^2 flops instead of PCG iterations that do not converge
-// on long chains (block-Jacobi PCG needs O(chain length) iterations).  One CTA walks the block columns; the
-// active (w+1) x (w+1) block window lives in shared memory as a ring, the forward substitution is fused into
-// the factorisation, the backward substitution streams L back from L2.  Deterministic (no atomics).
+// on long chains (block-Jacobi PCG needs O(chain length) iterations).
+//
+// A banded factorisation is a chain of N dependent 6x6 pivots, i.e. latency-bound.  Two measures:
+//  * per block column: one CTA of 128 threads (one warp per scheduler), the active window in a shared-memory
+//    ring filled by cp.async three columns ahead, the pivot block factored redundantly in registers, the
+//    forward substitution of all right-hand sides fused into the factorisation;
+//  * across block columns: SUBSTRUCTURING.  The N block columns are cut into P interiors separated by P-1
+//    separators of w block columns.  Interiors do not couple with each other, so P CTAs factor them
+//    concurrently, each carrying [b | C_left | C_right] (its couplings to the neighbouring separators) as
+//    1 + 12 w right-hand sides: Y = L^-1 [b | C].  The separator system  T = A_SS - sum_i Y_C^T Y_C  is again
+//    block-banded ((P-1) w block columns, half-bandwidth 2w-1) and is solved by the same kernel with one CTA;
+//    the interiors then back-substitute concurrently with  z = y_b - Y_C x_S.
+// The chain shrinks from N to about N/P + (P-1) w columns (C5: 1000 -> ~120).  Deterministic (no atomics).
 #include "ba_large.cuh"
+
+#include <algorithm>
+#include <cmath>
+#include <cstdlib>
 
 namespace b2 {
 namespace {
 
-constexpr int kBandThreads = 256;
+constexpr int kBandThreads = 128;
 constexpr int kBandAhead = 3;      // block columns loaded ahead of the active window
 
-// band block (j, k), k = 0..w, is A_{j+k, j} (6 x 6 row-major): the lower band, by block column.
-// A_{j+k, j}[r][c] = S(j, j+k)[c][r] (S is stored as its upper blocks).
-__global__ void large_band_fill_kernel(LargeData d) {
+// One SPD block-banded system.  band block (j, k), k = 0..w, is A_{j+k, j} (6 x 6 row-major): the lower
+// band by block column (in: A, out: L).  rhs: per block column 6 x nr row-major (in: B, out: Y = L^-1 B, and
+// after the backward pass column 0 holds z).  binv: 1 / diag(L).
+struct BandSys {
+  double* band;
+  double* rhs;
+  double* binv;
+  int N, w, nr;
+};
+
+// interior i of P over N block columns with separators of w columns between them
+__host__ __device__ inline void chunk_range(int N, int w, int P, int i, int& lo, int& hi) {
+  const int M = N - (P - 1) * w, q = M / P, rem = M % P;
+  lo = i * q + (i < rem ? i : rem) + i * w;
+  hi = lo + q + (i < rem ? 1 : 0);
+}
+
+__device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
+  const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(s), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory"); }
+
+// ------------------------------------------------------------------------------------------------ fill
+// S (upper block CSR) -> lower band by column; right-hand sides of the P interiors ([b | C_left | C_right])
+// or, for P == 1, the single right-hand side b = -g_red.
+__global__ void band_fill_kernel(LargeData d, BandSys s, int P) {
   const LargeCtrl* ctrl = d.ctrl;
   if (ctrl->stop || ctrl->step_bad) return;
-  const int W1 = d.bw + 1;
+  const int W1 = s.w + 1;
   const size_t gid = blockIdx.x * (size_t)blockDim.x + threadIdx.x, gsz = (size_t)gridDim.x * blockDim.x;
-  const size_t total = (size_t)d.nfree * W1 * 36;
+  const size_t total = (size_t)s.N * W1 * 36;
   for (size_t i = gid; i < total; i += gsz) {
     const int e = (int)(i % 36), k = (int)((i / 36) % W1), j = (int)(i / (36 * (size_t)W1));
     const int r = e / 6, c = e % 6;
@@ -31,36 +71,85 @@ __global__ void large_band_fill_kernel(LargeData d) {
         v = (k == 0 && r < c) ? d.Sg[(size_t)b * 36 + 6 * r + c] : d.Sg[(size_t)b * 36 + 6 * c + r];
         break;
       }
-    d.band[i] = v;
+    s.band[i] = v;
   }
 }
 
-__global__ void __launch_bounds__(kBandThreads) large_band_chol_kernel(LargeData d) {
-  LargeCtrl* ctrl = d.ctrl;
+// value of A_{row, col} [r][c] (block indices, any order) read from S; 0 outside the structure
+__device__ inline double s_entry(const LargeData& d, int row, int col, int r, int c) {
+  int a = row, b = col, rr = r, cc = c;
+  if (a > b) { a = col; b = row; rr = c; cc = r; }       // S stores (a <= b); A_{b,a} = A_{a,b}^T
+  for (int q = d.blk_ptr[a]; q < d.blk_ptr[a + 1]; ++q)
+    if (d.blk_col[q] == b) {
+      if (a == b && rr > cc) { const int t = rr; rr = cc; cc = t; }
+      return d.Sg[(size_t)q * 36 + 6 * rr + cc];
+    }
+  return 0.0;
+}
+
+__global__ void band_fill_rhs_kernel(LargeData d, BandSys s, int P) {
+  const LargeCtrl* ctrl = d.ctrl;
+  if (ctrl->stop || ctrl->step_bad) return;
+  const double* gred = d.Sg + (size_t)d.nblk * 36;
+  const size_t gid = blockIdx.x * (size_t)blockDim.x + threadIdx.x, gsz = (size_t)gridDim.x * blockDim.x;
+  const int nr = s.nr, w = s.w;
+  const size_t total = (size_t)s.N * 6 * nr;
+  for (size_t i = gid; i < total; i += gsz) {
+    const int q = (int)(i % nr), r = (int)((i / nr) % 6), j = (int)(i / ((size_t)6 * nr));
+    double v = 0.0;
+    if (q == 0) {
+      v = -gred[6 * j + r];
+    } else {
+      // which interior holds column j?  (separator columns keep zero rows: they are never read)
+      int ci = -1, lo = 0, hi = 0;
+      for (int t = 0; t < P; ++t) {
+        chunk_range(s.N, w, P, t, lo, hi);
+        if (j >= lo && j < hi) { ci = t; break; }
+        if (j < lo) break;
+      }
+      if (ci >= 0) {
+        const int qq = q - 1, side = qq / (6 * w), a = (qq % (6 * w)) / 6, c = qq % 6;
+        const int sep = side == 0 ? lo - w + a : hi + a;          // separator block column
+        const bool exists = side == 0 ? ci > 0 : ci < P - 1;
+        if (exists && abs(sep - j) <= w) v = s_entry(d, j, sep, r, c);
+      }
+    }
+    s.rhs[i] = v;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ forward
+// CTA i factors the block columns [lo_i, hi_i) of `s` and forward-substitutes their nr right-hand sides.
+template <int NT>
+__global__ void __launch_bounds__(NT) band_forward_kernel(LargeCtrl* ctrl, BandSys s, int P) {
   if (ctrl->stop || ctrl->step_bad) return;
   extern __shared__ __align__(16) double bsm[];
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int N = d.nfree, w = d.bw, W1 = w + 1;
-  const int SLOT = W1 * 36 + 6;                       // one block column (w+1 blocks) + its right-hand side
+  const int tid = threadIdx.x;
+  const int w = s.w, W1 = w + 1, nr = s.nr;
+  int lo, hi;
+  chunk_range(s.N, w, P, blockIdx.x, lo, hi);
+  const int NB = W1 * 36;                              // band part of a slot
+  const int SLOT = NB + 6 * nr;                        // one block column (w+1 blocks) + its right-hand sides
   const int RS = W1 + kBandAhead;                      // ring slots: the active window + columns loaded ahead
   double* ring = bsm;
-  double* xs = ring + (size_t)RS * SLOT;               // backward pass: ring of the last W1 solution blocks
-  double* Lsm = xs + 6 * W1;                           // factor of the current diagonal block (36)
+  double* Lsm = ring + (size_t)RS * SLOT;              // factor of the current diagonal block (36)
   __shared__ int bad;
   if (tid == 0) bad = 0;
-  const double* gred = d.Sg + (size_t)d.nblk * 36;
 
-  auto load_col = [&](int j) {                         // global band column j (+ rhs = -g_red) -> ring slot
-    double* s = ring + (size_t)(j % RS) * SLOT;
-    const double* g = d.band + (size_t)j * W1 * 36;
-    for (int i = tid; i < W1 * 36; i += kBandThreads) s[i] = g[i];
-    if (tid < 6) s[W1 * 36 + tid] = -gred[6 * j + tid];
+  auto load_col = [&](int j) {                         // global band column j + its rhs rows -> ring slot
+    double* sl = ring + (size_t)((j - lo) % RS) * SLOT;
+    const double* g = s.band + (size_t)j * NB;
+    for (int i = tid; i < NB / 2; i += NT) cp_async16(sl + 2 * i, g + 2 * i);
+    const double* gr = s.rhs + (size_t)j * 6 * nr;
+    for (int i = tid; i < 3 * nr; i += NT) cp_async16(sl + NB + 2 * i, gr + 2 * i);
   };
-  for (int j = 0; j < min(RS - 1, N); ++j) load_col(j);
+  for (int j = lo; j < min(lo + RS - 1, hi); ++j) load_col(j);
+  cp_async_commit();
+  cp_async_wait<0>();
   __syncthreads();
 
-  for (int j = 0; j < N; ++j) {
-    double* cj = ring + (size_t)(j % RS) * SLOT;
+  for (int j = lo; j < hi; ++j) {
+    double* cj = ring + (size_t)((j - lo) % RS) * SLOT;
     // ---- every thread factors the diagonal block redundantly in registers
     double L[6][6], inv[6];
     bool isbad = false;
@@ -90,109 +179,226 @@ __global__ void __launch_bounds__(kBandThreads) large_band_chol_kernel(LargeData
       }
     }
     if (isbad && tid == 0) bad = 1;
-    const int wj = min(w, N - 1 - j);                  // blocks below the diagonal in this column
-    // ---- panel rows: L_{j+k,j} = A_{j+k,j} L_jj^-T, one thread per row; thread 6*wj: y_j = L_jj^-1 b_j
-    if (tid < 6 * wj) {
-      double* row = cj + 36 + 6 * tid;                 // row (tid % 6) of block 1 + tid / 6
-      double x[6];
+    const int wj = min(w, hi - 1 - j);                 // blocks below the diagonal inside this interior
+    // ---- panel rows L_{j+k,j} = A_{j+k,j} L_jj^-T (one item per row) and Y_j = L_jj^-1 B_j (one item per
+    // right-hand side)
+    for (int it = tid; it < 6 * wj + nr; it += NT) {
+      if (it < 6 * wj) {
+        double* row = cj + 36 + 6 * it;                // row (it % 6) of block 1 + it / 6
+        double x[6];
 #pragma unroll
-      for (int c = 0; c < 6; ++c) {
-        double v = row[c];
+        for (int c = 0; c < 6; ++c) {
+          double v = row[c];
 #pragma unroll
-        for (int k = 0; k < 6; ++k)
-          if (k < c) v = fma(-x[k], L[c][k], v);
-        x[c] = v * inv[c];
+          for (int k = 0; k < 6; ++k)
+            if (k < c) v = fma(-x[k], L[c][k], v);
+          x[c] = v * inv[c];
+        }
+#pragma unroll
+        for (int c = 0; c < 6; ++c) row[c] = x[c];
+      } else {
+        double* b = cj + NB + (it - 6 * wj);           // column of the 6 x nr right-hand-side block
+        double y[6];
+#pragma unroll
+        for (int c = 0; c < 6; ++c) {
+          double v = b[c * nr];
+#pragma unroll
+          for (int k = 0; k < 6; ++k)
+            if (k < c) v = fma(-L[c][k], y[k], v);
+          y[c] = v * inv[c];
+        }
+#pragma unroll
+        for (int c = 0; c < 6; ++c) b[c * nr] = y[c];
       }
-#pragma unroll
-      for (int c = 0; c < 6; ++c) row[c] = x[c];
-    } else if (tid == 6 * wj) {
-      double* b = cj + W1 * 36;
-      double y[6];
-#pragma unroll
-      for (int c = 0; c < 6; ++c) {
-        double v = b[c];
-#pragma unroll
-        for (int k = 0; k < 6; ++k)
-          if (k < c) v = fma(-L[c][k], y[k], v);
-        y[c] = v * inv[c];
-      }
-#pragma unroll
-      for (int c = 0; c < 6; ++c) b[c] = y[c];
+    }
+    if (tid == NT - 1) {
 #pragma unroll
       for (int r = 0; r < 6; ++r) {
 #pragma unroll
         for (int c = 0; c < 6; ++c) Lsm[6 * r + c] = c <= r ? L[r][c] : 0.0;   // (block 0 of cj is still being read)
-        d.binv[6 * (size_t)j + r] = inv[r];
+        s.binv[6 * (size_t)j + r] = inv[r];
       }
     }
+    cp_async_wait<kBandAhead - 1>();                   // the column that enters the window at this step has landed
     __syncthreads();
-    // ---- trailing update inside the window: A_{j+a,j+b} -= L_{j+a,j} L_{j+b,j}^T (a >= b >= 1) and the
-    // right-hand sides b_{j+a} -= L_{j+a,j} y_j; work items = 6x6 entries, flattened over (b, a, r, c)
+    // ---- trailing update inside the window: A_{j+a,j+b} -= L_{j+a,j} L_{j+b,j}^T (a >= b >= 1), items = 6x6
+    // entries flattened over (b, a, r, c); right-hand sides B_{j+a} -= L_{j+a,j} Y_j, items = (r, column)
     const int npair = wj * (wj + 1) / 2;
-    for (int id = tid; id < npair * 36 + 6 * wj; id += kBandThreads) {
-      if (id < npair * 36) {
-        const int e = id % 36, pr = id / 36;
-        int b = 1, rem = pr, len = wj;                 // pairs enumerated b = 1..wj, a = b..wj
-        while (rem >= len) { rem -= len; --len; ++b; }
-        const int a = b + rem, r = e / 6, c = e % 6;
-        const double* la = cj + 36 * a + 6 * r;
-        const double* lb = cj + 36 * b + 6 * c;
-        double* dst = ring + (size_t)((j + b) % RS) * SLOT + 36 * (a - b) + 6 * r + c;
-        double v = *dst;
+    for (int id = tid; id < npair * 36; id += NT) {
+      const int e = id % 36, pr = id / 36;
+      int b = 1, rem = pr, len = wj;                   // pairs enumerated b = 1..wj, a = b..wj
+      while (rem >= len) { rem -= len; --len; ++b; }
+      const int a = b + rem, r = e / 6, c = e % 6;
+      const double* la = cj + 36 * a + 6 * r;
+      const double* lb = cj + 36 * b + 6 * c;
+      double* dst = ring + (size_t)((j + b - lo) % RS) * SLOT + 36 * (a - b) + 6 * r + c;
+      double v = *dst;
 #pragma unroll
-        for (int m = 0; m < 6; ++m) v = fma(-la[m], lb[m], v);
-        *dst = v;
-      } else {
-        const int q = id - npair * 36, a = 1 + q / 6, r = q % 6;
-        const double* la = cj + 36 * a + 6 * r;
-        const double* y = cj + W1 * 36;
-        double* dst = ring + (size_t)((j + a) % RS) * SLOT + W1 * 36 + r;
-        double v = *dst;
+      for (int m = 0; m < 6; ++m) v = fma(-la[m], lb[m], v);
+      *dst = v;
+    }
+    if (wj > 0) {
+      for (int id = tid; id < 6 * nr; id += NT) {
+        const int r = id / nr, q = id - r * nr;
+        double y[6];
 #pragma unroll
-        for (int m = 0; m < 6; ++m) v = fma(-la[m], y[m], v);
-        *dst = v;
+        for (int m = 0; m < 6; ++m) y[m] = cj[NB + m * nr + q];
+        for (int a = 1; a <= wj; ++a) {
+          const double* la = cj + 36 * a + 6 * r;
+          double* dst = ring + (size_t)((j + a - lo) % RS) * SLOT + NB + r * nr + q;
+          double v = *dst;
+#pragma unroll
+          for (int m = 0; m < 6; ++m) v = fma(-la[m], y[m], v);
+          *dst = v;
+        }
       }
     }
-    // ---- column j is final: L blocks back to the band array, y_j to dc; then its slot takes column j+W1
+    // ---- column j is final: L blocks back to the band array, Y_j to the rhs array
     {
-      double* g = d.band + (size_t)j * W1 * 36;
-      for (int i = tid; i < W1 * 36; i += kBandThreads) g[i] = i < 36 ? Lsm[i] : cj[i];
-      if (tid < 6) d.dc[6 * j + tid] = cj[W1 * 36 + tid];
+      double* g = s.band + (size_t)j * NB;
+      for (int i = tid; i < NB; i += NT) g[i] = i < 36 ? Lsm[i] : cj[i];
+      double* gr = s.rhs + (size_t)j * 6 * nr;
+      for (int i = tid; i < 6 * nr; i += NT) gr[i] = cj[NB + i];
     }
     // the slot of column j-1 is free since the previous barrier: it takes column j-1+RS, which is first
-    // touched kBandAhead steps from now (its global load latency is off the critical path)
-    if (j + RS - 1 < N) load_col(j + RS - 1);
+    // touched kBandAhead steps from now (asynchronous copy: nobody waits for it here)
+    if (j + RS - 1 < hi) load_col(j + RS - 1);
+    cp_async_commit();
     __syncthreads();
   }
-  if (bad) { if (tid == 0) ctrl->step_bad = 1; return; }
+  cp_async_wait<0>();
+  if (bad && tid == 0) ctrl->step_bad = 1;
+}
 
-  // ---- backward substitution L^T x = y by warp 0; x blocks of the last w columns stay in shared memory.
+// ------------------------------------------------------------------------------------------------ Gram
+// G_i = Y_i^T Y_i (nr x nr) over the rows of interior i.  grid (P, ceil(nr / 4)): CTA (i, g) computes the
+// rows 4g..4g+3 of G_i, thread q the column q; fixed summation order.
+__global__ void __launch_bounds__(kBandThreads) band_gram_kernel(LargeCtrl* ctrl, BandSys s, int P, double* gram) {
+  if (ctrl->stop || ctrl->step_bad) return;
+  const int nr = s.nr, q = threadIdx.x, p0 = 4 * blockIdx.y;
+  int lo, hi;
+  chunk_range(s.N, s.w, P, blockIdx.x, lo, hi);
+  if (q >= nr) return;
+  double acc[4] = {0, 0, 0, 0};
+  const double* y = s.rhs + (size_t)lo * 6 * nr;
+  const int rows = 6 * (hi - lo);
+  int pi[4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) pi[k] = min(p0 + k, nr - 1);
+  for (int r = 0; r < rows; ++r, y += nr) {
+    const double yq = y[q];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) acc[k] = fma(y[pi[k]], yq, acc[k]);
+  }
+  double* g = gram + (size_t)blockIdx.x * nr * nr;
+#pragma unroll
+  for (int k = 0; k < 4; ++k)
+    if (p0 + k < nr) g[(size_t)(p0 + k) * nr + q] = acc[k];
+}
+
+// ------------------------------------------------------------------------------------------------ separators
+// The separator system T x_S = b_S' as a band system `t` (N' = (P-1) w block columns, half-bandwidth 2w-1,
+// one right-hand side).  Separator i sits between interiors i and i+1: it is the RIGHT separator of interior
+// i (Gram columns 1 + 6w + 6a + c) and the LEFT separator of interior i+1 (Gram columns 1 + 6a + c).
+__global__ void band_sep_assemble_kernel(LargeData d, BandSys s, int P, const double* gram, BandSys t) {
+  const LargeCtrl* ctrl = d.ctrl;
+  if (ctrl->stop || ctrl->step_bad) return;
+  const double* gred = d.Sg + (size_t)d.nblk * 36;
+  const int w = s.w, nr = s.nr, W1t = t.w + 1;
+  const size_t gid = blockIdx.x * (size_t)blockDim.x + threadIdx.x, gsz = (size_t)gridDim.x * blockDim.x;
+  const size_t nband = (size_t)t.N * W1t * 36, total = nband + (size_t)t.N * 6;
+  for (size_t i = gid; i < total; i += gsz) {
+    if (i < nband) {
+      const int e = (int)(i % 36), k = (int)((i / 36) % W1t), jc = (int)(i / (36 * (size_t)W1t));
+      const int r = e / 6, c = e % 6;                  // entry [r][c] of block (row jc + k, column jc)
+      const int si = jc / w, a = jc % w;               // column: separator si, local block a
+      const int jr = jc + k, sj = jr / w, b = jr % w;  // row: separator sj, local block b
+      double v = 0.0;
+      if (jr < t.N) {
+        int lo, hi;
+        if (sj == si) {
+          chunk_range(s.N, w, P, si, lo, hi);          // separator si = block columns hi .. hi + w - 1
+          v = s_entry(d, hi + b, hi + a, r, c);
+          const double* gl = gram + (size_t)si * nr * nr;         // interior si: right separator
+          const double* gn = gram + (size_t)(si + 1) * nr * nr;   // interior si+1: left separator
+          v -= gl[(size_t)(1 + 6 * w + 6 * b + r) * nr + (1 + 6 * w + 6 * a + c)];
+          v -= gn[(size_t)(1 + 6 * b + r) * nr + (1 + 6 * a + c)];
+        } else if (sj == si + 1) {
+          const double* gn = gram + (size_t)sj * nr * nr;         // interior sj couples separators sj-1 and sj
+          v = -gn[(size_t)(1 + 6 * w + 6 * b + r) * nr + (1 + 6 * a + c)];
+        }
+      }
+      t.band[i] = v;
+    } else {
+      const size_t q = i - nband;
+      const int jc = (int)(q / 6), r = (int)(q % 6), si = jc / w, a = jc % w;
+      int lo, hi;
+      chunk_range(s.N, w, P, si, lo, hi);
+      const double* gl = gram + (size_t)si * nr * nr;
+      const double* gn = gram + (size_t)(si + 1) * nr * nr;
+      t.rhs[q] = -gred[6 * (hi + a) + r] - gl[(size_t)(1 + 6 * w + 6 * a + r) * nr] - gn[(size_t)(1 + 6 * a + r) * nr];
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ backward
+// CTA i: z = y_b - Y_C x_S over its interior (all threads), then L^T x = z by warp 0 (x blocks of the last
+// w columns stay in shared memory); x -> xout.  xsep (null for P == 1): the separator solution, (P-1) w x 6.
+__global__ void __launch_bounds__(kBandThreads) band_backward_kernel(LargeCtrl* ctrl, BandSys s, int P,
+                                                                     const double* xsep, double* xout) {
+  if (ctrl->stop || ctrl->step_bad) return;
+  extern __shared__ __align__(16) double bsm[];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int w = s.w, W1 = w + 1, nr = s.nr, NB = W1 * 36;
+  int lo, hi;
+  chunk_range(s.N, w, P, blockIdx.x, lo, hi);
+  double* xs = bsm;                                    // ring of the last W1 solution blocks (6 W1)
+  double* xc = xs + 6 * W1;                            // [x_left (6w) | x_right (6w)] of this interior
+  if (xsep) {
+    const int i = blockIdx.x;
+    for (int k = tid; k < 12 * w; k += kBandThreads) {
+      const int side = k / (6 * w), e = k % (6 * w);
+      const int sep = side == 0 ? i - 1 : i;
+      const double v = (sep >= 0 && sep < P - 1) ? xsep[(size_t)sep * 6 * w + e] : 0.0;
+      xc[k] = v;
+      // separator i's solution goes out with interior i
+      if (side == 1 && sep < P - 1) xout[6 * (size_t)hi + e] = v;
+    }
+    __syncthreads();
+    for (int row = tid; row < 6 * (hi - lo); row += kBandThreads) {
+      double* y = s.rhs + ((size_t)lo * 6 + row) * nr;
+      double z = y[0];
+      for (int q = 1; q < nr; ++q) z = fma(-y[q], xc[q - 1], z);
+      y[0] = z;
+    }
+    __syncthreads();
+  }
   // Lane layout: c = lane % 6 (component), sl = lane / 6 (a-slice, 5 slices; lanes 30, 31 idle).  The entries a
-  // lane needs from column j-1 (its first a-slice, the diagonal block column c, 1/diag, y) are loaded one step
+  // lane needs from column j-1 (its first a-slice, the diagonal block column c, 1/diag, z) are loaded one step
   // ahead, so the L2 latency of the band array is off the serial chain.
   if (warp == 0) {
     const int c = lane % 6, sl = lane / 6;
     double nb[6], nd[6], ninv = 0.0, ny = 0.0;          // prefetched for the column about to be processed
     auto fetch = [&](int j) {
-      const double* g = d.band + (size_t)j * W1 * 36;
-      const int wj = min(w, N - 1 - j);
+      const double* g = s.band + (size_t)j * NB;
+      const int wj = min(w, hi - 1 - j);
 #pragma unroll
       for (int r = 0; r < 6; ++r) {
         nb[r] = (lane < 30 && 1 + sl <= wj) ? g[36 * (1 + sl) + 6 * r + c] : 0.0;
         nd[r] = lane < 6 ? g[6 * r + c] : 0.0;          // column c of L_jj: L[r][c], r > c used
       }
-      ninv = lane < 6 ? d.binv[6 * (size_t)j + lane] : 0.0;
-      ny = lane < 6 ? d.dc[6 * j + lane] : 0.0;
+      ninv = lane < 6 ? s.binv[6 * (size_t)j + lane] : 0.0;
+      ny = lane < 6 ? s.rhs[((size_t)j * 6 + lane) * nr] : 0.0;
     };
-    if (N > 0) fetch(N - 1);
-    for (int j = N - 1; j >= 0; --j) {
-      const int wj = min(w, N - 1 - j);
-      const double* g = d.band + (size_t)j * W1 * 36;
+    if (hi > lo) fetch(hi - 1);
+    for (int j = hi - 1; j >= lo; --j) {
+      const int wj = min(w, hi - 1 - j);
+      const double* g = s.band + (size_t)j * NB;
       double blk[6], dg[6];
 #pragma unroll
       for (int r = 0; r < 6; ++r) { blk[r] = nb[r]; dg[r] = nd[r]; }
       const double inv_c = ninv, yc = ny;
-      if (j > 0) fetch(j - 1);
+      if (j > lo) fetch(j - 1);
       // t[c] = sum_a sum_r L_{j+a,j}[r][c] x_{j+a}[r]
       double t = 0.0;
       if (lane < 30 && 1 + sl <= wj) {
@@ -208,38 +414,105 @@ __global__ void __launch_bounds__(kBandThreads) large_band_chol_kernel(LargeData
       }
       t += __shfl_down_sync(0xffffffffu, t, 6) + __shfl_down_sync(0xffffffffu, t, 12) +
            __shfl_down_sync(0xffffffffu, t, 18) + __shfl_down_sync(0xffffffffu, t, 24);
-      // lanes 0..5: solve L_jj^T x = y - t by back substitution, one shuffle per component
-      double xc = yc - t;                               // lane c holds component c
+      // lanes 0..5: solve L_jj^T x = z - t by back substitution, one shuffle per component
+      double xv = yc - t;                               // lane c holds component c
 #pragma unroll
       for (int i = 5; i >= 0; --i) {
-        const double xi = __shfl_sync(0xffffffffu, xc * inv_c, i);   // x_i is final when its turn comes
-        if (lane == i) xc = xi;
-        else if (lane < i) xc = fma(-dg[i], xi, xc);    // L[i][c] of lane c = dg[i]
+        const double xi = __shfl_sync(0xffffffffu, xv * inv_c, i);   // x_i is final when its turn comes
+        if (lane == i) xv = xi;
+        else if (lane < i) xv = fma(-dg[i], xi, xv);    // L[i][c] of lane c = dg[i]
       }
-      if (lane < 6) { xs[6 * (j % W1) + lane] = xc; d.dc[6 * j + lane] = xc; }
+      if (lane < 6) { xs[6 * (j % W1) + lane] = xv; xout[6 * (size_t)j + lane] = xv; }
       __syncwarp();
     }
   }
-  if (tid == 0) ctrl->pcg_last = 0;
+  if (blockIdx.x == 0 && tid == 0) ctrl->pcg_last = 0;
 }
+
+// ------------------------------------------------------------------------------------------------ host
+struct BandPlan {
+  int P, nr, Nt, wt;
+  size_t off_rhs, off_gram, off_tband, off_trhs, off_tbinv, off_xsep, total;
+};
+
+inline size_t even(size_t x) { return (x + 1) & ~(size_t)1; }
+
+BandPlan make_plan(int N, int w, int P) {
+  BandPlan p{};
+  p.P = P;
+  p.nr = P > 1 ? 1 + 12 * w : 1;
+  p.Nt = (P - 1) * w;
+  p.wt = P > 1 ? 2 * w - 1 : 0;
+  size_t o = 0;
+  p.off_rhs = o;   o += even((size_t)N * 6 * p.nr);
+  p.off_gram = o;  o += even((size_t)P * p.nr * p.nr);
+  p.off_tband = o; o += even((size_t)p.Nt * (p.wt + 1) * 36);
+  p.off_trhs = o;  o += even((size_t)p.Nt * 6);
+  p.off_tbinv = o; o += even((size_t)p.Nt * 6);
+  p.off_xsep = o;  o += even((size_t)p.Nt * 6);
+  p.total = o;
+  return p;
+}
+
+size_t fwd_smem(int w, int nr) {
+  const size_t W1 = (size_t)w + 1;
+  return ((W1 + kBandAhead) * (W1 * 36 + 6 * (size_t)nr) + 36) * sizeof(double);
+}
+size_t bwd_smem(int w) { return ((size_t)6 * (w + 1) + 12 * (size_t)w) * sizeof(double); }
 
 }  // namespace
 
-size_t large_band_smem(int bw) {
-  const size_t W1 = (size_t)bw + 1;
-  return ((W1 + kBandAhead) * (W1 * 36 + 6) + W1 * 6 + 36) * sizeof(double);
+// number of interiors for N block columns of half-bandwidth w (1 = plain sequential factorisation)
+int large_band_chunks(int N, int w) {
+  if (const char* e = getenv("B2BA_BAND_CHUNKS")) {
+    const int P = atoi(e);
+    if (P >= 1 && (P == 1 || (w >= 1 && w <= kBandParMaxBw && (N - (P - 1) * w) / P >= w))) return P;
+    return 1;
+  }
+  if (w < 1 || w > kBandParMaxBw) return 1;
+  // chain length ~ N/P + 1.3 (P-1) w (the separator system has the wider band)
+  int P = (int)std::sqrt((double)N / (1.3 * w));
+  while (P > 1 && (N - (P - 1) * w) / P < 2 * w) --P;
+  return P < 2 ? 1 : P;
 }
 
-int large_band_solve(const LargeData& d, cudaStream_t s) {
+size_t large_band_ws_count(int N, int w, int P) { return make_plan(N, w, P).total; }
+
+size_t large_band_smem(int bw) { return fwd_smem(bw, 1); }
+
+int large_band_solve(const LargeData& d, cudaStream_t st) {
   static size_t configured = 0;
-  const size_t smem = large_band_smem(d.bw);
+  const int N = d.nfree, w = d.bw, P = d.band_P;
+  const BandPlan pl = make_plan(N, w, P);
+  const size_t smem = std::max(fwd_smem(w, pl.nr), P > 1 ? fwd_smem(pl.wt, 1) : (size_t)0);
   if (smem > configured) {
-    cudaError_t e = cudaFuncSetAttribute(large_band_chol_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = cudaFuncSetAttribute(band_forward_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(band_forward_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return (int)e;
     configured = smem;
   }
-  large_band_fill_kernel<<<296, 256, 0, s>>>(d);
-  large_band_chol_kernel<<<1, kBandThreads, smem, s>>>(d);
+  // wide bands: the trailing update is throughput-bound, 256 threads; narrow bands: latency-bound, one warp
+  // per scheduler
+  auto forward = [&](const BandSys& sys, int chunks, size_t sm) {
+    if (sys.w > 8) band_forward_kernel<256><<<chunks, 256, sm, st>>>(d.ctrl, sys, chunks);
+    else band_forward_kernel<128><<<chunks, 128, sm, st>>>(d.ctrl, sys, chunks);
+  };
+  BandSys s{d.band, d.band_ws + pl.off_rhs, d.binv, N, w, pl.nr};
+  band_fill_kernel<<<296, 256, 0, st>>>(d, s, P);
+  band_fill_rhs_kernel<<<296, 256, 0, st>>>(d, s, P);
+  forward(s, P, fwd_smem(w, pl.nr));
+  if (P > 1) {
+    double* gram = d.band_ws + pl.off_gram;
+    BandSys t{d.band_ws + pl.off_tband, d.band_ws + pl.off_trhs, d.band_ws + pl.off_tbinv, pl.Nt, pl.wt, 1};
+    double* xsep = d.band_ws + pl.off_xsep;
+    band_gram_kernel<<<dim3(P, (pl.nr + 3) / 4), kBandThreads, 0, st>>>(d.ctrl, s, P, gram);
+    band_sep_assemble_kernel<<<148, 256, 0, st>>>(d, s, P, gram, t);
+    forward(t, 1, fwd_smem(pl.wt, 1));
+    band_backward_kernel<<<1, kBandThreads, bwd_smem(pl.wt), st>>>(d.ctrl, t, 1, nullptr, xsep);
+    band_backward_kernel<<<P, kBandThreads, bwd_smem(w), st>>>(d.ctrl, s, P, xsep, d.dc);
+  } else {
+    band_backward_kernel<<<1, kBandThreads, bwd_smem(w), st>>>(d.ctrl, s, 1, nullptr, d.dc);
+  }
   return (int)cudaGetLastError();
 }
 

@@ -51,6 +51,8 @@ struct LargeData {
   int bw;                          // block half-bandwidth of S if the banded Cholesky is used, else -1 (PCG)
   double* band;                    // nfree x (bw+1) x 36: lower band by block column (A, then L in place)
   double* binv;                    // nfree x 6: 1 / diag(L)
+  int band_P;                      // interiors factored concurrently (1 = sequential), see ba_band.cu
+  double* band_ws;                 // right-hand sides, Gram blocks and the separator system (large_band_ws_count)
   double* part;                    // partial-sum scratch (grid partials)
   double* sums_part;               // 8 local partial sums (before the allreduce)
   LargeCtrl* ctrl;
@@ -81,7 +83,10 @@ int large_finish(const LargeData& d, cudaStream_t s);
 int large_pcg_grid(int n, int* blocks, size_t* smem);   // cooperative launch geometry
 // exact banded Cholesky solve of S dc = -g_red (ba_band.cu); needs d.bw >= 0
 size_t large_band_smem(int bw);
+int large_band_chunks(int N, int bw);                 // interiors factored concurrently (1 = sequential)
+size_t large_band_ws_count(int N, int bw, int P);     // doubles of workspace
 int large_band_solve(const LargeData& d, cudaStream_t s);
 constexpr int kBandMaxBw = 22;     // (bw+4) x (bw+1) blocks of shared memory: 26 x 23 x 288 B = 172 KB
+constexpr int kBandParMaxBw = 6;   // substructured solve: 1 + 12 bw right-hand sides per block column in the ring
 
 }  // namespace b2
