@@ -46,7 +46,7 @@ struct b2ba {
   LargeIndex lix;
   DevBuf<ObsRec> l_cm;
   DevBuf<int> l_cam_ptr;
-  DevBuf<double> l_poses_tri, l_lin_part, l_lin, l_Dc, l_Sg, l_dc, l_r, l_z, l_q, l_Minv, l_part, l_sums, l_band, l_binv, l_band_ws;
+  DevBuf<double> l_poses_tri, l_lin_part, l_lin, l_Dc, l_Sg, l_dc, l_r, l_z, l_q, l_Minv, l_part, l_sums, l_band, l_binv, l_band_ws, l_zbuf;
   int l_band_P = 1;  // interiors of the substructured banded solve (1 = sequential)
   int l_bw = -1;     // block half-bandwidth of S when the banded Cholesky is selected, else -1
   DevBuf<LargeCtrl> l_ctrl;
@@ -172,6 +172,8 @@ LargeData make_large(b2ba* h, bool hist) {
   d.lin_part = h->l_lin_part.p; d.lin = h->nranks > 1 ? h->l_lin.p : h->l_lin_part.p;
   d.Dc = h->l_Dc.p; d.pt_scratch = h->d_scratch.p; d.Sg = h->l_Sg.p; d.dc = h->l_dc.p;
   d.r = h->l_r.p; d.z = h->l_z.p; d.q = h->l_q.p; d.Minv = h->l_Minv.p; d.part = h->l_part.p;
+  d.pair_ptr = h->lix.pair_ptr.p; d.pair_ab = h->lix.pair_ab.p; d.blk_row = h->lix.blk_row.p; d.zbuf = h->l_zbuf.p;
+  d.pair_lanes = (h->lix.nblk > 0 && h->lix.npairs / h->lix.nblk < 24) ? 8 : 32;
   d.bw = h->l_bw; d.band = h->l_band.p; d.binv = h->l_binv.p; d.band_P = h->l_band_P; d.band_ws = h->l_band_ws.p;
   d.sums_part = h->l_sums.p; d.ctrl = h->l_ctrl.p; d.summary = h->d_summ.p;
   d.hist_cost = hist ? h->d_hist_cost.p : nullptr; d.hist_mu = hist ? h->d_hist_mu.p : nullptr;
@@ -192,6 +194,9 @@ int setup_large(b2ba* h) {
   CU(h->l_cm.alloc(h->no), "alloc"); CU(h->l_cam_ptr.alloc(nc + 1), "alloc");
   rc = large_build_cm_slice(h->nc_tot, h->p_lo, h->p_hi, h->d_pm.p, h->d_pt_ptr.p, h->l_cm.p, h->l_cam_ptr.p, nullptr);
   if (rc) return cuda_fail(h, (cudaError_t)rc, "large_build_cm_slice");
+  rc = large_build_pairs(h->p_lo, h->p_hi, h->d_pm.p, h->d_pt_ptr.p, h->lix, nullptr);
+  if (rc) return cuda_fail(h, (cudaError_t)rc, "large_build_pairs");
+  CU(h->l_zbuf.alloc((size_t)h->no * 24), "alloc");
   int blocks = 0;
   size_t smem = 0;
   rc = large_pcg_grid((int)n, &blocks, &smem);

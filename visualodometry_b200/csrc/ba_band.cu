@@ -272,28 +272,42 @@ __global__ void __launch_bounds__(NT) band_forward_kernel(LargeCtrl* ctrl, BandS
 
 // ------------------------------------------------------------------------------------------------ Gram
 // G_i = Y_i^T Y_i (nr x nr) over the rows of interior i.  grid (P, ceil(nr / 4)): CTA (i, g) computes the
-// rows 4g..4g+3 of G_i, thread q the column q; fixed summation order.
-__global__ void __launch_bounds__(kBandThreads) band_gram_kernel(LargeCtrl* ctrl, BandSys s, int P, double* gram) {
+// rows 4g..4g+3 of G_i; thread (slice, q): column q, the rows of Y congruent to `slice`; the slices are
+// added in a fixed order through shared memory.
+constexpr int kGramThreads = 256;
+__global__ void __launch_bounds__(kGramThreads) band_gram_kernel(LargeCtrl* ctrl, BandSys s, int P, double* gram) {
   if (ctrl->stop || ctrl->step_bad) return;
-  const int nr = s.nr, q = threadIdx.x, p0 = 4 * blockIdx.y;
+  __shared__ double red[kGramThreads * 4];
+  const int nr = s.nr, CQ = nr <= 64 ? 64 : 128, nsl = kGramThreads / CQ;
+  const int q = threadIdx.x % CQ, sl = threadIdx.x / CQ, p0 = 4 * blockIdx.y;
   int lo, hi;
   chunk_range(s.N, s.w, P, blockIdx.x, lo, hi);
-  if (q >= nr) return;
   double acc[4] = {0, 0, 0, 0};
-  const double* y = s.rhs + (size_t)lo * 6 * nr;
   const int rows = 6 * (hi - lo);
   int pi[4];
 #pragma unroll
   for (int k = 0; k < 4; ++k) pi[k] = min(p0 + k, nr - 1);
-  for (int r = 0; r < rows; ++r, y += nr) {
-    const double yq = y[q];
+  if (q < nr) {
+    const double* y = s.rhs + ((size_t)lo * 6 + sl) * nr;
+#pragma unroll 4
+    for (int r = sl; r < rows; r += nsl, y += (size_t)nsl * nr) {
+      const double yq = y[q];
 #pragma unroll
-    for (int k = 0; k < 4; ++k) acc[k] = fma(y[pi[k]], yq, acc[k]);
+      for (int k = 0; k < 4; ++k) acc[k] = fma(y[pi[k]], yq, acc[k]);
+    }
   }
-  double* g = gram + (size_t)blockIdx.x * nr * nr;
 #pragma unroll
-  for (int k = 0; k < 4; ++k)
-    if (p0 + k < nr) g[(size_t)(p0 + k) * nr + q] = acc[k];
+  for (int k = 0; k < 4; ++k) red[(sl * 4 + k) * CQ + q] = acc[k];
+  __syncthreads();
+  if (sl == 0 && q < nr) {
+    double* g = gram + (size_t)blockIdx.x * nr * nr;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      double v = 0.0;
+      for (int t = 0; t < nsl; ++t) v += red[(t * 4 + k) * CQ + q];
+      if (p0 + k < nr) g[(size_t)(p0 + k) * nr + q] = v;
+    }
+  }
 }
 
 // ------------------------------------------------------------------------------------------------ separators
@@ -505,7 +519,7 @@ int large_band_solve(const LargeData& d, cudaStream_t st) {
     double* gram = d.band_ws + pl.off_gram;
     BandSys t{d.band_ws + pl.off_tband, d.band_ws + pl.off_trhs, d.band_ws + pl.off_tbinv, pl.Nt, pl.wt, 1};
     double* xsep = d.band_ws + pl.off_xsep;
-    band_gram_kernel<<<dim3(P, (pl.nr + 3) / 4), kBandThreads, 0, st>>>(d.ctrl, s, P, gram);
+    band_gram_kernel<<<dim3(P, (pl.nr + 3) / 4), kGramThreads, 0, st>>>(d.ctrl, s, P, gram);
     band_sep_assemble_kernel<<<148, 256, 0, st>>>(d, s, P, gram, t);
     forward(t, 1, fwd_smem(pl.wt, 1));
     band_backward_kernel<<<1, kBandThreads, bwd_smem(pl.wt), st>>>(d.ctrl, t, 1, nullptr, xsep);

@@ -112,7 +112,118 @@ __global__ void fill_int(int* p, int n, int v) {
   if (i < n) p[i] = v;
 }
 
+__device__ __forceinline__ int find_blk_ix(const int* __restrict__ blk_ptr, const int* __restrict__ blk_col, int fi, int fj) {
+  int lo = blk_ptr[fi], hi = blk_ptr[fi + 1] - 1;
+  while (lo < hi) {
+    const int mid = (lo + hi) >> 1;
+    if (blk_col[mid] < fj) lo = mid + 1; else hi = mid;
+  }
+  return lo;
+}
+
+// Schur pair list: every (observation a, observation b >= a) of one landmark with both cameras free
+// contributes Z_a Z_b^T to the S block (f_a, f_b).
+__global__ void count_all_pairs(int p_lo, int p_hi, const ObsRec* __restrict__ pm, const int* __restrict__ pt_ptr,
+                                const int* __restrict__ fidx, int* cnt) {
+  const int p = p_lo + blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= p_hi) return;
+  int k = 0;
+  for (int a = pt_ptr[p]; a < pt_ptr[p + 1]; ++a) k += fidx[pm[a].idx] >= 0 ? 1 : 0;
+  cnt[p - p_lo] = k * (k + 1) / 2;
+}
+
+__global__ void emit_all_pairs(int p_lo, int p_hi, const ObsRec* __restrict__ pm, const int* __restrict__ pt_ptr,
+                               const int* __restrict__ fidx, const int* __restrict__ blk_ptr,
+                               const int* __restrict__ blk_col, const int* __restrict__ off, unsigned* keys, int2* vals) {
+  const int p = p_lo + blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= p_hi) return;
+  int o = off[p - p_lo];
+  const int a1 = pt_ptr[p + 1];
+  for (int a = pt_ptr[p]; a < a1; ++a) {
+    const int fa = fidx[pm[a].idx];
+    if (fa < 0) continue;
+    for (int b = a; b < a1; ++b) {
+      const int fb = fidx[pm[b].idx];
+      if (fb < 0) continue;
+      keys[o] = (unsigned)find_blk_ix(blk_ptr, blk_col, fa, fb);   // cameras ascend within a landmark
+      vals[o] = make_int2(a, b);
+      ++o;
+    }
+  }
+}
+
+__global__ void rows_of_blocks(int nfree, const int* __restrict__ blk_ptr, int* blk_row) {
+  const int f = blockIdx.x * blockDim.x + threadIdx.x;
+  if (f >= nfree) return;
+  for (int b = blk_ptr[f]; b < blk_ptr[f + 1]; ++b) blk_row[b] = f;
+}
+
+// sorted keys in [0, ndom) -> ptr[0..ndom]
+__global__ void keys_to_ptr(int n, int ndom, const unsigned* __restrict__ keys, int* ptr) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int k = (int)keys[i], prev = i == 0 ? -1 : (int)keys[i - 1];
+  for (int q = prev + 1; q <= k; ++q) ptr[q] = i;
+  if (i == n - 1)
+    for (int q = k + 1; q <= ndom; ++q) ptr[q] = n;
+}
+
 }  // namespace
+
+int large_build_pairs(int p_lo, int p_hi, const ObsRec* pm, const int* pt_ptr, LargeIndex& ix, cudaStream_t s) {
+  cudaError_t e = cudaSuccess;
+  const int npl = p_hi - p_lo, nblk = ix.nblk;
+  int *cnt = nullptr, *off = nullptr;
+  unsigned *k0 = nullptr, *k1 = nullptr;
+  int2* v0 = nullptr;
+  void* tmp = nullptr;
+  size_t tb = 0;
+  int last_cnt = 0, last_off = 0;
+  long long total = 0;
+  ix.npairs = 0;
+  B2_TRY(ix.pair_ptr.alloc((size_t)nblk + 1));
+  B2_TRY(ix.blk_row.alloc((size_t)nblk));
+  if (ix.nfree > 0) rows_of_blocks<<<(ix.nfree + 255) / 256, 256, 0, s>>>(ix.nfree, ix.blk_ptr.p, ix.blk_row.p);
+  if (npl > 0) {
+    B2_TRY(cudaMallocAsync(&cnt, (size_t)npl * sizeof(int), s));
+    B2_TRY(cudaMallocAsync(&off, (size_t)npl * sizeof(int), s));
+    count_all_pairs<<<(npl + 255) / 256, 256, 0, s>>>(p_lo, p_hi, pm, pt_ptr, ix.fidx.p, cnt);
+    cub::DeviceScan::ExclusiveSum(nullptr, tb, cnt, off, npl, s);
+    B2_TRY(cudaMallocAsync(&tmp, tb, s));
+    B2_TRY(cub::DeviceScan::ExclusiveSum(tmp, tb, cnt, off, npl, s));
+    B2_TRY(cudaMemcpyAsync(&last_cnt, cnt + npl - 1, sizeof(int), cudaMemcpyDeviceToHost, s));
+    B2_TRY(cudaMemcpyAsync(&last_off, off + npl - 1, sizeof(int), cudaMemcpyDeviceToHost, s));
+    B2_TRY(cudaStreamSynchronize(s));
+    B2_TRY(cudaFreeAsync(tmp, s));
+    tmp = nullptr;
+    total = (long long)last_cnt + last_off;
+  }
+  if (total >= (1ll << 31)) { e = cudaErrorInvalidValue; goto done; }
+  B2_TRY(ix.pair_ab.alloc((size_t)total));
+  if (total == 0) {
+    fill_int<<<(nblk + 256) / 256, 256, 0, s>>>(ix.pair_ptr.p, nblk + 1, 0);
+    goto done;
+  }
+  B2_TRY(cudaMallocAsync(&k0, (size_t)total * 4, s)); B2_TRY(cudaMallocAsync(&k1, (size_t)total * 4, s));
+  B2_TRY(cudaMallocAsync(&v0, (size_t)total * sizeof(int2), s));
+  emit_all_pairs<<<(npl + 255) / 256, 256, 0, s>>>(p_lo, p_hi, pm, pt_ptr, ix.fidx.p, ix.blk_ptr.p, ix.blk_col.p, off, k0, v0);
+  {
+    unsigned long long* vin = reinterpret_cast<unsigned long long*>(v0);
+    unsigned long long* vout = reinterpret_cast<unsigned long long*>(ix.pair_ab.p);
+    const int kb = bits_for(nblk);
+    cub::DeviceRadixSort::SortPairs(nullptr, tb, k0, k1, vin, vout, (int)total, 0, kb, s);
+    B2_TRY(cudaMallocAsync(&tmp, tb, s));
+    B2_TRY(cub::DeviceRadixSort::SortPairs(tmp, tb, k0, k1, vin, vout, (int)total, 0, kb, s));   // stable: landmark order kept
+  }
+  keys_to_ptr<<<(int)((total + 255) / 256), 256, 0, s>>>((int)total, nblk, k1, ix.pair_ptr.p);
+  B2_TRY(cudaGetLastError());
+  ix.npairs = total;
+done:
+  cudaFreeAsync(cnt, s); cudaFreeAsync(off, s); cudaFreeAsync(k0, s); cudaFreeAsync(k1, s);
+  cudaFreeAsync(v0, s); cudaFreeAsync(tmp, s);
+  cudaStreamSynchronize(s);
+  return (int)e;
+}
 
 int large_build_structure(int nc, int np, long long no, const ObsRec* pm, const int* pt_ptr,
                           const unsigned char* h_fixed, LargeIndex& ix, cudaStream_t s) {
@@ -303,11 +414,13 @@ __global__ void __launch_bounds__(kCamThreads) large_cam_kernel(LargeData d, Par
 __global__ void large_cam_finish_kernel(LargeData d) {
   const LargeCtrl* ctrl = d.ctrl;
   if (ctrl->stop || ctrl->have_lin) return;
-  if (threadIdx.x < 2) {
-    double v = 0.0;
-    for (int c = 0; c < d.nc; ++c) v += d.part[threadIdx.x * d.nc + c];
-    d.lin_part[(size_t)d.nc * 27 + threadIdx.x] = v;
-  }
+  // warp 0: cost, warp 1: invalid count; lane-strided partial sums, then a fixed shuffle tree
+  const int which = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  double v = 0.0;
+  for (int c = lane; c < d.nc; c += 32) v += d.part[which * d.nc + c];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  if (lane == 0) d.lin_part[(size_t)d.nc * 27 + which] = v;
 }
 
 // after the {B, g_c, cost} reduction: D_c, cost bookkeeping, S := blockdiag(B') (rank 0), g_red := g_c
@@ -356,10 +469,14 @@ __device__ __forceinline__ void atomic_max_pos(double* addr, double v) {   // v 
   atomicMax(reinterpret_cast<unsigned long long*>(addr), (unsigned long long)__double_as_longlong(v));
 }
 
-// a1-a4, point-major: one thread per landmark of this rank's range.  C_p, g_p -> F (C'^-1 = F F^T),
-// then S(fi,fj) -= Y_a E_b^T, g_red(fi) -= Y_a g_p with fp64 RED atomics on the block-sparse S
-// (contributions of one landmark go to k(k+1)/2 distinct blocks; cameras are not "hot" here).
-__global__ void __launch_bounds__(128) large_schur_kernel(LargeData d, Params P) {
+// a1-a4 in two passes without atomics (deterministic):
+//  (1) large_z_kernel, point-major, one thread per landmark of this rank's range: C_p, g_p -> F (C'^-1 = F F^T),
+//      per-landmark scratch for the back-substitution, and per observation  Z_k = E_k F (6 x 3)  and
+//      zy_k = Z_k F^T g_p (6)  into zbuf (24 doubles per observation; zero for fixed cameras / invalid);
+//  (2) large_sblock_kernel, one group of G lanes per S block: S(fa,fb) -= sum over the block's pair list of
+//      Z_a Z_b^T, and for diagonal blocks g_red(f) -= sum zy_a.  The pair list is sorted by block and keeps the
+//      landmark order inside a block, the lanes' partial sums are combined by a fixed shuffle tree.
+__global__ void __launch_bounds__(128) large_z_kernel(LargeData d, Params P) {
   LargeCtrl* ctrl = d.ctrl;
   if (ctrl->stop) return;
   const int p = d.p_lo + blockIdx.x * blockDim.x + threadIdx.x;
@@ -397,55 +514,93 @@ __global__ void __launch_bounds__(128) large_schur_kernel(LargeData d, Params P)
   for (int k = 0; k < 6; ++k) sc[k] = F[k];
   sc[6] = g[0]; sc[7] = g[1]; sc[8] = g[2]; sc[9] = D0; sc[10] = D1; sc[11] = D2;
   atomic_max_pos(&ctrl->sums[6], fmax(fabs(g[0]), fmax(fabs(g[1]), fabs(g[2]))));
-  // C'^-1 = F F^T (symmetric, upper)
-  const double I0 = F[0] * F[0] + F[1] * F[1] + F[2] * F[2], I1 = F[1] * F[3] + F[2] * F[4], I2 = F[2] * F[5];
-  const double I3 = F[3] * F[3] + F[4] * F[4], I4 = F[4] * F[5], I5 = F[5] * F[5];
-  double* gred = d.Sg + (size_t)d.nblk * 36;
+  // y = F^T g_p
+  const double y0 = F[0] * g[0], y1 = fma(F[1], g[0], F[3] * g[1]), y2 = fma(F[2], g[0], fma(F[4], g[1], F[5] * g[2]));
   for (int a = a0; a < a1; ++a) {
     const ObsRec ra = d.pm[a];
-    const int fa = d.fidx[ra.idx];
-    if (fa < 0) continue;
+    double2* zo = reinterpret_cast<double2*>(d.zbuf + (size_t)a * 24);
     const double* pose = d.poses + 12 * (size_t)ra.idx;
     Proj o;
     project(P, pose, X0, X1, X2, ra.u, ra.v, o);
-    if (!o.valid) continue;
-    double jp[6], jc[12], E[18], Y[18];
-    jac_point(P, pose, o, jp);
-    jac_cam(P, o, jc);
-    make_E(o.w, jc, jp, E);
+    double Z[24];
+    if (d.fidx[ra.idx] < 0 || !o.valid) {
 #pragma unroll
-    for (int r = 0; r < 6; ++r) {
-      const double e0 = E[3 * r], e1 = E[3 * r + 1], e2 = E[3 * r + 2];
-      Y[3 * r] = e0 * I0 + e1 * I1 + e2 * I2;
-      Y[3 * r + 1] = e0 * I1 + e1 * I3 + e2 * I4;
-      Y[3 * r + 2] = e0 * I2 + e1 * I4 + e2 * I5;
-      atomicAdd(&gred[6 * fa + r], -(Y[3 * r] * g[0] + Y[3 * r + 1] * g[1] + Y[3 * r + 2] * g[2]));
-    }
-    for (int b = a; b < a1; ++b) {
-      const ObsRec rb = d.pm[b];
-      const int fb = d.fidx[rb.idx];
-      if (fb < 0) continue;
-      double Eb[18];
-      if (b == a) {
+      for (int k = 0; k < 24; ++k) Z[k] = 0.0;
+    } else {
+      double jp[6], jc[12], E[18];
+      jac_point(P, pose, o, jp);
+      jac_cam(P, o, jc);
+      make_E(o.w, jc, jp, E);
 #pragma unroll
-        for (int k = 0; k < 18; ++k) Eb[k] = E[k];
-      } else {
-        const double* pb = d.poses + 12 * (size_t)rb.idx;
-        Proj ob;
-        project(P, pb, X0, X1, X2, rb.u, rb.v, ob);
-        if (!ob.valid) continue;
-        double jpb[6], jcb[12];
-        jac_point(P, pb, ob, jpb);
-        jac_cam(P, ob, jcb);
-        make_E(ob.w, jcb, jpb, Eb);
+      for (int r = 0; r < 6; ++r) {
+        const double e0 = E[3 * r], e1 = E[3 * r + 1], e2 = E[3 * r + 2];
+        Z[3 * r] = e0 * F[0];
+        Z[3 * r + 1] = fma(e0, F[1], e1 * F[3]);
+        Z[3 * r + 2] = fma(e0, F[2], fma(e1, F[4], e2 * F[5]));
+        Z[18 + r] = fma(Z[3 * r], y0, fma(Z[3 * r + 1], y1, Z[3 * r + 2] * y2));
       }
-      double* S = d.Sg + (size_t)find_blk(d.blk_ptr, d.blk_col, fa, fb) * 36;
-#pragma unroll
-      for (int r = 0; r < 6; ++r)
-#pragma unroll
-        for (int s = 0; s < 6; ++s)
-          atomicAdd(&S[6 * r + s], -(Y[3 * r] * Eb[3 * s] + Y[3 * r + 1] * Eb[3 * s + 1] + Y[3 * r + 2] * Eb[3 * s + 2]));
     }
+#pragma unroll
+    for (int k = 0; k < 12; ++k) zo[k] = make_double2(Z[2 * k], Z[2 * k + 1]);
+  }
+}
+
+template <int G>
+__global__ void __launch_bounds__(128) large_sblock_kernel(LargeData d) {
+  const LargeCtrl* ctrl = d.ctrl;
+  if (ctrl->stop) return;
+  const int gidx = (blockIdx.x * blockDim.x + threadIdx.x) / G, gl = threadIdx.x % G;
+  const bool live = gidx < d.nblk;                // (no early exit: the shuffles below name the full warp)
+  const int q0 = live ? d.pair_ptr[gidx] : 0, q1 = live ? d.pair_ptr[gidx + 1] : 0;
+  double acc[36], ag[6];
+#pragma unroll
+  for (int k = 0; k < 36; ++k) acc[k] = 0.0;
+#pragma unroll
+  for (int k = 0; k < 6; ++k) ag[k] = 0.0;
+  for (int q = q0 + gl; q < q1; q += G) {
+    const int2 ab = d.pair_ab[q];
+    const double2* za = reinterpret_cast<const double2*>(d.zbuf + (size_t)ab.x * 24);
+    double A[18], B[18];
+#pragma unroll
+    for (int k = 0; k < 9; ++k) { const double2 t = za[k]; A[2 * k] = t.x; A[2 * k + 1] = t.y; }
+    if (ab.x == ab.y) {
+#pragma unroll
+      for (int k = 0; k < 18; ++k) B[k] = A[k];
+#pragma unroll
+      for (int k = 0; k < 3; ++k) { const double2 t = za[9 + k]; ag[2 * k] += t.x; ag[2 * k + 1] += t.y; }
+    } else {
+      const double2* zb = reinterpret_cast<const double2*>(d.zbuf + (size_t)ab.y * 24);
+#pragma unroll
+      for (int k = 0; k < 9; ++k) { const double2 t = zb[k]; B[2 * k] = t.x; B[2 * k + 1] = t.y; }
+    }
+#pragma unroll
+    for (int r = 0; r < 6; ++r)
+#pragma unroll
+      for (int c = 0; c < 6; ++c)
+        acc[6 * r + c] = fma(A[3 * r], B[3 * c], fma(A[3 * r + 1], B[3 * c + 1], fma(A[3 * r + 2], B[3 * c + 2], acc[6 * r + c])));
+  }
+  // fixed shuffle tree over the G lanes of the group
+#pragma unroll
+  for (int m = G >> 1; m > 0; m >>= 1) {
+#pragma unroll
+    for (int k = 0; k < 36; ++k) acc[k] += __shfl_xor_sync(0xffffffffu, acc[k], m);
+#pragma unroll
+    for (int k = 0; k < 6; ++k) ag[k] += __shfl_xor_sync(0xffffffffu, ag[k], m);
+  }
+  if (q1 == q0) return;
+  double* S = d.Sg + (size_t)gidx * 36;
+#pragma unroll
+  for (int k = 0; k < 36; ++k)
+    if (k % G == gl) S[k] -= acc[k];
+  // a diagonal block's pair list is exactly the observation list of its camera: g_red(f) -= sum zy
+  const bool isdiag = d.pair_ab[q0].x == d.pair_ab[q0].y;
+  if (isdiag && gl < 6) {
+    const int f = d.blk_row[gidx];
+    double* gred = d.Sg + (size_t)d.nblk * 36;
+    double v = 0.0;
+#pragma unroll
+    for (int k = 0; k < 6; ++k) if (k == gl) v = ag[k];
+    gred[6 * f + gl] -= v;
   }
 }
 
@@ -639,7 +794,7 @@ namespace {
 __global__ void large_cam_update_kernel(LargeData d) {
   LargeCtrl* ctrl = d.ctrl;
   if (ctrl->stop) return;
-  __shared__ double red[8][4];
+  __shared__ double red[32][4];
   __shared__ int bad;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   if (tid == 0) bad = 0;
@@ -852,12 +1007,17 @@ int large_iteration(const LargeData& d, const Params& P, int pcg_max_iters, doub
   int rc;
   large_clear_accept_kernel<<<1, 1, 0, s>>>(d);
   if (d.nc > 0) large_cam_kernel<<<d.nc, kCamThreads, 0, s>>>(d, P);
-  large_cam_finish_kernel<<<1, 32, 0, s>>>(d);
+  large_cam_finish_kernel<<<1, 64, 0, s>>>(d);
   if (ar && (rc = ar(ar_user, d.lin_part, d.lin, d.lin_count(), s)) != 0) return rc;
   large_init_S_kernel<<<296, 256, 0, s>>>(d);
   large_init_diag_kernel<<<(d.nc + 127) / 128 + 1, 128, 0, s>>>(d);
   const int npl = d.p_hi - d.p_lo;
-  if (npl > 0) large_schur_kernel<<<(npl + 127) / 128, 128, 0, s>>>(d, P);
+  if (npl > 0) {
+    large_z_kernel<<<(npl + 127) / 128, 128, 0, s>>>(d, P);
+    // lanes per S block: dense visibility gives many blocks with a handful of pairs each
+    if (d.pair_lanes == 8) large_sblock_kernel<8><<<(int)(((size_t)d.nblk * 8 + 127) / 128), 128, 0, s>>>(d);
+    else large_sblock_kernel<32><<<(int)(((size_t)d.nblk * 32 + 127) / 128), 128, 0, s>>>(d);
+  }
   if (ar && (rc = ar(ar_user, d.Sg, d.Sg, d.sg_count(), s)) != 0) return rc;
   if (d.bw >= 0) {
     if ((rc = large_band_solve(d, s)) != 0) return rc;
@@ -872,7 +1032,7 @@ int large_iteration(const LargeData& d, const Params& P, int pcg_max_iters, doub
     cudaError_t e = cudaLaunchCooperativeKernel((void*)large_pcg_kernel, dim3(blocks), dim3(kPcgThreads), args, smem, s);
     if (e != cudaSuccess) return (int)e;
   }
-  large_cam_update_kernel<<<1, 256, 0, s>>>(d);
+  large_cam_update_kernel<<<1, 1024, 0, s>>>(d);
   const int nparts = (npl + kBsThreads - 1) / kBsThreads;
   if (nparts > 0) large_backsub_kernel<<<nparts, kBsThreads, 0, s>>>(d, P);
   large_reduce_kernel<<<1, 192, 0, s>>>(d, nparts);

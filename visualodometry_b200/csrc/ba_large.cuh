@@ -48,6 +48,11 @@ struct LargeData {
   double* dc;                      // n   delta_c (PCG x)
   double* r; double* z; double* q; // n each
   double* Minv;                    // nfree x 36
+  const int* pair_ptr;             // nblk+1: Schur pair list by S block (this rank's landmarks)
+  const int2* pair_ab;             // (observation a, observation b >= a) in point-major numbering
+  const int* blk_row;              // nblk: block row of each upper block
+  int pair_lanes;                  // lanes per S block in the Schur gather (8 or 32)
+  double* zbuf;                    // no x 24: per observation Z = E F (18) and Z F^T g_p (6)
   int bw;                          // block half-bandwidth of S if the banded Cholesky is used, else -1 (PCG)
   double* band;                    // nfree x (bw+1) x 36: lower band by block column (A, then L in place)
   double* binv;                    // nfree x 6: 1 / diag(L)
@@ -66,11 +71,15 @@ typedef int (*AllReduceFn)(void* user, const double* send, double* recv, size_t 
 
 // S block structure from the point-major stream (a8, device). Fills the DevBufs; returns cudaError.
 struct LargeIndex {
-  DevBuf<int> fidx, blk_ptr, blk_col, frow_ptr, fcol, fsrc;
+  DevBuf<int> fidx, blk_ptr, blk_col, frow_ptr, fcol, fsrc, pair_ptr, blk_row;
+  DevBuf<int2> pair_ab;
+  long long npairs = 0;
   int nblk = 0, nfull = 0, nfree = 0;
 };
 int large_build_structure(int nc, int np, long long no, const ObsRec* pm, const int* pt_ptr,
                           const unsigned char* h_fixed, LargeIndex& ix, cudaStream_t s);
+// Schur pair list of the landmarks [p_lo, p_hi) (needs the structure): ix.pair_ptr / pair_ab / blk_row
+int large_build_pairs(int p_lo, int p_hi, const ObsRec* pm, const int* pt_ptr, LargeIndex& ix, cudaStream_t s);
 // camera-major stream of the observations of landmarks [p_lo, p_hi)
 int large_build_cm_slice(int nc, int p_lo, int p_hi, const ObsRec* pm, const int* pt_ptr, ObsRec* cm,
                          int* cam_ptr, cudaStream_t s);
