@@ -173,7 +173,13 @@ LargeData make_large(b2ba* h, bool hist) {
   d.Dc = h->l_Dc.p; d.pt_scratch = h->d_scratch.p; d.Sg = h->l_Sg.p; d.dc = h->l_dc.p;
   d.r = h->l_r.p; d.z = h->l_z.p; d.q = h->l_q.p; d.Minv = h->l_Minv.p; d.part = h->l_part.p;
   d.pair_ptr = h->lix.pair_ptr.p; d.pair_ab = h->lix.pair_ab.p; d.blk_row = h->lix.blk_row.p; d.zbuf = h->l_zbuf.p;
-  d.pair_lanes = (h->lix.nblk > 0 && h->lix.npairs / h->lix.nblk < 24) ? 8 : 32;
+  d.pm_pt = h->lix.pm_pt.p; d.a_lo = h->lix.a_lo; d.a_hi = h->lix.a_hi;
+  {
+    // average pair-list length of the off-diagonal blocks (a diagonal list = the camera's observations)
+    const long long noff = h->lix.nblk - h->lix.nfree;
+    const long long per = noff > 0 ? (h->lix.npairs - (h->p_hi > h->p_lo ? h->lix.a_hi - h->lix.a_lo : 0)) / noff : 1000;
+    d.pair_lanes = per < 10 ? 1 : per < 48 ? 8 : 32;
+  }
   d.bw = h->l_bw; d.band = h->l_band.p; d.binv = h->l_binv.p; d.band_P = h->l_band_P; d.band_ws = h->l_band_ws.p;
   d.sums_part = h->l_sums.p; d.ctrl = h->l_ctrl.p; d.summary = h->d_summ.p;
   d.hist_cost = hist ? h->d_hist_cost.p : nullptr; d.hist_mu = hist ? h->d_hist_mu.p : nullptr;
@@ -194,7 +200,7 @@ int setup_large(b2ba* h) {
   CU(h->l_cm.alloc(h->no), "alloc"); CU(h->l_cam_ptr.alloc(nc + 1), "alloc");
   rc = large_build_cm_slice(h->nc_tot, h->p_lo, h->p_hi, h->d_pm.p, h->d_pt_ptr.p, h->l_cm.p, h->l_cam_ptr.p, nullptr);
   if (rc) return cuda_fail(h, (cudaError_t)rc, "large_build_cm_slice");
-  rc = large_build_pairs(h->p_lo, h->p_hi, h->d_pm.p, h->d_pt_ptr.p, h->lix, nullptr);
+  rc = large_build_pairs(h->p_lo, h->p_hi, h->no, h->d_pm.p, h->d_pt_ptr.p, h->lix, nullptr);
   if (rc) return cuda_fail(h, (cudaError_t)rc, "large_build_pairs");
   CU(h->l_zbuf.alloc((size_t)h->no * 24), "alloc");
   int blocks = 0;

@@ -25,6 +25,7 @@ namespace {
 
 constexpr int kBandThreads = 128;
 constexpr int kBandAhead = 3;      // block columns loaded ahead of the active window
+constexpr int kBackAhead = 5;      // backward pass: columns L1-prefetched ahead of their register fetch
 
 // One SPD block-banded system.  band block (j, k), k = 0..w, is A_{j+k, j} (6 x 6 row-major): the lower
 // band by block column (in: A, out: L).  rhs: per block column 6 x nr row-major (in: B, out: Y = L^-1 B, and
@@ -134,22 +135,31 @@ __global__ void __launch_bounds__(NT) band_forward_kernel(LargeCtrl* ctrl, BandS
   double* ring = bsm;
   double* Lsm = ring + (size_t)RS * SLOT;              // factor of the current diagonal block (36)
   __shared__ int bad;
-  if (tid == 0) bad = 0;
+  __shared__ unsigned char pairA[kBandMaxBw * (kBandMaxBw + 1) / 2], pairB[kBandMaxBw * (kBandMaxBw + 1) / 2];
+  if (tid == 0) {
+    bad = 0;
+    int k = 0;                                         // block pairs (a >= b >= 1) of a full window, b-major
+    for (int b = 1; b <= w; ++b)
+      for (int a = b; a <= w; ++a) { pairA[k] = (unsigned char)a; pairB[k] = (unsigned char)b; ++k; }
+  }
+  const int npair_full = w * (w + 1) / 2;
 
-  auto load_col = [&](int j) {                         // global band column j + its rhs rows -> ring slot
-    double* sl = ring + (size_t)((j - lo) % RS) * SLOT;
+  auto load_col = [&](int j, int slot) {               // global band column j + its rhs rows -> ring slot
+    double* sl = ring + (size_t)slot * SLOT;
     const double* g = s.band + (size_t)j * NB;
     for (int i = tid; i < NB / 2; i += NT) cp_async16(sl + 2 * i, g + 2 * i);
     const double* gr = s.rhs + (size_t)j * 6 * nr;
     for (int i = tid; i < 3 * nr; i += NT) cp_async16(sl + NB + 2 * i, gr + 2 * i);
   };
-  for (int j = lo; j < min(lo + RS - 1, hi); ++j) load_col(j);
+  for (int j = lo; j < min(lo + RS - 1, hi); ++j) load_col(j, j - lo);
   cp_async_commit();
   cp_async_wait<0>();
   __syncthreads();
 
-  for (int j = lo; j < hi; ++j) {
-    double* cj = ring + (size_t)((j - lo) % RS) * SLOT;
+  int sj = 0;                                          // ring slot of column j (incremental: no division)
+  for (int j = lo; j < hi; ++j, sj = (sj + 1 == RS ? 0 : sj + 1)) {
+    double* cj = ring + (size_t)sj * SLOT;
+    auto slot_of = [&](int a) { const int t = sj + a; return ring + (size_t)(t >= RS ? t - RS : t) * SLOT; };
     // ---- every thread factors the diagonal block redundantly in registers
     double L[6][6], inv[6];
     bool isbad = false;
@@ -223,34 +233,34 @@ __global__ void __launch_bounds__(NT) band_forward_kernel(LargeCtrl* ctrl, BandS
     __syncthreads();
     // ---- trailing update inside the window: A_{j+a,j+b} -= L_{j+a,j} L_{j+b,j}^T (a >= b >= 1), items = 6x6
     // entries flattened over (b, a, r, c); right-hand sides B_{j+a} -= L_{j+a,j} Y_j, items = (r, column)
-    const int npair = wj * (wj + 1) / 2;
-    for (int id = tid; id < npair * 36; id += NT) {
+    for (int id = tid; id < npair_full * 36; id += NT) {
       const int e = id % 36, pr = id / 36;
-      int b = 1, rem = pr, len = wj;                   // pairs enumerated b = 1..wj, a = b..wj
-      while (rem >= len) { rem -= len; --len; ++b; }
-      const int a = b + rem, r = e / 6, c = e % 6;
-      const double* la = cj + 36 * a + 6 * r;
-      const double* lb = cj + 36 * b + 6 * c;
-      double* dst = ring + (size_t)((j + b - lo) % RS) * SLOT + 36 * (a - b) + 6 * r + c;
-      double v = *dst;
+      const int a = pairA[pr], b = pairB[pr], r = e / 6, c = e % 6;
+      if (a <= wj) {
+        const double* la = cj + 36 * a + 6 * r;
+        const double* lb = cj + 36 * b + 6 * c;
+        double* dst = slot_of(b) + 36 * (a - b) + 6 * r + c;
+        double v = *dst;
 #pragma unroll
-      for (int m = 0; m < 6; ++m) v = fma(-la[m], lb[m], v);
-      *dst = v;
+        for (int m = 0; m < 6; ++m) v = fma(-la[m], lb[m], v);
+        *dst = v;
+      }
     }
-    if (wj > 0) {
-      for (int id = tid; id < 6 * nr; id += NT) {
-        const int r = id / nr, q = id - r * nr;
-        double y[6];
+    // items = (block a, right-hand side q): the 6 rows of B_{j+a}[:, q] with Y_j[:, q] in registers
+    for (int id = tid; id < wj * nr; id += NT) {
+      int q = id, a = 1;
+      while (q >= nr) { q -= nr; ++a; }
+      double y[6];
 #pragma unroll
-        for (int m = 0; m < 6; ++m) y[m] = cj[NB + m * nr + q];
-        for (int a = 1; a <= wj; ++a) {
-          const double* la = cj + 36 * a + 6 * r;
-          double* dst = ring + (size_t)((j + a - lo) % RS) * SLOT + NB + r * nr + q;
-          double v = *dst;
+      for (int m = 0; m < 6; ++m) y[m] = cj[NB + m * nr + q];
+      const double* la = cj + 36 * a;
+      double* dst = slot_of(a) + NB + q;
 #pragma unroll
-          for (int m = 0; m < 6; ++m) v = fma(-la[m], y[m], v);
-          *dst = v;
-        }
+      for (int r = 0; r < 6; ++r) {
+        double v = dst[r * nr];
+#pragma unroll
+        for (int m = 0; m < 6; ++m) v = fma(-la[6 * r + m], y[m], v);
+        dst[r * nr] = v;
       }
     }
     // ---- column j is final: L blocks back to the band array, Y_j to the rhs array
@@ -262,7 +272,7 @@ __global__ void __launch_bounds__(NT) band_forward_kernel(LargeCtrl* ctrl, BandS
     }
     // the slot of column j-1 is free since the previous barrier: it takes column j-1+RS, which is first
     // touched kBandAhead steps from now (asynchronous copy: nobody waits for it here)
-    if (j + RS - 1 < hi) load_col(j + RS - 1);
+    if (j + RS - 1 < hi) load_col(j + RS - 1, sj == 0 ? RS - 1 : sj - 1);
     cp_async_commit();
     __syncthreads();
   }
@@ -412,6 +422,13 @@ __global__ void __launch_bounds__(kBandThreads) band_backward_kernel(LargeCtrl* 
 #pragma unroll
       for (int r = 0; r < 6; ++r) { blk[r] = nb[r]; dg[r] = nd[r]; }
       const double inv_c = ninv, yc = ny;
+      if (j - kBackAhead >= lo) {                       // L1 prefetch of a column a few steps ahead of its fetch
+        const int jp = j - kBackAhead;
+        const char* pc = reinterpret_cast<const char*>(s.band + (size_t)jp * NB);
+        for (int i = lane; i * 128 < NB * 8; i += 32) prefetch_l1(pc + i * 128);
+        if (lane < 6) prefetch_l1(s.rhs + ((size_t)jp * 6 + lane) * nr);
+        else if (lane == 6) prefetch_l1(s.binv + 6 * (size_t)jp);
+      }
       if (j > lo) fetch(j - 1);
       // t[c] = sum_a sum_r L_{j+a,j}[r][c] x_{j+a}[r]
       double t = 0.0;
@@ -502,13 +519,17 @@ int large_band_solve(const LargeData& d, cudaStream_t st) {
   if (smem > configured) {
     cudaError_t e = cudaFuncSetAttribute(band_forward_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(band_forward_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(band_forward_kernel<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return (int)e;
     configured = smem;
   }
   // wide bands: the trailing update is throughput-bound, 256 threads; narrow bands: latency-bound, one warp
   // per scheduler
+  static const int env_threads = getenv("B2BA_BAND_THREADS") ? atoi(getenv("B2BA_BAND_THREADS")) : 0;
   auto forward = [&](const BandSys& sys, int chunks, size_t sm) {
-    if (sys.w > 8) band_forward_kernel<256><<<chunks, 256, sm, st>>>(d.ctrl, sys, chunks);
+    const int nt = env_threads ? env_threads : 256;
+    if (nt >= 512) band_forward_kernel<512><<<chunks, 512, sm, st>>>(d.ctrl, sys, chunks);
+    else if (nt >= 256) band_forward_kernel<256><<<chunks, 256, sm, st>>>(d.ctrl, sys, chunks);
     else band_forward_kernel<128><<<chunks, 128, sm, st>>>(d.ctrl, sys, chunks);
   };
   BandSys s{d.band, d.band_ws + pl.off_rhs, d.binv, N, w, pl.nr};

@@ -170,7 +170,7 @@ __global__ void keys_to_ptr(int n, int ndom, const unsigned* __restrict__ keys, 
 
 }  // namespace
 
-int large_build_pairs(int p_lo, int p_hi, const ObsRec* pm, const int* pt_ptr, LargeIndex& ix, cudaStream_t s) {
+int large_build_pairs(int p_lo, int p_hi, long long no, const ObsRec* pm, const int* pt_ptr, LargeIndex& ix, cudaStream_t s) {
   cudaError_t e = cudaSuccess;
   const int npl = p_hi - p_lo, nblk = ix.nblk;
   int *cnt = nullptr, *off = nullptr;
@@ -183,6 +183,11 @@ int large_build_pairs(int p_lo, int p_hi, const ObsRec* pm, const int* pt_ptr, L
   ix.npairs = 0;
   B2_TRY(ix.pair_ptr.alloc((size_t)nblk + 1));
   B2_TRY(ix.blk_row.alloc((size_t)nblk));
+  B2_TRY(ix.pm_pt.alloc((size_t)no));
+  B2_TRY(cudaMemcpyAsync(&ix.a_lo, pt_ptr + p_lo, sizeof(int), cudaMemcpyDeviceToHost, s));
+  B2_TRY(cudaMemcpyAsync(&ix.a_hi, pt_ptr + p_hi, sizeof(int), cudaMemcpyDeviceToHost, s));
+  B2_TRY(cudaStreamSynchronize(s));
+  if (npl > 0) pt_of_obs<<<(npl + 255) / 256, 256, 0, s>>>(p_lo, p_hi, pt_ptr, 0, ix.pm_pt.p);
   if (ix.nfree > 0) rows_of_blocks<<<(ix.nfree + 255) / 256, 256, 0, s>>>(ix.nfree, ix.blk_ptr.p, ix.blk_row.p);
   if (npl > 0) {
     B2_TRY(cudaMallocAsync(&cnt, (size_t)npl * sizeof(int), s));
@@ -476,13 +481,14 @@ __device__ __forceinline__ void atomic_max_pos(double* addr, double v) {   // v 
 //  (2) large_sblock_kernel, one group of G lanes per S block: S(fa,fb) -= sum over the block's pair list of
 //      Z_a Z_b^T, and for diagonal blocks g_red(f) -= sum zy_a.  The pair list is sorted by block and keeps the
 //      landmark order inside a block, the lanes' partial sums are combined by a fixed shuffle tree.
-__global__ void __launch_bounds__(128) large_z_kernel(LargeData d, Params P) {
+__global__ void __launch_bounds__(128) large_pt_kernel(LargeData d, Params P) {
   LargeCtrl* ctrl = d.ctrl;
   if (ctrl->stop) return;
-  const int p = d.p_lo + blockIdx.x * blockDim.x + threadIdx.x;
-  if (p >= d.p_hi) return;
+  const int pi = d.p_lo + blockIdx.x * blockDim.x + threadIdx.x;
+  const bool live = pi < d.p_hi;                  // (no early exit: warp-wide max below)
+  const int p = live ? pi : d.p_lo;
   const double imu = 1.0 / ctrl->mu;
-  const int a0 = d.pt_ptr[p], a1 = d.pt_ptr[p + 1];
+  const int a0 = d.pt_ptr[p], a1 = live ? d.pt_ptr[p + 1] : a0;
   const double X0 = d.pts[3 * (size_t)p], X1 = d.pts[3 * (size_t)p + 1], X2 = d.pts[3 * (size_t)p + 2];
   double C[6] = {0, 0, 0, 0, 0, 0}, g[3] = {0, 0, 0};
   for (int a = a0; a < a1; ++a) {
@@ -506,51 +512,69 @@ __global__ void __launch_bounds__(128) large_z_kernel(LargeData d, Params P) {
     if (!sym3_inv_factor(Cd, F)) {
 #pragma unroll
       for (int k = 0; k < 6; ++k) F[k] = 0.0;
-      ctrl->step_bad = 1;
+      if (live) ctrl->step_bad = 1;
     }
   }
-  double* sc = d.pt_scratch + (size_t)p * 12;
-#pragma unroll
-  for (int k = 0; k < 6; ++k) sc[k] = F[k];
-  sc[6] = g[0]; sc[7] = g[1]; sc[8] = g[2]; sc[9] = D0; sc[10] = D1; sc[11] = D2;
-  atomic_max_pos(&ctrl->sums[6], fmax(fabs(g[0]), fmax(fabs(g[1]), fabs(g[2]))));
-  // y = F^T g_p
-  const double y0 = F[0] * g[0], y1 = fma(F[1], g[0], F[3] * g[1]), y2 = fma(F[2], g[0], fma(F[4], g[1], F[5] * g[2]));
-  for (int a = a0; a < a1; ++a) {
-    const ObsRec ra = d.pm[a];
-    double2* zo = reinterpret_cast<double2*>(d.zbuf + (size_t)a * 24);
-    const double* pose = d.poses + 12 * (size_t)ra.idx;
-    Proj o;
-    project(P, pose, X0, X1, X2, ra.u, ra.v, o);
-    double Z[24];
-    if (d.fidx[ra.idx] < 0 || !o.valid) {
-#pragma unroll
-      for (int k = 0; k < 24; ++k) Z[k] = 0.0;
-    } else {
-      double jp[6], jc[12], E[18];
-      jac_point(P, pose, o, jp);
-      jac_cam(P, o, jc);
-      make_E(o.w, jc, jp, E);
-#pragma unroll
-      for (int r = 0; r < 6; ++r) {
-        const double e0 = E[3 * r], e1 = E[3 * r + 1], e2 = E[3 * r + 2];
-        Z[3 * r] = e0 * F[0];
-        Z[3 * r + 1] = fma(e0, F[1], e1 * F[3]);
-        Z[3 * r + 2] = fma(e0, F[2], fma(e1, F[4], e2 * F[5]));
-        Z[18 + r] = fma(Z[3 * r], y0, fma(Z[3 * r + 1], y1, Z[3 * r + 2] * y2));
-      }
-    }
-#pragma unroll
-    for (int k = 0; k < 12; ++k) zo[k] = make_double2(Z[2 * k], Z[2 * k + 1]);
+  if (live) {
+    double2* sc = reinterpret_cast<double2*>(d.pt_scratch + (size_t)p * 12);
+    sc[0] = make_double2(F[0], F[1]); sc[1] = make_double2(F[2], F[3]); sc[2] = make_double2(F[4], F[5]);
+    sc[3] = make_double2(g[0], g[1]); sc[4] = make_double2(g[2], D0); sc[5] = make_double2(D1, D2);
   }
+  double gm = live ? fmax(fabs(g[0]), fmax(fabs(g[1]), fabs(g[2]))) : 0.0;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) gm = fmax(gm, __shfl_xor_sync(0xffffffffu, gm, o));
+  if ((threadIdx.x & 31) == 0) atomic_max_pos(&ctrl->sums[6], gm);
 }
 
-template <int G>
+// per observation of this rank's range: Z = E F (6 x 3), zy = Z F^T g_p (6) -> zbuf
+__global__ void __launch_bounds__(256) large_z_kernel(LargeData d, Params P, int a_lo, int a_hi) {
+  const LargeCtrl* ctrl = d.ctrl;
+  if (ctrl->stop) return;
+  const int a = a_lo + blockIdx.x * blockDim.x + threadIdx.x;
+  if (a >= a_hi) return;
+  const ObsRec ra = d.pm[a];
+  const int p = d.pm_pt[a];
+  double2* zo = reinterpret_cast<double2*>(d.zbuf + (size_t)a * 24);
+  const double* pose = d.poses + 12 * (size_t)ra.idx;
+  Proj o;
+  project(P, pose, d.pts[3 * (size_t)p], d.pts[3 * (size_t)p + 1], d.pts[3 * (size_t)p + 2], ra.u, ra.v, o);
+  double Z[24];
+  if (d.fidx[ra.idx] < 0 || !o.valid) {
+#pragma unroll
+    for (int k = 0; k < 24; ++k) Z[k] = 0.0;
+  } else {
+    const double2* sc = reinterpret_cast<const double2*>(d.pt_scratch + (size_t)p * 12);
+    const double2 s0 = sc[0], s1 = sc[1], s2 = sc[2], s3 = sc[3], s4 = sc[4];
+    const double F0 = s0.x, F1 = s0.y, F2 = s1.x, F3 = s1.y, F4 = s2.x, F5 = s2.y;
+    const double g0 = s3.x, g1 = s3.y, g2 = s4.x;
+    const double y0 = F0 * g0, y1 = fma(F1, g0, F3 * g1), y2 = fma(F2, g0, fma(F4, g1, F5 * g2));   // y = F^T g_p
+    double jp[6], jc[12], E[18];
+    jac_point(P, pose, o, jp);
+    jac_cam(P, o, jc);
+    make_E(o.w, jc, jp, E);
+#pragma unroll
+    for (int r = 0; r < 6; ++r) {
+      const double e0 = E[3 * r], e1 = E[3 * r + 1], e2 = E[3 * r + 2];
+      Z[3 * r] = e0 * F0;
+      Z[3 * r + 1] = fma(e0, F1, e1 * F3);
+      Z[3 * r + 2] = fma(e0, F2, fma(e1, F4, e2 * F5));
+      Z[18 + r] = fma(Z[3 * r], y0, fma(Z[3 * r + 1], y1, Z[3 * r + 2] * y2));
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < 12; ++k) zo[k] = make_double2(Z[2 * k], Z[2 * k + 1]);
+}
+
+// MODE 0: every block; 1: diagonal blocks only (group index = block row); 2: off-diagonal blocks only.  Dense
+// visibility has diagonal pair lists of ~observations-per-camera entries next to off-diagonal lists of a handful.
+template <int G, int MODE>
 __global__ void __launch_bounds__(128) large_sblock_kernel(LargeData d) {
   const LargeCtrl* ctrl = d.ctrl;
   if (ctrl->stop) return;
-  const int gidx = (blockIdx.x * blockDim.x + threadIdx.x) / G, gl = threadIdx.x % G;
-  const bool live = gidx < d.nblk;                // (no early exit: the shuffles below name the full warp)
+  const int gi = (blockIdx.x * blockDim.x + threadIdx.x) / G, gl = threadIdx.x % G;
+  bool live = gi < (MODE == 1 ? d.nfree : d.nblk);   // (no early exit: the shuffles below name the full warp)
+  const int gidx = !live ? 0 : MODE == 1 ? d.blk_ptr[gi] : gi;   // the diagonal block is the first of its row
+  if (MODE == 2 && live && d.blk_row[gidx] == d.blk_col[gidx]) live = false;
   const int q0 = live ? d.pair_ptr[gidx] : 0, q1 = live ? d.pair_ptr[gidx + 1] : 0;
   double acc[36], ag[6];
 #pragma unroll
@@ -594,13 +618,12 @@ __global__ void __launch_bounds__(128) large_sblock_kernel(LargeData d) {
     if (k % G == gl) S[k] -= acc[k];
   // a diagonal block's pair list is exactly the observation list of its camera: g_red(f) -= sum zy
   const bool isdiag = d.pair_ab[q0].x == d.pair_ab[q0].y;
-  if (isdiag && gl < 6) {
+  if (isdiag) {
     const int f = d.blk_row[gidx];
     double* gred = d.Sg + (size_t)d.nblk * 36;
-    double v = 0.0;
 #pragma unroll
-    for (int k = 0; k < 6; ++k) if (k == gl) v = ag[k];
-    gred[6 * f + gl] -= v;
+    for (int k = 0; k < 6; ++k)
+      if (k % G == gl) gred[6 * f + k] -= ag[k];
   }
 }
 
@@ -1013,10 +1036,16 @@ int large_iteration(const LargeData& d, const Params& P, int pcg_max_iters, doub
   large_init_diag_kernel<<<(d.nc + 127) / 128 + 1, 128, 0, s>>>(d);
   const int npl = d.p_hi - d.p_lo;
   if (npl > 0) {
-    large_z_kernel<<<(npl + 127) / 128, 128, 0, s>>>(d, P);
+    large_pt_kernel<<<(npl + 127) / 128, 128, 0, s>>>(d, P);
+    if (d.a_hi > d.a_lo) large_z_kernel<<<(d.a_hi - d.a_lo + 255) / 256, 256, 0, s>>>(d, P, d.a_lo, d.a_hi);
     // lanes per S block: dense visibility gives many blocks with a handful of pairs each
-    if (d.pair_lanes == 8) large_sblock_kernel<8><<<(int)(((size_t)d.nblk * 8 + 127) / 128), 128, 0, s>>>(d);
-    else large_sblock_kernel<32><<<(int)(((size_t)d.nblk * 32 + 127) / 128), 128, 0, s>>>(d);
+    if (d.pair_lanes == 32) {
+      large_sblock_kernel<32, 0><<<(int)(((size_t)d.nblk * 32 + 127) / 128), 128, 0, s>>>(d);
+    } else {
+      large_sblock_kernel<32, 1><<<(int)(((size_t)d.nfree * 32 + 127) / 128), 128, 0, s>>>(d);
+      if (d.pair_lanes == 1) large_sblock_kernel<1, 2><<<(d.nblk + 127) / 128, 128, 0, s>>>(d);
+      else large_sblock_kernel<8, 2><<<(int)(((size_t)d.nblk * 8 + 127) / 128), 128, 0, s>>>(d);
+    }
   }
   if (ar && (rc = ar(ar_user, d.Sg, d.Sg, d.sg_count(), s)) != 0) return rc;
   if (d.bw >= 0) {

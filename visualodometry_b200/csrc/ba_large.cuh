@@ -51,6 +51,8 @@ struct LargeData {
   const int* pair_ptr;             // nblk+1: Schur pair list by S block (this rank's landmarks)
   const int2* pair_ab;             // (observation a, observation b >= a) in point-major numbering
   const int* blk_row;              // nblk: block row of each upper block
+  const int* pm_pt;                // no: landmark of each point-major observation (this rank's range)
+  int a_lo, a_hi;                  // this rank's observation range in the point-major stream
   int pair_lanes;                  // lanes per S block in the Schur gather (8 or 32)
   double* zbuf;                    // no x 24: per observation Z = E F (18) and Z F^T g_p (6)
   int bw;                          // block half-bandwidth of S if the banded Cholesky is used, else -1 (PCG)
@@ -71,7 +73,8 @@ typedef int (*AllReduceFn)(void* user, const double* send, double* recv, size_t 
 
 // S block structure from the point-major stream (a8, device). Fills the DevBufs; returns cudaError.
 struct LargeIndex {
-  DevBuf<int> fidx, blk_ptr, blk_col, frow_ptr, fcol, fsrc, pair_ptr, blk_row;
+  DevBuf<int> fidx, blk_ptr, blk_col, frow_ptr, fcol, fsrc, pair_ptr, blk_row, pm_pt;
+  int a_lo = 0, a_hi = 0;
   DevBuf<int2> pair_ab;
   long long npairs = 0;
   int nblk = 0, nfull = 0, nfree = 0;
@@ -79,7 +82,7 @@ struct LargeIndex {
 int large_build_structure(int nc, int np, long long no, const ObsRec* pm, const int* pt_ptr,
                           const unsigned char* h_fixed, LargeIndex& ix, cudaStream_t s);
 // Schur pair list of the landmarks [p_lo, p_hi) (needs the structure): ix.pair_ptr / pair_ab / blk_row
-int large_build_pairs(int p_lo, int p_hi, const ObsRec* pm, const int* pt_ptr, LargeIndex& ix, cudaStream_t s);
+int large_build_pairs(int p_lo, int p_hi, long long no, const ObsRec* pm, const int* pt_ptr, LargeIndex& ix, cudaStream_t s);
 // camera-major stream of the observations of landmarks [p_lo, p_hi)
 int large_build_cm_slice(int nc, int p_lo, int p_hi, const ObsRec* pm, const int* pt_ptr, ObsRec* cm,
                          int* cam_ptr, cudaStream_t s);
