@@ -25,7 +25,7 @@ namespace {
 
 constexpr int kBandThreads = 128;
 constexpr int kBandAhead = 3;      // block columns loaded ahead of the active window
-constexpr int kBackAhead = 5;      // backward pass: columns L1-prefetched ahead of their register fetch
+constexpr int kBackRing = 8;       // backward pass: columns staged ahead in shared memory
 
 // One SPD block-banded system.  band block (j, k), k = 0..w, is A_{j+k, j} (6 x 6 row-major): the lower
 // band by block column (in: A, out: L).  rhs: per block column 6 x nr row-major (in: B, out: Y = L^-1 B, and
@@ -47,6 +47,10 @@ __host__ __device__ inline void chunk_range(int N, int w, int P, int i, int& lo,
 __device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
   const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(s), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async8(void* smem, const void* gmem) {
+  const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;\n" ::"r"(s), "l"(gmem) : "memory");
 }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
 template <int N>
@@ -397,50 +401,44 @@ __global__ void __launch_bounds__(kBandThreads) band_backward_kernel(LargeCtrl* 
     }
     __syncthreads();
   }
-  // Lane layout: c = lane % 6 (component), sl = lane / 6 (a-slice, 5 slices; lanes 30, 31 idle).  The entries a
-  // lane needs from column j-1 (its first a-slice, the diagonal block column c, 1/diag, z) are loaded one step
-  // ahead, so the L2 latency of the band array is off the serial chain.
+  // Warp 0 walks the columns backwards.  Lane layout: c = lane % 6 (component), sl = lane / 6 (a-slice, 5
+  // slices; lanes 30, 31 idle).  Column j's L blocks, 1/diag and z come from a shared-memory ring that the warp
+  // itself fills kBackRing columns ahead with cp.async, so no global-memory latency sits on the serial chain.
   if (warp == 0) {
     const int c = lane % 6, sl = lane / 6;
-    double nb[6], nd[6], ninv = 0.0, ny = 0.0;          // prefetched for the column about to be processed
-    auto fetch = [&](int j) {
+    const int CS = NB + 12;                            // ring slot: L column | 1/diag (6) | z (6)
+    double* bring = xc + 12 * w;
+    auto issue = [&](int j, int slot) {
+      double* dst = bring + (size_t)slot * CS;
       const double* g = s.band + (size_t)j * NB;
-      const int wj = min(w, hi - 1 - j);
-#pragma unroll
-      for (int r = 0; r < 6; ++r) {
-        nb[r] = (lane < 30 && 1 + sl <= wj) ? g[36 * (1 + sl) + 6 * r + c] : 0.0;
-        nd[r] = lane < 6 ? g[6 * r + c] : 0.0;          // column c of L_jj: L[r][c], r > c used
-      }
-      ninv = lane < 6 ? s.binv[6 * (size_t)j + lane] : 0.0;
-      ny = lane < 6 ? s.rhs[((size_t)j * 6 + lane) * nr] : 0.0;
+      for (int i = lane; i < NB / 2; i += 32) cp_async16(dst + 2 * i, g + 2 * i);
+      if (lane < 3) cp_async16(dst + NB + 2 * lane, s.binv + 6 * (size_t)j + 2 * lane);
+      else if (lane >= 8 && lane < 14) cp_async8(dst + NB + 6 + (lane - 8), s.rhs + ((size_t)j * 6 + (lane - 8)) * nr);
     };
-    if (hi > lo) fetch(hi - 1);
+    for (int k = 0; k < kBackRing; ++k) {
+      if (hi - 1 - k >= lo) issue(hi - 1 - k, k);
+      cp_async_commit();
+    }
+    int slot = 0, xj = (hi - 1) % W1;                   // ring slot of column j; x-ring slot j % W1
     for (int j = hi - 1; j >= lo; --j) {
+      cp_async_wait<kBackRing - 1>();
+      __syncwarp();
+      const double* col = bring + (size_t)slot * CS;
       const int wj = min(w, hi - 1 - j);
-      const double* g = s.band + (size_t)j * NB;
-      double blk[6], dg[6];
+      const double inv_c = lane < 6 ? col[NB + lane] : 0.0, yc = lane < 6 ? col[NB + 6 + lane] : 0.0;
+      double dg[6];
 #pragma unroll
-      for (int r = 0; r < 6; ++r) { blk[r] = nb[r]; dg[r] = nd[r]; }
-      const double inv_c = ninv, yc = ny;
-      if (j - kBackAhead >= lo) {                       // L1 prefetch of a column a few steps ahead of its fetch
-        const int jp = j - kBackAhead;
-        const char* pc = reinterpret_cast<const char*>(s.band + (size_t)jp * NB);
-        for (int i = lane; i * 128 < NB * 8; i += 32) prefetch_l1(pc + i * 128);
-        if (lane < 6) prefetch_l1(s.rhs + ((size_t)jp * 6 + lane) * nr);
-        else if (lane == 6) prefetch_l1(s.binv + 6 * (size_t)jp);
-      }
-      if (j > lo) fetch(j - 1);
+      for (int r = 0; r < 6; ++r) dg[r] = lane < 6 ? col[6 * r + c] : 0.0;   // column c of L_jj: L[r][c], r > c used
       // t[c] = sum_a sum_r L_{j+a,j}[r][c] x_{j+a}[r]
       double t = 0.0;
-      if (lane < 30 && 1 + sl <= wj) {
-        const double* xa = xs + 6 * ((j + 1 + sl) % W1);
+      if (lane < 30) {
+        for (int a = 1 + sl; a <= wj; a += 5) {
+          int xa_i = xj + a;
+          while (xa_i >= W1) xa_i -= W1;
+          const double* bl = col + 36 * a + c;
+          const double* xa = xs + 6 * xa_i;
 #pragma unroll
-        for (int r = 0; r < 6; ++r) t = fma(blk[r], xa[r], t);
-        for (int a = 6 + sl; a <= wj; a += 5) {         // bandwidths > 5: further slices, loaded in place
-          const double* bl2 = g + 36 * a;
-          const double* xa2 = xs + 6 * ((j + a) % W1);
-#pragma unroll
-          for (int r = 0; r < 6; ++r) t = fma(bl2[6 * r + c], xa2[r], t);
+          for (int r = 0; r < 6; ++r) t = fma(bl[6 * r], xa[r], t);
         }
       }
       t += __shfl_down_sync(0xffffffffu, t, 6) + __shfl_down_sync(0xffffffffu, t, 12) +
@@ -453,9 +451,14 @@ __global__ void __launch_bounds__(kBandThreads) band_backward_kernel(LargeCtrl* 
         if (lane == i) xv = xi;
         else if (lane < i) xv = fma(-dg[i], xi, xv);    // L[i][c] of lane c = dg[i]
       }
-      if (lane < 6) { xs[6 * (j % W1) + lane] = xv; xout[6 * (size_t)j + lane] = xv; }
+      if (lane < 6) { xs[6 * xj + lane] = xv; xout[6 * (size_t)j + lane] = xv; }
       __syncwarp();
+      if (j - kBackRing >= lo) issue(j - kBackRing, slot);   // the slot just consumed takes the next column
+      cp_async_commit();
+      slot = slot + 1 == kBackRing ? 0 : slot + 1;
+      xj = xj == 0 ? W1 - 1 : xj - 1;
     }
+    cp_async_wait<0>();
   }
   if (blockIdx.x == 0 && tid == 0) ctrl->pcg_last = 0;
 }
@@ -489,7 +492,7 @@ size_t fwd_smem(int w, int nr) {
   const size_t W1 = (size_t)w + 1;
   return ((W1 + kBandAhead) * (W1 * 36 + 6 * (size_t)nr) + 36) * sizeof(double);
 }
-size_t bwd_smem(int w) { return ((size_t)6 * (w + 1) + 12 * (size_t)w) * sizeof(double); }
+size_t bwd_smem(int w) { return ((size_t)6 * (w + 1) + 12 * (size_t)w + (size_t)kBackRing * ((size_t)(w + 1) * 36 + 12)) * sizeof(double); }
 
 }  // namespace
 
@@ -522,6 +525,13 @@ int large_band_solve(const LargeData& d, cudaStream_t st) {
     if (e == cudaSuccess) e = cudaFuncSetAttribute(band_forward_kernel<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return (int)e;
     configured = smem;
+  }
+  static size_t configured_b = 48 * 1024;
+  const size_t smem_b = std::max(bwd_smem(w), P > 1 ? bwd_smem(pl.wt) : (size_t)0);
+  if (smem_b > configured_b) {
+    cudaError_t e = cudaFuncSetAttribute(band_backward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_b);
+    if (e != cudaSuccess) return (int)e;
+    configured_b = smem_b;
   }
   // wide bands: the trailing update is throughput-bound, 256 threads; narrow bands: latency-bound, one warp
   // per scheduler
