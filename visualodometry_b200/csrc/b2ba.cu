@@ -3,11 +3,13 @@
 // device fails with B2BA_E_CUDA when it is missing.
 #include "../../include/b2ba.h"
 
+#include <algorithm>
 #include <cstdio>
 #include <cstdlib>
 #include <dlfcn.h>
 #include <cstring>
 #include <string>
+#include <utility>
 #include <vector>
 
 #include "ba_index.cuh"
@@ -47,6 +49,7 @@ struct b2ba {
   DevBuf<ObsRec> l_cm;
   DevBuf<int> l_cam_ptr;
   DevBuf<double> l_poses_tri, l_lin_part, l_lin, l_Dc, l_Sg, l_dc, l_r, l_z, l_q, l_Minv, l_part, l_sums, l_band, l_binv, l_band_ws, l_zbuf;
+  bool sched_order = false;   // pm / pt_ptr laid out in landmark-schedule order (window path), else canonical
   int l_band_P = 1;  // interiors of the substructured banded solve (1 = sequential)
   int l_bw = -1;     // block half-bandwidth of S when the banded Cholesky is selected, else -1
   DevBuf<LargeCtrl> l_ctrl;
@@ -93,6 +96,11 @@ IndexIn make_index_in(const b2ba* h) {
   in.cam_off = h->d_cam_off.p; in.pt_off = h->d_pt_off.p; in.obs_off = h->d_obs_off.p;
   in.obs_cam = h->d_obs_cam.p; in.obs_pt = h->d_obs_pt.p; in.obs_uv = h->d_uv.p;
   return in;
+}
+
+// window path: landmark rows between the caller's order and the engine's schedule order (src != dst)
+int permute_pts(b2ba* h, const double* src, double* dst, bool to_sched, cudaStream_t s) {
+  return permute_points(h->B, h->np_tot, h->d_pt_off.p, h->d_sched.p, src, dst, to_sched, s);
 }
 
 WinData make_win(b2ba* h, bool hist, double* dbg) {
@@ -373,15 +381,22 @@ int b2ba_set_problem_batch(b2ba_t* h, int32_t B, const int32_t* cam_off, const i
     if (nf > h->max_nfree) h->max_nfree = nf;
     if (cam_off[b + 1] - cam_off[b] > h->max_nc) h->max_nc = cam_off[b + 1] - cam_off[b];
   }
-  // a8: index
-  IndexOut io{h->d_pm.p, h->d_pt_ptr.p, h->d_cm.p, h->d_cam_ptr.p, h->d_flags.p, h->d_sched.p};
+  // a8: index.  The window kernels walk the landmarks of a window by decreasing observation count and want the
+  // point-major stream in that order; the large path keeps the canonical order (by landmark id).
+  const bool want_pcg = h->opt.solver == B2BA_SOLVER_PCG;
+  h->sched_order = !want_pcg && h->max_nc <= kMaxCam && h->max_nfree <= kBigMaxFree && np > 0;
+  IndexOut io{h->d_pm.p, h->d_pt_ptr.p, h->d_cm.p, h->d_cam_ptr.p, h->d_flags.p, h->sched_order ? h->d_sched.p : nullptr};
   int rc = build_index(make_index_in(h), io, nullptr);
   if (rc) return cuda_fail(h, (cudaError_t)rc, "build_index");
   int flags[2] = {0, 0};
   CU(cudaMemcpy(flags, h->d_flags.p, sizeof(flags), cudaMemcpyDeviceToHost), "read index flags");
   if (flags[0]) { h->path = PATH_NONE; return fail(h, B2BA_E_INVALID, "observation index out of range"); }
   if (flags[1]) { h->path = PATH_NONE; return fail(h, B2BA_E_DUPLICATE, "duplicate (camera, point) observation"); }
-  const bool want_pcg = h->opt.solver == B2BA_SOLVER_PCG;
+  if (h->sched_order) {   // the engine keeps the landmarks in schedule order from here on
+    rc = permute_pts(h, h->d_ptsinit.p, h->d_pts0.p, true, nullptr);
+    if (rc) return cuda_fail(h, (cudaError_t)rc, "permute points");
+    CU(cudaMemcpy(h->d_ptsinit.p, h->d_pts0.p, np * 3 * sizeof(double), cudaMemcpyDeviceToDevice), "keep points");
+  }
   if (!want_pcg && h->max_nc <= kSmallMaxCam && h->max_nfree <= kSmallMaxFree) h->path = PATH_WIN_SMALL;
   else if (!want_pcg && h->max_nc <= kMaxCam && h->max_nfree <= kBigMaxFree) h->path = PATH_WIN_BIG;
   else if (h->opt.solver == B2BA_SOLVER_WINDOW)
@@ -414,7 +429,13 @@ int b2ba_set_state(b2ba_t* h, const double* poses_cw, const double* points, int 
     CU(cudaMemcpy(h->d_poses0.p, h->d_poses.p, (size_t)h->nc_tot * 12 * sizeof(double), cudaMemcpyDeviceToDevice), "keep poses");
   }
   if (points) {
-    CU(cudaMemcpy(h->d_pts0.p, points, (size_t)h->np_tot * 3 * sizeof(double), k), "copy points");
+    if (h->sched_order) {
+      CU(cudaMemcpy(h->d_pts1.p, points, (size_t)h->np_tot * 3 * sizeof(double), k), "copy points");
+      const int rc = permute_pts(h, h->d_pts1.p, h->d_pts0.p, true, nullptr);
+      if (rc) return cuda_fail(h, (cudaError_t)rc, "permute points");
+    } else {
+      CU(cudaMemcpy(h->d_pts0.p, points, (size_t)h->np_tot * 3 * sizeof(double), k), "copy points");
+    }
     CU(cudaMemcpy(h->d_ptsinit.p, h->d_pts0.p, (size_t)h->np_tot * 3 * sizeof(double), cudaMemcpyDeviceToDevice), "keep points");
   }
   return B2BA_OK;
@@ -474,7 +495,15 @@ int b2ba_get(b2ba_t* h, double* poses_cw, double* points, int mem) {
   cudaStream_t s = h->last_stream;
   const cudaMemcpyKind k = out_kind(mem);
   if (poses_cw) CU(cudaMemcpyAsync(poses_cw, h->d_poses.p, (size_t)h->nc_tot * 12 * sizeof(double), k, s), "read poses");
-  if (points) CU(cudaMemcpyAsync(points, h->d_pts0.p, (size_t)h->np_tot * 3 * sizeof(double), k, s), "read points");
+  if (points) {
+    const double* src = h->d_pts0.p;
+    if (h->sched_order) {   // back to the caller's landmark order (pts1 is scratch between solves)
+      const int rc = permute_pts(h, h->d_pts0.p, h->d_pts1.p, false, s);
+      if (rc) return cuda_fail(h, (cudaError_t)rc, "permute points");
+      src = h->d_pts1.p;
+    }
+    CU(cudaMemcpyAsync(points, src, (size_t)h->np_tot * 3 * sizeof(double), k, s), "read points");
+  }
   CU(cudaStreamSynchronize(s), "get");
   return B2BA_OK;
 }
@@ -587,7 +616,8 @@ int b2ba_optimize_batch(b2ba_t* h, int32_t B, const int32_t* cam_off, const int3
     CU(cudaMemcpyAsync(k->d_obs_off.p, so, (nb + 1) * sizeof(long long), hd, cs), "copy");
     CU(cudaMemcpyAsync(k->d_fixed.p, fixed_cam + c0, nc, hd, cs), "copy");
     CU(cudaMemcpyAsync(k->d_poses.p, poses_cw + c0 * 12, nc * 12 * sizeof(double), hd, cs), "copy");
-    CU(cudaMemcpyAsync(k->d_pts0.p, points + p0 * 3, np * 3 * sizeof(double), hd, cs), "copy");
+    k->sched_order = np > 0;   // landmarks arrive in the caller's order (pts1) and are put into schedule order (pts0)
+    CU(cudaMemcpyAsync(k->sched_order ? k->d_pts1.p : k->d_pts0.p, points + p0 * 3, np * 3 * sizeof(double), hd, cs), "copy");
     if (no) {
       CU(cudaMemcpyAsync(k->d_obs_cam.p, obs_cam + o0, no * sizeof(int), hd, cs), "copy");
       CU(cudaMemcpyAsync(k->d_obs_pt.p, obs_pt + o0, no * sizeof(int), hd, cs), "copy");
@@ -595,15 +625,17 @@ int b2ba_optimize_batch(b2ba_t* h, int32_t B, const int32_t* cam_off, const int3
     }
     CU(cudaEventRecord(h->ev_in[c], cs), "event");
     CU(cudaStreamWaitEvent(ks, h->ev_in[c], 0), "wait");
-    IndexOut io{k->d_pm.p, k->d_pt_ptr.p, k->d_cm.p, k->d_cam_ptr.p, k->d_flags.p, k->d_sched.p};
+    IndexOut io{k->d_pm.p, k->d_pt_ptr.p, k->d_cm.p, k->d_cam_ptr.p, k->d_flags.p, k->sched_order ? k->d_sched.p : nullptr};
     int rc = build_index(make_index_in(k), io, ks);
     if (rc) return cuda_fail(h, (cudaError_t)rc, "build_index");
+    if (k->sched_order && (rc = permute_pts(k, k->d_pts1.p, k->d_pts0.p, true, ks)) != 0) return cuda_fail(h, (cudaError_t)rc, "permute");
     rc = launch_window_path(k, make_win(k, false, nullptr), P, ks);
     if (rc) return cuda_fail(h, (cudaError_t)rc, "launch");
+    if (k->sched_order && (rc = permute_pts(k, k->d_pts0.p, k->d_pts1.p, false, ks)) != 0) return cuda_fail(h, (cudaError_t)rc, "permute");
     CU(cudaEventRecord(h->ev_done[c], ks), "event");
     CU(cudaStreamWaitEvent(bs, h->ev_done[c], 0), "wait");
     CU(cudaMemcpyAsync(out_poses_cw + c0 * 12, k->d_poses.p, nc * 12 * sizeof(double), dh, bs), "read");
-    CU(cudaMemcpyAsync(out_points + p0 * 3, k->d_pts0.p, np * 3 * sizeof(double), dh, bs), "read");
+    CU(cudaMemcpyAsync(out_points + p0 * 3, k->sched_order ? k->d_pts1.p : k->d_pts0.p, np * 3 * sizeof(double), dh, bs), "read");
     CU(cudaMemcpyAsync(st_summ + w0, k->d_summ.p, nb * sizeof(b2ba_summary), dh, bs), "read");
     CU(cudaMemcpyAsync(h->pinned_flags + 2 * c, k->d_flags.p, 2 * sizeof(int), dh, bs), "read");
   }
@@ -688,6 +720,15 @@ int64_t put(b2ba* h, const void* src, size_t bytes, void* dst, int64_t cap) {
 
 }  // namespace
 
+// pt_ptr (point_major) or cam_ptr and the landmark schedule on the host, for the canonical index dumps
+static int canonical_inputs(b2ba* h, bool point_major, std::vector<int>& ptr, std::vector<int>& sched) {
+  ptr.resize((point_major ? h->np_tot : h->nc_tot) + 1);
+  sched.resize(h->np_tot);
+  CU(cudaMemcpy(ptr.data(), point_major ? h->d_pt_ptr.p : h->d_cam_ptr.p, ptr.size() * 4, cudaMemcpyDeviceToHost), "read");
+  if (h->np_tot) CU(cudaMemcpy(sched.data(), h->d_sched.p, sched.size() * 4, cudaMemcpyDeviceToHost), "read");
+  return 0;
+}
+
 int64_t b2ba_dump(b2ba_t* h, int what, void* dst, int64_t bytes) {
   if (!h || h->path == PATH_NONE || !dst) return fail(h, B2BA_E_STATE, "no problem set");
   CU(cudaSetDevice(h->device), "cudaSetDevice");
@@ -704,6 +745,33 @@ int64_t b2ba_dump(b2ba_t* h, int what, void* dst, int64_t bytes) {
         while ((long long)a >= h->h_obs_off[b + 1]) ++b;
         perm[a] = rec[a].orig - (int)h->h_obs_off[b];
       }
+      if (h->sched_order) {
+        // the engine keeps the streams in landmark-schedule order; the dump is the CANONICAL order of
+        // ba_index.cuh (point-major by landmark id, camera-major by (camera, landmark id)), rebuilt here
+        std::vector<int> ptr, sched;
+        if (int rc = canonical_inputs(h, what == B2BA_D_PM_PERM, ptr, sched)) return rc;
+        std::vector<int> out(no);
+        if (what == B2BA_D_PM_PERM) {
+          size_t o = 0;
+          for (int w = 0; w < h->B; ++w) {
+            const int p0 = h->h_pt_off[w], npw = h->h_pt_off[w + 1] - p0;
+            std::vector<int> pos(npw);
+            for (int q = 0; q < npw; ++q) pos[sched[p0 + q]] = q;
+            for (int p = 0; p < npw; ++p)
+              for (int a = ptr[p0 + pos[p]]; a < ptr[p0 + pos[p] + 1]; ++a) out[o++] = perm[a];
+          }
+        } else {
+          int w = 0;
+          for (int c = 0; c < h->nc_tot; ++c) {
+            while (c >= h->h_cam_off[w + 1]) ++w;
+            std::vector<std::pair<int, int>> seg;   // (landmark id, original observation): rec.idx is a slot
+            for (int a = ptr[c]; a < ptr[c + 1]; ++a) seg.emplace_back(sched[h->h_pt_off[w] + rec[a].idx], perm[a]);
+            std::sort(seg.begin(), seg.end());
+            for (int a = ptr[c]; a < ptr[c + 1]; ++a) out[a] = seg[a - ptr[c]].second;
+          }
+        }
+        return put(h, out.data(), no * 4, dst, bytes);
+      }
       return put(h, perm.data(), no * 4, dst, bytes);
     }
     case B2BA_D_PT_PTR:
@@ -711,6 +779,19 @@ int64_t b2ba_dump(b2ba_t* h, int what, void* dst, int64_t bytes) {
       const size_t n = (what == B2BA_D_PT_PTR ? h->np_tot : h->nc_tot) + 1;
       std::vector<int> v(n);
       CU(cudaMemcpy(v.data(), what == B2BA_D_PT_PTR ? h->d_pt_ptr.p : h->d_cam_ptr.p, n * 4, cudaMemcpyDeviceToHost), "read");
+      if (what == B2BA_D_PT_PTR && h->sched_order) {
+        std::vector<int> ptr, sched, out(n);
+        if (int rc = canonical_inputs(h, true, ptr, sched)) return rc;
+        int acc = 0;
+        for (int w = 0; w < h->B; ++w) {
+          const int p0 = h->h_pt_off[w], npw = h->h_pt_off[w + 1] - p0;
+          std::vector<int> pos(npw);
+          for (int q = 0; q < npw; ++q) pos[sched[p0 + q]] = q;
+          for (int p = 0; p < npw; ++p) { out[p0 + p] = acc; acc += ptr[p0 + pos[p] + 1] - ptr[p0 + pos[p]]; }
+        }
+        out[h->np_tot] = acc;
+        return put(h, out.data(), n * 4, dst, bytes);
+      }
       return put(h, v.data(), n * 4, dst, bytes);
     }
     case B2BA_D_SCHED: {
@@ -730,7 +811,13 @@ int64_t b2ba_dump(b2ba_t* h, int what, void* dst, int64_t bytes) {
       const size_t per = what == B2BA_D_RESIDUALS ? 2 : what == B2BA_D_WEIGHTS ? 1 : what == B2BA_D_JC ? 12 : 6;
       DevBuf<double> tmp;
       CU(tmp.alloc(no * per), "alloc");
-      int rc = dump_obs_terms(make_index_in(h), make_params(h, 1), h->d_poses.p, h->d_pts0.p,
+      const double* pts_lm = h->d_pts0.p;
+      if (h->sched_order) {
+        const int rcp = permute_pts(h, h->d_pts0.p, h->d_pts1.p, false, nullptr);
+        if (rcp) return cuda_fail(h, (cudaError_t)rcp, "permute points");
+        pts_lm = h->d_pts1.p;
+      }
+      int rc = dump_obs_terms(make_index_in(h), make_params(h, 1), h->d_poses.p, pts_lm,
                               what == B2BA_D_RESIDUALS ? tmp.p : nullptr, what == B2BA_D_WEIGHTS ? tmp.p : nullptr,
                               what == B2BA_D_JC ? tmp.p : nullptr, what == B2BA_D_JP ? tmp.p : nullptr, nullptr);
       if (rc) return cuda_fail(h, (cudaError_t)rc, "dump_obs_terms");
@@ -801,12 +888,20 @@ int64_t b2ba_dump(b2ba_t* h, int what, void* dst, int64_t bytes) {
       switch (what) {
         case B2BA_D_B: return put(h, &o[L.off_B()], nc * 36 * 8, dst, bytes);
         case B2BA_D_GC: return put(h, &o[L.off_gc()], nc * 6 * 8, dst, bytes);
-        case B2BA_D_C: return put(h, &o[L.off_C()], np * 6 * 8, dst, bytes);
-        case B2BA_D_GP: return put(h, &o[L.off_gp()], np * 3 * 8, dst, bytes);
+        case B2BA_D_C: case B2BA_D_GP: case B2BA_D_DP: {
+          const size_t per = what == B2BA_D_C ? 6 : 3;
+          const double* src = &o[what == B2BA_D_C ? L.off_C() : what == B2BA_D_GP ? L.off_gp() : L.off_dp()];
+          if (!h->sched_order) return put(h, src, np * per * 8, dst, bytes);
+          std::vector<int> ptr, sched;       // single window: slot q holds landmark sched[q]
+          if (int rcs = canonical_inputs(h, true, ptr, sched)) return rcs;
+          std::vector<double> lm(np * per);
+          for (size_t q = 0; q < np; ++q)
+            for (size_t e = 0; e < per; ++e) lm[(size_t)sched[q] * per + e] = src[q * per + e];
+          return put(h, lm.data(), np * per * 8, dst, bytes);
+        }
         case B2BA_D_S: return put(h, &o[L.off_S()], n * n * 8, dst, bytes);
         case B2BA_D_GRED: return put(h, &o[L.off_gred()], n * 8, dst, bytes);
         case B2BA_D_DC: return put(h, &o[L.off_dc()], n * 8, dst, bytes);
-        case B2BA_D_DP: return put(h, &o[L.off_dp()], np * 3 * 8, dst, bytes);
         default: return put(h, &o[L.off_scal()], 4 * 8, dst, bytes);
       }
     }

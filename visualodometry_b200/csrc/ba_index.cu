@@ -17,15 +17,36 @@ __device__ __forceinline__ int find_window(const long long* __restrict__ obs_off
   return lo;
 }
 
-__global__ void make_pm_keys(IndexIn in, unsigned long long* keys, int* vals, int* flags) {
+// pos_of (or null): global landmark -> global schedule position; the point-major stream is then laid out in
+// schedule order (the canonical order is by landmark id)
+__global__ void make_pm_keys(IndexIn in, const int* __restrict__ pos_of, unsigned long long* keys, int* vals, int* flags) {
   const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
   if (i >= in.no) return;
   const int b = find_window(in.obs_off, in.nb, i);
   const int nc = in.cam_off[b + 1] - in.cam_off[b], np = in.pt_off[b + 1] - in.pt_off[b];
   int c = in.obs_cam[i], p = in.obs_pt[i];
   if (c < 0 || c >= nc || p < 0 || p >= np) { flags[0] = 1; c = 0; p = 0; }
-  keys[i] = ((unsigned long long)(unsigned)(in.pt_off[b] + p) << 32) | (unsigned)c;
+  const int g = in.pt_off[b] + p;
+  keys[i] = ((unsigned long long)(unsigned)(pos_of ? pos_of[g] : g) << 32) | (unsigned)c;
   vals[i] = (int)i;
+}
+
+// observations per landmark (integer atomics: the counts are exact whatever the order)
+__global__ void count_obs(IndexIn in, int* cnt) {
+  const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (i >= in.no) return;
+  const int b = find_window(in.obs_off, in.nb, i);
+  const int np = in.pt_off[b + 1] - in.pt_off[b];
+  const int p = in.obs_pt[i];
+  if (p >= 0 && p < np) atomicAdd(&cnt[in.pt_off[b] + p], 1);
+}
+
+__global__ void invert_sched(IndexIn in, const int* __restrict__ sched, int* pos_of) {
+  const int g = blockIdx.x * blockDim.x + threadIdx.x;   // global schedule position
+  if (g >= in.np_tot) return;
+  int lo = 0, hi = in.nb;
+  while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (in.pt_off[mid] <= g) lo = mid; else hi = mid; }
+  pos_of[in.pt_off[lo] + sched[g]] = g;
 }
 
 // sorted (key, original index) -> point-major records, pt_ptr boundaries, camera keys for pass 2
@@ -51,7 +72,7 @@ __global__ void build_pm(IndexIn in, const unsigned long long* __restrict__ keys
 
 __global__ void build_cm(IndexIn in, const unsigned* __restrict__ cam_keys, const int* __restrict__ pos,
                          const ObsRec* __restrict__ pm, const unsigned long long* __restrict__ pm_keys,
-                         ObsRec* cm, int* cam_ptr) {
+                         const int* __restrict__ sched, ObsRec* cm, int* cam_ptr) {
   const long long a = blockIdx.x * (long long)blockDim.x + threadIdx.x;
   if (a >= in.no) return;
   const int gc = (int)cam_keys[a];
@@ -59,7 +80,7 @@ __global__ void build_cm(IndexIn in, const unsigned* __restrict__ cam_keys, cons
   ObsRec r = pm[src];
   const int gp = (int)(pm_keys[src] >> 32);
   const int b = find_window(in.obs_off, in.nb, r.orig);
-  r.idx = gp - in.pt_off[b];
+  r.idx = gp - in.pt_off[b];      // window-local landmark slot (schedule position when the stream is schedule-ordered)
   cm[a] = r;
   const int prev = a == 0 ? -1 : (int)cam_keys[a - 1];
   for (int q = prev + 1; q <= gc; ++q) cam_ptr[q] = (int)a;
@@ -77,11 +98,11 @@ __device__ __forceinline__ int find_window_pt(const int* __restrict__ pt_off, in
 }
 
 // landmark schedule keys: (window, 31 - min(observation count, 31)); value = window-local landmark id
-__global__ void make_sched_keys(IndexIn in, const int* __restrict__ pt_ptr, unsigned* keys, int* vals) {
+__global__ void make_sched_keys(IndexIn in, const int* __restrict__ cnt, unsigned* keys, int* vals) {
   const int g = blockIdx.x * blockDim.x + threadIdx.x;
   if (g >= in.np_tot) return;
   const int b = find_window_pt(in.pt_off, in.nb, g);
-  const int k = pt_ptr[g + 1] - pt_ptr[g];
+  const int k = cnt[g];
   keys[g] = ((unsigned)b << 5) | (unsigned)(31 - min(k, 31));
   vals[g] = g - in.pt_off[b];
 }
@@ -93,10 +114,11 @@ __global__ void fill_ptr(int* p, int n, int v) {
 
 inline int bits_for(long long n) { int b = 1; while ((1ll << b) < n && b < 32) ++b; return b; }
 
-cudaError_t sort_sched(const IndexIn& in, const IndexOut& out, void* tmp, size_t tmp_bytes, cudaStream_t s) {
+// landmark schedule (out.sched) and its inverse pos_of (np_tot ints, caller-owned): counts -> stable sort
+cudaError_t sort_sched(const IndexIn& in, const IndexOut& out, int* pos_of, cudaStream_t s) {
   const int np = in.np_tot;
   unsigned *k0 = nullptr, *k1 = nullptr;
-  int* v0 = nullptr;
+  int *v0 = nullptr, *cnt = nullptr;
   void* t = nullptr;
   size_t need = 0;
   const int bits = 5 + bits_for(in.nb);
@@ -105,18 +127,39 @@ cudaError_t sort_sched(const IndexIn& in, const IndexOut& out, void* tmp, size_t
   if ((e = cudaMallocAsync(&k0, (size_t)np * 4, s)) != cudaSuccess) goto done;
   if ((e = cudaMallocAsync(&k1, (size_t)np * 4, s)) != cudaSuccess) goto done;
   if ((e = cudaMallocAsync(&v0, (size_t)np * 4, s)) != cudaSuccess) goto done;
-  if (need > tmp_bytes) {
-    if ((e = cudaMallocAsync(&t, need, s)) != cudaSuccess) goto done;
-    tmp = t;
-  }
-  make_sched_keys<<<(np + 255) / 256, 256, 0, s>>>(in, out.pt_ptr, k0, v0);
-  e = cub::DeviceRadixSort::SortPairs(tmp, need, k0, k1, v0, out.sched, np, 0, bits, s);
+  if ((e = cudaMallocAsync(&cnt, (size_t)np * 4, s)) != cudaSuccess) goto done;
+  if ((e = cudaMallocAsync(&t, need, s)) != cudaSuccess) goto done;
+  if ((e = cudaMemsetAsync(cnt, 0, (size_t)np * 4, s)) != cudaSuccess) goto done;
+  if (in.no > 0) count_obs<<<(int)((in.no + 255) / 256), 256, 0, s>>>(in, cnt);
+  make_sched_keys<<<(np + 255) / 256, 256, 0, s>>>(in, cnt, k0, v0);
+  e = cub::DeviceRadixSort::SortPairs(t, need, k0, k1, v0, out.sched, np, 0, bits, s);
+  if (e == cudaSuccess && pos_of) invert_sched<<<(np + 255) / 256, 256, 0, s>>>(in, out.sched, pos_of);
 done:
-  cudaFreeAsync(k0, s); cudaFreeAsync(k1, s); cudaFreeAsync(v0, s); cudaFreeAsync(t, s);
+  cudaFreeAsync(k0, s); cudaFreeAsync(k1, s); cudaFreeAsync(v0, s); cudaFreeAsync(cnt, s); cudaFreeAsync(t, s);
   return e;
 }
 
 }  // namespace
+
+namespace {
+// rows of 3 doubles between landmark order and schedule order: to_sched ? dst[pos] = src[landmark] : dst[landmark] = src[pos]
+__global__ void permute_rows3(int nb, int np_tot, const int* __restrict__ pt_off, const int* __restrict__ sched,
+                              const double* __restrict__ src, double* dst, int to_sched) {
+  const int g = blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= np_tot) return;
+  const int b = find_window_pt(pt_off, nb, g);
+  const size_t l = (size_t)pt_off[b] + sched[g];
+  const size_t from = to_sched ? l : (size_t)g, to = to_sched ? (size_t)g : l;
+  dst[3 * to] = src[3 * from]; dst[3 * to + 1] = src[3 * from + 1]; dst[3 * to + 2] = src[3 * from + 2];
+}
+}  // namespace
+
+int permute_points(int nb, int np_tot, const int* pt_off, const int* sched, const double* src, double* dst,
+                   bool to_sched, cudaStream_t s) {
+  if (np_tot == 0) return 0;
+  permute_rows3<<<(np_tot + 255) / 256, 256, 0, s>>>(nb, np_tot, pt_off, sched, src, dst, to_sched ? 1 : 0);
+  return (int)cudaGetLastError();
+}
 
 int build_index(const IndexIn& in, const IndexOut& out, cudaStream_t s) {
   cudaError_t e;
@@ -126,11 +169,11 @@ int build_index(const IndexIn& in, const IndexOut& out, cudaStream_t s) {
   if (no == 0) {
     fill_ptr<<<(in.np_tot + 256) / 256, 256, 0, s>>>(out.pt_ptr, in.np_tot + 1, 0);
     fill_ptr<<<(in.nc_tot + 256) / 256, 256, 0, s>>>(out.cam_ptr, in.nc_tot + 1, 0);
-    if (out.sched && in.np_tot > 0) return (int)sort_sched(in, out, nullptr, 0, s);
+    if (out.sched && in.np_tot > 0) return (int)sort_sched(in, out, nullptr, s);
     return (int)cudaGetLastError();
   }
   unsigned long long *k0 = nullptr, *k1 = nullptr;
-  int *v0 = nullptr, *v1 = nullptr, *p1 = nullptr;
+  int *v0 = nullptr, *v1 = nullptr, *p1 = nullptr, *pos_of = nullptr;
   unsigned *ck0 = nullptr, *ck1 = nullptr;
   void* tmp = nullptr;
   size_t tmp_bytes = 0, t2 = 0;
@@ -146,22 +189,23 @@ int build_index(const IndexIn& in, const IndexOut& out, cudaStream_t s) {
   B2_TRY(cudaMallocAsync(&tmp, tmp_bytes, s));
   {
     const int nblk = (int)((no + 255) / 256);
-    make_pm_keys<<<nblk, 256, 0, s>>>(in, k0, v0, out.flags);
+    if (out.sched && in.np_tot > 0) {
+      // window path: the landmarks of a window are walked by decreasing observation count; the point-major
+      // stream (pm, pt_ptr) is laid out in that order so that a batch's records are one contiguous run
+      B2_TRY(cudaMallocAsync(&pos_of, (size_t)in.np_tot * 4, s));
+      B2_TRY(sort_sched(in, out, pos_of, s));
+    }
+    make_pm_keys<<<nblk, 256, 0, s>>>(in, pos_of, k0, v0, out.flags);
     B2_TRY(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, k0, k1, v0, v1, no, 0, pbits, s));
     build_pm<<<nblk, 256, 0, s>>>(in, k1, v1, out.pm, out.pt_ptr, ck0, v0, out.flags);
     B2_TRY(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, ck0, ck1, v0, p1, no, 0, cbits, s));
-    build_cm<<<nblk, 256, 0, s>>>(in, ck1, p1, out.pm, k1, out.cm, out.cam_ptr);
+    build_cm<<<nblk, 256, 0, s>>>(in, ck1, p1, out.pm, k1, pos_of ? out.sched : nullptr, out.cm, out.cam_ptr);
     B2_TRY(cudaGetLastError());
-    if (out.sched && in.np_tot > 0) {
-      // stable sort of (window, observation-count class): the temporaries above are free again
-      // (np_tot <= no is not guaranteed, so the keys/values get their own small buffers)
-      B2_TRY(sort_sched(in, out, tmp, tmp_bytes, s));
-    }
   }
 done:
 #undef B2_TRY
   cudaFreeAsync(k0, s); cudaFreeAsync(k1, s); cudaFreeAsync(v0, s); cudaFreeAsync(v1, s);
-  cudaFreeAsync(p1, s); cudaFreeAsync(ck0, s); cudaFreeAsync(ck1, s); cudaFreeAsync(tmp, s);
+  cudaFreeAsync(p1, s); cudaFreeAsync(ck0, s); cudaFreeAsync(ck1, s); cudaFreeAsync(tmp, s); cudaFreeAsync(pos_of, s);
   return (int)e;
 }
 

@@ -25,13 +25,19 @@ struct IndexOut {
   int* cam_ptr;    // nc_tot+1
   int* flags;      // [0] out-of-range index, [1] duplicate (cam,pt) observation
   int* sched;      // np_tot or nullptr: per window, the window-local landmark ids ordered by decreasing
-                   // observation count (stable).  The window kernel walks landmarks in this order so that
-                   // the landmarks sharing a warp have (nearly) the same number of observations.
+                   // observation count (stable).  When given, the whole point side is laid out in this order
+                   // (slot q of a window = landmark sched[q]): pm, pt_ptr, the landmark index of cm records;
+                   // the landmarks sharing a warp of the window kernel then have (nearly) the same number of
+                   // observations and every per-landmark array is walked contiguously.
 };
 
 // Builds both streams. Returns cudaError_t as int. Temporary storage is allocated and freed
 // internally (stream-ordered); the call is asynchronous on `s`.
 int build_index(const IndexIn& in, const IndexOut& out, cudaStream_t s);
+
+// landmark rows (3 doubles) between landmark order and schedule order (src != dst)
+int permute_points(int nb, int np_tot, const int* pt_off, const int* sched, const double* src, double* dst,
+                   bool to_sched, cudaStream_t s);
 
 // a1 dump in ORIGINAL observation order (parity tests): r (no x 2), w (no), Jc (no x 12), Jp (no x 6)
 int dump_obs_terms(const IndexIn& in, const Params& P, const double* poses, const double* pts,

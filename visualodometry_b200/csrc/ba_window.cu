@@ -256,24 +256,22 @@ window_lm_kernel(const WinData d, const Params P) {
     int a0n = 0, a1n = 0;
     double Xn0 = 0, Xn1 = 0, Xn2 = 0;
     const int bfirst = crank * PB;            // this CTA takes batches bfirst, bfirst + BS, ...
-    // landmarks are walked in schedule order (decreasing observation count): position q -> landmark sch[q]
-    const int* const sch = d.sched + p0;
-    int pcur = 0, pnx = 0;                    // landmark of this position in the current / next batch
+    // landmark slots are in schedule order (decreasing observation count, set up by the index builder), so the
+    // landmarks sharing a warp do the same number of rounds and all per-landmark arrays are contiguous
     if (bfirst + slot < npw) {
-      pcur = sch[bfirst + slot];
-      a0n = d.pt_ptr[p0 + pcur]; a1n = d.pt_ptr[p0 + pcur + 1];
-      Xn0 = X[3 * pcur]; Xn1 = X[3 * pcur + 1]; Xn2 = X[3 * pcur + 2];
+      const int pf = bfirst + slot;
+      a0n = d.pt_ptr[p0 + pf]; a1n = d.pt_ptr[p0 + pf + 1];
+      Xn0 = X[3 * pf]; Xn1 = X[3 * pf + 1]; Xn2 = X[3 * pf + 2];
     }
-    if (bfirst + BS + slot < npw) pnx = sch[bfirst + BS + slot];
+    // record range of the batch AFTER the current one: L1-prefetched while the current batch's DMMA runs; the
+    // range itself is loaded one batch earlier
+    int pf_s = d.pt_ptr[p0 + min(bfirst + BS, npw)], pf_e = d.pt_ptr[p0 + min(bfirst + BS + PB, npw)];
 
     for (int b0 = bfirst; b0 < npw; b0 += BS) {
-      const int p = pcur;
-      const bool act = b0 + slot < npw;
+      const int p = b0 + slot;
+      const bool act = p < npw;
       const int a0 = a0n, a1 = a1n;
       const double X0 = Xn0, X1 = Xn1, X2 = Xn2;
-      const bool nx = b0 + BS + slot < npw;
-      a0n = 0; a1n = 0;
-      if (nx) { a0n = d.pt_ptr[p0 + pnx]; a1n = d.pt_ptr[p0 + pnx + 1]; }   // next batch's record range
       // clear the column block (rows of cameras that do not see the landmark must be zero; the
       // block is contiguous, so this is TPP lanes x STS.128)
       {
@@ -394,10 +392,17 @@ window_lm_kernel(const WinData d, const Params P) {
       __syncthreads();
       // the next batch's landmark (registers) and records (L1 prefetch: a landmark's records are one
       // contiguous run of <= 2-3 lines) are fetched while the tensor pipe works
-      pcur = pnx;
-      if (nx) { Xn0 = X[3 * pcur]; Xn1 = X[3 * pcur + 1]; Xn2 = X[3 * pcur + 2]; }
-      if (a1n > a0n && (a0n >> 3) + sub <= ((a1n - 1) >> 3)) prefetch_l1(d.pm + a0n + 8 * sub);
-      pnx = (b0 + 2 * BS + slot < npw) ? sch[b0 + 2 * BS + slot] : 0;
+      {
+        const int pn = p + BS;
+        a0n = 0; a1n = 0;
+        if (pn < npw) {
+          a0n = d.pt_ptr[p0 + pn]; a1n = d.pt_ptr[p0 + pn + 1];
+          Xn0 = X[3 * pn]; Xn1 = X[3 * pn + 1]; Xn2 = X[3 * pn + 2];
+        }
+        for (int a = (pf_s & ~7) + tid * 8; a < pf_e; a += NTHREADS * 8) prefetch_l1(d.pm + a);
+        pf_s = d.pt_ptr[p0 + min(b0 + 2 * BS, npw)];
+        pf_e = d.pt_ptr[p0 + min(b0 + 2 * BS + PB, npw)];
+      }
       // Z Z^T accumulate: DMMA over this batch's 3*PB columns (this warp's k-slice)
       syrk_dispatch<Cfg>(grp, zf, ksp * (Cfg::KSTEPS / KS), acc);
       __syncthreads();
@@ -640,31 +645,27 @@ window_lm_kernel(const WinData d, const Params P) {
     // ------------------------------------------------------------------ back-substitution + trial cost (a7)
     double s_tc = 0.0, s_dDd = 0.0, s_gd = 0.0, s_dn2 = 0.0, s_xn2 = 0.0, s_inv = 0.0;
     if (step_ok) {
-      // schedule order as in the point pass; the landmark id of the next batch is loaded one batch ahead,
-      // its record range / landmark / scratch row are L1-prefetched while this batch is processed
-      const int* const sch = d.sched + p0;
       const int qfirst = crank * PB + slot;
-      int pcur = 0, pnx = 0, a0n = 0, a1n = 0;
-      if (qfirst < npw) { pcur = sch[qfirst]; a0n = d.pt_ptr[p0 + pcur]; a1n = d.pt_ptr[p0 + pcur + 1]; }
-      if (qfirst + BS < npw) pnx = sch[qfirst + BS];
-      for (int qi = qfirst; qi < np_round; qi += BS) {
-        const bool act = qi < npw;
-        const int p = pcur;
+      int a0n = 0, a1n = 0;
+      if (qfirst < npw) { a0n = d.pt_ptr[p0 + qfirst]; a1n = d.pt_ptr[p0 + qfirst + 1]; }
+      for (int p = qfirst; p < np_round; p += BS) {
+        const bool act = p < npw;
         const int a0 = a0n, a1 = a1n;
         double X0 = 0, X1 = 0, X2 = 0;
         if (act) { X0 = X[3 * p]; X1 = X[3 * p + 1]; X2 = X[3 * p + 2]; }
-        // next batch: record range into registers (used next round, and for the record prefetch at the
-        // end of this one), landmark and scratch row into L1; the landmark id after that into a register
-        pcur = pnx;
         a0n = 0; a1n = 0;
-        if (qi + BS < npw) {
-          a0n = d.pt_ptr[p0 + pcur]; a1n = d.pt_ptr[p0 + pcur + 1];
-          if (sub == 0) prefetch_l1(X + 3 * pcur);
-          else if (sub == 1) prefetch_l1(X + 3 * pcur + 2);
-          else if (sub == 2) prefetch_l1(scratch + (size_t)pcur * kPtScratch);
-          else prefetch_l1(scratch + (size_t)pcur * kPtScratch + kPtScratch - 1);
+        if (p + BS < npw) { a0n = d.pt_ptr[p0 + p + BS]; a1n = d.pt_ptr[p0 + p + BS + 1]; }   // used next round
+        {   // L1-prefetch the next batch: landmark offsets, landmarks, scratch rows, records
+          const int bn = p - slot + BS, bnn = min(bn + PB, npw);
+          if (bn < npw) {
+            const int* pp = d.pt_ptr + p0 + bn;
+            if (tid * 32 <= bnn - bn) prefetch_l1(pp + tid * 32);
+            if (tid * 16 < 3 * (bnn - bn)) prefetch_l1(X + 3 * bn + tid * 16);
+            if (tid * 16 < kPtScratch * (bnn - bn)) prefetch_l1(scratch + (size_t)bn * kPtScratch + tid * 16);
+            const int rs = d.pt_ptr[p0 + bn], re = d.pt_ptr[p0 + bnn];
+            for (int a = (rs & ~7) + tid * 8; a < re; a += NTHREADS * 8) prefetch_l1(d.pm + a);
+          }
         }
-        pnx = (qi + 2 * BS < npw) ? sch[qi + 2 * BS] : 0;
         const int rounds = (int)((__reduce_max_sync(0xffffffffu, (unsigned)(a1 - a0)) + TPP - 1) / TPP);
         const ObsRec zrec{0.f, 0.f, 0, 0};
         double v[3] = {0, 0, 0};
@@ -724,7 +725,6 @@ window_lm_kernel(const WinData d, const Params P) {
             if (dbg) { double* dp = d.dbg + dbgL.off_dp() + (size_t)p * 3; dp[0] = d0; dp[1] = d1; dp[2] = d2; }
           }
         }
-        if (a1n > a0n && (a0n >> 3) + sub <= ((a1n - 1) >> 3)) prefetch_l1(d.pm + a0n + 8 * sub);
         auto trial = [&](const ObsRec& rec, bool lv) {
           Pose12 q;
           load_pose(pose_tri + 12 * rec.idx, q);
