@@ -192,6 +192,63 @@ def run_c2(args, impl):
     print(json.dumps(out))
 
 
+def run_pnp(args):
+    """SURVEY §8 row f-2 (motion-only BA): `--windows` pose problems x 2048 fixed landmarks (one KITTI frame's
+    keypoints, frontend.py max_keypoints), `--iters` LM iterations; value = observations*iterations/s with the
+    arrays resident on the device, e2e = the same call with host arrays; CPU = oracle/pose_numpy.py (numpy)."""
+    import torch
+    from visualodometry_b200 import BAConfig, BundleAdjuster
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from test_pose import KITTI as intr, make_pose_problem
+    B, n = min(args.windows, 1024), 2048
+    probs = [make_pose_problem(s_, n=n) for s_ in range(32)]
+    T0 = np.stack([probs[i % 32][1] for i in range(B)])
+    X = np.concatenate([probs[i % 32][2] for i in range(B)]); uv = np.concatenate([probs[i % 32][3] for i in range(B)])
+    off = (np.arange(B + 1) * n).astype(np.int64)
+    K = np.array([[intr[0], 0, intr[2]], [0, intr[1], intr[3]], [0, 0, 1.0]])
+    ba = BundleAdjuster(K, BAConfig(max_iters=args.iters))
+    Xd, uvd = torch.as_tensor(X).cuda(), torch.as_tensor(uv).cuda()
+
+    def timed(fn, reps):
+        for _ in range(args.warmup):
+            fn()
+        torch.cuda.synchronize(); t0 = time.perf_counter()
+        for _ in range(reps):
+            fn()
+        torch.cuda.synchronize()
+        return (time.perf_counter() - t0) / reps
+    t_dev = timed(lambda: ba.refine_poses(T0, Xd, uvd, off), args.steps)
+    t_e2e = timed(lambda: ba.refine_poses(T0, X, uv, off), args.steps)
+    _, sms = ba.refine_poses(T0, X, uv, off)
+    work = float(sum(s_.iterations for s_ in sms)) * n
+    out = {"metric": "BA observations*iterations/sec", "value": work / t_dev, "unit": "obs*iter/s", "n_gpus": 1,
+           "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t_dev, "higher_is_better": True,
+           "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+           "config": {"workload": f"f-2 motion-only BA: {B} poses x {n} fixed landmarks, {args.iters} LM iterations "
+                                  "(pose_lm_kernel, one CTA per pose; timed with host wall clock around the synchronous call)"},
+           "e2e": {"value": work / t_e2e, "unit": "obs*iter/s", "ms_per_step": 1e3 * t_e2e,
+                   "h2d_bytes_per_step": int(X.nbytes + uv.nbytes + T0.shape[0] * 96), "d2h_bytes_per_step": int(T0.shape[0] * 96)},
+           "gpu_launches": args.steps}
+    # algorithmic flops per observation*iteration: projection + J_c (~60), 27 weighted sums (108), trial (~40)
+    tf = 208.0 * work / t_dev / 1e12
+    out["roofline"] = {"bound": "tensor", "kernel": "pose_lm_kernel", "achieved": tf, "peak": FP64_PEAK_TFLOPS,
+                       "unit": "TFLOP/s", "frac": tf / FP64_PEAK_TFLOPS, "traffic": None,
+                       "note": "FP64 pipe (DFMA); 208 algorithmic flop per observation*iteration; the 64 KB of one pose "
+                               "problem stay in L1/L2 across iterations"}
+    if not args.no_cpu:
+        from oracle import pose_numpy
+        m = min(B, 16)
+        t0 = time.perf_counter()
+        its = 0
+        for i in range(m):
+            _, so = pose_numpy.refine_pose(T0[i], X[i * n:(i + 1) * n], uv[i * n:(i + 1) * n], intr, max_iters=args.iters)
+            its += so.iterations
+        dt = time.perf_counter() - t0
+        out["cpu_baseline"] = {"value": its * n / dt, "unit": "obs*iter/s", "cores": 1, "kind": "port",
+                               "sample": f"first {m} poses, oracle/pose_numpy.py (numpy, one core), {dt:.2f} s"}
+    print(json.dumps(out))
+
+
 def run_reference(args, rank, world):
     """--impl reference: the reference has no BA; the CPU arm is the oracle port on
     the host cores, all threads, on a bounded sample of the same workload."""
@@ -199,6 +256,8 @@ def run_reference(args, rank, world):
         return
     if args.workload == "c2":
         return run_c2(args, "reference")
+    if args.workload == "pnp":
+        raise SystemExit("bench.py: --workload pnp reports its CPU baseline (oracle/pose_numpy.py) in the b200 line")
     b, name = make_workload(argparse.Namespace(**{**vars(args), "windows": min(args.windows, args.cpu_windows),
                                                   "distinct": None}), 0)
     loss = "huber" if args.workload == "c3" else "trivial"
@@ -224,7 +283,7 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default="c4", choices=["c1", "c2", "c3", "c4", "c5"])
+    ap.add_argument("--workload", default="c4", choices=["c1", "c2", "c3", "c4", "c5", "pnp"])
     ap.add_argument("--frames", type=int, default=2700, help="C2: frames of the synthetic sequence")
     ap.add_argument("--windows", type=int, default=4096)
     ap.add_argument("--distinct", type=int, default=256, help="distinct geometries generated (set-up time bound)")
@@ -249,6 +308,8 @@ def main():
         raise SystemExit("bench.py: no CUDA device; the b2ba engine has no CPU fallback")
     if args.workload == "c2":
         return run_c2(args, "b200") if rank == 0 else None
+    if args.workload == "pnp":
+        return run_pnp(args) if rank == 0 else None
     torch.cuda.set_device(local)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")

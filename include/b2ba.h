@@ -89,6 +89,16 @@ int b2ba_get_summaries(b2ba_t* h, b2ba_summary* summaries);
 
 int b2ba_get(b2ba_t* h, double* poses_cw, double* points, int mem);
 
+/* Motion-only bundle adjustment: refine B camera poses, each against its own FIXED landmarks
+ * -- the refinement the reference leaves to cv2.solvePnPRansac (src/modules/vo.py:131-150: X = map points of the
+ * matched ids, uv = current keypoints, pose = inv(T_wc)).  obs_off (B+1, HOST, obs_off[0] = 0): problem b owns
+ * observations [obs_off[b], obs_off[b+1]); points: No x 3 (the landmark of every observation); obs_uv: No x 2
+ * float32; poses_cw: B x 12 [R | t], in/out; intr: fx, fy, cx, cy.  Same residual, robust loss, damping rule and
+ * stopping tests as b2ba_solve (the handle's options), restricted to the 6 x 6 camera block.  Independent of the
+ * problem set with b2ba_set_problem.  Returns the worst status (>0) or an error (<0); summaries (B, HOST) may be NULL. */
+int b2ba_refine_poses(b2ba_t* h, int32_t B, const int64_t* obs_off, double* poses_cw, const double* points,
+                      const float* obs_uv, const double intr[4], int32_t max_iters, b2ba_summary* summaries, int mem);
+
 /* Pipelined end-to-end batch solve (BASELINE config 4): set_problem_batch + solve + get in one call, with the
  * windows cut into `chunks` (<= 0: 8) contiguous chunks whose host->device copies, index build + solve and
  * device->host read-back overlap on three streams.  HOST buffers only (pinned memory makes the copies
@@ -110,7 +120,8 @@ enum {
   B2BA_D_RESIDUALS = 16, B2BA_D_WEIGHTS, B2BA_D_JC, B2BA_D_JP,   /* a1, original obs order */
   B2BA_D_B = 32, B2BA_D_GC, B2BA_D_C, B2BA_D_GP, B2BA_D_S, B2BA_D_GRED, B2BA_D_DC, B2BA_D_DP,
   B2BA_D_SCALARS,                       /* one LM iteration at init_mu from the CURRENT state */
-  B2BA_D_HIST_COST = 64, B2BA_D_HIST_MU, B2BA_D_HIST_ACCEPT      /* B x 64 */
+  B2BA_D_HIST_COST = 64, B2BA_D_HIST_MU, B2BA_D_HIST_ACCEPT,     /* B x 64 */
+  B2BA_D_POSE_HIST_COST = 80, B2BA_D_POSE_HIST_MU, B2BA_D_POSE_HIST_ACCEPT   /* b2ba_refine_poses: B x 64 */
 };
 int64_t b2ba_dump(b2ba_t* h, int what, void* dst, int64_t bytes);
 

@@ -253,6 +253,36 @@ class BundleAdjuster:
         poses_o, pts_o = self.get()
         return BAResult(T_from_poses(poses_o), pts_o, sm[0], sm)
 
+    # ------------------------------------------------------------------ motion-only BA
+    def refine_poses(self, T_cw, points, obs_uv, obs_off=None, max_iters=0):
+        """Refine B camera poses against FIXED landmarks: the step the reference leaves to cv2.solvePnPRansac
+        (`vo.py:131-150`: `X` = map points of the matched ids, `uv` = current keypoints).  T_cw (B,4,4) or (4,4);
+        points (No,3) = the landmark of every observation; obs_uv (No,2); obs_off (B+1,) CSR offsets (one problem
+        when omitted).  numpy (host) or torch CUDA arrays.  Returns (T_cw (B,4,4), [BASummary])."""
+        dev = any(_is_cuda_tensor(a) for a in (points, obs_uv))
+        if _is_cuda_tensor(T_cw):
+            T_cw = T_cw.detach().cpu().numpy()
+        poses = poses_from_T(T_cw)
+        nb = poses.shape[0]
+        a_pts, a_uv = _Arg(points, np.float64, "float64", dev), _Arg(obs_uv, np.float32, "float32", dev)
+        no = int(np.prod(a_pts.keep.shape)) // 3
+        off = np.array([0, no], np.int64) if obs_off is None else np.ascontiguousarray(obs_off, np.int64)
+        if off.shape != (nb + 1,) or int(off[-1]) != no or int(np.prod(a_uv.keep.shape)) != 2 * no:
+            raise ValueError("refine_poses: obs_off must have B+1 entries ending at the observation count")
+        a_pose = _Arg(poses, np.float64, "float64", dev)
+        sms = (_lib.Summary * max(nb, 1))()
+        rc = self._lib.b2ba_refine_poses(self._h, nb, off.ctypes.data, a_pose.ptr, a_pts.ptr, a_uv.ptr,
+                                         self.intr.ctypes.data_as(C.POINTER(C.c_double)), int(max_iters), sms,
+                                         _lib.MEM_DEVICE if dev else _lib.MEM_HOST)
+        self._check(rc, "b2ba_refine_poses")
+        out = a_pose.keep.cpu().numpy() if dev else a_pose.keep
+        return T_from_poses(out), [self._summary(sms[i]) for i in range(nb)]
+
+    def refine_pose(self, T_cw, points, obs_uv, max_iters=0):
+        """One pose: (4,4) in, (4,4) out + its summary."""
+        T, sm = self.refine_poses(np.asarray(T_cw, np.float64).reshape(1, 4, 4), points, obs_uv, None, max_iters)
+        return T[0], sm[0]
+
     def optimize_batch(self, batch, out=None, chunks=0) -> BAResult:
         """C4: a synth.BABatch-like object with CSR offsets; poses in (Nc,12) layout.  Host arrays go through the
         pipelined C-ABI call (copies of one chunk of windows overlap the solve of another); `out=(poses, points)`

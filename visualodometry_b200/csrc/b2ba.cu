@@ -16,6 +16,7 @@
 #include "devbuf.cuh"
 #include "ba_large.cuh"
 #include "ba_window.cuh"
+#include "ba_pose.cuh"
 
 using namespace b2;
 
@@ -49,6 +50,13 @@ struct b2ba {
   DevBuf<ObsRec> l_cm;
   DevBuf<int> l_cam_ptr;
   DevBuf<double> l_poses_tri, l_lin_part, l_lin, l_Dc, l_Sg, l_dc, l_r, l_z, l_q, l_Minv, l_part, l_sums, l_band, l_binv, l_band_ws, l_zbuf;
+  // motion-only BA (b2ba_refine_poses): own buffers, independent of the problem set with b2ba_set_problem
+  DevBuf<long long> r_off;
+  DevBuf<double> r_poses, r_pts, r_hist_cost, r_hist_mu;
+  DevBuf<float2> r_uv;
+  DevBuf<b2ba_summary> r_summ;
+  DevBuf<int> r_hist_accept;
+  int r_nb = 0;
   bool sched_order = false;   // pm / pt_ptr laid out in landmark-schedule order (window path), else canonical
   int l_band_P = 1;  // interiors of the substructured banded solve (1 = sequential)
   int l_bw = -1;     // block half-bandwidth of S when the banded Cholesky is selected, else -1
@@ -508,6 +516,55 @@ int b2ba_get(b2ba_t* h, double* poses_cw, double* points, int mem) {
   return B2BA_OK;
 }
 
+int b2ba_refine_poses(b2ba_t* h, int32_t B, const int64_t* obs_off, double* poses_cw, const double* points,
+                      const float* obs_uv, const double intr[4], int32_t max_iters, b2ba_summary* summaries, int mem) {
+  if (!h) return B2BA_E_INVALID;
+  if (B < 0 || !obs_off || (B > 0 && (!poses_cw || !intr))) return fail(h, B2BA_E_INVALID, "refine_poses: null argument");
+  for (int b = 0; b < B; ++b)
+    if (obs_off[b + 1] < obs_off[b] || obs_off[0] != 0) return fail(h, B2BA_E_INVALID, "refine_poses: obs_off must start at 0 and be non-decreasing");
+  const int64_t no = B > 0 ? obs_off[B] : 0;
+  if (no > 0 && (!points || !obs_uv)) return fail(h, B2BA_E_INVALID, "refine_poses: null argument");
+  CU(cudaSetDevice(h->device), "cudaSetDevice");
+  h->r_nb = B;
+  if (B == 0) return B2BA_OK;
+  const cudaMemcpyKind ki = in_kind(mem), ko = out_kind(mem);
+  cudaStream_t s = nullptr;
+  CU(h->r_off.alloc(B + 1), "alloc"); CU(h->r_poses.alloc((size_t)B * 12), "alloc"); CU(h->r_summ.alloc(B), "alloc");
+  CU(h->r_pts.alloc((size_t)no * 3), "alloc"); CU(h->r_uv.alloc(no), "alloc");
+  static_assert(sizeof(long long) == sizeof(int64_t), "offset type");
+  CU(cudaMemcpyAsync(h->r_off.p, obs_off, (size_t)(B + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, s), "copy offsets");
+  CU(cudaMemcpyAsync(h->r_poses.p, poses_cw, (size_t)B * 12 * sizeof(double), ki, s), "copy poses");
+  if (no) {
+    CU(cudaMemcpyAsync(h->r_pts.p, points, (size_t)no * 3 * sizeof(double), ki, s), "copy points");
+    CU(cudaMemcpyAsync(h->r_uv.p, obs_uv, (size_t)no * sizeof(float2), ki, s), "copy uv");
+  }
+  PoseData d{};
+  d.nb = B; d.obs_off = h->r_off.p; d.poses = h->r_poses.p; d.points = h->r_pts.p; d.obs_uv = h->r_uv.p;
+  d.summaries = h->r_summ.p;
+  if (h->opt.flags & 1) {
+    CU(h->r_hist_cost.alloc((size_t)B * kPoseHist), "alloc"); CU(h->r_hist_mu.alloc((size_t)B * kPoseHist), "alloc");
+    CU(h->r_hist_accept.alloc((size_t)B * kPoseHist), "alloc");
+    CU(cudaMemsetAsync(h->r_hist_cost.p, 0, (size_t)B * kPoseHist * 8, s), "memset");
+    CU(cudaMemsetAsync(h->r_hist_mu.p, 0, (size_t)B * kPoseHist * 8, s), "memset");
+    CU(cudaMemsetAsync(h->r_hist_accept.p, 0, (size_t)B * kPoseHist * 4, s), "memset");
+    d.hist_cost = h->r_hist_cost.p; d.hist_mu = h->r_hist_mu.p; d.hist_accept = h->r_hist_accept.p;
+  }
+  Params P = make_params(h, max_iters);
+  P.fx = intr[0]; P.fy = intr[1]; P.cx = intr[2]; P.cy = intr[3];
+  const int rc = launch_pose_lm(d, P, s);
+  if (rc) return cuda_fail(h, (cudaError_t)rc, "pose_lm_kernel");
+  CU(cudaMemcpyAsync(poses_cw, h->r_poses.p, (size_t)B * 12 * sizeof(double), ko, s), "read poses");
+  std::vector<b2ba_summary> sm(B);
+  CU(cudaMemcpyAsync(sm.data(), h->r_summ.p, (size_t)B * sizeof(b2ba_summary), cudaMemcpyDeviceToHost, s), "read summaries");
+  CU(cudaStreamSynchronize(s), "refine_poses");
+  int worst = 0;
+  for (int b = 0; b < B; ++b) {
+    if (summaries) summaries[b] = sm[b];
+    if (sm[b].status > worst) worst = sm[b].status;
+  }
+  return worst;
+}
+
 // Pipelined batch solve (C4 end to end): the windows are cut into `chunks` contiguous chunks; chunk i's host->device
 // copies (copy stream), index build + LM solve (solve stream) and device->host read-back (read-back stream)
 // overlap with the neighbouring chunks', so the copies hide behind the solves.  Host buffers only; pinned
@@ -730,7 +787,8 @@ static int canonical_inputs(b2ba* h, bool point_major, std::vector<int>& ptr, st
 }
 
 int64_t b2ba_dump(b2ba_t* h, int what, void* dst, int64_t bytes) {
-  if (!h || h->path == PATH_NONE || !dst) return fail(h, B2BA_E_STATE, "no problem set");
+  const bool pose_hist = what >= B2BA_D_POSE_HIST_COST && what <= B2BA_D_POSE_HIST_ACCEPT;   // needs no problem
+  if (!h || !dst || (h->path == PATH_NONE && !pose_hist)) return fail(h, B2BA_E_STATE, "no problem set");
   CU(cudaSetDevice(h->device), "cudaSetDevice");
   CU(cudaDeviceSynchronize(), "sync");
   const size_t no = (size_t)h->no;
@@ -904,6 +962,15 @@ int64_t b2ba_dump(b2ba_t* h, int what, void* dst, int64_t bytes) {
         case B2BA_D_DC: return put(h, &o[L.off_dc()], n * 8, dst, bytes);
         default: return put(h, &o[L.off_scal()], 4 * 8, dst, bytes);
       }
+    }
+    case B2BA_D_POSE_HIST_COST: case B2BA_D_POSE_HIST_MU: case B2BA_D_POSE_HIST_ACCEPT: {
+      if (!h->r_nb || !(h->opt.flags & 1)) return fail(h, B2BA_E_STATE, "pose history not recorded (options.flags bit 0)");
+      const size_t n = (size_t)h->r_nb * kPoseHist, sz = what == B2BA_D_POSE_HIST_ACCEPT ? 4 : 8;
+      if ((int64_t)(n * sz) > bytes) return fail(h, B2BA_E_INVALID, "dump: destination too small");
+      const void* src = what == B2BA_D_POSE_HIST_COST ? (void*)h->r_hist_cost.p
+                        : what == B2BA_D_POSE_HIST_MU ? (void*)h->r_hist_mu.p : (void*)h->r_hist_accept.p;
+      CU(cudaMemcpy(dst, src, n * sz, cudaMemcpyDeviceToHost), "read");
+      return (int64_t)(n * sz);
     }
     case B2BA_D_HIST_COST: case B2BA_D_HIST_MU: case B2BA_D_HIST_ACCEPT: {
       if (!h->solved || !(h->opt.flags & 1)) return fail(h, B2BA_E_STATE, "history not recorded (options.flags bit 0)");

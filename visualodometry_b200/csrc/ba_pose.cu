@@ -1,0 +1,193 @@
+// Motion-only bundle adjustment: refine ONE camera pose against fixed landmarks, the step
+// the reference leaves to cv2.solvePnPRansac's internal refinement (`src/modules/vo.py:131-150`).  Same
+// projection / residual / robust-loss / Jacobian code and the same Levenberg-Marquardt rule as the full
+// problem (Spec a0) restricted to a single 6 x 6 camera block: H = sum w J_c^T J_c, g = sum w J_c^T r,
+// D = clamp(diag H), (H + D/mu) delta = -g, left retraction, step quality against the model decrease.
+//
+// One CTA per pose problem, the whole LM loop in one launch: observations are strided over the CTA, the 21 + 6
+// + 2 sums are reduced by a fixed shuffle tree + fixed-order cross-warp sum (no atomics, deterministic), thread
+// 0 factors the damped 6 x 6 system, every thread evaluates the trial cost of its observations.
+#include "ba_pose.cuh"
+
+namespace b2 {
+namespace {
+
+constexpr int kPoseThreads = 128;
+constexpr int kPoseWarps = kPoseThreads / 32;
+constexpr int kNV = 29;   // B_c upper (21) | g_c (6) | cost | invalid count
+
+__device__ __forceinline__ int packed21(int r, int s) { return r * 6 - r * (r - 1) / 2 + (s - r); }
+
+// sum of v[0..n) over the CTA into out[0..n) (shared), identical on every thread afterwards
+template <int N>
+__device__ __forceinline__ void cta_sum(double* v, double* red, double* out) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int k = 0; k < N; ++k) {
+    const double s = warp_sum(v[k]);
+    if (lane == 0) red[warp * N + k] = s;
+  }
+  __syncthreads();
+  if (threadIdx.x < N) {
+    double s = 0.0;
+#pragma unroll
+    for (int w = 0; w < kPoseWarps; ++w) s += red[w * N + threadIdx.x];
+    out[threadIdx.x] = s;
+  }
+  __syncthreads();
+}
+
+__global__ void __launch_bounds__(kPoseThreads) pose_lm_kernel(PoseData d, Params P) {
+  __shared__ double red[kPoseWarps * kNV], lin[kNV], tri[2], pose[12], ptri[12], dl[8];
+  __shared__ int ctl[2];
+  const int b = blockIdx.x, tid = threadIdx.x;
+  const long long o0 = d.obs_off[b], o1 = d.obs_off[b + 1];
+  if (tid < 12) pose[tid] = d.poses[12 * (size_t)b + tid];
+  __syncthreads();
+
+  double mu = P.init_mu, nu = 2.0, cost = 0.0, initial_cost = 0.0;
+  int n_acc = 0, n_rej = 0, ninv = 0, status = B2BA_MAX_ITERS, it = 0;
+  bool have_lin = false;
+  for (; it < P.max_iters; ++it) {
+    const bool fresh = !have_lin;
+    if (!have_lin) {
+      // ---- linearise: B_c, g_c, cost, invalid count
+      double v[kNV];
+#pragma unroll
+      for (int k = 0; k < kNV; ++k) v[k] = 0.0;
+      for (long long i = o0 + tid; i < o1; i += kPoseThreads) {
+        const double* X = d.points + 3 * (size_t)i;
+        const float2 uv = d.obs_uv[i];
+        Proj o;
+        project(P, pose, X[0], X[1], X[2], uv.x, uv.y, o);
+        double jc[12];
+        jac_cam(P, o, jc);
+#pragma unroll
+        for (int r = 0; r < 6; ++r) {
+#pragma unroll
+          for (int s = r; s < 6; ++s) v[packed21(r, s)] += o.w * (jc[r] * jc[s] + jc[6 + r] * jc[6 + s]);
+          v[21 + r] += o.w * (jc[r] * o.r0 + jc[6 + r] * o.r1);
+        }
+        v[27] += 0.5 * o.rho;
+        v[28] += o.valid ? 0.0 : 1.0;
+      }
+      cta_sum<kNV>(v, red, lin);
+      cost = lin[27];
+      ninv = (int)lin[28];
+      if (it == 0) initial_cost = cost;
+      have_lin = true;
+    }
+    // ---- thread 0: damped 6 x 6 Cholesky, delta, model-decrease terms
+    if (tid == 0) {
+      const double imu = 1.0 / mu;
+      double A[6][6], D[6], g[6], x[6];
+      bool ok = true;
+      double gm = 0.0;
+      for (int r = 0; r < 6; ++r) {
+        D[r] = clampd(lin[packed21(r, r)]);
+        g[r] = lin[21 + r];
+        gm = fmax(gm, fabs(g[r]));
+        for (int s = r; s < 6; ++s) A[s][r] = lin[packed21(r, s)] + (r == s ? D[r] * imu : 0.0);
+      }
+      for (int c = 0; c < 6 && ok; ++c) {              // A = L L^T, lower, in place
+        double dj = A[c][c];
+        for (int k = 0; k < c; ++k) dj -= A[c][k] * A[c][k];
+        if (!(dj > 0.0) || !isfinite(dj)) { ok = false; break; }
+        const double l = sqrt(dj);
+        A[c][c] = l;
+        for (int r = c + 1; r < 6; ++r) {
+          double t = A[r][c];
+          for (int k = 0; k < c; ++k) t -= A[r][k] * A[c][k];
+          A[r][c] = t / l;
+        }
+      }
+      double dDd = 0.0, gd = 0.0;
+      if (ok) {
+        for (int r = 0; r < 6; ++r) { double t = -g[r]; for (int k = 0; k < r; ++k) t -= A[r][k] * x[k]; x[r] = t / A[r][r]; }
+        for (int r = 5; r >= 0; --r) { double t = x[r]; for (int k = r + 1; k < 6; ++k) t -= A[k][r] * x[k]; x[r] = t / A[r][r]; }
+        for (int r = 0; r < 6; ++r) {
+          ok = ok && isfinite(x[r]);
+          dDd += x[r] * x[r] * D[r];
+          gd += x[r] * g[r];
+          dl[r] = x[r];
+        }
+      }
+      dl[6] = 0.5 * (dDd * imu - gd);                  // model decrease
+      dl[7] = gm;
+      ctl[0] = ok ? 1 : 0;
+      if (ok) retract_pose(pose, x, ptri);
+    }
+    __syncthreads();
+    const bool step_ok = ctl[0] != 0;
+    // ---- trial cost with the retracted pose
+    double tv[2] = {0.0, 0.0};
+    if (step_ok) {
+      for (long long i = o0 + tid; i < o1; i += kPoseThreads) {
+        const double* X = d.points + 3 * (size_t)i;
+        const float2 uv = d.obs_uv[i];
+        Proj o;
+        project(P, ptri, X[0], X[1], X[2], uv.x, uv.y, o);
+        tv[0] += 0.5 * o.rho;
+        tv[1] += o.valid ? 0.0 : 1.0;
+      }
+    }
+    cta_sum<2>(tv, red, tri);
+    // ---- LM control (identical on every thread: all inputs are in shared memory)
+    const double tc = tri[0], model = dl[6], gm = dl[7];
+    int accept = 0, stop = 0;
+    double rho = 0.0;
+    if (step_ok && model > 0.0) {
+      rho = (cost - tc) / model;
+      accept = (isfinite(tc) && rho > kMinRatio) ? 1 : 0;
+    }
+    if (P.gtol > 0.0 && fresh && gm <= P.gtol) { status = B2BA_CONVERGED; break; }   // before taking the step
+    if (accept) {
+      if (P.ftol > 0.0 && fabs(cost - tc) <= P.ftol * cost) stop = B2BA_CONVERGED;
+      double dn2 = 0.0, xn2 = 0.0;
+      for (int r = 0; r < 6; ++r) dn2 += dl[r] * dl[r];
+      for (int r = 0; r < 12; ++r) xn2 += pose[r] * pose[r];
+      if (P.ptol > 0.0 && sqrt(dn2) <= P.ptol * (sqrt(xn2) + P.ptol)) stop = B2BA_CONVERGED;
+    }
+    const double mu_used = mu;
+    __syncthreads();                                   // everyone has read pose / dl before they change
+    if (accept) {
+      const double t = 2.0 * rho - 1.0;
+      mu = fmin(kMuMax, mu / fmax(1.0 / 3.0, 1.0 - t * t * t));
+      nu = 2.0;
+      cost = tc;
+      ninv = (int)tri[1];
+      if (tid < 12) pose[tid] = ptri[tid];
+      have_lin = false;
+      ++n_acc;
+    } else {
+      mu = mu / nu;
+      nu *= 2.0;
+      ++n_rej;
+    }
+    if (tid == 0 && d.hist_cost != nullptr && it < kPoseHist) {
+      d.hist_cost[(size_t)b * kPoseHist + it] = cost;
+      d.hist_mu[(size_t)b * kPoseHist + it] = mu_used;
+      d.hist_accept[(size_t)b * kPoseHist + it] = accept;
+    }
+    if (!stop && !(mu > kMuMin)) stop = B2BA_NUMERICAL_FAILURE;
+    __syncthreads();
+    if (stop) { status = stop; ++it; break; }
+  }
+  if (tid < 12) d.poses[12 * (size_t)b + tid] = pose[tid];
+  if (tid == 0) {
+    b2ba_summary s;
+    s.status = status; s.iterations = it; s.accepted = n_acc; s.rejected = n_rej; s.n_invalid = ninv; s.pcg_iters = 0;
+    s.initial_cost = initial_cost; s.final_cost = cost; s.final_mu = mu;
+    d.summaries[b] = s;
+  }
+}
+
+}  // namespace
+
+int launch_pose_lm(const PoseData& d, const Params& P, cudaStream_t s) {
+  if (d.nb <= 0) return 0;
+  pose_lm_kernel<<<d.nb, kPoseThreads, 0, s>>>(d, P);
+  return (int)cudaGetLastError();
+}
+
+}  // namespace b2

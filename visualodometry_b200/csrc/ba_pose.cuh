@@ -1,0 +1,24 @@
+// Motion-only BA (pose refinement against fixed landmarks), SURVEY §8 row f-2 -- see ba_pose.cu.
+#pragma once
+#include "ba_math.cuh"
+#include "../../include/b2ba.h"
+
+namespace b2 {
+
+constexpr int kPoseHist = 64;
+
+struct PoseData {
+  int nb;                      // pose problems
+  const long long* obs_off;    // nb+1 (device): problem b owns observations [obs_off[b], obs_off[b+1])
+  double* poses;               // nb x 12 [R row-major | t] world->camera, in/out
+  const double* points;        // No x 3: the landmark of every observation (fixed)
+  const float2* obs_uv;        // No
+  b2ba_summary* summaries;     // nb
+  double* hist_cost;           // nb x kPoseHist or null
+  double* hist_mu;
+  int* hist_accept;
+};
+
+int launch_pose_lm(const PoseData& d, const Params& P, cudaStream_t s);
+
+}  // namespace b2

@@ -75,6 +75,9 @@ class VOLoop:
         self.keyframe = None
         self.trajectory = []
         self.initialized = False
+        # NOT in the reference: optional motion-only BA after the PnP, a callable
+        # (T_cw, X, uv) -> T_cw, e.g. `lambda T, X, uv: ba.refine_pose(T, X, uv)[0]`.  None = the reference's loop.
+        self.pose_refiner = None
 
     # ------------------------------------------------------------------ vo.py:49-250
     def process_frame(self, img) -> None:
@@ -135,6 +138,10 @@ class VOLoop:
         R, _ = cv2.Rodrigues(rvec)
         T_cw = np.eye(4)
         T_cw[:3, :3], T_cw[:3, 3] = R, tvec.flatten()
+        if self.pose_refiner is not None and inliers is not None and len(inliers) >= 6:
+            sel = inliers.flatten()
+            T_cw = self.pose_refiner(T_cw, X[sel], uv[sel])
+            R = T_cw[:3, :3]
         T_raw = np.linalg.inv(T_cw)
         self._speed_control(R, T_raw)
         self.last_pos = self.T_wc[:3, 3].copy()
