@@ -89,6 +89,12 @@ int b2ba_get_summaries(b2ba_t* h, b2ba_summary* summaries);
 
 int b2ba_get(b2ba_t* h, double* poses_cw, double* points, int mem);
 
+/* Reprojection error of every observation at the CURRENT state (after b2ba_solve: the refined one), in pixels,
+ * in the caller's observation order; -1 where the landmark is behind the cheirality gate.  The quantity the
+ * reference gates new landmarks on (`frontend.py:139-142`: |projectPoints(X) - uv| < max_reproj_err, config.py:32),
+ * here as the input of outlier culling after BA.  err: No doubles, HOST or DEVICE per `mem`. */
+int b2ba_reproj_errors(b2ba_t* h, double* err, int mem);
+
 /* Motion-only bundle adjustment: refine B camera poses, each against its own FIXED landmarks
  * -- the refinement the reference leaves to cv2.solvePnPRansac (src/modules/vo.py:131-150: X = map points of the
  * matched ids, uv = current keypoints, pose = inv(T_wc)).  obs_off (B+1, HOST, obs_off[0] = 0): problem b owns

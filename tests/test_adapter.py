@@ -96,3 +96,53 @@ def test_adapter_in_the_frame_loop_with_oracle_solver(loop_runs):
     gt = seq.T_wc[:, :3, 3]
     e_ba, e_plain = vo_synth.ate_sim3(traj[20:], gt[20:]), vo_synth.ate_sim3(out["plain"][2][20:], gt[20:])
     assert np.isfinite(e_ba) and e_ba < 2.0 * e_plain + 1.0                              # and does not wreck the trajectory
+
+
+def test_cull_window_marks_observations_and_drops_dead_landmarks():
+    """row f-4: an observation failing the reference's gate (frontend.py:139-142) loses its id in its keyframe,
+    a landmark whose window observations all fail leaves the map; others stay."""
+    vo = FakeVO()
+    vo.map_points = {5: np.array([0.0, 0, 10]), 7: np.array([1.0, 0, 12]), 9: np.array([2.0, 0, 9])}
+    w = [kf([[1, 1], [2, 2], [3, 3]], [5, 7, 9], 0.0), kf([[5, 5], [6, 6], [7, 7]], [7, 5, 9], 1.0)]
+    p = adapter.pack_window(w, vo.map_points, n_fixed=1)
+    assert p.pids.tolist() == [5, 7, 9] and p.obs_kp.tolist() == [0, 1, 2, 0, 1, 2]
+    err = np.zeros(len(p.obs_cam))
+    err[(p.obs_cam == 1) & (p.obs_pt == 0)] = 7.5            # landmark 5: one bad observation (keyframe 1, keypoint 1)
+    err[p.obs_pt == 2] = [-1.0, 9.0]                          # landmark 9: behind the camera / too far off -> dead
+    n = adapter.cull_window(vo, w, p, err, max_err=5.0)
+    assert n == 3
+    assert w[0]["ids"].tolist() == [5, 7, -1] and w[1]["ids"].tolist() == [7, -1, -1]
+    assert sorted(vo.map_points) == [5, 7]
+    assert adapter.cull_window(vo, w, p, np.zeros(len(p.obs_cam)), 5.0) == 0
+
+
+@pytest.mark.gpu
+def test_reproj_errors_match_the_reference_gate_call():
+    """b2ba_reproj_errors against cv2.projectPoints, the call the reference gates landmarks with
+    (frontend.py:139-141), before and after a solve, in the caller's observation order."""
+    from visualodometry_b200 import BundleAdjuster, synth
+    from visualodometry_b200.ba import T_from_poses
+    p = synth.make_window(4, n_cams=6, n_pts=400, n_obs=1800)
+    K = np.array([[p.intr[0], 0, p.intr[2]], [0, p.intr[1], p.intr[3]], [0, 0, 1.0]])
+    ba = BundleAdjuster(K, BAConfig(max_iters=5, loss="huber", loss_scale=2.0))
+    ba.set_problem(p.poses, p.points, p.obs_cam, p.obs_pt, p.obs_uv, p.fixed_cam)
+
+    def ref_err(poses, pts):
+        T = T_from_poses(poses)
+        e = np.empty(len(p.obs_cam))
+        for c in range(T.shape[0]):
+            m = p.obs_cam == c
+            proj, _ = cv2.projectPoints(pts[p.obs_pt[m]], T[c, :3, :3], T[c, :3, 3], K, None)
+            e[m] = np.linalg.norm(proj.reshape(-1, 2) - p.obs_uv[m].astype(np.float64), axis=1)
+        return e
+    assert np.abs(ba.reproj_errors() - ref_err(p.poses, p.points)).max() < 1e-9
+    ba.solve()
+    poses, pts = ba.get()
+    e1, r1 = ba.reproj_errors(), ref_err(poses, pts)
+    T = T_from_poses(poses)
+    depth = np.einsum("nj,nj->n", T[p.obs_cam, 2, :3], pts[p.obs_pt]) + T[p.obs_cam, 2, 3]
+    gated = depth < 1e-3                                   # config.py:31 min_depth: cv2.projectPoints has no such gate
+    assert np.array_equal(e1 < 0, gated) and gated.sum() < 0.01 * len(e1)
+    assert np.abs(e1 - r1)[~gated].max() < 1e-9
+    assert np.median(e1[~gated]) < np.median(ref_err(p.poses, p.points))
+    ba.close()

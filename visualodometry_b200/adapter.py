@@ -52,6 +52,7 @@ class PackedWindow:
     obs_uv: np.ndarray      # (No,2) f32
     fixed_cam: np.ndarray   # (Nc,) bool
     pids: np.ndarray        # (Np,) int64 landmark ids (slot -> id)
+    obs_kp: np.ndarray = None   # (No,) keypoint index of every observation in its keyframe (for culling)
 
     @property
     def poses(self):
@@ -72,7 +73,7 @@ def pack_window(window, map_points, n_fixed: int = 2, min_obs: int = 2) -> Packe
     nc = len(kfs)
     if nc < 2:
         return None
-    cams, pids, uvs = [], [], []
+    cams, pids, uvs, kps = [], [], [], []
     for j, kf in enumerate(kfs):
         ids = np.asarray(kf["ids"]).astype(np.int64)
         kp = _keypoints_numpy(kf["feats"])
@@ -85,14 +86,16 @@ def pack_window(window, map_points, n_fixed: int = 2, min_obs: int = 2) -> Packe
         cams.append(np.full(sel.size, j, np.int32))
         pids.append(ids[sel])
         uvs.append(kp[sel])
+        kps.append(sel)
     if not cams:
         return None
     cam = np.concatenate(cams)
     pid = np.concatenate(pids)
     uv = np.concatenate(uvs).astype(np.float32)
+    kpi = np.concatenate(kps)
     # landmarks that still exist in the map (`_prune_map`, vo.py:35-47, may have dropped old ids)
     known = np.fromiter((p in map_points for p in pid.tolist()), bool, pid.size)
-    cam, pid, uv = cam[known], pid[known], uv[known]
+    cam, pid, uv, kpi = cam[known], pid[known], uv[known], kpi[known]
     if pid.size == 0:
         return None
     upid, inv, cnt = np.unique(pid, return_inverse=True, return_counts=True)
@@ -109,7 +112,7 @@ def pack_window(window, map_points, n_fixed: int = 2, min_obs: int = 2) -> Packe
     T_cw = np.stack([np.linalg.inv(np.asarray(kf["T_wc"], np.float64)) for kf in kfs])
     fixed = np.zeros(nc, bool)
     fixed[:max(1, min(n_fixed, nc - 1))] = True
-    return PackedWindow(T_cw, points, obs_cam, obs_pt, obs_uv, fixed, upid)
+    return PackedWindow(T_cw, points, obs_cam, obs_pt, obs_uv, fixed, upid, kpi[keep_obs])
 
 
 def write_back(vo, window, packed: PackedWindow, T_cw: np.ndarray, points: np.ndarray) -> None:
@@ -127,8 +130,28 @@ def write_back(vo, window, packed: PackedWindow, T_cw: np.ndarray, points: np.nd
             mp[p] = x.copy()
 
 
-def refine_window(vo, window, ba: BundleAdjuster, n_fixed: int = 2):
-    """Pack -> BundleAdjuster.optimize -> write back.  Returns the BASummary (or None if skipped)."""
+def cull_window(vo, window, packed: PackedWindow, err: np.ndarray, max_err: float) -> int:
+    """Outlier culling after BA with the reference's own landmark gate (`frontend.py:139-142`:
+    reprojection error < `max_reproj_err`, `config.py:32`; depth gate `config.py:31` = err < 0 here): an
+    observation that fails it loses its id in its keyframe (`kf["ids"][kp] = -1`, the reference's "untracked"
+    marker, `vo.py:53`), a landmark whose window observations ALL fail is dropped from `vo.map_points`.
+    Returns the number of observations culled."""
+    bad = (err < 0) | (err > max_err)
+    if not bad.any():
+        return 0
+    kfs = list(window)
+    for j, kf in enumerate(kfs):
+        m = bad & (packed.obs_cam == j)
+        if m.any():
+            kf["ids"][packed.obs_kp[m]] = -1
+    left = np.bincount(packed.obs_pt[~bad], minlength=len(packed.pids))
+    for p in packed.pids[left == 0].tolist():
+        vo.map_points.pop(int(p), None)
+    return int(bad.sum())
+
+
+def refine_window(vo, window, ba: BundleAdjuster, n_fixed: int = 2, cull_px: float | None = None):
+    """Pack -> BundleAdjuster.optimize -> write back (-> cull).  Returns the BASummary (or None if skipped)."""
     packed = pack_window(window, vo.map_points, n_fixed=n_fixed)
     if packed is None:
         return None
@@ -136,14 +159,17 @@ def refine_window(vo, window, ba: BundleAdjuster, n_fixed: int = 2):
     if not res.summary.ok or not np.isfinite(res.T_cw).all() or not np.isfinite(res.points).all():
         return res.summary                        # numerical failure: keep the reference's state
     write_back(vo, window, packed, res.T_cw, res.points)
+    if cull_px is not None and hasattr(ba, "reproj_errors"):
+        cull_window(vo, window, packed, ba.reproj_errors(), cull_px)
     return res.summary
 
 
 class WindowAdapter:
     """Keyframe window + BA call, hooked onto one VisualOdometry instance."""
 
-    def __init__(self, vo, config: BAConfig | None = None, ba=None, n_fixed: int = 2):
+    def __init__(self, vo, config: BAConfig | None = None, ba=None, n_fixed: int = 2, cull_px: float | None = None):
         self.vo = vo
+        self.cull_px = cull_px                    # e.g. config.max_reproj_err (config.py:32); None = no culling
         self.config = config or BAConfig()
         self.ba = ba if ba is not None else BundleAdjuster(vo.K, self.config)
         self.n_fixed = n_fixed
@@ -166,7 +192,7 @@ class WindowAdapter:
         if prev is not None:
             backfill_ids(prev, new, ref_indices, curr_indices)
         self.window.append(new)
-        self.summaries.append(refine_window(vo, self.window, self.ba, self.n_fixed))
+        self.summaries.append(refine_window(vo, self.window, self.ba, self.n_fixed, self.cull_px))
 
     def install(self):
         self._orig = self.vo._create_keyframe
@@ -190,6 +216,6 @@ def backfill_ids(prev_kf, new_kf, ref_indices, curr_indices) -> int:
     return int(m.sum())
 
 
-def install(vo, config: BAConfig | None = None, ba=None, n_fixed: int = 2) -> WindowAdapter:
+def install(vo, config: BAConfig | None = None, ba=None, n_fixed: int = 2, cull_px: float | None = None) -> WindowAdapter:
     """The one call a maintainer adds after constructing VisualOdometry."""
-    return WindowAdapter(vo, config, ba, n_fixed).install()
+    return WindowAdapter(vo, config, ba, n_fixed, cull_px).install()

@@ -231,6 +231,16 @@ class BundleAdjuster:
             self._check(self._lib.b2ba_get(self._h, poses.ctypes.data, pts.ctypes.data, _lib.MEM_HOST), "b2ba_get")
         return poses, pts
 
+    def reproj_errors(self) -> np.ndarray:
+        """(No,) reprojection error in pixels of every observation at the current (after solve: refined) state, in
+        the caller's observation order; -1 behind the cheirality gate.  The reference's landmark gate quantity
+        (`frontend.py:139-142`), used for culling after BA (`adapter.cull_window`)."""
+        if self._shape is None:
+            raise RuntimeError("reproj_errors: no problem set")
+        out = np.empty(self._shape[2], np.float64)
+        self._check(self._lib.b2ba_reproj_errors(self._h, out.ctypes.data, _lib.MEM_HOST), "b2ba_reproj_errors")
+        return out
+
     def dump(self, what: str, shape, dtype=np.float64):
         out = np.zeros(shape, dtype)
         n = self._lib.b2ba_dump(self._h, _lib.D[what], out.ctypes.data, out.nbytes)

@@ -516,6 +516,28 @@ int b2ba_get(b2ba_t* h, double* poses_cw, double* points, int mem) {
   return B2BA_OK;
 }
 
+int b2ba_reproj_errors(b2ba_t* h, double* err, int mem) {
+  if (!h || h->path == PATH_NONE) return fail(h, B2BA_E_STATE, "no problem set");
+  if (!err && h->no > 0) return fail(h, B2BA_E_INVALID, "reproj_errors: null destination");
+  CU(cudaSetDevice(h->device), "cudaSetDevice");
+  cudaStream_t s = h->last_stream;
+  if (h->no == 0) return B2BA_OK;
+  const double* pts_lm = h->d_pts0.p;
+  if (h->sched_order) {   // the observation arrays index landmarks in the caller's order
+    const int rcp = permute_pts(h, h->d_pts0.p, h->d_pts1.p, false, s);
+    if (rcp) return cuda_fail(h, (cudaError_t)rcp, "permute points");
+    pts_lm = h->d_pts1.p;
+  }
+  DevBuf<double> tmp;
+  double* dst = err;
+  if (mem != B2BA_MEM_DEVICE) { CU(tmp.alloc((size_t)h->no), "alloc"); dst = tmp.p; }
+  const int rc = obs_errors(make_index_in(h), make_params(h, 1), h->d_poses.p, pts_lm, dst, s);
+  if (rc) return cuda_fail(h, (cudaError_t)rc, "obs_errors");
+  if (mem != B2BA_MEM_DEVICE) CU(cudaMemcpyAsync(err, tmp.p, (size_t)h->no * sizeof(double), cudaMemcpyDeviceToHost, s), "read errors");
+  CU(cudaStreamSynchronize(s), "reproj_errors");
+  return B2BA_OK;
+}
+
 int b2ba_refine_poses(b2ba_t* h, int32_t B, const int64_t* obs_off, double* poses_cw, const double* points,
                       const float* obs_uv, const double intr[4], int32_t max_iters, b2ba_summary* summaries, int mem) {
   if (!h) return B2BA_E_INVALID;

@@ -231,6 +231,31 @@ __global__ void obs_terms_kernel(IndexIn in, Params P, const double* __restrict_
 }
 }  // namespace
 
+namespace {
+// reprojection error in pixels per observation, ORIGINAL observation order; -1 behind the cheirality gate
+__global__ void obs_error_kernel(IndexIn in, Params P, const double* __restrict__ poses,
+                                 const double* __restrict__ pts, double* err) {
+  const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (i >= in.no) return;
+  const int b = find_window(in.obs_off, in.nb, i);
+  const double* pose = poses + 12 * (size_t)(in.cam_off[b] + in.obs_cam[i]);
+  const double* X = pts + 3 * (size_t)(in.pt_off[b] + in.obs_pt[i]);
+  const float2 uv = in.obs_uv[i];
+  Params Q = P;
+  Q.loss = 0;                        // the plain pixel residual, whatever the solver's loss
+  Proj o;
+  project(Q, pose, X[0], X[1], X[2], uv.x, uv.y, o);
+  err[i] = o.valid ? sqrt(o.r0 * o.r0 + o.r1 * o.r1) : -1.0;
+}
+}  // namespace
+
+int obs_errors(const IndexIn& in, const Params& P, const double* poses, const double* pts, double* err,
+               cudaStream_t s) {
+  if (in.no == 0) return 0;
+  obs_error_kernel<<<(int)((in.no + 255) / 256), 256, 0, s>>>(in, P, poses, pts, err);
+  return (int)cudaGetLastError();
+}
+
 int dump_obs_terms(const IndexIn& in, const Params& P, const double* poses, const double* pts,
                    double* r, double* w, double* jc, double* jp, cudaStream_t s) {
   if (in.no == 0) return 0;

@@ -39,6 +39,11 @@ int build_index(const IndexIn& in, const IndexOut& out, cudaStream_t s);
 int permute_points(int nb, int np_tot, const int* pt_off, const int* sched, const double* src, double* dst,
                    bool to_sched, cudaStream_t s);
 
+// reprojection error (pixels) per observation in ORIGINAL observation order from landmark-ordered points;
+// -1 where the landmark is behind the cheirality gate (the input of outlier culling)
+int obs_errors(const IndexIn& in, const Params& P, const double* poses, const double* pts, double* err,
+               cudaStream_t s);
+
 // a1 dump in ORIGINAL observation order (parity tests): r (no x 2), w (no), Jc (no x 12), Jp (no x 6)
 int dump_obs_terms(const IndexIn& in, const Params& P, const double* poses, const double* pts,
                    double* r, double* w, double* jc, double* jp, cudaStream_t s);
