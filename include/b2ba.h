@@ -95,6 +95,14 @@ int b2ba_get(b2ba_t* h, double* poses_cw, double* points, int mem);
  * here as the input of outlier culling after BA.  err: No doubles, HOST or DEVICE per `mem`. */
 int b2ba_reproj_errors(b2ba_t* h, double* err, int mem);
 
+/* Batched two-view triangulation + gating: `triangulate_points` of the reference
+ * (`src/modules/frontend.py:115-148`, called at `vo.py:262-270`).  P1, P2: K [R|t] of the two views (3 x 4 row-major,
+ * HOST, the arguments of cv2.triangulatePoints at frontend.py:128-131); uv1, uv2: N x 2 float32 matched keypoints;
+ * X: N x 3 (every match, like the reference's pts_3d before masking); keep[i] = depth in view 2 > min_depth &&
+ * reprojection error in view 2 < max_reproj_err (frontend.py:135-143, config.py:31-32).  uv / X / keep HOST or DEVICE. */
+int b2ba_triangulate(b2ba_t* h, int32_t N, const double P1[12], const double P2[12], const float* uv1,
+                     const float* uv2, double min_depth, double max_reproj_err, double* X, uint8_t* keep, int mem);
+
 /* Motion-only bundle adjustment: refine B camera poses, each against its own FIXED landmarks
  * -- the refinement the reference leaves to cv2.solvePnPRansac (src/modules/vo.py:131-150: X = map points of the
  * matched ids, uv = current keypoints, pose = inv(T_wc)).  obs_off (B+1, HOST, obs_off[0] = 0): problem b owns

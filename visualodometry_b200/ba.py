@@ -231,6 +231,33 @@ class BundleAdjuster:
             self._check(self._lib.b2ba_get(self._h, poses.ctypes.data, pts.ctypes.data, _lib.MEM_HOST), "b2ba_get")
         return poses, pts
 
+    def triangulate(self, T_cw1, T_cw2, pts1, pts2, min_depth=1e-3, max_reproj_err=5.0):
+        """`triangulate_points(T_cw1, T_cw2, pts1, pts2, K, config)` of the reference (`frontend.py:115-148`) on the
+        GPU: returns (X[keep] (M,3) f64, keep (N,) bool) like the reference; `K` is the adjuster's."""
+        n = len(pts1)
+        if n == 0:
+            return np.empty((0, 3)), np.zeros(0, dtype=bool)
+        K = np.array([[self.intr[0], 0, self.intr[2]], [0, self.intr[1], self.intr[3]], [0, 0, 1.0]])
+        P1 = np.ascontiguousarray(K @ np.asarray(T_cw1, np.float64)[:3, :])
+        P2 = np.ascontiguousarray(K @ np.asarray(T_cw2, np.float64)[:3, :])
+        dev = _is_cuda_tensor(pts1) or _is_cuda_tensor(pts2)
+        a, b = _Arg(pts1, np.float32, "float32", dev), _Arg(pts2, np.float32, "float32", dev)
+        dp = C.POINTER(C.c_double)
+        if dev:
+            X = torch.empty((n, 3), dtype=torch.float64, device="cuda"); keep = torch.empty(n, dtype=torch.uint8, device="cuda")
+            xp, kp = C.c_void_p(X.data_ptr()), C.c_void_p(keep.data_ptr())
+        else:
+            X = np.empty((n, 3), np.float64); keep = np.empty(n, np.uint8)
+            xp, kp = C.c_void_p(X.ctypes.data), C.c_void_p(keep.ctypes.data)
+        rc = self._lib.b2ba_triangulate(self._h, n, P1.ctypes.data_as(dp), P2.ctypes.data_as(dp), a.ptr, b.ptr,
+                                        float(min_depth), float(max_reproj_err), xp, kp,
+                                        _lib.MEM_DEVICE if dev else _lib.MEM_HOST)
+        self._check(rc, "b2ba_triangulate")
+        if dev:
+            X, keep = X.cpu().numpy(), keep.cpu().numpy()
+        keep = keep.astype(bool)
+        return X[keep], keep
+
     def reproj_errors(self) -> np.ndarray:
         """(No,) reprojection error in pixels of every observation at the current (after solve: refined) state, in
         the caller's observation order; -1 behind the cheirality gate.  The reference's landmark gate quantity

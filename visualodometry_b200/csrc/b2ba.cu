@@ -538,6 +538,33 @@ int b2ba_reproj_errors(b2ba_t* h, double* err, int mem) {
   return B2BA_OK;
 }
 
+int b2ba_triangulate(b2ba_t* h, int32_t N, const double P1[12], const double P2[12], const float* uv1,
+                     const float* uv2, double min_depth, double max_reproj_err, double* X, uint8_t* keep, int mem) {
+  if (!h) return B2BA_E_INVALID;
+  if (N < 0 || !P1 || !P2 || (N > 0 && (!uv1 || !uv2 || !X || !keep))) return fail(h, B2BA_E_INVALID, "triangulate: null argument");
+  CU(cudaSetDevice(h->device), "cudaSetDevice");
+  if (N == 0) return B2BA_OK;
+  cudaStream_t s = nullptr;
+  if (mem == B2BA_MEM_DEVICE) {
+    const int rc = launch_triangulate(N, P1, P2, (const float2*)uv1, (const float2*)uv2, min_depth, max_reproj_err, X, keep, s);
+    if (rc) return cuda_fail(h, (cudaError_t)rc, "triangulate_kernel");
+    CU(cudaStreamSynchronize(s), "triangulate");
+    return B2BA_OK;
+  }
+  DevBuf<float2> a, b;
+  DevBuf<double> x;
+  DevBuf<unsigned char> k;
+  CU(a.alloc(N), "alloc"); CU(b.alloc(N), "alloc"); CU(x.alloc((size_t)N * 3), "alloc"); CU(k.alloc(N), "alloc");
+  CU(cudaMemcpyAsync(a.p, uv1, (size_t)N * sizeof(float2), cudaMemcpyHostToDevice, s), "copy uv1");
+  CU(cudaMemcpyAsync(b.p, uv2, (size_t)N * sizeof(float2), cudaMemcpyHostToDevice, s), "copy uv2");
+  const int rc = launch_triangulate(N, P1, P2, a.p, b.p, min_depth, max_reproj_err, x.p, k.p, s);
+  if (rc) return cuda_fail(h, (cudaError_t)rc, "triangulate_kernel");
+  CU(cudaMemcpyAsync(X, x.p, (size_t)N * 3 * sizeof(double), cudaMemcpyDeviceToHost, s), "read X");
+  CU(cudaMemcpyAsync(keep, k.p, (size_t)N, cudaMemcpyDeviceToHost, s), "read keep");
+  CU(cudaStreamSynchronize(s), "triangulate");
+  return B2BA_OK;
+}
+
 int b2ba_refine_poses(b2ba_t* h, int32_t B, const int64_t* obs_off, double* poses_cw, const double* points,
                       const float* obs_uv, const double intr[4], int32_t max_iters, b2ba_summary* summaries, int mem) {
   if (!h) return B2BA_E_INVALID;

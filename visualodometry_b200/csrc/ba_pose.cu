@@ -184,6 +184,91 @@ __global__ void __launch_bounds__(kPoseThreads) pose_lm_kernel(PoseData d, Param
 
 }  // namespace
 
+namespace {
+// batched two-view linear triangulation + the reference's gates, one thread per match.
+// `triangulate_points` (`src/modules/frontend.py:115-148`): cv2.triangulatePoints (DLT: right singular vector of
+// the smallest singular value of the 4 x 4 system below), X / w, depth and reprojection error in the SECOND view,
+// keep = depth > min_depth && err < max_reproj_err.  The SVD is a one-sided Jacobi (Hestenes) iteration on the
+// columns of A with V accumulated, all in registers.
+struct TriData {
+  int n;
+  double P1[12], P2[12];           // K [R | t] of the two views, row-major 3 x 4
+  const float2* uv1;
+  const float2* uv2;
+  double min_depth, max_err;
+  double* X;                       // n x 3
+  unsigned char* keep;             // n
+};
+
+__global__ void __launch_bounds__(128) triangulate_kernel(TriData d) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= d.n) return;
+  const float2 a = d.uv1[i], b = d.uv2[i];
+  double A[4][4], V[4][4];
+#pragma unroll
+  for (int c = 0; c < 4; ++c) {
+    A[0][c] = (double)a.x * d.P1[8 + c] - d.P1[c];
+    A[1][c] = (double)a.y * d.P1[8 + c] - d.P1[4 + c];
+    A[2][c] = (double)b.x * d.P2[8 + c] - d.P2[c];
+    A[3][c] = (double)b.y * d.P2[8 + c] - d.P2[4 + c];
+#pragma unroll
+    for (int r = 0; r < 4; ++r) V[r][c] = r == c ? 1.0 : 0.0;
+  }
+  for (int sweep = 0; sweep < 12; ++sweep) {
+#pragma unroll
+    for (int p = 0; p < 3; ++p)
+#pragma unroll
+      for (int q = p + 1; q < 4; ++q) {
+        double al = 0.0, be = 0.0, ga = 0.0;
+#pragma unroll
+        for (int r = 0; r < 4; ++r) { al = fma(A[r][p], A[r][p], al); be = fma(A[r][q], A[r][q], be); ga = fma(A[r][p], A[r][q], ga); }
+        if (fabs(ga) > 1e-300 + 1e-17 * sqrt(al * be)) {
+          const double zeta = (be - al) / (2.0 * ga);
+          const double t = (zeta >= 0.0 ? 1.0 : -1.0) / (fabs(zeta) + sqrt(1.0 + zeta * zeta));
+          const double c = 1.0 / sqrt(1.0 + t * t), s = c * t;
+#pragma unroll
+          for (int r = 0; r < 4; ++r) {
+            const double ap = A[r][p], aq = A[r][q], vp = V[r][p], vq = V[r][q];
+            A[r][p] = c * ap - s * aq; A[r][q] = s * ap + c * aq;
+            V[r][p] = c * vp - s * vq; V[r][q] = s * vp + c * vq;
+          }
+        }
+      }
+  }
+  double best = 0.0, v[4] = {0, 0, 0, 1};
+#pragma unroll
+  for (int c = 0; c < 4; ++c) {
+    double nrm = 0.0;
+#pragma unroll
+    for (int r = 0; r < 4; ++r) nrm = fma(A[r][c], A[r][c], nrm);
+    if (c == 0 || nrm < best) {
+      best = nrm;
+#pragma unroll
+      for (int r = 0; r < 4; ++r) v[r] = V[r][c];
+    }
+  }
+  const double X0 = v[0] / v[3], X1 = v[1] / v[3], X2 = v[2] / v[3];
+  const double h0 = fma(d.P2[0], X0, fma(d.P2[1], X1, fma(d.P2[2], X2, d.P2[3])));
+  const double h1 = fma(d.P2[4], X0, fma(d.P2[5], X1, fma(d.P2[6], X2, d.P2[7])));
+  const double h2 = fma(d.P2[8], X0, fma(d.P2[9], X1, fma(d.P2[10], X2, d.P2[11])));
+  const double e0 = h0 / h2 - (double)b.x, e1 = h1 / h2 - (double)b.y;
+  const double err = sqrt(e0 * e0 + e1 * e1);
+  d.X[3 * (size_t)i] = X0; d.X[3 * (size_t)i + 1] = X1; d.X[3 * (size_t)i + 2] = X2;
+  d.keep[i] = (h2 > d.min_depth && err < d.max_err) ? 1 : 0;    // NaN compares false: degenerate matches are dropped
+}
+}  // namespace
+
+int launch_triangulate(int n, const double* P1, const double* P2, const float2* uv1, const float2* uv2,
+                       double min_depth, double max_err, double* X, unsigned char* keep, cudaStream_t s) {
+  if (n <= 0) return 0;
+  TriData d;
+  d.n = n;
+  for (int k = 0; k < 12; ++k) { d.P1[k] = P1[k]; d.P2[k] = P2[k]; }
+  d.uv1 = uv1; d.uv2 = uv2; d.min_depth = min_depth; d.max_err = max_err; d.X = X; d.keep = keep;
+  triangulate_kernel<<<(n + 127) / 128, 128, 0, s>>>(d);
+  return (int)cudaGetLastError();
+}
+
 int launch_pose_lm(const PoseData& d, const Params& P, cudaStream_t s) {
   if (d.nb <= 0) return 0;
   pose_lm_kernel<<<d.nb, kPoseThreads, 0, s>>>(d, P);

@@ -21,4 +21,8 @@ struct PoseData {
 
 int launch_pose_lm(const PoseData& d, const Params& P, cudaStream_t s);
 
+// row f-3: two-view DLT triangulation + the reference's depth / reprojection gates (device arrays; P1, P2 on the host)
+int launch_triangulate(int n, const double* P1, const double* P2, const float2* uv1, const float2* uv2,
+                       double min_depth, double max_err, double* X, unsigned char* keep, cudaStream_t s);
+
 }  // namespace b2

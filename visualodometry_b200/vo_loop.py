@@ -78,6 +78,9 @@ class VOLoop:
         # NOT in the reference: optional motion-only BA after the PnP, a callable
         # (T_cw, X, uv) -> T_cw, e.g. `lambda T, X, uv: ba.refine_pose(T, X, uv)[0]`.  None = the reference's loop.
         self.pose_refiner = None
+        # NOT in the reference either: replacement of `triangulate`, same signature and return
+        # values, e.g. the CUDA kernel behind `BundleAdjuster.triangulate`.  None = cv2, as the reference does.
+        self.triangulator = None
 
     # ------------------------------------------------------------------ vo.py:49-250
     def process_frame(self, img) -> None:
@@ -177,8 +180,8 @@ class VOLoop:
         T_ref, T_cur = np.linalg.inv(self.keyframe["T_wc"]), np.linalg.inv(self.T_wc)
         fresh = curr_ids[curr_indices] == -1
         if np.sum(fresh) > 0:
-            X, keep = triangulate(T_ref, T_cur, _kp(self.keyframe["feats"])[ref_indices[fresh]],
-                                  _kp(curr_feats)[curr_indices[fresh]], self.K, self.cfg)
+            X, keep = (self.triangulator or triangulate)(T_ref, T_cur, _kp(self.keyframe["feats"])[ref_indices[fresh]],
+                                                         _kp(curr_feats)[curr_indices[fresh]], self.K, self.cfg)
             slots = curr_indices[fresh][keep]
             for j in range(len(X)):
                 # a keypoint matched twice gets the LAST id, and every id is stored (vo.py:277-284)
