@@ -691,6 +691,7 @@ __global__ void __launch_bounds__(kPcgThreads) large_pcg_kernel(LargeData d, int
   if (ctrl->stop || ctrl->step_bad) return;       // uniform across the grid
   extern __shared__ double psh[];                  // p (n doubles)
   __shared__ double red[kPcgThreads / 32][4];
+  __shared__ double rowred[kPcgThreads / 32][6];
   __shared__ double bcast[4];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int nwarp_cta = kPcgThreads / 32;
@@ -743,11 +744,13 @@ __global__ void __launch_bounds__(kPcgThreads) large_pcg_kernel(LargeData d, int
       // ---- phase A: p = z + beta p (whole vector, every CTA), q = S p on own rows, p.q
       for (int i = tid; i < n; i += kPcgThreads) psh[i] = d.z[i] + beta * psh[i];
       __syncthreads();
+      // one CTA per block row: its warps stride over the row's blocks (5 block slots per warp and step), so every
+      // warp of the grid has loads in flight even when there are fewer rows than warps (dense S: 1000 rows)
       double s_pq = 0.0;
-      for (int f = gwarp; f < nfree; f += nwarps) {
+      for (int f = blockIdx.x; f < nfree; f += gridDim.x) {
         double v = 0.0;
         if (lane < 30) {
-          for (int b = d.frow_ptr[f] + bl; b < d.frow_ptr[f + 1]; b += 5) {
+          for (int b = d.frow_ptr[f] + warp * 5 + bl; b < d.frow_ptr[f + 1]; b += 5 * nwarp_cta) {
             const int src = d.fsrc[b];
             const double* M = S + (size_t)(src & 0x7fffffff) * 36;
             const double* x = psh + 6 * d.fcol[b];
@@ -762,7 +765,16 @@ __global__ void __launch_bounds__(kPcgThreads) large_pcg_kernel(LargeData d, int
         }
         v += __shfl_down_sync(0xffffffffu, v, 6) + __shfl_down_sync(0xffffffffu, v, 12) +
              __shfl_down_sync(0xffffffffu, v, 18) + __shfl_down_sync(0xffffffffu, v, 24);
-        if (lane < 6) { d.q[6 * f + lane] = v; s_pq += v * psh[6 * f + lane]; }
+        if (lane < 6) rowred[warp][lane] = v;
+        __syncthreads();
+        if (warp == 0 && lane < 6) {
+          double t = 0.0;
+#pragma unroll
+          for (int w = 0; w < nwarp_cta; ++w) t += rowred[w][lane];    // fixed order
+          d.q[6 * f + lane] = t;
+          s_pq += t * psh[6 * f + lane];
+        }
+        __syncthreads();
       }
       s_pq = warp_sum(s_pq);
       if (lane == 0) red[warp][0] = s_pq;
