@@ -289,6 +289,8 @@ def main():
     ap.add_argument("--distinct", type=int, default=256, help="distinct geometries generated (set-up time bound)")
     ap.add_argument("--iters", type=int, default=None, help="LM iterations per step (10 windows, 20 C5)")
     ap.add_argument("--c5-mode", default="local", choices=["local", "random"])
+    ap.add_argument("--solver", default="auto", choices=["auto", "pcg", "dense"],
+                    help="C5: auto = banded Cholesky if S is block-banded else PCG; dense = blocked DMMA Cholesky")
     ap.add_argument("--cpu-windows", type=int, default=128)
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()
@@ -318,7 +320,7 @@ def main():
     loss = "huber" if args.workload == "c3" else "trivial"
     c5 = args.workload == "c5"
     ba = BundleAdjuster(K_of(b.intr), BAConfig(max_iters=args.iters, loss=loss, device=local,
-                                               solver="auto"))            # C5: banded Cholesky if S is block-banded, else PCG
+                                               solver=args.solver if c5 else "auto"))
     if c5 and world > 1:
         ba.init_distributed()
     offs = (None, None, None) if c5 else (b.cam_off, b.pt_off, b.obs_off)

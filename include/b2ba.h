@@ -30,7 +30,8 @@ enum { B2BA_OK = 0, B2BA_E_INVALID = -1, B2BA_E_CUDA = -2, B2BA_E_NCCL = -3, B2B
 /* solver outcomes (b2ba_summary.status; b2ba_solve returns the max over windows) */
 enum { B2BA_MAX_ITERS = 1, B2BA_CONVERGED = 2, B2BA_NUMERICAL_FAILURE = 3 };
 enum { B2BA_LOSS_TRIVIAL = 0, B2BA_LOSS_HUBER = 1 };
-enum { B2BA_SOLVER_AUTO = 0, B2BA_SOLVER_WINDOW = 1, B2BA_SOLVER_PCG = 2 };
+enum { B2BA_SOLVER_AUTO = 0, B2BA_SOLVER_WINDOW = 1, B2BA_SOLVER_PCG = 2,
+       B2BA_SOLVER_DENSE = 3 /* large path, dense blocked Cholesky of S on the FP64 tensor cores */ };
 enum { B2BA_MEM_HOST = 0, B2BA_MEM_DEVICE = 1 };
 
 /* Spec a0 parameters. Zero tolerances disable the test (parity / bench mode). */

@@ -130,3 +130,50 @@ def test_window_problem_on_large_path_matches_window_kernel():
     sb = b.solve()[0]; pb, xb = b.get()
     assert sa.accepted == sb.accepted and abs(sa.final_cost - sb.final_cost) <= 1e-7 * sa.final_cost
     assert np.abs(pa - pb).max() <= 1e-5
+
+
+@pytest.mark.parametrize("mode", ["0", "1", "2"])
+@pytest.mark.parametrize("visibility,nc,npts", [("random", 60, 4000), ("local", 60, 4000), ("random", 150, 12000),
+                                                ("random", 8, 400)])
+def test_dense_cholesky_step_matches_oracle_cholesky_step(oracle, monkeypatch, mode, visibility, nc, npts):
+    """one LM iteration with solver="dense" (blocked Cholesky, DMMA trailing updates, ba_dense.cu): delta_c
+    against the oracle's dense Cholesky.  Modes: 0 one update per 64-column panel, 1 two panels per trailing
+    update, 2 look-ahead on a second stream (the default).  Sizes cover n < 64 (one padded panel), n not a
+    multiple of 64, and several 128-column steps."""
+    monkeypatch.setenv("B2BA_DENSE_MODE", mode)
+    p = synth.make_large(5, n_cams=nc, n_pts=npts, mode=visibility)
+    from visualodometry_b200 import BAConfig, BundleAdjuster
+    ba = BundleAdjuster(K_of(p), BAConfig(solver="dense"))
+    ba.set_problem(p.poses, p.points, p.obs_cam, p.obs_pt, p.obs_uv, p.fixed_cam)
+    st = oracle.stage(p, mu=1e4, solver="chol")
+    n = st["S"].shape[0]
+    assert rel(ba.dump("S", (n, n)), st["S"]) <= 1e-11
+    assert rel(ba.dump("DC", (n,)), st["dc"]) <= 1e-9
+    ba.close()
+
+
+def test_lm_result_random_visibility_dense_cholesky(oracle):
+    """full LM trajectory on a dense reduced camera system: engine solver="dense" vs the oracle's dense Cholesky
+    (exact solves on both sides: tighter than the PCG comparison); reset + solve is bit-reproducible."""
+    p = synth.make_large(3, n_cams=200, n_pts=20000, mode="random")
+    from visualodometry_b200 import BAConfig, BundleAdjuster
+    ba = BundleAdjuster(K_of(p), BAConfig(max_iters=8, record_history=True, solver="dense"))
+    ba.set_problem(p.poses, p.points, p.obs_cam, p.obs_pt, p.obs_uv, p.fixed_cam)
+    sm = ba.solve()[0]
+    poses, pts = ba.get()
+    po, xo, so = oracle.solve(p, max_iters=8, solver="chol")
+    assert sm.pcg_iters == 0 and sm.iterations == so.iterations
+    ch = np.array([so.initial_cost] + list(so.cost_hist[:8]))
+    moving = np.concatenate([[True], (ch[:-1] - ch[1:])[:-1] > 1e-7 * ch[:-2]])
+    ha = ba.dump("HIST_ACCEPT", (1, 64), np.int32)[0, :8]
+    assert np.array_equal(ha[moving], np.array(so.accept_hist[:8])[moving])
+    assert rel(ba.dump("HIST_COST", (1, 64))[0, :8], np.array(so.cost_hist[:8])) <= 1e-9
+    r_gpu, r_cpu = synth.rmse_px(p, poses, pts), synth.rmse_px(p, po, xo)
+    assert abs(r_gpu - r_cpu) <= 1e-6 * r_cpu and r_gpu < 0.1 * synth.rmse_px(p)
+    assert np.abs(poses - po).max() <= 1e-5
+    assert (np.linalg.norm(pts - xo, axis=1) / np.maximum(1, np.linalg.norm(xo, axis=1))).max() <= 1e-5
+    ba.reset()
+    ba.solve()
+    poses2, pts2 = ba.get()
+    assert np.array_equal(poses, poses2) and np.array_equal(pts, pts2)
+    ba.close()

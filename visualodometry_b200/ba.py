@@ -34,7 +34,7 @@ class BAConfig:
     ftol: float = 0.0
     gtol: float = 0.0
     ptol: float = 0.0
-    solver: str = "auto"           # "auto" | "chol" (window kernel) | "pcg" (large path)
+    solver: str = "auto"           # "auto" | "chol" (window kernel) | "pcg" | "dense" (large path: PCG / dense DMMA Cholesky)
     pcg_max_iters: int = 200
     pcg_tol: float = 1e-10
     device: int = 0
@@ -44,7 +44,7 @@ class BAConfig:
     def to_options(self) -> _lib.Options:
         return _lib.Options(self.max_iters, {"trivial": 0, "huber": 1}[self.loss], self.loss_scale,
                             self.z_min, self.init_radius, self.ftol, self.gtol, self.ptol,
-                            {"auto": 0, "chol": 1, "pcg": 2}[self.solver], self.pcg_max_iters,
+                            {"auto": 0, "chol": 1, "pcg": 2, "dense": 3}[self.solver], self.pcg_max_iters,
                             self.pcg_tol, (1 if self.record_history else 0) | (0 if self.cluster else 2), 0)
 
 

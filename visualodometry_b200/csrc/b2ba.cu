@@ -49,7 +49,9 @@ struct b2ba {
   LargeIndex lix;
   DevBuf<ObsRec> l_cm;
   DevBuf<int> l_cam_ptr;
-  DevBuf<double> l_poses_tri, l_lin_part, l_lin, l_Dc, l_Sg, l_dc, l_r, l_z, l_q, l_Minv, l_part, l_sums, l_band, l_binv, l_band_ws, l_zbuf;
+  DevBuf<double> l_poses_tri, l_lin_part, l_lin, l_Dc, l_Sg, l_dc, l_r, l_z, l_q, l_Minv, l_part, l_sums, l_band, l_binv, l_band_ws, l_zbuf, l_dense, l_dense_winv, l_dense_x;
+  DevBuf<int> l_dense_flags;
+  int l_dense_ld = 0;
   // motion-only BA (b2ba_refine_poses): own buffers, independent of the problem set with b2ba_set_problem
   DevBuf<long long> r_off;
   DevBuf<double> r_poses, r_pts, r_hist_cost, r_hist_mu;
@@ -197,6 +199,8 @@ LargeData make_large(b2ba* h, bool hist) {
     d.pair_lanes = per < 10 ? 1 : per < 48 ? 8 : 32;
   }
   d.bw = h->l_bw; d.band = h->l_band.p; d.binv = h->l_binv.p; d.band_P = h->l_band_P; d.band_ws = h->l_band_ws.p;
+  d.dense = h->l_dense_ld ? h->l_dense.p : nullptr; d.dense_ld = h->l_dense_ld; d.dense_winv = h->l_dense_winv.p;
+  d.dense_x = h->l_dense_x.p; d.dense_flags = h->l_dense_flags.p;
   d.sums_part = h->l_sums.p; d.ctrl = h->l_ctrl.p; d.summary = h->d_summ.p;
   d.hist_cost = hist ? h->d_hist_cost.p : nullptr; d.hist_mu = hist ? h->d_hist_mu.p : nullptr;
   d.hist_accept = hist ? h->d_hist_accept.p : nullptr;
@@ -235,7 +239,15 @@ int setup_large(b2ba* h) {
   // solver choice on the large path: S block-banded (half-bandwidth <= kBandMaxBw camera blocks) -> exact banded
   // Cholesky, unless PCG was asked for explicitly; otherwise block-Jacobi PCG
   h->l_bw = -1;
-  if (h->opt.solver != B2BA_SOLVER_PCG && h->lix.nfree > 0) {
+  h->l_dense_ld = 0;
+  if (h->opt.solver == B2BA_SOLVER_DENSE && h->lix.nfree > 0) {
+    if ((int)n > large_dense_max_n()) return fail(h, B2BA_E_UNSUPPORTED, "dense Cholesky: too many free cameras for one resident CTA per 64-block");
+    const int npad = large_dense_npad((int)n);
+    CU(h->l_dense.alloc(large_dense_count((int)n)), "alloc"); CU(h->l_dense_winv.alloc((size_t)npad * 64), "alloc");
+    CU(h->l_dense_x.alloc(npad), "alloc"); CU(h->l_dense_flags.alloc(npad / 64), "alloc");
+    CU(cudaMemset(h->l_dense_flags.p, 0, (size_t)(npad / 64) * sizeof(int)), "memset");
+    h->l_dense_ld = npad;
+  } else if (h->opt.solver != B2BA_SOLVER_PCG && h->lix.nfree > 0) {
     std::vector<int> bp(h->lix.nfree + 1), bc(h->lix.nblk);
     CU(cudaMemcpy(bp.data(), h->lix.blk_ptr.p, bp.size() * 4, cudaMemcpyDeviceToHost), "read structure");
     CU(cudaMemcpy(bc.data(), h->lix.blk_col.p, bc.size() * 4, cudaMemcpyDeviceToHost), "read structure");
@@ -391,7 +403,7 @@ int b2ba_set_problem_batch(b2ba_t* h, int32_t B, const int32_t* cam_off, const i
   }
   // a8: index.  The window kernels walk the landmarks of a window by decreasing observation count and want the
   // point-major stream in that order; the large path keeps the canonical order (by landmark id).
-  const bool want_pcg = h->opt.solver == B2BA_SOLVER_PCG;
+  const bool want_pcg = h->opt.solver == B2BA_SOLVER_PCG || h->opt.solver == B2BA_SOLVER_DENSE;   // = the large path
   h->sched_order = !want_pcg && h->max_nc <= kMaxCam && h->max_nfree <= kBigMaxFree && np > 0;
   IndexOut io{h->d_pm.p, h->d_pt_ptr.p, h->d_cm.p, h->d_cam_ptr.p, h->d_flags.p, h->sched_order ? h->d_sched.p : nullptr};
   int rc = build_index(make_index_in(h), io, nullptr);

@@ -1060,7 +1060,9 @@ int large_iteration(const LargeData& d, const Params& P, int pcg_max_iters, doub
     }
   }
   if (ar && (rc = ar(ar_user, d.Sg, d.Sg, d.sg_count(), s)) != 0) return rc;
-  if (d.bw >= 0) {
+  if (d.dense) {
+    if ((rc = large_dense_solve(d, s)) != 0) return rc;
+  } else if (d.bw >= 0) {
     if ((rc = large_band_solve(d, s)) != 0) return rc;
   } else {
     int blocks = 0;

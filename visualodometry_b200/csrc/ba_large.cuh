@@ -60,6 +60,11 @@ struct LargeData {
   double* binv;                    // nfree x 6: 1 / diag(L)
   int band_P;                      // interiors factored concurrently (1 = sequential), see ba_band.cu
   double* band_ws;                 // right-hand sides, Gram blocks and the separator system (large_band_ws_count)
+  double* dense;                   // dense Cholesky (ba_dense.cu): (dense_ld + 64) x dense_ld lower matrix + rhs rows, else null
+  int dense_ld;                    // n rounded up to the 64-column panel width
+  double* dense_winv;              // dense_ld / 64 inverse diagonal factors (64 x 64 each)
+  double* dense_x;                 // dense_ld solution blocks published by the backward pass
+  int* dense_flags;                // dense_ld / 64 publication flags (epoch numbers)
   double* part;                    // partial-sum scratch (grid partials)
   double* sums_part;               // 8 local partial sums (before the allreduce)
   LargeCtrl* ctrl;
@@ -98,6 +103,11 @@ size_t large_band_smem(int bw);
 int large_band_chunks(int N, int bw);                 // interiors factored concurrently (1 = sequential)
 size_t large_band_ws_count(int N, int bw, int P);     // doubles of workspace
 int large_band_solve(const LargeData& d, cudaStream_t s);
+// exact dense blocked Cholesky with DMMA trailing updates (ba_dense.cu); needs d.dense
+int large_dense_npad(int n);
+size_t large_dense_count(int n);                      // doubles of matrix storage
+int large_dense_max_n();                              // one resident CTA per 64-block in the backward pass
+int large_dense_solve(const LargeData& d, cudaStream_t s);
 constexpr int kBandMaxBw = 22;     // (bw+4) x (bw+1) blocks of shared memory: 26 x 23 x 288 B = 172 KB
 constexpr int kBandParMaxBw = 6;   // substructured solve: 1 + 12 bw right-hand sides per block column in the ring
 
