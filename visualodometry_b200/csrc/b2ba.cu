@@ -246,6 +246,7 @@ int setup_large(b2ba* h) {
     CU(h->l_dense.alloc(large_dense_count((int)n)), "alloc"); CU(h->l_dense_winv.alloc((size_t)npad * 64), "alloc");
     CU(h->l_dense_x.alloc(npad), "alloc"); CU(h->l_dense_flags.alloc(npad / 64), "alloc");
     CU(cudaMemset(h->l_dense_flags.p, 0, (size_t)(npad / 64) * sizeof(int)), "memset");
+    CU(cudaMemset(h->l_dense.p, 0, large_dense_count((int)n) * sizeof(double)), "memset");   // rhs rows 1.. stay zero
     h->l_dense_ld = npad;
   } else if (h->opt.solver != B2BA_SOLVER_PCG && h->lix.nfree > 0) {
     std::vector<int> bp(h->lix.nfree + 1), bc(h->lix.nblk);

@@ -11,8 +11,8 @@
 //              through a cp.async double buffer, C loaded straight into the DMMA accumulators.
 //              Two panels (K = 128) are folded into one trailing update; the 64-column strip between them gets
 //              its own narrow update.
-//   look-ahead the strip of the trailing update the next panels need runs on the main stream, the rest of the
-//              update on a second stream under the next panels.
+//   look-ahead the panel chain (panels and the strips of the trailing update the next panels need) runs on a
+//              high-priority stream, the bulk of every trailing update on the caller's stream underneath it.
 //   backward   L^T x = y: one CTA per 64-block, resident together (cooperative launch); block k publishes x_k
 //              through a release/acquire flag, block j < k folds L[k][j]^T x_k into its y_j (the L block
 //              prefetched by cp.async one step ahead) and ends with x_j = L_jj^-T y_j.
@@ -26,6 +26,7 @@ namespace {
 constexpr int NB = 64;            // panel width
 constexpr int LDL = NB + 1;       // shared-memory leading dimension of the panel matrices
 constexpr int PT = 256;           // panel threads
+constexpr int RPC = 64;           // rows per panel CTA (one row per thread in the triangular solve)
 constexpr int TL = 128;           // update tile
 constexpr int KC = 32;            // update K chunk
 constexpr int LDK = KC + 4;       // == 4 mod 16: conflict-free DMMA fragment loads
@@ -141,20 +142,26 @@ __device__ bool potrf64(double (*L)[LDL], double* invd, int tid) {
   return ok;
 }
 
-// blockIdx.x < nrb: rows [row_begin + 64 b, +64) of columns [c0, c0 + 64) := A21 L11^-T;  blockIdx.x == nrb: L11^-1
+// blockIdx.x < nrb: rows [row_begin + RPC b, + RPC) of columns [c0, c0 + 64) := A21 L11^-T;  blockIdx.x == nrb: L11^-1.
+// Every CTA factors the diagonal block itself (a latency-bound chain: repeating it costs no time and saves a
+// launch boundary); RPC rows per CTA keep the number of SMs the chain takes away from the bulk update small.
 __global__ void __launch_bounds__(PT) dense_panel_kernel(LargeCtrl* ctrl, double* A, int ld, int c0, int row_begin,
-                                                         int nrb, double* winv) {
+                                                         int row_end, int nrb, double* winv) {
   if (ctrl->stop || ctrl->step_bad) return;
   extern __shared__ __align__(16) double psm[];
   double (*L)[LDL] = reinterpret_cast<double (*)[LDL]>(psm);
-  double (*X)[LDL] = reinterpret_cast<double (*)[LDL]>(psm + NB * LDL);
-  double* invd = psm + 2 * NB * LDL;
+  double* invd = psm + NB * LDL;
+  double (*X)[LDL] = reinterpret_cast<double (*)[LDL]>(psm + NB * LDL + NB);
   const int tid = threadIdx.x;
   const bool inverse = (int)blockIdx.x == nrb;
-  const size_t row0 = (size_t)row_begin + (size_t)blockIdx.x * NB;
+  const size_t row0 = (size_t)row_begin + (size_t)blockIdx.x * RPC;
+  const int rows = inverse ? NB : min(RPC, row_end - (int)row0);
   for (int q = tid; q < NB * NB; q += PT) {
     const int r = q >> 6, c = q & 63;
     L[r][c] = c <= r ? A[(size_t)(c0 + r) * ld + c0 + c] : 0.0;
+  }
+  for (int q = tid; q < rows * NB; q += PT) {
+    const int r = q >> 6, c = q & 63;
     X[r][c] = inverse ? (r == c ? 1.0 : 0.0) : A[(row0 + r) * ld + c0 + c];
   }
   __syncthreads();
@@ -163,7 +170,7 @@ __global__ void __launch_bounds__(PT) dense_panel_kernel(LargeCtrl* ctrl, double
     if (tid == 0) ctrl->step_bad = 1;
     return;
   }
-  if (tid < NB) {                            // x L^T = a, right-looking, the row in registers
+  if (tid < rows) {                          // x L^T = a, right-looking, the row in registers
     double a[NB];
 #pragma unroll
     for (int c = 0; c < NB; ++c) a[c] = X[tid][c];
@@ -183,13 +190,13 @@ __global__ void __launch_bounds__(PT) dense_panel_kernel(LargeCtrl* ctrl, double
       winv[q] = X[r][m];
     }
   } else {
-    for (int q = tid; q < NB * NB; q += PT) {
+    for (int q = tid; q < rows * NB; q += PT) {
       const int r = q >> 6, c = q & 63;
       A[(row0 + r) * ld + c0 + c] = X[r][c];
     }
   }
 }
-constexpr size_t kPanelSmem = (2 * NB * LDL + NB) * sizeof(double);
+constexpr size_t kPanelSmem = (NB * LDL + NB + RPC * LDL) * sizeof(double);
 
 // ---------------------------------------------------------------- trailing update (DMMA)
 struct UpdArgs {
@@ -341,8 +348,8 @@ constexpr size_t kBackwardSmem = (size_t)(3 * NB * NB + 2 * NB + 4 * NB) * sizeo
 
 struct DenseRt {               // per-process launch state (one device per process)
   bool ready = false;
-  cudaStream_t side = nullptr;
-  cudaEvent_t ev_fork = nullptr, ev_panel[2] = {nullptr, nullptr}, ev_rest[2] = {nullptr, nullptr};
+  cudaStream_t chain = nullptr;                   // high priority: the panel chain runs ahead of the bulk updates
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_panel[2] = {nullptr, nullptr}, ev_rest[2] = {nullptr, nullptr};
   int epoch = 0;
   int sms = 0;
 };
@@ -356,8 +363,8 @@ int dense_runtime() {
   if (e != cudaSuccess) return (int)e;
   int lo = 0, hi = 0, dev = 0;
   cudaDeviceGetStreamPriorityRange(&lo, &hi);
-  if ((e = cudaStreamCreateWithPriority(&g_rt.side, cudaStreamNonBlocking, lo)) != cudaSuccess) return (int)e;
-  cudaEvent_t* evs[] = {&g_rt.ev_fork, &g_rt.ev_panel[0], &g_rt.ev_panel[1], &g_rt.ev_rest[0], &g_rt.ev_rest[1]};
+  if ((e = cudaStreamCreateWithPriority(&g_rt.chain, cudaStreamNonBlocking, hi)) != cudaSuccess) return (int)e;   // hi = greatest priority
+  cudaEvent_t* evs[] = {&g_rt.ev_fork, &g_rt.ev_join, &g_rt.ev_panel[0], &g_rt.ev_panel[1], &g_rt.ev_rest[0], &g_rt.ev_rest[1]};
   for (cudaEvent_t* ev : evs)
     if ((e = cudaEventCreateWithFlags(ev, cudaEventDisableTiming)) != cudaSuccess) return (int)e;
   cudaGetDevice(&dev);
@@ -375,8 +382,8 @@ void launch_update(const LargeData& d, int i_begin, int j_begin, int j_end, int 
 }
 
 void launch_panel(const LargeData& d, int c0, cudaStream_t st) {
-  const int row_begin = c0 + NB, nrb = (d.dense_ld + NB - row_begin) / NB;
-  dense_panel_kernel<<<nrb + 1, PT, kPanelSmem, st>>>(d.ctrl, d.dense, d.dense_ld, c0, row_begin, nrb,
+  const int row_begin = c0 + NB, row_end = d.dense_ld + NB, nrb = (row_end - row_begin + RPC - 1) / RPC;
+  dense_panel_kernel<<<nrb + 1, PT, kPanelSmem, st>>>(d.ctrl, d.dense, d.dense_ld, c0, row_begin, row_end, nrb,
                                                       d.dense_winv + (size_t)(c0 / NB) * NB * NB);
 }
 
@@ -392,7 +399,7 @@ int large_dense_max_n() {
 }
 
 // mode (B2BA_DENSE_MODE): 0 = one update per 64-column panel; 1 = two panels per trailing update (K = 128);
-// 2 (default) = 1 + look-ahead on a second stream
+// 2 (default) = 1 + look-ahead: panel chain on a high-priority stream
 int large_dense_solve(const LargeData& d, cudaStream_t st) {
   int rc = dense_runtime();
   if (rc) return rc;
@@ -407,37 +414,40 @@ int large_dense_solve(const LargeData& d, cudaStream_t st) {
     }
   } else {
     const bool ahead = mode >= 2;
-    cudaStream_t side = ahead ? g_rt.side : st;
+    cudaStream_t cs = ahead ? g_rt.chain : st;  // the panel chain; the bulk updates stay on the caller's stream
     if (ahead) {
       cudaEventRecord(g_rt.ev_fork, st);
-      cudaStreamWaitEvent(side, g_rt.ev_fork, 0);
+      cudaStreamWaitEvent(cs, g_rt.ev_fork, 0);
     }
-    int step = 0, pending = -1;                 // pending: event index of the last side-stream update
+    int step = 0, pending = -1;                 // pending: event index of the last bulk update
     for (int c0 = 0; c0 < npad; c0 += 2 * NB, ++step) {
-      launch_panel(d, c0, st);
+      launch_panel(d, c0, cs);
       if (c0 + NB >= npad) break;
-      launch_update(d, c0 + NB, c0 + NB, c0 + 2 * NB, c0, NB, st);       // the strip the second panel needs
-      launch_panel(d, c0 + NB, st);
+      launch_update(d, c0 + NB, c0 + NB, c0 + 2 * NB, c0, NB, cs);       // the strip the second panel needs
+      launch_panel(d, c0 + NB, cs);
       const int t0 = c0 + 2 * NB;
       if (t0 >= npad) break;
       if (!ahead) {
         launch_update(d, t0, t0, npad, c0, 2 * NB, st);
         continue;
       }
-      // columns [t0, t0 + 128) feed the next two panels: main stream; the rest runs under them on the side stream
+      // columns [t0, t0 + 128) feed the next two panels: chain stream; the rest runs under them on the caller's
       const int t1 = t0 + 2 * NB < npad ? t0 + 2 * NB : npad;
-      cudaEventRecord(g_rt.ev_panel[step & 1], st);
-      if (pending >= 0) cudaStreamWaitEvent(st, g_rt.ev_rest[pending], 0);   // the previous rest wrote these columns
+      cudaEventRecord(g_rt.ev_panel[step & 1], cs);
+      if (pending >= 0) cudaStreamWaitEvent(cs, g_rt.ev_rest[pending], 0);   // the previous bulk update wrote these columns
       pending = -1;
-      launch_update(d, t0, t0, t1, c0, 2 * NB, st);
+      launch_update(d, t0, t0, t1, c0, 2 * NB, cs);
       if (t1 < npad) {
-        cudaStreamWaitEvent(side, g_rt.ev_panel[step & 1], 0);
-        launch_update(d, t1, t1, npad, c0, 2 * NB, side);
-        cudaEventRecord(g_rt.ev_rest[step & 1], side);
+        cudaStreamWaitEvent(st, g_rt.ev_panel[step & 1], 0);
+        launch_update(d, t1, t1, npad, c0, 2 * NB, st);
+        cudaEventRecord(g_rt.ev_rest[step & 1], st);
         pending = step & 1;
       }
     }
-    if (pending >= 0) cudaStreamWaitEvent(st, g_rt.ev_rest[pending], 0);
+    if (ahead) {
+      cudaEventRecord(g_rt.ev_join, cs);
+      cudaStreamWaitEvent(st, g_rt.ev_join, 0);
+    }
   }
   {
     const double* A = d.dense;
