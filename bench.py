@@ -136,10 +136,20 @@ def run_c2(args, impl):
     seq = vo_synth.SynthSequence(n_frames=args.frames, seed=0)
     cfg = BAConfig(window=10, max_iters=args.iters, loss="huber", loss_scale=2.0)
 
-    def one_run(kind):
+    def one_run(kind, gpu_tracker=False):
         cv2.setRNGSeed(0)
-        vo = vo_loop.VOLoop(seq.K, vo_loop.LoopConfig(), vo_synth.SynthFrontend(seq))
+        lcfg = vo_loop.LoopConfig()
+        vo = vo_loop.VOLoop(seq.K, lcfg, vo_synth.SynthFrontend(seq))
         ad, t_ba, n_obs = None, [0.0], [0]
+        if gpu_tracker:
+            # SURVEY 8 row f-2 widened: the tracker's cv2.solvePnPRansac call (vo.py:135-141) replaced by the
+            # sampling-free GPU tracker (b2ba_track_pose) started from the previous pose
+            from visualodometry_b200 import BundleAdjuster
+            trk = BundleAdjuster(seq.K, BAConfig())
+            if gpu_tracker == "ransac":      # b2ba_ransac_pose: 1024 hypotheses per frame, sampled consensus
+                vo.pnp_solver = lambda X, uv, T: trk.ransac_pose(T, X, uv, lcfg.pnp_reproj_err, n_hyp=1024, seed=vo.frame_id)[:3]
+            else:                            # b2ba_track_pose: graduated robust refinement from the previous pose
+                vo.pnp_solver = lambda X, uv, T: trk.track_pose(T, X, uv, lcfg.pnp_reproj_err)[:3]
         if kind != "none":
             if kind == "gpu":
                 from visualodometry_b200 import BundleAdjuster
@@ -165,6 +175,7 @@ def run_c2(args, impl):
         nkf = len([s_ for s_ in ad.summaries if s_ is not None]) if ad else 0
         ate = vo_synth.ate_sim3(np.array(vo.trajectory), seq.T_wc[-len(vo.trajectory):, :3, 3]) if len(vo.trajectory) > 10 else None
         return {"fps": seq.n_frames / dt, "s": dt, "ba_s": t_ba[0], "ba_calls": nkf, "ba_obs_iters": n_obs[0],
+                "pnp_fallbacks_to_ransac": vo.pnp_fallbacks if gpu_tracker else None,
                 "frames_since_last_reset": len(vo.trajectory), "ate_sim3_m": ate}
 
     plain = one_run("none")
@@ -173,6 +184,8 @@ def run_c2(args, impl):
     else:
         one_run("gpu")                       # warm-up (module load, allocations)
         r = one_run("gpu")
+        r_trk = one_run("gpu", gpu_tracker="track")
+        r_rsc = one_run("gpu", gpu_tracker="ransac")
     name = (f"C2: end-to-end VO, synthetic KITTI-05-shaped sequence ({args.frames} frames, 1241x376 K, <=2048 keypoints "
             f"per frame, 5% wrong matches), 10-keyframe window BA ({args.iters} LM iterations, Huber) once per keyframe")
     out = {"metric": "VO frames/sec", "value": r["fps"], "unit": "frames/s", "n_gpus": 1, "steps": 1, "warmup": 1,
@@ -182,6 +195,10 @@ def run_c2(args, impl):
                   "ba_ms_per_keyframe": 1e3 * r["ba_s"] / max(1, r["ba_calls"]),
                   "ba_obs_iters_per_s": r["ba_obs_iters"] / r["ba_s"] if r["ba_s"] > 0 else None},
            "e2e": {"value": r["fps"], "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    if impl != "reference":
+        # the same loop with the PnP-RANSAC of the tracker on the GPU as well (not the pinned loop: reported beside it)
+        out["vo"]["with_ba_and_gpu_tracker"] = r_trk
+        out["vo"]["with_ba_and_gpu_ransac"] = r_rsc
     if impl == "reference":
         from oracle import ba_cpu
         out["impl"] = "reference"

@@ -114,6 +114,35 @@ int b2ba_triangulate(b2ba_t* h, int32_t N, const double P1[12], const double P2[
 int b2ba_refine_poses(b2ba_t* h, int32_t B, const int64_t* obs_off, double* poses_cw, const double* points,
                       const float* obs_uv, const double intr[4], int32_t max_iters, b2ba_summary* summaries, int mem);
 
+/* Robust pose tracking against FIXED landmarks from a pose prior: the GPU stand-in for the reference's
+ * cv2.solvePnPRansac(X, uv, K, None, reprojectionError = pnp_reproj_err) call (src/modules/vo.py:131-150, config.py:35)
+ * once the tracker has a previous pose.  `rounds` rounds of [motion-only LM on the current inlier set, Huber with
+ * a = thr_r (the last of several rounds: trivial loss) -> every observation re-classified: inlier = depth >=
+ * z_min and |reprojection error| < thr_r], thr_r = reproj_err * 2^(rounds - 2 - r) >= reproj_err (graduated; 6 rounds:
+ * 16, 8, 4, 2, 1, 1 x reproj_err), which ends the way OpenCV's RANSAC does (consensus set by that threshold, pose
+ * refined on it); no random sampling, so the result is deterministic.  pose_cw: 12 doubles [R | t], in (prior) /
+ * out; points N x 3, obs_uv N x 2 float32; inliers: N bytes out; n_inliers (HOST) out.  pose / points / uv / inliers
+ * HOST or DEVICE per `mem`.  Damping rule and stopping tests as b2ba_solve (the handle's options).  Returns the status of
+ * the last round (>0) or an error (<0); fewer than 6 inliers after a round ends the call (the caller resets, as the
+ * reference does when solvePnPRansac fails, vo.py:142-143). */
+int b2ba_track_pose(b2ba_t* h, int64_t N, double* pose_cw, const double* points, const float* obs_uv,
+                    const double intr[4], double reproj_err, int32_t rounds, int32_t iters_per_round,
+                    uint8_t* inliers, int32_t* n_inliers, b2ba_summary* summary, int mem);
+
+/* Sampled-consensus pose from 2D-3D matches: the GPU counterpart of the reference's
+ * cv2.solvePnPRansac(X, uv, K, None, reprojectionError = pnp_reproj_err) call (src/modules/vo.py:135-141) for a tracker
+ * that has a previous pose.  n_hyp hypotheses are evaluated at once: hypothesis j = the motion-only LM fit (hyp_iters
+ * iterations, started from the prior pose_cw) of 4 distinct observations picked by a stateless hash of (seed, j);
+ * every hypothesis is scored by its consensus (depth >= z_min and |reprojection error| < reproj_err over ALL N
+ * observations); the largest consensus wins (ties: the lowest j) and is refined like OpenCV's RANSAC ends -- LM on the
+ * consensus set, here two rounds (Huber a = reproj_err, then trivial loss; refine_iters iterations each) with the set
+ * re-classified after each.  Deterministic for a given seed.  best_consensus (HOST, may be NULL): the winning
+ * hypothesis's count before refinement; the other arguments as b2ba_track_pose.  N < 6: status 3, no inliers. */
+int b2ba_ransac_pose(b2ba_t* h, int64_t N, double* pose_cw, const double* points, const float* obs_uv,
+                     const double intr[4], double reproj_err, int32_t n_hyp, int32_t hyp_iters, uint64_t seed,
+                     int32_t refine_iters, uint8_t* inliers, int32_t* n_inliers, int32_t* best_consensus,
+                     b2ba_summary* summary, int mem);
+
 /* Pipelined end-to-end batch solve (BASELINE config 4): set_problem_batch + solve + get in one call, with the
  * windows cut into `chunks` (<= 0: 8) contiguous chunks whose host->device copies, index build + solve and
  * device->host read-back overlap on three streams.  HOST buffers only (pinned memory makes the copies

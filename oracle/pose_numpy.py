@@ -153,3 +153,96 @@ def refine_pose(T_cw, X, uv, intr, max_iters=10, loss="trivial", loss_scale=1.0,
     out = np.eye(4)
     out[:3, :3], out[:3, 3] = R, t
     return out, sm
+
+
+def track_pose(T_cw_prior, X, uv, intr, reproj_err=1.0, rounds=6, iters_per_round=10, z_min=1e-3, init_mu=1e4):
+    """CPU restatement of `b2ba_track_pose` (include/b2ba.h): the stand-in for the reference's
+    `cv2.solvePnPRansac(X, uv, K, None, reprojectionError=pnp_reproj_err)` (`src/modules/vo.py:135-141`) when a pose
+    prior exists.  `rounds` x [`refine_pose` on the current inliers (Huber a = thr_r; last of several rounds:
+    trivial loss) -> re-classify EVERY observation: inlier = z >= z_min and |reprojection error| < thr_r], with the
+    graduated threshold thr_r = reproj_err * 2^(rounds - 2 - r) >= reproj_err (6 rounds: 16, 8, 4, 2, 1, 1).
+    Returns (ok, T_cw, inlier indices, PoseSummary of the last round).  PINNED to the reference's call in
+    tests/test_pose.py::test_oracle_tracker_matches_solvepnpransac (same inlier set, pose to the RANSAC refinement's
+    own tolerance)."""
+    T = np.asarray(T_cw_prior, np.float64).copy()
+    X = np.asarray(X, np.float64).reshape(-1, 3)
+    uv = np.asarray(uv, np.float32).reshape(-1, 2)
+    mask = np.ones(len(X), bool)
+    sm = None
+    for r in range(rounds):
+        loss = "trivial" if (rounds > 1 and r == rounds - 1) else "huber"
+        thr = reproj_err * float(1 << max(0, rounds - 2 - r))
+        T, sm = refine_pose(T, X[mask], uv[mask], intr, max_iters=iters_per_round, loss=loss, loss_scale=thr,
+                            z_min=z_min, init_mu=init_mu)
+        _, _, res, _, rho, valid = _terms(T[:3, :3], T[:3, 3], X, uv, intr, z_min, "trivial", 1.0)
+        mask = valid & (rho < thr * thr)
+        if mask.sum() < 6:
+            break
+    ok = bool(mask.sum() >= 6 and np.isfinite(T).all())
+    return ok, T, np.flatnonzero(mask), sm
+
+
+def _splitmix64(x):
+    """x: uint64 array -> uint64 array (wrapping arithmetic), the hash `b2ba_ransac_pose` samples with."""
+    x = np.asarray(x, np.uint64)
+    with np.errstate(over="ignore"):
+        x = x + np.uint64(0x9E3779B97F4A7C15)
+        x = (x ^ (x >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
+        x = (x ^ (x >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
+        return x ^ (x >> np.uint64(31))
+
+
+def ransac_samples(n, n_hyp, seed, k=4):
+    """the (n_hyp, k) observation indices `b2ba_ransac_pose` draws: hash(seed + j*k + q) mod n, collisions moved on."""
+    with np.errstate(over="ignore"):
+        base = np.uint64(seed) + np.arange(n_hyp * k, dtype=np.uint64)
+    idx = (_splitmix64(base) % np.uint64(n)).astype(np.int64).reshape(n_hyp, k)
+    for j in range(n_hyp):
+        for q in range(k):
+            i = int(idx[j, q])
+            again = True
+            while again:
+                again = False
+                for p in range(q):
+                    if idx[j, p] == i:
+                        i = (i + 1) % n
+                        again = True
+            idx[j, q] = i
+    return idx
+
+
+def ransac_pose(T_cw_prior, X, uv, intr, reproj_err=1.0, n_hyp=1024, hyp_iters=8, seed=0, refine_iters=10, z_min=1e-3):
+    """CPU restatement of `b2ba_ransac_pose` (include/b2ba.h), the GPU counterpart of the reference's
+    `cv2.solvePnPRansac` call (`src/modules/vo.py:135-141`): hypotheses = LM fits of 4 sampled matches from the prior,
+    consensus = z >= z_min and |reprojection error| < reproj_err over all matches, best consensus (lowest index on ties)
+    refined by two rounds of LM on the consensus set (Huber, then trivial) with re-classification.
+    Returns (ok, T_cw, inlier indices, PoseSummary, winning consensus)."""
+    T0 = np.asarray(T_cw_prior, np.float64)
+    X = np.asarray(X, np.float64).reshape(-1, 3)
+    uv = np.asarray(uv, np.float32).reshape(-1, 2)
+    n = len(X)
+    if n < 6:
+        return False, T0.copy(), np.zeros(0, np.int64), None, 0
+    idx = ransac_samples(n, n_hyp, seed)
+    best, best_T = -1, T0
+    for j in range(n_hyp):
+        T, sm = refine_pose(T0, X[idx[j]], uv[idx[j]], intr, max_iters=hyp_iters, z_min=z_min)
+        c = 0
+        if sm.status != 3 and np.isfinite(T).all():
+            _, _, _, _, rho, valid = _terms(T[:3, :3], T[:3, 3], X, uv, intr, z_min, "trivial", 1.0)
+            c = int((valid & (rho < reproj_err * reproj_err)).sum())
+        if c > best:
+            best, best_T = c, T
+    T = best_T
+    _, _, _, _, rho, valid = _terms(T[:3, :3], T[:3, 3], X, uv, intr, z_min, "trivial", 1.0)
+    mask = valid & (rho < reproj_err * reproj_err)
+    sm = None
+    for r in range(2):
+        T, sm = refine_pose(T, X[mask], uv[mask], intr, max_iters=refine_iters, loss="huber" if r == 0 else "trivial",
+                            loss_scale=reproj_err, z_min=z_min)
+        _, _, _, _, rho, valid = _terms(T[:3, :3], T[:3, 3], X, uv, intr, z_min, "trivial", 1.0)
+        mask = valid & (rho < reproj_err * reproj_err)
+        if mask.sum() < 6:
+            break
+    ok = bool(mask.sum() >= 6 and np.isfinite(T).all())
+    return ok, T, np.flatnonzero(mask), sm, best

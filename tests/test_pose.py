@@ -83,6 +83,64 @@ def _engine(**kw):
     return BundleAdjuster(K, BAConfig(**kw))
 
 
+def _ransac(X, uv, thr):
+    import cv2
+    K = np.array([[KITTI[0], 0, KITTI[2]], [0, KITTI[1], KITTI[3]], [0, 0, 1.0]])
+    cv2.setRNGSeed(0)
+    ok, rvec, tvec, inl = cv2.solvePnPRansac(X, uv.astype(np.float64), K, None, reprojectionError=thr)
+    T = np.eye(4)
+    T[:3, :3], T[:3, 3] = cv2.Rodrigues(rvec)[0], tvec.flatten()
+    return ok, T, inl.flatten()
+
+
+@pytest.mark.parametrize("seed,outliers,thr", [(20, 0.05, 1.0), (21, 0.15, 2.0), (22, 0.0, 1.0)])
+def test_oracle_tracker_matches_solvepnpransac(seed, outliers, thr):
+    """the reference's tracker call, `cv2.solvePnPRansac(X, uv, K, None, reprojectionError=thr)` (`vo.py:135-141`),
+    against the sampling-free tracker started from a perturbed pose.  OpenCV reports the consensus set of its best
+    MINIMAL-sample model (before its final refinement), which is a subset of the set a refined pose reaches: the
+    tracker's set must contain it (up to observations on the threshold), hold about every true inlier, and the two
+    poses agree to the accuracy of RANSAC's own final refinement."""
+    T_gt, T0, X, uv = make_pose_problem(seed, n=600, noise=0.3, outliers=outliers, rot=0.03, trans=0.8)
+    ok_r, T_r, inl_r = _ransac(X, uv, thr)
+    ok, T, inl, sm = pose_numpy.track_pose(T0, X, uv, KITTI, reproj_err=thr)
+    assert ok and ok_r
+    a, b = set(inl.tolist()), set(inl_r.tolist())
+    assert len(b - a) <= 0.02 * len(b) and len(a) >= 0.97 * (1 - outliers) * len(X) and len(a) >= len(b)
+    assert pose_err(T, T_r) < 5e-3 and pose_err(T, T_gt) < 2e-2
+    # on its own consensus set the tracker's pose is the minimiser: the RANSAC pose does not have a lower cost
+    cost = lambda T_: float((pose_numpy._terms(T_[:3, :3], T_[:3, 3], X[inl], uv[inl], KITTI, 1e-3, "trivial", 1.0)[4]).sum())
+    assert cost(T) <= cost(T_r) * (1 + 1e-9)
+
+
+def test_oracle_tracker_reports_failure_without_consensus():
+    rng = np.random.default_rng(5)
+    T_gt, T0, X, uv = make_pose_problem(23, n=200)
+    uv = rng.uniform(0, 1000, uv.shape).astype(np.float32)         # no geometry at all
+    ok, T, inl, sm = pose_numpy.track_pose(T0, X, uv, KITTI, reproj_err=1.0)
+    assert not ok and len(inl) < 6
+
+
+def test_oracle_ransac_samples_are_distinct_and_reproducible():
+    idx = pose_numpy.ransac_samples(37, 500, seed=3)
+    assert idx.shape == (500, 4) and idx.min() >= 0 and idx.max() < 37
+    assert all(len(set(r)) == 4 for r in idx.tolist())
+    assert np.array_equal(idx, pose_numpy.ransac_samples(37, 500, seed=3))
+    assert not np.array_equal(idx, pose_numpy.ransac_samples(37, 500, seed=4))
+    assert int(pose_numpy._splitmix64(np.array([0], np.uint64))[0]) == 0xE220A8397B1DCDAF    # splitmix64's first output
+
+
+def test_oracle_ransac_matches_solvepnpransac_with_many_outliers():
+    """40 % wrong matches and a poor prior: the sampled-consensus restatement finds the consensus set the reference's
+    cv2.solvePnPRansac call finds (and the rest of the true inliers), and the same pose."""
+    T_gt, T0, X, uv = make_pose_problem(40, n=400, noise=0.3, outliers=0.4, rot=0.05, trans=1.5)
+    ok_r, T_r, inl_r = _ransac(X, uv, 1.0)
+    ok, T, inl, sm, best = pose_numpy.ransac_pose(T0, X, uv, KITTI, reproj_err=1.0, n_hyp=128)
+    assert ok and ok_r and best >= 0.5 * len(inl)
+    a, b = set(inl.tolist()), set(inl_r.tolist())
+    assert len(b - a) <= 0.02 * len(b) and len(a) >= len(b) and len(a) >= 0.9 * 0.6 * len(X)
+    assert pose_err(T, T_r) < 1e-2 and pose_err(T, T_gt) < 2e-2
+
+
 @pytest.mark.gpu
 @pytest.mark.parametrize("loss", ["trivial", "huber"])
 def test_refine_poses_matches_oracle_ragged_batch(loss):
@@ -156,4 +214,105 @@ def test_vo_loop_with_pose_refiner_tracks_at_least_as_well():
     assert n1 == n0 == seq.n_frames and len(log) > 100
     assert all(f <= i * (1 + 1e-12) and st in (1, 2) for i, f, st in log)
     assert ate1 <= 1.5 * ate0 + 0.05
+    ba.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("seed,n,outliers,thr,behind", [(30, 600, 0.05, 1.0, 0), (31, 2048, 0.2, 2.0, 7), (32, 40, 0.0, 1.0, 0),
+                                                       (33, 300, 0.1, 1.0, 0)])
+def test_track_pose_matches_oracle_and_ransac(seed, n, outliers, thr, behind):
+    """b2ba_track_pose against its numpy restatement (same inlier set bit for bit, pose 1e-8) and against the
+    reference's own call, cv2.solvePnPRansac, on the same problem."""
+    T_gt, T0, X, uv = make_pose_problem(seed, n=n, noise=0.3, outliers=outliers, behind=behind, rot=0.03, trans=0.8)
+    ba = _engine()
+    ok, T, inl, sm = ba.track_pose(T0, X, uv, reproj_err=thr)
+    ok_o, T_o, inl_o, sm_o = pose_numpy.track_pose(T0, X, uv, KITTI, reproj_err=thr)
+    assert ok and ok_o and np.array_equal(inl, inl_o)
+    assert pose_err(T, T_o) <= 1e-8 and abs(sm.final_cost - sm_o.final_cost) <= 1e-9 * max(1.0, sm_o.final_cost)
+    ok_r, T_r, inl_r = _ransac(X, uv, thr)
+    assert ok_r and len(set(inl_r.tolist()) - set(inl.tolist())) <= max(2, 0.02 * len(inl_r)) and len(inl) >= len(inl_r)
+    assert pose_err(T, T_r) < 1e-2
+    ba.close()
+
+
+@pytest.mark.gpu
+def test_track_pose_device_arrays_failure_and_empty():
+    import torch
+    T_gt, T0, X, uv = make_pose_problem(34, n=500, outliers=0.1)
+    ba = _engine()
+    ok_h, T_h, inl_h, _ = ba.track_pose(T0, X, uv, reproj_err=1.0)
+    ok_d, T_d, inl_d, _ = ba.track_pose(T0, torch.as_tensor(X).cuda(), torch.as_tensor(uv).cuda(), reproj_err=1.0)
+    assert ok_h and ok_d and np.array_equal(T_h, T_d) and np.array_equal(inl_h, inl_d)
+    rng = np.random.default_rng(5)
+    ok, _, inl, _ = ba.track_pose(T0, X, rng.uniform(0, 1000, uv.shape).astype(np.float32), reproj_err=1.0)
+    assert not ok and len(inl) < 6
+    ok, T, inl, _ = ba.track_pose(T0, np.empty((0, 3)), np.empty((0, 2), np.float32))
+    assert not ok and len(inl) == 0 and np.allclose(T, T0)
+    with pytest.raises(RuntimeError):
+        ba.track_pose(T0, X, uv, reproj_err=0.0)
+    ba.close()
+
+
+@pytest.mark.gpu
+def test_vo_loop_with_gpu_tracker_follows_the_reference_loop():
+    """VOLoop.pnp_solver = the GPU tracker instead of cv2.solvePnPRansac: the loop runs every frame without a reset
+    and the trajectory is as close to ground truth as the reference loop's."""
+    import cv2
+    from visualodometry_b200 import vo_loop, vo_synth
+    seq = vo_synth.SynthSequence(n_frames=150, seed=0)
+    ba = _engine()
+    cfg = vo_loop.LoopConfig()
+
+    def run(gpu):
+        cv2.setRNGSeed(0)
+        vo = vo_loop.VOLoop(seq.K, cfg, vo_synth.SynthFrontend(seq))
+        if gpu == "track":
+            vo.pnp_solver = lambda X, uv, T: ba.track_pose(T, X, uv, cfg.pnp_reproj_err)[:3]
+        elif gpu == "ransac":
+            vo.pnp_solver = lambda X, uv, T: ba.ransac_pose(T, X, uv, cfg.pnp_reproj_err)[:3]
+        for i in range(seq.n_frames):
+            vo.process_frame(seq.image(i))
+        tr = np.array(vo.trajectory)
+        return vo_synth.ate_sim3(tr, seq.T_wc[-len(tr):, :3, 3]), len(tr)
+    ate0, n0 = run(None)
+    for kind in ("track", "ransac"):
+        ate1, n1 = run(kind)
+        assert n1 == n0 == seq.n_frames, kind
+        assert ate1 <= 1.5 * ate0 + 0.05, (kind, ate1, ate0)
+    ba.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("seed,n,outliers,thr,n_hyp", [(50, 400, 0.4, 1.0, 128), (51, 1500, 0.6, 2.0, 256), (52, 60, 0.1, 1.0, 64)])
+def test_ransac_pose_matches_oracle_and_solvepnpransac(seed, n, outliers, thr, n_hyp):
+    """b2ba_ransac_pose against its numpy restatement (same samples, same winning consensus, same inlier set, pose
+    1e-8) and against the reference's cv2.solvePnPRansac call on the same matches."""
+    T_gt, T0, X, uv = make_pose_problem(seed, n=n, noise=0.3, outliers=outliers, rot=0.05, trans=1.5)
+    ba = _engine()
+    ok, T, inl, sm, best = ba.ransac_pose(T0, X, uv, reproj_err=thr, n_hyp=n_hyp, seed=7)
+    ok_o, T_o, inl_o, sm_o, best_o = pose_numpy.ransac_pose(T0, X, uv, KITTI, reproj_err=thr, n_hyp=n_hyp, seed=7)
+    assert ok and ok_o and best == best_o and np.array_equal(inl, inl_o)
+    assert pose_err(T, T_o) <= 1e-8
+    ok2, T2, inl2, _, best2 = ba.ransac_pose(T0, X, uv, reproj_err=thr, n_hyp=n_hyp, seed=7)
+    assert np.array_equal(T, T2) and np.array_equal(inl, inl2) and best == best2      # deterministic for a seed
+    ok_r, T_r, inl_r = _ransac(X, uv, thr)
+    assert ok_r and len(set(inl_r.tolist()) - set(inl.tolist())) <= max(2, 0.02 * len(inl_r)) and len(inl) >= len(inl_r)
+    # OpenCV draws at most 100 minimal samples: at 60 % wrong matches its pose is the looser one; the bar is ground truth
+    assert pose_err(T, T_gt) < 3e-2 and pose_err(T, T_gt) <= pose_err(T_r, T_gt) + 1e-2
+    if outliers <= 0.4:
+        assert pose_err(T, T_r) < 1e-2
+    ba.close()
+
+
+@pytest.mark.gpu
+def test_ransac_pose_edge_cases():
+    T_gt, T0, X, uv = make_pose_problem(53, n=300, outliers=0.2)
+    ba = _engine()
+    ok, T, inl, sm, best = ba.ransac_pose(T0, X[:5], uv[:5])                      # fewer than 6 matches
+    assert not ok and len(inl) == 0 and sm.status == 3
+    rng = np.random.default_rng(1)
+    ok, _, inl, _, best = ba.ransac_pose(T0, X, rng.uniform(0, 1000, uv.shape).astype(np.float32), n_hyp=64)
+    assert best < 12 and (not ok or len(inl) < 12)                                # no geometry: no consensus
+    with pytest.raises(RuntimeError):
+        ba.ransac_pose(T0, X, uv, n_hyp=0)
     ba.close()

@@ -320,6 +320,61 @@ class BundleAdjuster:
         T, sm = self.refine_poses(np.asarray(T_cw, np.float64).reshape(1, 4, 4), points, obs_uv, None, max_iters)
         return T[0], sm[0]
 
+    def track_pose(self, T_cw_prior, points, obs_uv, reproj_err=1.0, rounds=6, iters_per_round=10):
+        """Robust pose tracking from a prior: the GPU stand-in for the reference's
+        `cv2.solvePnPRansac(X, uv, K, None, reprojectionError=pnp_reproj_err)` (`vo.py:135-141`, `config.py:35`) once the
+        tracker has a previous pose.  `rounds` x [motion-only LM on the current inliers (Huber a = thr_r; last
+        round: trivial loss) -> re-classify every observation by |reprojection error| < thr_r], thr_r = reproj_err x
+        2^(rounds - 2 - r) >= reproj_err (graduated: 16, 8, 4, 2, 1, 1 for 6 rounds).  Deterministic
+        (no sampling).  Returns (ok, T_cw (4,4), inliers (n,) int -- indices like solvePnPRansac's, BASummary);
+        ok is False when fewer than 6 inliers remain or the pose is not finite (the caller resets, `vo.py:142-143`)."""
+        dev = any(_is_cuda_tensor(a) for a in (points, obs_uv))
+        pose = poses_from_T(np.asarray(T_cw_prior, np.float64).reshape(1, 4, 4))
+        a_pts, a_uv = _Arg(points, np.float64, "float64", dev), _Arg(obs_uv, np.float32, "float32", dev)
+        n = int(np.prod(a_pts.keep.shape)) // 3
+        if int(np.prod(a_uv.keep.shape)) != 2 * n:
+            raise ValueError("track_pose: points (N,3) and obs_uv (N,2) required")
+        a_pose = _Arg(pose, np.float64, "float64", dev)
+        a_inl = _Arg(np.zeros(max(n, 1), np.uint8), np.uint8, "uint8", dev)
+        cnt, sm = C.c_int32(0), _lib.Summary()
+        rc = self._lib.b2ba_track_pose(self._h, n, a_pose.ptr, a_pts.ptr, a_uv.ptr,
+                                       self.intr.ctypes.data_as(C.POINTER(C.c_double)), float(reproj_err), int(rounds),
+                                       int(iters_per_round), a_inl.ptr, C.byref(cnt), C.byref(sm),
+                                       _lib.MEM_DEVICE if dev else _lib.MEM_HOST)
+        self._check(rc, "b2ba_track_pose")
+        out = a_pose.keep.cpu().numpy() if dev else a_pose.keep
+        mask = (a_inl.keep.cpu().numpy() if dev else a_inl.keep)[:n]
+        T = T_from_poses(out)[0]
+        inl = np.flatnonzero(mask)
+        ok = bool(cnt.value >= 6 and np.isfinite(T).all())
+        return ok, T, inl, self._summary(sm)
+
+    def ransac_pose(self, T_cw_prior, points, obs_uv, reproj_err=1.0, n_hyp=1024, hyp_iters=8, seed=0, refine_iters=10):
+        """Sampled-consensus pose on the GPU: the counterpart of the reference's
+        `cv2.solvePnPRansac(X, uv, K, None, reprojectionError=pnp_reproj_err)` (`vo.py:135-141`) for a tracker with a
+        previous pose.  `n_hyp` hypotheses at once (each the LM fit of 4 hashed-sampled matches from the prior), scored
+        by consensus over all matches, the best one refined on its consensus set (include/b2ba.h b2ba_ransac_pose).
+        Returns (ok, T_cw (4,4), inlier indices, BASummary, consensus of the winning hypothesis)."""
+        dev = any(_is_cuda_tensor(a) for a in (points, obs_uv))
+        pose = poses_from_T(np.asarray(T_cw_prior, np.float64).reshape(1, 4, 4))
+        a_pts, a_uv = _Arg(points, np.float64, "float64", dev), _Arg(obs_uv, np.float32, "float32", dev)
+        n = int(np.prod(a_pts.keep.shape)) // 3
+        if int(np.prod(a_uv.keep.shape)) != 2 * n:
+            raise ValueError("ransac_pose: points (N,3) and obs_uv (N,2) required")
+        a_pose = _Arg(pose, np.float64, "float64", dev)
+        a_inl = _Arg(np.zeros(max(n, 1), np.uint8), np.uint8, "uint8", dev)
+        cnt, best, sm = C.c_int32(0), C.c_int32(0), _lib.Summary()
+        rc = self._lib.b2ba_ransac_pose(self._h, n, a_pose.ptr, a_pts.ptr, a_uv.ptr,
+                                        self.intr.ctypes.data_as(C.POINTER(C.c_double)), float(reproj_err), int(n_hyp),
+                                        int(hyp_iters), int(seed), int(refine_iters), a_inl.ptr, C.byref(cnt),
+                                        C.byref(best), C.byref(sm), _lib.MEM_DEVICE if dev else _lib.MEM_HOST)
+        self._check(rc, "b2ba_ransac_pose")
+        out = a_pose.keep.cpu().numpy() if dev else a_pose.keep
+        mask = (a_inl.keep.cpu().numpy() if dev else a_inl.keep)[:n]
+        T = T_from_poses(out)[0]
+        ok = bool(cnt.value >= 6 and np.isfinite(T).all())
+        return ok, T, np.flatnonzero(mask), self._summary(sm), int(best.value)
+
     def optimize_batch(self, batch, out=None, chunks=0) -> BAResult:
         """C4: a synth.BABatch-like object with CSR offsets; poses in (Nc,12) layout.  Host arrays go through the
         pipelined C-ABI call (copies of one chunk of windows overlap the solve of another); `out=(poses, points)`

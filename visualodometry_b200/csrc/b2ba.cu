@@ -57,7 +57,12 @@ struct b2ba {
   DevBuf<double> r_poses, r_pts, r_hist_cost, r_hist_mu;
   DevBuf<float2> r_uv;
   DevBuf<b2ba_summary> r_summ;
-  DevBuf<int> r_hist_accept;
+  DevBuf<int> r_hist_accept, r_cnt, q_idx, q_score, q_best;
+  DevBuf<double> q_pts, q_poses;
+  DevBuf<float2> q_uv;
+  DevBuf<long long> q_off;
+  DevBuf<b2ba_summary> q_summ;
+  DevBuf<unsigned char> r_mask;
   int r_nb = 0;
   bool sched_order = false;   // pm / pt_ptr laid out in landmark-schedule order (window path), else canonical
   int l_band_P = 1;  // interiors of the substructured banded solve (1 = sequential)
@@ -625,6 +630,102 @@ int b2ba_refine_poses(b2ba_t* h, int32_t B, const int64_t* obs_off, double* pose
     if (sm[b].status > worst) worst = sm[b].status;
   }
   return worst;
+}
+
+int b2ba_track_pose(b2ba_t* h, int64_t N, double* pose_cw, const double* points, const float* obs_uv,
+                    const double intr[4], double reproj_err, int32_t rounds, int32_t iters_per_round,
+                    uint8_t* inliers, int32_t* n_inliers, b2ba_summary* summary, int mem) {
+  if (!h) return B2BA_E_INVALID;
+  if (N < 0 || !pose_cw || !intr || !n_inliers || (N > 0 && (!points || !obs_uv || !inliers)))
+    return fail(h, B2BA_E_INVALID, "track_pose: null argument");
+  if (!(reproj_err > 0.0) || rounds < 1) return fail(h, B2BA_E_INVALID, "track_pose: reproj_err > 0 and rounds >= 1 required");
+  CU(cudaSetDevice(h->device), "cudaSetDevice");
+  const cudaMemcpyKind ki = in_kind(mem), ko = out_kind(mem);
+  cudaStream_t s = nullptr;
+  const size_t no = (size_t)N;
+  const long long off[2] = {0, (long long)N};
+  CU(h->r_off.alloc(2), "alloc"); CU(h->r_poses.alloc(12), "alloc"); CU(h->r_summ.alloc(1), "alloc");
+  CU(h->r_pts.alloc(no * 3), "alloc"); CU(h->r_uv.alloc(no), "alloc"); CU(h->r_mask.alloc(no), "alloc"); CU(h->r_cnt.alloc(1), "alloc");
+  CU(cudaMemcpyAsync(h->r_off.p, off, sizeof(off), cudaMemcpyHostToDevice, s), "copy offsets");
+  CU(cudaMemcpyAsync(h->r_poses.p, pose_cw, 12 * sizeof(double), ki, s), "copy pose");
+  if (no) {
+    CU(cudaMemcpyAsync(h->r_pts.p, points, no * 3 * sizeof(double), ki, s), "copy points");
+    CU(cudaMemcpyAsync(h->r_uv.p, obs_uv, no * sizeof(float2), ki, s), "copy uv");
+    CU(cudaMemsetAsync(h->r_mask.p, 1, no, s), "memset");
+  }
+  CU(cudaMemsetAsync(h->r_cnt.p, 0, sizeof(int), s), "memset");
+  PoseData d{};
+  d.nb = 1; d.obs_off = h->r_off.p; d.poses = h->r_poses.p; d.points = h->r_pts.p; d.obs_uv = h->r_uv.p;
+  d.summaries = h->r_summ.p;
+  Params P = make_params(h, iters_per_round);
+  P.fx = intr[0]; P.fy = intr[1]; P.cx = intr[2]; P.cy = intr[3];
+  const int rc = launch_pose_track(d, P, reproj_err, rounds, h->r_mask.p, h->r_cnt.p, s);
+  if (rc) return cuda_fail(h, (cudaError_t)rc, "pose_track_kernel");
+  CU(cudaMemcpyAsync(pose_cw, h->r_poses.p, 12 * sizeof(double), ko, s), "read pose");
+  if (no) CU(cudaMemcpyAsync(inliers, h->r_mask.p, no, ko, s), "read inliers");
+  b2ba_summary sm;
+  int cnt = 0;
+  CU(cudaMemcpyAsync(&sm, h->r_summ.p, sizeof(sm), cudaMemcpyDeviceToHost, s), "read summary");
+  CU(cudaMemcpyAsync(&cnt, h->r_cnt.p, sizeof(int), cudaMemcpyDeviceToHost, s), "read count");
+  CU(cudaStreamSynchronize(s), "track_pose");
+  *n_inliers = cnt;
+  if (summary) *summary = sm;
+  return sm.status;
+}
+
+int b2ba_ransac_pose(b2ba_t* h, int64_t N, double* pose_cw, const double* points, const float* obs_uv,
+                     const double intr[4], double reproj_err, int32_t n_hyp, int32_t hyp_iters, uint64_t seed,
+                     int32_t refine_iters, uint8_t* inliers, int32_t* n_inliers, int32_t* best_consensus,
+                     b2ba_summary* summary, int mem) {
+  if (!h) return B2BA_E_INVALID;
+  if (N < 0 || !pose_cw || !intr || !n_inliers || (N > 0 && (!points || !obs_uv || !inliers)))
+    return fail(h, B2BA_E_INVALID, "ransac_pose: null argument");
+  if (!(reproj_err > 0.0) || n_hyp < 1 || hyp_iters < 1) return fail(h, B2BA_E_INVALID, "ransac_pose: reproj_err > 0, n_hyp >= 1, hyp_iters >= 1 required");
+  *n_inliers = 0;
+  if (best_consensus) *best_consensus = 0;
+  if (N < 6) {                                   // nothing to vote on: the caller treats it as a failure
+    if (summary) { std::memset(summary, 0, sizeof(*summary)); summary->status = B2BA_NUMERICAL_FAILURE; }
+    if (N > 0 && mem == B2BA_MEM_HOST) std::memset(inliers, 0, (size_t)N);
+    return B2BA_NUMERICAL_FAILURE;
+  }
+  CU(cudaSetDevice(h->device), "cudaSetDevice");
+  const cudaMemcpyKind ki = in_kind(mem), ko = out_kind(mem);
+  cudaStream_t s = nullptr;
+  const size_t no = (size_t)N, nh = (size_t)n_hyp;
+  const long long off[2] = {0, (long long)N};
+  CU(h->r_off.alloc(2), "alloc"); CU(h->r_poses.alloc(12), "alloc"); CU(h->r_summ.alloc(1), "alloc");
+  CU(h->r_pts.alloc(no * 3), "alloc"); CU(h->r_uv.alloc(no), "alloc"); CU(h->r_mask.alloc(no), "alloc"); CU(h->r_cnt.alloc(1), "alloc");
+  CU(h->q_pts.alloc(nh * kRansacSample * 3), "alloc"); CU(h->q_uv.alloc(nh * kRansacSample), "alloc");
+  CU(h->q_poses.alloc(nh * 12), "alloc"); CU(h->q_off.alloc(nh + 1), "alloc"); CU(h->q_idx.alloc(nh * kRansacSample), "alloc");
+  CU(h->q_summ.alloc(nh), "alloc"); CU(h->q_score.alloc(nh), "alloc"); CU(h->q_best.alloc(2), "alloc");
+  CU(cudaMemcpyAsync(h->r_off.p, off, sizeof(off), cudaMemcpyHostToDevice, s), "copy offsets");
+  CU(cudaMemcpyAsync(h->r_poses.p, pose_cw, 12 * sizeof(double), ki, s), "copy pose");
+  CU(cudaMemcpyAsync(h->r_pts.p, points, no * 3 * sizeof(double), ki, s), "copy points");
+  CU(cudaMemcpyAsync(h->r_uv.p, obs_uv, no * sizeof(float2), ki, s), "copy uv");
+  CU(cudaMemsetAsync(h->r_cnt.p, 0, sizeof(int), s), "memset");
+  PoseData d{};
+  d.nb = 1; d.obs_off = h->r_off.p; d.poses = h->r_poses.p; d.points = h->r_pts.p; d.obs_uv = h->r_uv.p;
+  d.summaries = h->r_summ.p;
+  Params P = make_params(h, refine_iters);
+  P.fx = intr[0]; P.fy = intr[1]; P.cx = intr[2]; P.cy = intr[3];
+  RansacData r{n_hyp, hyp_iters, (long long)N, (unsigned long long)seed, h->q_pts.p, h->q_uv.p, h->q_poses.p, h->q_off.p,
+               h->q_idx.p, h->q_summ.p, h->q_score.p, h->q_best.p};
+  int rc = launch_pose_ransac(r, d, P, reproj_err, s);
+  if (rc) return cuda_fail(h, (cudaError_t)rc, "pose ransac kernels");
+  rc = launch_pose_track(d, P, reproj_err, 2, h->r_mask.p, h->r_cnt.p, s, 1);
+  if (rc) return cuda_fail(h, (cudaError_t)rc, "pose_track_kernel");
+  CU(cudaMemcpyAsync(pose_cw, h->r_poses.p, 12 * sizeof(double), ko, s), "read pose");
+  CU(cudaMemcpyAsync(inliers, h->r_mask.p, no, ko, s), "read inliers");
+  b2ba_summary sm;
+  int cnt = 0, best[2] = {0, 0};
+  CU(cudaMemcpyAsync(&sm, h->r_summ.p, sizeof(sm), cudaMemcpyDeviceToHost, s), "read summary");
+  CU(cudaMemcpyAsync(&cnt, h->r_cnt.p, sizeof(int), cudaMemcpyDeviceToHost, s), "read count");
+  CU(cudaMemcpyAsync(best, h->q_best.p, sizeof(best), cudaMemcpyDeviceToHost, s), "read best");
+  CU(cudaStreamSynchronize(s), "ransac_pose");
+  *n_inliers = cnt;
+  if (best_consensus) *best_consensus = best[1];
+  if (summary) *summary = sm;
+  return sm.status;
 }
 
 // Pipelined batch solve (C4 end to end): the windows are cut into `chunks` contiguous chunks; chunk i's host->device

@@ -37,10 +37,11 @@ __device__ __forceinline__ void cta_sum(double* v, double* red, double* out) {
   __syncthreads();
 }
 
-__global__ void __launch_bounds__(kPoseThreads) pose_lm_kernel(PoseData d, Params P) {
+// the LM loop of problem b by one CTA; mask (per observation, or null) switches observations off
+__device__ void pose_lm_run(const PoseData& d, const Params& P, int b, const unsigned char* __restrict__ mask) {
   __shared__ double red[kPoseWarps * kNV], lin[kNV], tri[2], pose[12], ptri[12], dl[8];
   __shared__ int ctl[2];
-  const int b = blockIdx.x, tid = threadIdx.x;
+  const int tid = threadIdx.x;
   const long long o0 = d.obs_off[b], o1 = d.obs_off[b + 1];
   if (tid < 12) pose[tid] = d.poses[12 * (size_t)b + tid];
   __syncthreads();
@@ -56,6 +57,7 @@ __global__ void __launch_bounds__(kPoseThreads) pose_lm_kernel(PoseData d, Param
 #pragma unroll
       for (int k = 0; k < kNV; ++k) v[k] = 0.0;
       for (long long i = o0 + tid; i < o1; i += kPoseThreads) {
+        if (mask != nullptr && !mask[i]) continue;
         const double* X = d.points + 3 * (size_t)i;
         const float2 uv = d.obs_uv[i];
         Proj o;
@@ -123,6 +125,7 @@ __global__ void __launch_bounds__(kPoseThreads) pose_lm_kernel(PoseData d, Param
     double tv[2] = {0.0, 0.0};
     if (step_ok) {
       for (long long i = o0 + tid; i < o1; i += kPoseThreads) {
+        if (mask != nullptr && !mask[i]) continue;
         const double* X = d.points + 3 * (size_t)i;
         const float2 uv = d.obs_uv[i];
         Proj o;
@@ -180,6 +183,145 @@ __global__ void __launch_bounds__(kPoseThreads) pose_lm_kernel(PoseData d, Param
     s.initial_cost = initial_cost; s.final_cost = cost; s.final_mu = mu;
     d.summaries[b] = s;
   }
+  __syncthreads();                                     // the shared state may be reused by another run
+}
+
+__global__ void __launch_bounds__(kPoseThreads) pose_lm_kernel(PoseData d, Params P) {
+  pose_lm_run(d, P, blockIdx.x, nullptr);
+}
+
+// Robust pose tracking: the GPU stand-in for the cv2.solvePnPRansac call of the reference's tracker
+// (`src/modules/vo.py:131-150`) when a pose prior exists (the previous frame's pose).  `rounds` rounds of
+//   motion-only LM on the current inlier set (Huber with a = thr_r; the last of several rounds: trivial loss)
+//   -> every observation re-classified: inlier = in front of the camera and |reprojection error| < thr_r
+// with thr_r = thr x 2^(rounds - 2 - r) >= thr (graduated: the last two rounds run at thr itself)
+// (thr = the reference's `pnp_reproj_err`, `config.py:35`; OpenCV's RANSAC ends the same way: its consensus set is
+// |error| < reprojectionError and the pose is refined on it).  One CTA; mask = the inlier flags (in: all ones).
+__global__ void __launch_bounds__(kPoseThreads) pose_track_kernel(PoseData d, Params P, double thr, int rounds,
+                                                                  unsigned char* mask, int* n_inliers, int classify_first) {
+  __shared__ double cred[kPoseWarps], cnt[1];
+  __shared__ double cpose[12];
+  const int tid = threadIdx.x;
+  const long long o0 = d.obs_off[0], o1 = d.obs_off[1];
+  Params C = P;                                         // classification: plain pixel error
+  C.loss = 0;
+  if (classify_first) {                                 // the consensus set of the input pose (a RANSAC hypothesis) at thr
+    if (tid < 12) cpose[tid] = d.poses[tid];
+    __syncthreads();
+    for (long long i = o0 + tid; i < o1; i += kPoseThreads) {
+      const double* X = d.points + 3 * (size_t)i;
+      const float2 uv = d.obs_uv[i];
+      Proj o;
+      project(C, cpose, X[0], X[1], X[2], uv.x, uv.y, o);
+      mask[i] = (o.valid && o.rho < thr * thr) ? 1 : 0;
+    }
+    __syncthreads();
+  }
+  for (int r = 0; r < rounds; ++r) {
+    // graduated threshold: thr x 2^(rounds - 2 - r), at least thr (6 rounds: 16, 8, 4, 2, 1, 1) -- the wide rounds pull
+    // the pose into the dominant consensus, the narrow ones select it
+    const int sh = classify_first ? 0 : rounds - 2 - r;
+    const double tr = sh > 0 ? thr * (double)(1 << (sh > 20 ? 20 : sh)) : thr;
+    Params Q = P;
+    Q.loss = (rounds > 1 && r == rounds - 1) ? 0 : 1;
+    Q.huber_a = tr;
+    pose_lm_run(d, Q, 0, mask);
+    if (tid < 12) cpose[tid] = d.poses[tid];            // written by the same threads at the end of the run
+    __syncthreads();
+    double c[1] = {0.0};
+    for (long long i = o0 + tid; i < o1; i += kPoseThreads) {
+      const double* X = d.points + 3 * (size_t)i;
+      const float2 uv = d.obs_uv[i];
+      Proj o;
+      project(C, cpose, X[0], X[1], X[2], uv.x, uv.y, o);
+      const bool in = o.valid && o.rho < tr * tr;
+      mask[i] = in ? 1 : 0;
+      c[0] += in ? 1.0 : 0.0;
+    }
+    cta_sum<1>(c, cred, cnt);
+    const int n = (int)cnt[0];
+    if (tid == 0) *n_inliers = n;
+    __syncthreads();
+    if (n < 6) break;                                   // nothing left to fit: the caller treats it as a failure
+  }
+}
+
+// ---- sampled consensus (GPU RANSAC) around the pose LM: hypotheses from minimal samples, scored on all observations
+__host__ __device__ inline unsigned long long splitmix64(unsigned long long x) {
+  x += 0x9E3779B97F4A7C15ull;
+  x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
+  x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+  return x ^ (x >> 31);
+}
+
+// hypothesis j: kSample distinct observations (stateless hash of (seed, j, k); a collision moves on to the next index),
+// gathered into problem j of a pose batch that starts from the prior
+__global__ void ransac_sample_kernel(int nh, long long n, unsigned long long seed, const double* __restrict__ points,
+                                     const float2* __restrict__ uv, const double* __restrict__ prior,
+                                     double* hp_pts, float2* hp_uv, double* hp_poses, long long* hp_off, int* hp_idx) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j > nh) return;
+  if (j == nh) { hp_off[nh] = (long long)nh * kRansacSample; return; }
+  hp_off[j] = (long long)j * kRansacSample;
+  long long pick[kRansacSample];
+  for (int k = 0; k < kRansacSample; ++k) {
+    long long i = (long long)(splitmix64(seed + (unsigned long long)j * kRansacSample + k) % (unsigned long long)n);
+    for (bool again = true; again;) {
+      again = false;
+      for (int q = 0; q < k; ++q) if (pick[q] == i) { i = (i + 1) % n; again = true; }
+    }
+    pick[k] = i;
+    const size_t o = (size_t)j * kRansacSample + k;
+    hp_pts[3 * o] = points[3 * i]; hp_pts[3 * o + 1] = points[3 * i + 1]; hp_pts[3 * o + 2] = points[3 * i + 2];
+    hp_uv[o] = uv[i];
+    hp_idx[o] = (int)i;
+  }
+  for (int k = 0; k < 12; ++k) hp_poses[12 * (size_t)j + k] = prior[k];
+}
+
+// consensus of hypothesis blockIdx.x: observations in front of the camera with |reprojection error| < thr
+__global__ void __launch_bounds__(kPoseThreads) ransac_score_kernel(long long n, const double* __restrict__ points,
+                                                                    const float2* __restrict__ uv, const double* __restrict__ hp_poses,
+                                                                    const b2ba_summary* __restrict__ hp_summ, Params P,
+                                                                    double thr, int* score) {
+  __shared__ double pose[12];
+  __shared__ int red[kPoseWarps];
+  const int j = blockIdx.x, tid = threadIdx.x;
+  if (tid < 12) pose[tid] = hp_poses[12 * (size_t)j + tid];
+  __syncthreads();
+  bool fin = true;
+  for (int k = 0; k < 12; ++k) fin = fin && isfinite(pose[k]);
+  int c = 0;
+  if (fin && hp_summ[j].status != B2BA_NUMERICAL_FAILURE) {
+    Params C = P;
+    C.loss = 0;
+    for (long long i = tid; i < n; i += kPoseThreads) {
+      Proj o;
+      project(C, pose, points[3 * i], points[3 * i + 1], points[3 * i + 2], uv[i].x, uv[i].y, o);
+      c += (o.valid && o.rho < thr * thr) ? 1 : 0;
+    }
+  }
+  c = __reduce_add_sync(0xffffffffu, c);
+  if ((tid & 31) == 0) red[tid >> 5] = c;
+  __syncthreads();
+  if (tid == 0) { int t = 0; for (int w = 0; w < kPoseWarps; ++w) t += red[w]; score[j] = t; }
+}
+
+// the hypothesis with the largest consensus (ties: the lowest index) becomes pose 0 of the tracking problem
+__global__ void ransac_pick_kernel(int nh, const int* __restrict__ score, const double* __restrict__ hp_poses,
+                                   double* pose, int* best) {
+  __shared__ int bs[256], bi[256];
+  const int tid = threadIdx.x;
+  int s = -1, idx = 0x7fffffff;
+  for (int j = tid; j < nh; j += 256) if (score[j] > s) { s = score[j]; idx = j; }
+  bs[tid] = s; bi[tid] = idx;
+  __syncthreads();
+  for (int m = 128; m > 0; m >>= 1) {
+    if (tid < m && (bs[tid + m] > bs[tid] || (bs[tid + m] == bs[tid] && bi[tid + m] < bi[tid]))) { bs[tid] = bs[tid + m]; bi[tid] = bi[tid + m]; }
+    __syncthreads();
+  }
+  if (tid < 12) pose[tid] = hp_poses[12 * (size_t)bi[0] + tid];
+  if (tid == 0) { best[0] = bi[0]; best[1] = bs[0]; }
 }
 
 }  // namespace
@@ -266,6 +408,25 @@ int launch_triangulate(int n, const double* P1, const double* P2, const float2* 
   for (int k = 0; k < 12; ++k) { d.P1[k] = P1[k]; d.P2[k] = P2[k]; }
   d.uv1 = uv1; d.uv2 = uv2; d.min_depth = min_depth; d.max_err = max_err; d.X = X; d.keep = keep;
   triangulate_kernel<<<(n + 127) / 128, 128, 0, s>>>(d);
+  return (int)cudaGetLastError();
+}
+
+int launch_pose_track(const PoseData& d, const Params& P, double thr, int rounds, unsigned char* mask,
+                      int* n_inliers, cudaStream_t s, int classify_first) {
+  pose_track_kernel<<<1, kPoseThreads, 0, s>>>(d, P, thr, rounds, mask, n_inliers, classify_first);
+  return (int)cudaGetLastError();
+}
+
+int launch_pose_ransac(const RansacData& r, const PoseData& track, const Params& P, double thr, cudaStream_t s) {
+  ransac_sample_kernel<<<(r.nh + 1 + 127) / 128, 128, 0, s>>>(r.nh, r.n, r.seed, track.points, track.obs_uv, track.poses,
+                                                            r.hp_pts, r.hp_uv, r.hp_poses, r.hp_off, r.hp_idx);
+  PoseData hd{};
+  hd.nb = r.nh; hd.obs_off = r.hp_off; hd.poses = r.hp_poses; hd.points = r.hp_pts; hd.obs_uv = r.hp_uv; hd.summaries = r.hp_summ;
+  Params H = P;
+  H.loss = 0; H.max_iters = r.hyp_iters; H.ftol = H.gtol = H.ptol = 0.0;
+  pose_lm_kernel<<<r.nh, kPoseThreads, 0, s>>>(hd, H);
+  ransac_score_kernel<<<r.nh, kPoseThreads, 0, s>>>(r.n, track.points, track.obs_uv, r.hp_poses, r.hp_summ, P, thr, r.score);
+  ransac_pick_kernel<<<1, 256, 0, s>>>(r.nh, r.score, r.hp_poses, track.poses, r.best);
   return (int)cudaGetLastError();
 }
 

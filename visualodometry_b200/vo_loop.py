@@ -81,6 +81,13 @@ class VOLoop:
         # NOT in the reference either: replacement of `triangulate`, same signature and return
         # values, e.g. the CUDA kernel behind `BundleAdjuster.triangulate`.  None = cv2, as the reference does.
         self.triangulator = None
+        # NOT in the reference: replacement of the `cv2.solvePnPRansac` call (`vo.py:135-141`) by a tracker that starts
+        # from the previous pose, a callable (X, uv, T_cw_prior) -> (ok, T_cw, inlier indices), e.g.
+        # `lambda X, uv, T: ba.track_pose(T, X, uv, cfg.pnp_reproj_err)[:3]` (robust motion-only BA on the GPU, no
+        # sampling).  When it reports no consensus the loop falls through to cv2.solvePnPRansac, so it never resets
+        # where the reference would not.  None = cv2.solvePnPRansac only, as the reference does (the pinned loop).
+        self.pnp_solver = None
+        self.pnp_fallbacks = 0
 
     # ------------------------------------------------------------------ vo.py:49-250
     def process_frame(self, img) -> None:
@@ -134,13 +141,22 @@ class VOLoop:
             return
         X = np.array([mp[p] for p in kf_ids[valid]])
         uv = _kp(feats)[cur_idx[valid]]
-        ok, rvec, tvec, inliers = cv2.solvePnPRansac(X, uv, self.K, None, reprojectionError=cfg.pnp_reproj_err)
+        ok = False
+        if self.pnp_solver is not None:
+            ok, T_cw, inliers = self.pnp_solver(X, uv, np.linalg.inv(self.T_wc))
+            if ok:
+                R = T_cw[:3, :3]
+                inliers = np.asarray(inliers).reshape(-1, 1)
+            else:
+                self.pnp_fallbacks += 1                # no consensus around the prior: the reference's own call decides
         if not ok:
-            self._reset_system()
-            return
-        R, _ = cv2.Rodrigues(rvec)
-        T_cw = np.eye(4)
-        T_cw[:3, :3], T_cw[:3, 3] = R, tvec.flatten()
+            ok, rvec, tvec, inliers = cv2.solvePnPRansac(X, uv, self.K, None, reprojectionError=cfg.pnp_reproj_err)
+            if not ok:
+                self._reset_system()
+                return
+            R, _ = cv2.Rodrigues(rvec)
+            T_cw = np.eye(4)
+            T_cw[:3, :3], T_cw[:3, 3] = R, tvec.flatten()
         if self.pose_refiner is not None and inliers is not None and len(inliers) >= 6:
             sel = inliers.flatten()
             T_cw = self.pose_refiner(T_cw, X[sel], uv[sel])
