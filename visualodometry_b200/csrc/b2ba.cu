@@ -776,7 +776,14 @@ int b2ba_optimize_batch(b2ba_t* h, int32_t B, const int32_t* cam_off, const int3
   if (B <= 18) cut.push_back(B);
   else if (chunks > 0) { const int K = chunks > B ? B : chunks; for (int c = 1; c <= K; ++c) cut.push_back((int)((long long)B * c / K)); }
   else if (wave <= 0 || B <= 2 * wave) cut.push_back(B);
-  else { int w = wave; while (w < B) { cut.push_back(w); w += 2 * wave; } cut.push_back(B); }
+  else {
+    // B2BA_CHUNK_PLAN="first,step" in quarter waves (default 4,8: one wave, then two waves per chunk)
+    int q_first = 4, q_step = 8;
+    if (const char* e = getenv("B2BA_CHUNK_PLAN")) { if (sscanf(e, "%d,%d", &q_first, &q_step) != 2 || q_first < 1 || q_step < 1) { q_first = 4; q_step = 8; } }
+    int w = wave * q_first / 4;
+    while (w < B) { cut.push_back(w); w += wave * q_step / 4; }
+    cut.push_back(B);
+  }
   const int K = (int)cut.size() - 1;
   while ((int)h->kids.size() < K) {
     b2ba* k = nullptr;
