@@ -462,8 +462,8 @@ def main():
                "wall_s_timed_region": t_wall}
         if c5:
             # dominant kernel: the cooperative PCG (block-sparse mat-vec, HBM/L2 bound).  Algorithmic bytes of
-            # the step: 46.4 B per observation*iteration + 288 B per S block read per CG iteration
-            # (upper blocks are read twice: row and transposed row) + 7 vectors of 6*Nfree doubles.
+            # the step: 46.4 B per observation*iteration + 288 B per STORED (upper) S block per CG iteration
+            # (the mat-vec reads every upper block once) + 7 vectors of 6*Nfree doubles.
             pcg_its = sum(s_.pcg_iters for s_ in sms)
             ncam = int(b.cam_off[-1])
             pairs = set()
@@ -476,8 +476,8 @@ def main():
                 for i in range(cams.shape[1]):
                     for j in range(i, cams.shape[1]):
                         pairs.update((cams[:, i].astype(np.int64) * ncam + cams[:, j]).tolist())
-            nfull = 2 * len(pairs) - ncam
-            byt = (46.4 * b.no * iters_done + pcg_its * (288.0 * nfull + 7 * 48.0 * ncam))
+            nupper = len(pairs)
+            byt = (46.4 * b.no * iters_done + pcg_its * (288.0 * nupper + 7 * 48.0 * ncam))
             gbs5 = byt / (ms_total / args.steps * 1e-3) / 1e9
             banded = pcg_its == 0    # block-banded S: substructured Cholesky (a chain of dependent 6x6 pivots)
             out["roofline"] = {"bound": "hbm",

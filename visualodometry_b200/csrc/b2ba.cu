@@ -49,7 +49,7 @@ struct b2ba {
   LargeIndex lix;
   DevBuf<ObsRec> l_cm;
   DevBuf<int> l_cam_ptr;
-  DevBuf<double> l_poses_tri, l_lin_part, l_lin, l_Dc, l_Sg, l_dc, l_r, l_z, l_q, l_Minv, l_part, l_sums, l_band, l_binv, l_band_ws, l_zbuf, l_dense, l_dense_winv, l_dense_x;
+  DevBuf<double> l_poses_tri, l_lin_part, l_lin, l_Dc, l_Sg, l_dc, l_r, l_z, l_q, l_Minv, l_part, l_sums, l_band, l_binv, l_band_ws, l_zbuf, l_dense, l_dense_winv, l_dense_x, l_tbuf;
   DevBuf<int> l_dense_flags;
   int l_dense_ld = 0;
   // motion-only BA (b2ba_refine_poses): own buffers, independent of the problem set with b2ba_set_problem
@@ -194,7 +194,7 @@ LargeData make_large(b2ba* h, bool hist) {
   d.poses = h->d_poses.p; d.poses_tri = h->l_poses_tri.p; d.pts = h->d_pts0.p; d.pts_tri = h->d_pts1.p;
   d.lin_part = h->l_lin_part.p; d.lin = h->nranks > 1 ? h->l_lin.p : h->l_lin_part.p;
   d.Dc = h->l_Dc.p; d.pt_scratch = h->d_scratch.p; d.Sg = h->l_Sg.p; d.dc = h->l_dc.p;
-  d.r = h->l_r.p; d.z = h->l_z.p; d.q = h->l_q.p; d.Minv = h->l_Minv.p; d.part = h->l_part.p;
+  d.r = h->l_r.p; d.z = h->l_z.p; d.q = h->l_q.p; d.Minv = h->l_Minv.p; d.tbuf = h->l_tbuf.p; d.part = h->l_part.p;
   d.pair_ptr = h->lix.pair_ptr.p; d.pair_ab = h->lix.pair_ab.p; d.blk_row = h->lix.blk_row.p; d.zbuf = h->l_zbuf.p;
   d.pm_pt = h->lix.pm_pt.p; d.a_lo = h->lix.a_lo; d.a_hi = h->lix.a_hi;
   {
@@ -239,7 +239,7 @@ int setup_large(b2ba* h) {
   CU(h->l_poses_tri.alloc(nc * 12), "alloc"); CU(h->l_lin_part.alloc(nc * 27 + 2), "alloc");
   CU(h->l_lin.alloc(nc * 27 + 2), "alloc"); CU(h->l_Dc.alloc(nc * 6), "alloc");
   CU(h->l_Sg.alloc(nblk * 36 + n), "alloc"); CU(h->l_dc.alloc(n), "alloc"); CU(h->l_r.alloc(n), "alloc");
-  CU(h->l_z.alloc(n), "alloc"); CU(h->l_q.alloc(n), "alloc"); CU(h->l_Minv.alloc(6 * n), "alloc");
+  CU(h->l_z.alloc(n), "alloc"); CU(h->l_q.alloc(n), "alloc"); CU(h->l_Minv.alloc(6 * n), "alloc"); CU(h->l_tbuf.alloc(nblk * 6), "alloc");
   CU(h->l_part.alloc(part + 8), "alloc"); CU(h->l_sums.alloc(16), "alloc"); CU(h->l_ctrl.alloc(1), "alloc");
   // solver choice on the large path: S block-banded (half-bandwidth <= kBandMaxBw camera blocks) -> exact banded
   // Cholesky, unless PCG was asked for explicitly; otherwise block-Jacobi PCG

@@ -744,23 +744,30 @@ __global__ void __launch_bounds__(kPcgThreads) large_pcg_kernel(LargeData d, int
       // ---- phase A: p = z + beta p (whole vector, every CTA), q = S p on own rows, p.q
       for (int i = tid; i < n; i += kPcgThreads) psh[i] = d.z[i] + beta * psh[i];
       __syncthreads();
-      // one CTA per block row: its warps stride over the row's blocks (5 block slots per warp and step), so every
-      // warp of the grid has loads in flight even when there are fewer rows than warps (dense S: 1000 rows)
-      double s_pq = 0.0;
-      for (int f = blockIdx.x; f < nfree; f += gridDim.x) {
+      // q = S p with every stored (upper) block read ONCE.  Pass 1, one CTA per block row f: its warps stride over the
+      // row's upper blocks (5 block slots per warp and step): the row's own part of q_f = sum_c S(f,c) p_c, and per
+      // off-diagonal block the transposed product S(f,c)^T p_f (6 doubles) into tbuf.  Pass 2 (after a grid sync):
+      // q_c += the tbuf entries of column c, i.e. of the transposed entries of row c of the full index.  Rows are
+      // dealt out in serpentine order (long and short rows alternate per CTA): pass 1 rows get shorter with f, pass 2
+      // lists longer.
+      const int G_ = (int)gridDim.x;
+      for (int j = 0; j * G_ < nfree; ++j) {
+        const int f = j * G_ + ((j & 1) ? G_ - 1 - (int)blockIdx.x : (int)blockIdx.x);
+        if (f >= nfree) continue;                       // uniform per CTA
+        const double* pf = psh + 6 * f;
         double v = 0.0;
         if (lane < 30) {
-          for (int b = d.frow_ptr[f] + warp * 5 + bl; b < d.frow_ptr[f + 1]; b += 5 * nwarp_cta) {
-            const int src = d.fsrc[b];
-            const double* M = S + (size_t)(src & 0x7fffffff) * 36;
-            const double* x = psh + 6 * d.fcol[b];
-            if (src < 0) {
+          for (int b = d.blk_ptr[f] + warp * 5 + bl; b < d.blk_ptr[f + 1]; b += 5 * nwarp_cta) {
+            const double* M = S + (size_t)b * 36;
+            const int c = d.blk_col[b];
+            const double* x = psh + 6 * c;
+            double t = 0.0;
 #pragma unroll
-              for (int s_ = 0; s_ < 6; ++s_) v += M[6 * s_ + rr] * x[s_];
-            } else {
-#pragma unroll
-              for (int s_ = 0; s_ < 6; ++s_) v += M[6 * rr + s_] * x[s_];
+            for (int s_ = 0; s_ < 6; ++s_) {
+              v += M[6 * rr + s_] * x[s_];
+              t += M[6 * s_ + rr] * pf[s_];
             }
+            if (c != f) d.tbuf[(size_t)b * 6 + rr] = t;
           }
         }
         v += __shfl_down_sync(0xffffffffu, v, 6) + __shfl_down_sync(0xffffffffu, v, 12) +
@@ -769,6 +776,30 @@ __global__ void __launch_bounds__(kPcgThreads) large_pcg_kernel(LargeData d, int
         __syncthreads();
         if (warp == 0 && lane < 6) {
           double t = 0.0;
+#pragma unroll
+          for (int w = 0; w < nwarp_cta; ++w) t += rowred[w][lane];    // fixed order
+          d.q[6 * f + lane] = t;
+        }
+        __syncthreads();
+      }
+      grid.sync();
+      double s_pq = 0.0;
+      for (int j = 0; j * G_ < nfree; ++j) {
+        const int f = nfree - 1 - (j * G_ + ((j & 1) ? G_ - 1 - (int)blockIdx.x : (int)blockIdx.x));   // long lists first
+        if (f < 0) continue;
+        double v = 0.0;
+        if (lane < 30) {
+          // transposed entries of row f = the entries with column < f: a prefix of the row (columns ascending)
+          const int lo = d.frow_ptr[f], hi = d.frow_ptr[f + 1] - (d.blk_ptr[f + 1] - d.blk_ptr[f]);
+          for (int b = lo + warp * 5 + bl; b < hi; b += 5 * nwarp_cta)
+            v += d.tbuf[(size_t)(d.fsrc[b] & 0x7fffffff) * 6 + rr];
+        }
+        v += __shfl_down_sync(0xffffffffu, v, 6) + __shfl_down_sync(0xffffffffu, v, 12) +
+             __shfl_down_sync(0xffffffffu, v, 18) + __shfl_down_sync(0xffffffffu, v, 24);
+        if (lane < 6) rowred[warp][lane] = v;
+        __syncthreads();
+        if (warp == 0 && lane < 6) {
+          double t = d.q[6 * f + lane];
 #pragma unroll
           for (int w = 0; w < nwarp_cta; ++w) t += rowred[w][lane];    // fixed order
           d.q[6 * f + lane] = t;

@@ -48,6 +48,7 @@ struct LargeData {
   double* dc;                      // n   delta_c (PCG x)
   double* r; double* z; double* q; // n each
   double* Minv;                    // nfree x 36
+  double* tbuf;                    // nblk x 6: PCG mat-vec, transposed products S(f,c)^T p_f of the upper blocks
   const int* pair_ptr;             // nblk+1: Schur pair list by S block (this rank's landmarks)
   const int2* pair_ab;             // (observation a, observation b >= a) in point-major numbering
   const int* blk_row;              // nblk: block row of each upper block
