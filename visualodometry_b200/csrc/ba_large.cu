@@ -750,8 +750,10 @@ __global__ void __launch_bounds__(kPcgThreads) large_pcg_kernel(LargeData d, int
       // q_c += the tbuf entries of column c, i.e. of the transposed entries of row c of the full index.  Rows are
       // dealt out in serpentine order (long and short rows alternate per CTA): pass 1 rows get shorter with f, pass 2
       // lists longer.
-      const int G_ = (int)gridDim.x;
-      for (int j = 0; j * G_ < nfree; ++j) {
+      // Odd CG iterations walk the passes backwards: what the previous iteration read last is still in L2.
+      const int G_ = (int)gridDim.x, J_ = (nfree + G_ - 1) / G_;
+      for (int jj = 0; jj < J_; ++jj) {
+        const int j = (it & 1) ? J_ - 1 - jj : jj;
         const int f = j * G_ + ((j & 1) ? G_ - 1 - (int)blockIdx.x : (int)blockIdx.x);
         if (f >= nfree) continue;                       // uniform per CTA
         const double* pf = psh + 6 * f;
