@@ -9,3 +9,8 @@ timeout 900 python bench.py --workload c2 --frames 1000 --impl reference > gpuru
 timeout 600 python bench.py --workload c5 --c5-mode random --solver dense --no-cpu > gpurun_out/b_c5r_dense.json 2> gpurun_out/b_c5r_dense.err; echo rc $?
 B2BA_DENSE_MODE=1 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 800 --csv --log-file gpurun_out/r1_launches_c5r_dense.csv python bench.py --workload c5 --c5-mode random --solver dense --steps 1 --warmup 0 --iters 1 --no-cpu > gpurun_out/ncu_dense.log 2>&1; echo rc $?
 ls -la gpurun_out | tail -12
+for w in c1 c3; do timeout 300 python bench.py --workload $w > gpurun_out/b_$w.json 2> gpurun_out/b_$w.err; echo rc $?; done
+timeout 600 python bench.py --workload c5 --c5-mode local > gpurun_out/b_c5.json 2> gpurun_out/b_c5.err; echo rc $?
+timeout 600 python bench.py --workload c5 --c5-mode random > gpurun_out/b_c5r.json 2> gpurun_out/b_c5r.err; echo rc $?
+timeout 300 python bench.py --workload pnp > gpurun_out/b_pnp.json 2> gpurun_out/b_pnp.err; echo rc $?
+timeout 300 python tools/c2_profile.py 600 > gpurun_out/r1_c2_profile.txt 2>&1; echo rc $?

@@ -93,13 +93,11 @@ def pack_window(window, map_points, n_fixed: int = 2, min_obs: int = 2) -> Packe
     pid = np.concatenate(pids)
     uv = np.concatenate(uvs).astype(np.float32)
     kpi = np.concatenate(kps)
-    # landmarks that still exist in the map (`_prune_map`, vo.py:35-47, may have dropped old ids)
-    known = np.fromiter((p in map_points for p in pid.tolist()), bool, pid.size)
-    cam, pid, uv, kpi = cam[known], pid[known], uv[known], kpi[known]
-    if pid.size == 0:
-        return None
     upid, inv, cnt = np.unique(pid, return_inverse=True, return_counts=True)
-    keep_pt = cnt >= min_obs
+    # landmarks that still exist in the map (`_prune_map`, vo.py:35-47, may have dropped old ids): looked up once per
+    # landmark, not once per observation
+    known = np.fromiter((p in map_points for p in upid.tolist()), bool, upid.size)
+    keep_pt = known & (cnt >= min_obs)
     if not keep_pt.any():
         return None
     slot = np.cumsum(keep_pt) - 1
@@ -125,9 +123,8 @@ def write_back(vo, window, packed: PackedWindow, T_cw: np.ndarray, points: np.nd
     vo.T_wc = newest["T_wc"].copy()
     vo.last_pos = vo.T_wc[:3, 3].copy()          # vo.py:204
     mp = vo.map_points
-    for p, x in zip(packed.pids.tolist(), points):
-        if p in mp:
-            mp[p] = x.copy()
+    rows = np.array(points, np.float64)             # one copy; every landmark gets its own row (an ndarray(3,) view)
+    mp.update((p, x) for p, x in zip(packed.pids.tolist(), rows) if p in mp)
 
 
 def cull_window(vo, window, packed: PackedWindow, err: np.ndarray, max_err: float) -> int:
