@@ -88,7 +88,7 @@ __device__ bool potrf64(double (*L)[LDL], double* invd, int tid) {
     for (int c = 0; c < 8; ++c) {
       const double p = D[c][c];
       ok = ok && (p > 0.0);
-      const double inv = rsqrt(p);
+      const double inv = rsqrt_pos(p);
       dinv[c] = inv;
       D[c][c] = p * inv;
 #pragma unroll
