@@ -346,16 +346,22 @@ __global__ void __launch_bounds__(BT) dense_backward_kernel(const LargeCtrl* ctr
 }
 constexpr size_t kBackwardSmem = (size_t)(3 * NB * NB + 2 * NB + 4 * NB) * sizeof(double);
 
-struct DenseRt {               // per-process launch state (one device per process)
+struct DenseRt {               // launch state of one device (streams and events belong to a device)
   bool ready = false;
   cudaStream_t chain = nullptr;                   // high priority: the panel chain runs ahead of the bulk updates
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_panel[2] = {nullptr, nullptr}, ev_rest[2] = {nullptr, nullptr};
   int epoch = 0;
   int sms = 0;
 };
-DenseRt g_rt;
+DenseRt g_rts[16];             // indexed by device ordinal
+int g_epoch = 0;               // publication epochs of the backward pass: monotonic across handles and devices
 
-int dense_runtime() {
+int dense_runtime(DenseRt** out) {
+  int dev_ = 0;
+  cudaGetDevice(&dev_);
+  if (dev_ < 0 || dev_ >= 16) return (int)cudaErrorInvalidDevice;
+  DenseRt& g_rt = g_rts[dev_];
+  *out = &g_rt;
   if (g_rt.ready) return 0;
   cudaError_t e = cudaFuncSetAttribute(dense_panel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPanelSmem);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(dense_update_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kUpdateSmem);
@@ -401,8 +407,10 @@ int large_dense_max_n() {
 // mode (B2BA_DENSE_MODE): 0 = one update per 64-column panel; 1 = two panels per trailing update (K = 128);
 // 2 (default) = 1 + look-ahead: panel chain on a high-priority stream
 int large_dense_solve(const LargeData& d, cudaStream_t st) {
-  int rc = dense_runtime();
+  DenseRt* rt = nullptr;
+  int rc = dense_runtime(&rt);
   if (rc) return rc;
+  DenseRt& g_rt = *rt;
   static const int mode = getenv("B2BA_DENSE_MODE") ? atoi(getenv("B2BA_DENSE_MODE")) : 2;
   const int npad = d.dense_ld, nb = npad / NB;
   dense_zero_kernel<<<dim3(nb, nb + 1), 256, 0, st>>>(d.ctrl, d.dense, npad);
@@ -452,7 +460,7 @@ int large_dense_solve(const LargeData& d, cudaStream_t st) {
   {
     const double* A = d.dense;
     const LargeCtrl* ctrl = d.ctrl;
-    int ld = npad, np_ = npad, n = d.n, epoch = ++g_rt.epoch;
+    int ld = npad, np_ = npad, n = d.n, epoch = ++g_epoch;
     const double* winv = d.dense_winv;
     double* xg = d.dense_x;
     int* flags = d.dense_flags;
