@@ -384,22 +384,27 @@ int b2ba_set_problem_batch(b2ba_t* h, int32_t B, const int32_t* cam_off, const i
   CU(h->d_pt_ptr.alloc(np + 1), "alloc"); CU(h->d_cam_ptr.alloc(nc + 1), "alloc"); CU(h->d_flags.alloc(2), "alloc");
   CU(h->d_sched.alloc(np), "alloc");
   CU(h->d_summ.alloc(B), "alloc");
-  CU(cudaMemcpy(h->d_cam_off.p, cam_off, (B + 1) * sizeof(int), cudaMemcpyHostToDevice), "copy offsets");
-  CU(cudaMemcpy(h->d_pt_off.p, pt_off, (B + 1) * sizeof(int), cudaMemcpyHostToDevice), "copy offsets");
-  CU(cudaMemcpy(h->d_obs_off.p, obs_off, (B + 1) * sizeof(long long), cudaMemcpyHostToDevice), "copy offsets");
-  CU(cudaMemcpy(h->d_fixed.p, fixed_cam, nc, k), "copy fixed");
-  CU(cudaMemcpy(h->d_poses.p, poses_cw, nc * 12 * sizeof(double), k), "copy poses");
-  CU(cudaMemcpy(h->d_pts0.p, points, np * 3 * sizeof(double), k), "copy points");
+  // asynchronous copies on the default stream (pinned caller buffers: no per-copy round trip; pageable ones are staged
+  // by the runtime before the call returns); the index builder's flag read-back below waits for all of them, so no
+  // caller pointer is in use after set_problem returns
+  cudaStream_t cs = nullptr;
+  CU(cudaMemcpyAsync(h->d_cam_off.p, cam_off, (B + 1) * sizeof(int), cudaMemcpyHostToDevice, cs), "copy offsets");
+  CU(cudaMemcpyAsync(h->d_pt_off.p, pt_off, (B + 1) * sizeof(int), cudaMemcpyHostToDevice, cs), "copy offsets");
+  CU(cudaMemcpyAsync(h->d_obs_off.p, obs_off, (B + 1) * sizeof(long long), cudaMemcpyHostToDevice, cs), "copy offsets");
+  CU(cudaMemcpyAsync(h->d_fixed.p, fixed_cam, nc, k, cs), "copy fixed");
+  CU(cudaMemcpyAsync(h->d_poses.p, poses_cw, nc * 12 * sizeof(double), k, cs), "copy poses");
+  CU(cudaMemcpyAsync(h->d_pts0.p, points, np * 3 * sizeof(double), k, cs), "copy points");
   if (no) {
-    CU(cudaMemcpy(h->d_obs_cam.p, obs_cam, no * sizeof(int), k), "copy obs_cam");
-    CU(cudaMemcpy(h->d_obs_pt.p, obs_pt, no * sizeof(int), k), "copy obs_pt");
-    CU(cudaMemcpy(h->d_uv.p, obs_uv, no * sizeof(float2), k), "copy obs_uv");
+    CU(cudaMemcpyAsync(h->d_obs_cam.p, obs_cam, no * sizeof(int), k, cs), "copy obs_cam");
+    CU(cudaMemcpyAsync(h->d_obs_pt.p, obs_pt, no * sizeof(int), k, cs), "copy obs_pt");
+    CU(cudaMemcpyAsync(h->d_uv.p, obs_uv, no * sizeof(float2), k, cs), "copy obs_uv");
   }
-  CU(cudaMemcpy(h->d_poses0.p, h->d_poses.p, nc * 12 * sizeof(double), cudaMemcpyDeviceToDevice), "keep poses");
-  CU(cudaMemcpy(h->d_ptsinit.p, h->d_pts0.p, np * 3 * sizeof(double), cudaMemcpyDeviceToDevice), "keep points");
+  CU(cudaMemcpyAsync(h->d_poses0.p, h->d_poses.p, nc * 12 * sizeof(double), cudaMemcpyDeviceToDevice, cs), "keep poses");
+  CU(cudaMemcpyAsync(h->d_ptsinit.p, h->d_pts0.p, np * 3 * sizeof(double), cudaMemcpyDeviceToDevice, cs), "keep points");
   // gauge / path selection needs the fixed mask on the host
   h->h_fixed.resize(nc);
-  CU(cudaMemcpy(h->h_fixed.data(), h->d_fixed.p, nc, cudaMemcpyDeviceToHost), "read fixed");
+  if (mem == B2BA_MEM_HOST) std::memcpy(h->h_fixed.data(), fixed_cam, nc);
+  else CU(cudaMemcpy(h->h_fixed.data(), h->d_fixed.p, nc, cudaMemcpyDeviceToHost), "read fixed");
   h->max_nfree = 0; h->max_nc = 0;
   for (int b = 0; b < B; ++b) {
     int nf = 0;
@@ -413,7 +418,7 @@ int b2ba_set_problem_batch(b2ba_t* h, int32_t B, const int32_t* cam_off, const i
   h->sched_order = !want_pcg && h->max_nc <= kMaxCam && h->max_nfree <= kBigMaxFree && np > 0;
   IndexOut io{h->d_pm.p, h->d_pt_ptr.p, h->d_cm.p, h->d_cam_ptr.p, h->d_flags.p, h->sched_order ? h->d_sched.p : nullptr};
   int rc = build_index(make_index_in(h), io, nullptr);
-  if (rc) return cuda_fail(h, (cudaError_t)rc, "build_index");
+  if (rc) { cudaDeviceSynchronize(); return cuda_fail(h, (cudaError_t)rc, "build_index"); }   // copies above are done with the caller's buffers
   int flags[2] = {0, 0};
   CU(cudaMemcpy(flags, h->d_flags.p, sizeof(flags), cudaMemcpyDeviceToHost), "read index flags");
   if (flags[0]) { h->path = PATH_NONE; return fail(h, B2BA_E_INVALID, "observation index out of range"); }

@@ -350,7 +350,6 @@ struct DenseRt {               // launch state of one device (streams and events
   bool ready = false;
   cudaStream_t chain = nullptr;                   // high priority: the panel chain runs ahead of the bulk updates
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_panel[2] = {nullptr, nullptr}, ev_rest[2] = {nullptr, nullptr};
-  int epoch = 0;
   int sms = 0;
 };
 DenseRt g_rts[16];             // indexed by device ordinal
