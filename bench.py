@@ -145,7 +145,7 @@ def run_c2(args, impl):
             # SURVEY 8 row f-2 widened: the tracker's cv2.solvePnPRansac call (vo.py:135-141) replaced by the
             # sampling-free GPU tracker (b2ba_track_pose) started from the previous pose
             from visualodometry_b200 import BundleAdjuster
-            trk = BundleAdjuster(seq.K, BAConfig())
+            trk = BundleAdjuster(seq.K, BAConfig(ftol=1e-10))   # the refinement rounds stop when the cost stops moving
             if gpu_tracker == "ransac":      # b2ba_ransac_pose: 1024 hypotheses per frame, sampled consensus
                 vo.pnp_solver = lambda X, uv, T: trk.ransac_pose(T, X, uv, lcfg.pnp_reproj_err, n_hyp=1024, seed=vo.frame_id)[:3]
             else:                            # b2ba_track_pose: graduated robust refinement from the previous pose

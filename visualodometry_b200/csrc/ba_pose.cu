@@ -30,8 +30,8 @@ __device__ __forceinline__ void cta_sum(double* v, double* red, double* out) {
   __syncthreads();
   if (threadIdx.x < N) {
     double s = 0.0;
-#pragma unroll
-    for (int w = 0; w < kPoseWarps; ++w) s += red[w * N + threadIdx.x];
+    const int nw = (int)blockDim.x >> 5;               // 4 warps per pose problem, 1 for the minimal-sample fits
+    for (int w = 0; w < nw; ++w) s += red[w * N + threadIdx.x];
     out[threadIdx.x] = s;
   }
   __syncthreads();
@@ -56,7 +56,7 @@ __device__ void pose_lm_run(const PoseData& d, const Params& P, int b, const uns
       double v[kNV];
 #pragma unroll
       for (int k = 0; k < kNV; ++k) v[k] = 0.0;
-      for (long long i = o0 + tid; i < o1; i += kPoseThreads) {
+      for (long long i = o0 + tid; i < o1; i += blockDim.x) {
         if (mask != nullptr && !mask[i]) continue;
         const double* X = d.points + 3 * (size_t)i;
         const float2 uv = d.obs_uv[i];
@@ -124,7 +124,7 @@ __device__ void pose_lm_run(const PoseData& d, const Params& P, int b, const uns
     // ---- trial cost with the retracted pose
     double tv[2] = {0.0, 0.0};
     if (step_ok) {
-      for (long long i = o0 + tid; i < o1; i += kPoseThreads) {
+      for (long long i = o0 + tid; i < o1; i += blockDim.x) {
         if (mask != nullptr && !mask[i]) continue;
         const double* X = d.points + 3 * (size_t)i;
         const float2 uv = d.obs_uv[i];
@@ -187,6 +187,12 @@ __device__ void pose_lm_run(const PoseData& d, const Params& P, int b, const uns
 }
 
 __global__ void __launch_bounds__(kPoseThreads) pose_lm_kernel(PoseData d, Params P) {
+  pose_lm_run(d, P, blockIdx.x, nullptr);
+}
+
+// the same loop by ONE warp per problem: the minimal-sample fits of the sampled consensus (4 observations each) have no
+// use for more lanes, and 1024 of them fit the GPU in one wave
+__global__ void __launch_bounds__(32) pose_lm_warp_kernel(PoseData d, Params P) {
   pose_lm_run(d, P, blockIdx.x, nullptr);
 }
 
@@ -424,7 +430,7 @@ int launch_pose_ransac(const RansacData& r, const PoseData& track, const Params&
   hd.nb = r.nh; hd.obs_off = r.hp_off; hd.poses = r.hp_poses; hd.points = r.hp_pts; hd.obs_uv = r.hp_uv; hd.summaries = r.hp_summ;
   Params H = P;
   H.loss = 0; H.max_iters = r.hyp_iters; H.ftol = H.gtol = H.ptol = 0.0;
-  pose_lm_kernel<<<r.nh, kPoseThreads, 0, s>>>(hd, H);
+  pose_lm_warp_kernel<<<r.nh, 32, 0, s>>>(hd, H);
   ransac_score_kernel<<<r.nh, kPoseThreads, 0, s>>>(r.n, track.points, track.obs_uv, r.hp_poses, r.hp_summ, P, thr, r.score);
   ransac_pick_kernel<<<1, 256, 0, s>>>(r.nh, r.score, r.hp_poses, track.poses, r.best);
   return (int)cudaGetLastError();
