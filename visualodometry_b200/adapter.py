@@ -96,8 +96,11 @@ def pack_window(window, map_points, n_fixed: int = 2, min_obs: int = 2) -> Packe
     upid, inv, cnt = np.unique(pid, return_inverse=True, return_counts=True)
     # landmarks that still exist in the map (`_prune_map`, vo.py:35-47, may have dropped old ids): looked up once per
     # landmark, not once per observation
-    known = np.fromiter((p in map_points for p in upid.tolist()), bool, upid.size)
-    keep_pt = known & (cnt >= min_obs)
+    keep_pt = cnt >= min_obs
+    cand = np.flatnonzero(keep_pt)                  # only landmarks that can enter the problem are looked up
+    if cand.size == 0:
+        return None
+    keep_pt[cand] = np.fromiter((p in map_points for p in upid[cand].tolist()), bool, cand.size)
     if not keep_pt.any():
         return None
     slot = np.cumsum(keep_pt) - 1
@@ -106,7 +109,7 @@ def pack_window(window, map_points, n_fixed: int = 2, min_obs: int = 2) -> Packe
     obs_cam = cam[keep_obs]
     obs_uv = np.ascontiguousarray(uv[keep_obs])
     upid = upid[keep_pt]
-    points = np.array([map_points[int(p)] for p in upid], np.float64).reshape(-1, 3)
+    points = np.array([map_points[p] for p in upid.tolist()], np.float64).reshape(-1, 3)
     T_cw = np.stack([np.linalg.inv(np.asarray(kf["T_wc"], np.float64)) for kf in kfs])
     fixed = np.zeros(nc, bool)
     fixed[:max(1, min(n_fixed, nc - 1))] = True
