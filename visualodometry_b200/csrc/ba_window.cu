@@ -136,14 +136,85 @@ window_lm_kernel(const WinData d, const Params P) {
     // ------------------------------------------------------------------ camera pass (a1+a2)
     const int fresh_lin = !have_lin;
     if (!have_lin) {
+      // one observation of camera pose q into the 21 + 6 + 2 sums (structural zeros of J_c skipped)
+      auto cam_accum = [&](const ObsRec& rec, const Pose12& q, bool isfree, double* acc) {
+        const double* Xp = X + 3 * rec.idx;
+        Geo o;
+        geo_project<LOSS>(P, q, Xp[0], Xp[1], Xp[2], rec.u, rec.v, o);
+        if (!o.valid) { acc[28] += 1.0; return; }
+        acc[27] = fma(0.5, o.rho, acc[27]);
+        if (isfree) {
+          double j0[6], j1[6];
+          geo_jc(o, j0, j1);
+          int k = 0;
+#pragma unroll
+          for (int r = 0; r < 6; ++r) {
+            const double w0 = o.w * j0[r], w1 = o.w * j1[r];
+#pragma unroll
+            for (int s = r; s < 6; ++s, ++k) {
+              if (r != 4 && s != 4) acc[k] = fma(w0, j0[s], acc[k]);
+              if (r != 3 && s != 3) acc[k] = fma(w1, j1[s], acc[k]);
+            }
+            if (r != 4) acc[21 + r] = fma(w0, o.r0, acc[21 + r]);
+            if (r != 3) acc[21 + r] = fma(w1, o.r1, acc[21 + r]);
+          }
+        }
+      };
+      // transposing butterfly: 31 shuffles instead of 29 x 5; lane l ends with the warp total of acc[l]
+      auto warp_totals = [&](const double* acc) {
+        double v[32];
+#pragma unroll
+        for (int k = 0; k < 32; ++k) v[k] = k < 29 ? acc[k] : 0.0;
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) {
+          const bool up = (lane & off) != 0;
+#pragma unroll
+          for (int j = 0; j < off; ++j) {
+            const double keep = up ? v[j + off] : v[j];
+            const double send = up ? v[j] : v[j + off];
+            v[j] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+          }
+        }
+        return v[0];
+      };
       double cst_tot = 0.0, ninv_tot = 0.0;   // live in thread 27 / 28
-      for (int c = 0; c < nc; ++c) {
-        int b = d.cam_ptr[c0 + c], e = d.cam_ptr[c0 + c + 1];
-        if constexpr (CS > 1) {   // this CTA's contiguous share of the camera's observations
+      if constexpr (CS > 1) {
+        // latency path: the CTA holds only 1/CS of every camera's observations (a few per lane), so each WARP takes
+        // whole cameras -- no cross-warp sum and no block barrier per camera
+        double cst_w = 0.0, ninv_w = 0.0;     // lanes 27 / 28
+        for (int c = warp; c < nc; c += NWARPS) {
+          int b = d.cam_ptr[c0 + c], e = d.cam_ptr[c0 + c + 1];
           const int len = e - b;
           e = b + (int)(((long long)len * (crank + 1)) / CS);
           b = b + (int)(((long long)len * crank) / CS);
+          Pose12 q;
+          load_pose(pose_cur + 12 * c, q);
+          const bool isfree = fidx[c] >= 0;
+          double acc[29];
+#pragma unroll
+          for (int k = 0; k < 29; ++k) acc[k] = 0.0;
+          const ObsRec zrec{0.f, 0.f, 0, 0};
+          ObsRec rec_n = zrec;
+          if (b + lane < e) rec_n = d.cm[b + lane];
+          for (int a = b + lane; a < e; a += 32) {
+            const ObsRec rec = rec_n;
+            if (a + 32 < e) { rec_n = d.cm[a + 32]; prefetch_l1(X + 3 * rec_n.idx); prefetch_l1(X + 3 * rec_n.idx + 2); }
+            cam_accum(rec, q, isfree, acc);
+          }
+          const double v = warp_totals(acc);
+          if (lane < 21) Bc[c * 21 + lane] = v;
+          else if (lane < 27) gc[c * 6 + lane - 21] = v;
+          else if (lane == 27) cst_w += v;
+          else if (lane == 28) ninv_w += v;
         }
+        if (lane == 27) red[warp] = cst_w;
+        if (lane == 28) red[32 + warp] = ninv_w;
+        __syncthreads();
+        if (tid == 27) for (int w = 0; w < NWARPS; ++w) cst_tot += red[w];
+        if (tid == 28) for (int w = 0; w < NWARPS; ++w) ninv_tot += red[32 + w];
+      } else {
+      for (int c = 0; c < nc; ++c) {
+        const int b = d.cam_ptr[c0 + c], e = d.cam_ptr[c0 + c + 1];
         Pose12 q;
         load_pose(pose_cur + 12 * c, q);
         const bool isfree = fidx[c] >= 0;
@@ -160,45 +231,9 @@ window_lm_kernel(const WinData d, const Params P) {
           rec_n = rec_nn;
           if (a + 2 * NTHREADS < e) rec_nn = d.cm[a + 2 * NTHREADS];
           if (a + NTHREADS < e) { prefetch_l1(X + 3 * rec_n.idx); prefetch_l1(X + 3 * rec_n.idx + 2); }
-          const double* Xp = X + 3 * rec.idx;
-          Geo o;
-          geo_project<LOSS>(P, q, Xp[0], Xp[1], Xp[2], rec.u, rec.v, o);
-          if (!o.valid) { acc[28] += 1.0; continue; }
-          acc[27] = fma(0.5, o.rho, acc[27]);
-          if (isfree) {
-            double j0[6], j1[6];
-            geo_jc(o, j0, j1);
-            int k = 0;
-#pragma unroll
-            for (int r = 0; r < 6; ++r) {
-              const double w0 = o.w * j0[r], w1 = o.w * j1[r];
-#pragma unroll
-              for (int s = r; s < 6; ++s, ++k) {
-                if (r != 4 && s != 4) acc[k] = fma(w0, j0[s], acc[k]);
-                if (r != 3 && s != 3) acc[k] = fma(w1, j1[s], acc[k]);
-              }
-              if (r != 4) acc[21 + r] = fma(w0, o.r0, acc[21 + r]);
-              if (r != 3) acc[21 + r] = fma(w1, o.r1, acc[21 + r]);
-            }
-          }
+          cam_accum(rec, q, isfree, acc);
         }
-        // transposing butterfly: 31 shuffles instead of 29 x 5; lane l ends with the warp total of acc[l]
-        {
-          double v[32];
-#pragma unroll
-          for (int k = 0; k < 32; ++k) v[k] = k < 29 ? acc[k] : 0.0;
-#pragma unroll
-          for (int off = 16; off > 0; off >>= 1) {
-            const bool up = (lane & off) != 0;
-#pragma unroll
-            for (int j = 0; j < off; ++j) {
-              const double keep = up ? v[j + off] : v[j];
-              const double send = up ? v[j] : v[j + off];
-              v[j] = keep + __shfl_xor_sync(0xffffffffu, send, off);
-            }
-          }
-          red[warp * 32 + lane] = v[0];
-        }
+        red[warp * 32 + lane] = warp_totals(acc);
         __syncthreads();
         if (tid < 29) {
           double v = 0.0;
@@ -209,6 +244,7 @@ window_lm_kernel(const WinData d, const Params P) {
           else ninv_tot += v;
         }
         __syncthreads();
+      }
       }
       if (tid == 27) scal[0] = cst_tot;
       if (tid == 28) scal[1] = ninv_tot;
