@@ -610,36 +610,53 @@ window_lm_kernel(const WinData d, const Params P) {
     }
     __syncthreads();
     if (warp == 0) {
-      // L y = -g_red, L^T x = y with the vector in registers (row k of lane k % 32), one shuffle per step
+      // L y = -g_red, L^T x = y with the vector in registers (row k of lane k % 32), one shuffle per step.  Every
+      // lane keeps its unknowns pre-scaled by its own 1 / L_kk (x_k = d_k b_k - sum (d_k L_ki) y_i), so the dependent
+      // chain of a step is shuffle + FMA only; the coefficients of step i + 1 are loaded before step i is consumed.
       constexpr int RPL = Cfg::NR / 32 + (Cfg::NR % 32 ? 1 : 0);
-      double x[RPL], di[RPL];
+      double x[RPL], di[RPL], cn[RPL];
 #pragma unroll
       for (int q = 0; q < RPL; ++q) {
         const int k = lane + 32 * q;
-        x[q] = k < n ? -gred[k] : 0.0;
         di[q] = k < n ? red[k] : 0.0;
+        x[q] = k < n ? -gred[k] * di[q] : 0.0;
+        cn[q] = (k > 0 && k < n) ? S[k * LDS] * di[q] : 0.0;
       }
       for (int i = 0; i < n; ++i) {
-        double xi = 0.0;
-#pragma unroll
-        for (int q = 0; q < RPL; ++q)
-          if ((i >> 5) == q) { x[q] = (lane == (i & 31)) ? x[q] * di[q] : x[q]; xi = __shfl_sync(0xffffffffu, x[q], i & 31); }
+        double c[RPL];
 #pragma unroll
         for (int q = 0; q < RPL; ++q) {
           const int k = lane + 32 * q;
-          if (k > i && k < n) x[q] = fma(-S[k * LDS + i], xi, x[q]);
+          c[q] = cn[q];
+          cn[q] = (k > i + 1 && k < n) ? S[k * LDS + i + 1] * di[q] : 0.0;
         }
+        double xi = 0.0;
+#pragma unroll
+        for (int q = 0; q < RPL; ++q)
+          if ((i >> 5) == q) xi = __shfl_sync(0xffffffffu, x[q], i & 31);
+#pragma unroll
+        for (int q = 0; q < RPL; ++q) x[q] = fma(-c[q], xi, x[q]);
+      }
+#pragma unroll
+      for (int q = 0; q < RPL; ++q) {
+        const int k = lane + 32 * q;
+        x[q] *= di[q];
+        cn[q] = (k < n - 1) ? S[(n - 1) * LDS + k] * di[q] : 0.0;
       }
       for (int i = n - 1; i >= 0; --i) {
-        double xi = 0.0;
-#pragma unroll
-        for (int q = 0; q < RPL; ++q)
-          if ((i >> 5) == q) { x[q] = (lane == (i & 31)) ? x[q] * di[q] : x[q]; xi = __shfl_sync(0xffffffffu, x[q], i & 31); }
+        double c[RPL];
 #pragma unroll
         for (int q = 0; q < RPL; ++q) {
           const int k = lane + 32 * q;
-          if (k < i) x[q] = fma(-S[i * LDS + k], xi, x[q]);
+          c[q] = cn[q];
+          cn[q] = (i > 0 && k < i - 1) ? S[(i - 1) * LDS + k] * di[q] : 0.0;
         }
+        double xi = 0.0;
+#pragma unroll
+        for (int q = 0; q < RPL; ++q)
+          if ((i >> 5) == q) xi = __shfl_sync(0xffffffffu, x[q], i & 31);
+#pragma unroll
+        for (int q = 0; q < RPL; ++q) x[q] = fma(-c[q], xi, x[q]);
       }
 #pragma unroll
       for (int q = 0; q < RPL; ++q) {
