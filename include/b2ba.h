@@ -47,7 +47,10 @@ typedef struct b2ba_options {
   double pcg_tol;         /* 1e-10 */
   int32_t flags;          /* bit0: record per-iteration history (b2ba_dump B2BA_D_HIST_*);
                              bit1: never split a window over a thread-block cluster (<= 18 windows per
-                             handle are otherwise solved by one 8-CTA cluster each: the latency path) */
+                             handle are otherwise solved by one 8- or 16-CTA cluster each: the latency path);
+                             bit2 / bit3 force kernel instantiations that the engine would not pick by itself
+                             (256-thread CTAs on the batched small path / the portable 8-CTA cluster for <= 8
+                             windows): same results up to summation order; used by the parity tests */
   int32_t pad_;
 } b2ba_options;
 

@@ -35,7 +35,10 @@ struct ba_opts {
   int32_t pcg_max_iters; // 200
   double pcg_tol;        // 1e-10 on ||r||/||b||
   int32_t threads;       // OpenMP threads (<=0: all)
-  int32_t pad_;
+  int32_t flags;         // bit 0: linearise ONCE per accepted state -- r, w, J_c, J_p of every observation are stored by
+                         // linearize() and re-used by the Schur and back-substitution passes (same values, so the
+                         // results are bit-identical; this is the form a tuned CPU BA takes and the one timed as the
+                         // CPU baseline; 0 keeps the recompute-per-pass form of the first round)
 };
 
 struct ba_summary {
@@ -225,9 +228,17 @@ struct Problem {
 
 struct Lin {  // one linearisation (a2) + damping + a3
   std::vector<double> B, gc, C, gp, Cinv, Dc, Dp;  // B nc*36 (full sym), C np*6 (upper), Cinv np*6
+  std::vector<ObsLin> obs;                         // per observation (original order), only with flags bit 0
   double cost = 0;
   int n_invalid = 0;
 };
+
+// the linearisation of observation i: stored (flags bit 0) or recomputed
+inline const ObsLin& obs_lin(const Problem& P, const Lin& L, const double* poses, const double* pts, int i, ObsLin& tmp) {
+  if (!L.obs.empty()) return L.obs[(size_t)i];
+  obs_eval(poses + 12 * P.oc[i], pts + 3 * P.op[i], P.uv[2 * i], P.uv[2 * i + 1], P.intr, P.o, true, tmp);
+  return tmp;
+}
 
 // a1+a2: cost, B_c, g_c (camera-major pass), C_p, g_p (point-major pass).  Deterministic: each
 // block is summed in canonical order by exactly one thread.
@@ -237,14 +248,21 @@ void linearize(const Problem& P, const double* poses, const double* pts, Lin& L)
   L.C.assign((size_t)P.np * 6, 0);  L.gp.assign((size_t)P.np * 3, 0);
   std::vector<double> ccost(P.nc, 0.0);
   std::vector<int> cinv(P.nc, 0);
+  const bool once = (P.o.flags & 1) != 0;
+  if (once) {
+    L.obs.resize((size_t)P.no);
+#pragma omp parallel for schedule(static)
+    for (int64_t i = 0; i < P.no; ++i)
+      obs_eval(poses + 12 * P.oc[i], pts + 3 * P.op[i], P.uv[2 * i], P.uv[2 * i + 1], P.intr, P.o, true, L.obs[i]);
+  } else L.obs.clear();
 #pragma omp parallel for schedule(dynamic, 1)
   for (int c = 0; c < P.nc; ++c) {
     double* B = &L.B[(size_t)c * 36];
     double* g = &L.gc[(size_t)c * 6];
-    ObsLin o;
+    ObsLin tmp;
     for (int a = ix.cam_ptr[c]; a < ix.cam_ptr[c + 1]; ++a) {
       int i = ix.cm_perm[a];
-      obs_eval(poses + 12 * c, pts + 3 * P.op[i], P.uv[2 * i], P.uv[2 * i + 1], P.intr, P.o, true, o);
+      const ObsLin& o = obs_lin(P, L, poses, pts, i, tmp);
       if (!o.valid) { cinv[c]++; continue; }
       ccost[c] += 0.5 * o.rho;
       for (int r = 0; r < 6; ++r) {
@@ -260,10 +278,10 @@ void linearize(const Problem& P, const double* poses, const double* pts, Lin& L)
   for (int p = 0; p < P.np; ++p) {
     double* C = &L.C[(size_t)p * 6];
     double* g = &L.gp[(size_t)p * 3];
-    ObsLin o;
+    ObsLin tmp;
     for (int a = ix.pt_ptr[p]; a < ix.pt_ptr[p + 1]; ++a) {
       int i = ix.pm_perm[a];
-      obs_eval(poses + 12 * P.oc[i], pts + 3 * p, P.uv[2 * i], P.uv[2 * i + 1], P.intr, P.o, true, o);
+      const ObsLin& o = obs_lin(P, L, poses, pts, i, tmp);
       if (!o.valid) continue;
       const double* J = o.Jp;
       double w = o.w;
@@ -353,12 +371,12 @@ void schur(const Problem& P, const double* poses, const double* pts, const Lin& 
     for (int p = 0; p < P.np; ++p) {
       int a0 = ix.pt_ptr[p], a1 = ix.pt_ptr[p + 1];
       Es.clear(); Ys.clear(); fs.clear();
-      ObsLin o;
+      ObsLin tmp;
       for (int a = a0; a < a1; ++a) {
         int i = ix.pm_perm[a];
         int f = ix.fidx[P.oc[i]];
         if (f < 0) continue;
-        obs_eval(poses + 12 * P.oc[i], pts + 3 * p, P.uv[2 * i], P.uv[2 * i + 1], P.intr, P.o, true, o);
+        const ObsLin& o = obs_lin(P, L, poses, pts, i, tmp);
         if (!o.valid) continue;
         size_t k = fs.size();
         fs.push_back(f);
@@ -540,13 +558,13 @@ void back_substitute(const Problem& P, const double* poses, const double* pts, c
 #pragma omp parallel for schedule(static) reduction(+ : s1, s2)
   for (int p = 0; p < P.np; ++p) {
     double v[3] = {L.gp[3 * (size_t)p], L.gp[3 * (size_t)p + 1], L.gp[3 * (size_t)p + 2]};
-    ObsLin o;
+    ObsLin tmp;
     double E[18];
     for (int a = ix.pt_ptr[p]; a < ix.pt_ptr[p + 1]; ++a) {
       int i = ix.pm_perm[a];
       int f = ix.fidx[P.oc[i]];
       if (f < 0) continue;
-      obs_eval(poses + 12 * P.oc[i], pts + 3 * p, P.uv[2 * i], P.uv[2 * i + 1], P.intr, P.o, true, o);
+      const ObsLin& o = obs_lin(P, L, poses, pts, i, tmp);
       if (!o.valid) continue;
       make_E(o, E);
       for (int r = 0; r < 6; ++r)
@@ -644,11 +662,13 @@ int lm_solve(Problem& P, double* poses, double* pts, ba_summary* sm) {
   sm->status = 1;
   bool have_lin = false;
   double cost = 0;
+  int ninv_cur = 0;   // observations behind the cheirality gate at the current state
   for (; it < P.o.max_iters; ++it) {
     if (!have_lin) {  // re-linearise only after an accepted step (same state => same values)
       linearize(P, poses, pts, L);
       have_lin = true;
       cost = L.cost;
+      ninv_cur = L.n_invalid;
       if (it == 0) sm->initial_cost = cost;
       if (P.o.gtol > 0) {
         double gmax = 0;
@@ -663,9 +683,14 @@ int lm_solve(Problem& P, double* poses, double* pts, ba_summary* sm) {
     double tcost = cost, rho = 0;
     if (st.ok && st.model_decrease > 0) {
       apply_step(P, poses, pts, st, tposes.data(), tpts.data());
-      tcost = total_cost(P, tposes.data(), tpts.data(), nullptr);
+      int ninv_trial = 0;
+      tcost = total_cost(P, tposes.data(), tpts.data(), &ninv_trial);
       rho = (cost - tcost) / st.model_decrease;
-      accept = std::isfinite(tcost) && rho > kMinRatio;
+      // An observation behind the cheirality gate costs 0, so a step that pushes MORE observations behind it would be
+      // rewarded for discarding them: such a step is rejected like a failed evaluation and the radius shrinks (the
+      // behaviour of a Ceres cost functor that returns false for z < z_min).  n_invalid never grows.
+      accept = std::isfinite(tcost) && rho > kMinRatio && ninv_trial <= ninv_cur;
+      if (accept) ninv_cur = ninv_trial;
     }
     if (it < 64) sm->mu_hist[it] = mu;
     bool converged = false;

@@ -19,7 +19,7 @@ class Opts(C.Structure):
                 ("z_min", C.c_double), ("init_mu", C.c_double), ("ftol", C.c_double),
                 ("gtol", C.c_double), ("ptol", C.c_double), ("solver", C.c_int32),
                 ("pcg_max_iters", C.c_int32), ("pcg_tol", C.c_double), ("threads", C.c_int32),
-                ("pad_", C.c_int32)]
+                ("flags", C.c_int32)]
 
 
 class Summary(C.Structure):
@@ -31,9 +31,14 @@ class Summary(C.Structure):
 
 
 def make_opts(max_iters=10, loss="trivial", loss_scale=1.0, z_min=1e-3, init_mu=1e4, ftol=0.0,
-              gtol=0.0, ptol=0.0, solver="chol", pcg_max_iters=200, pcg_tol=1e-10, threads=1):
+              gtol=0.0, ptol=0.0, solver="chol", pcg_max_iters=200, pcg_tol=1e-10, threads=1, lin_once=False,
+              fast=False):
+    """lin_once: store r / w / J per observation at linearisation and re-use them in the Schur and back-substitution
+    passes (bit-identical results, fewer flops).  fast: run the -O3 -march=native -ffp-contract=fast build (timing only;
+    contraction changes the rounding, so the parity tests keep the strict build)."""
+    del fast
     return Opts(max_iters, {"trivial": 0, "huber": 1}[loss], loss_scale, z_min, init_mu, ftol, gtol,
-                ptol, {"chol": 0, "pcg": 1}[solver], pcg_max_iters, pcg_tol, threads, 0)
+                ptol, {"chol": 0, "pcg": 1}[solver], pcg_max_iters, pcg_tol, threads, 1 if lin_once else 0)
 
 
 def build(force=False):
@@ -44,8 +49,41 @@ def build(force=False):
     return so
 
 
-def lib():
-    global _LIB
+FAST_FLAGS = ["-O3", "-march=native", "-ffp-contract=fast", "-fopenmp", "-fPIC", "-std=c++17"]
+_FAST = None
+
+
+def build_fast(force=False):
+    """Timing-only build of the same source: -O3 -march=native, FMA contraction on.  Compiled ON THE MACHINE THAT
+    RUNS IT (the GPU box's host CPU differs from the build container's, so a -march=native binary must not travel):
+    the output is keyed by the CPU model and lives under oracle/_fast/ (git-ignored)."""
+    import hashlib
+    tag = hashlib.sha1(cpu_model().encode()).hexdigest()[:10]
+    d = os.path.join(_HERE, "_fast")
+    os.makedirs(d, exist_ok=True)
+    so, src = os.path.join(d, f"libba_cpu_fast_{tag}.so"), os.path.join(_HERE, "ba_cpu.cpp")
+    if force or not os.path.exists(so) or os.path.getmtime(so) < os.path.getmtime(src):
+        subprocess.check_call(["/usr/bin/g++", *FAST_FLAGS, "-shared", "-o", so, src])
+    return so
+
+
+def cpu_model():
+    try:
+        for line in open("/proc/cpuinfo"):
+            if line.startswith("model name"):
+                return line.split(":", 1)[1].strip()
+    except OSError:
+        pass
+    return "unknown"
+
+
+def lib(fast=False):
+    global _LIB, _FAST
+    if fast:
+        if _FAST is None:
+            _FAST = C.CDLL(build_fast())
+            _FAST.ba_cpu_index.restype = C.c_int64
+        return _FAST
     if _LIB is None:
         so = os.path.join(_HERE, "libba_cpu.so")
         if not os.path.exists(so):
@@ -71,7 +109,7 @@ def solve(p, **kw):
     poses = np.array(p.poses, np.float64, order="C", copy=True)
     pts = np.array(p.points, np.float64, order="C", copy=True)
     o, sm = make_opts(**kw), Summary()
-    rc = lib().ba_cpu_solve(C.c_int(p.nc), C.c_int(p.np_), C.c_int64(p.no), _p(poses, C.c_double),
+    rc = lib(kw.get("fast", False)).ba_cpu_solve(C.c_int(p.nc), C.c_int(p.np_), C.c_int64(p.no), _p(poses, C.c_double),
                             _p(pts, C.c_double), _p(oc, C.c_int32), _p(op, C.c_int32), _p(uv, C.c_float),
                             _p(fx, C.c_uint8), _p(intr, C.c_double), C.byref(o), C.byref(sm))
     if rc < 0:
@@ -89,7 +127,7 @@ def solve_batch(b, **kw):
     co = np.ascontiguousarray(b.cam_off, np.int32)
     po = np.ascontiguousarray(b.pt_off, np.int32)
     oo = np.ascontiguousarray(b.obs_off, np.int64)
-    rc = lib().ba_cpu_solve_batch(C.c_int(b.nb), _p(co, C.c_int32), _p(po, C.c_int32), _p(oo, C.c_int64),
+    rc = lib(kw.get("fast", False)).ba_cpu_solve_batch(C.c_int(b.nb), _p(co, C.c_int32), _p(po, C.c_int32), _p(oo, C.c_int64),
                                   _p(poses, C.c_double), _p(pts, C.c_double), _p(oc, C.c_int32),
                                   _p(op, C.c_int32), _p(uv, C.c_float), _p(fx, C.c_uint8),
                                   _p(intr, C.c_double), C.byref(o), sms)

@@ -124,7 +124,8 @@ def refine_pose(T_cw, X, uv, intr, max_iters=10, loss="trivial", loss_scale=1.0,
             model = 0.5 * (float(d @ (D * d)) / mu - float(g @ d))
             if model > 0.0:
                 rho_q = (cost - tc) / model
-                accept = bool(np.isfinite(tc) and rho_q > 1e-3)
+                # a step that pushes MORE observations behind the cheirality gate (they cost 0) is rejected
+                accept = bool(np.isfinite(tc) and rho_q > 1e-3 and int((~valid_t).sum()) <= ninv)
         if accept:
             if ftol > 0.0 and abs(cost - tc) <= ftol * cost:
                 stop = 2

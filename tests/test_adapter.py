@@ -89,7 +89,11 @@ def test_adapter_in_the_frame_loop_with_oracle_solver(loop_runs):
     sms = [s for s in ad.summaries if s is not None]
     assert len(sms) >= 10 and all(s.ok for s in sms)
     assert len(ad.window) == 6 and ad.window[-1] is vo.keyframe                         # the reference's own dict objects
-    assert np.mean([s.final_cost / s.initial_cost for s in sms]) < 0.9                  # BA lowers the window cost
+    # BA never raises a window's cost and lowers it on average.  (Windows of the real loop hold ~5 % wrong matches; a step
+    # that would push such a landmark behind a camera is rejected since round 2 -- n_invalid never grows -- so the
+    # decrease per 5-iteration call is smaller than it was when discarding observations counted as progress.)
+    assert all(s.final_cost <= s.initial_cost for s in sms) and all(s.n_invalid == 0 for s in sms)
+    assert np.mean([s.final_cost / s.initial_cost for s in sms]) < 0.98
     assert vo.initialized and len(traj) == len(out["plain"][2])                          # tracking never reset
     # landmarks of the previous keyframe carry ids (back-fill), so windows have multi-view tracks
     assert (ad.window[-2]["ids"] >= 0).sum() > 200

@@ -177,3 +177,31 @@ def test_lm_result_random_visibility_dense_cholesky(oracle):
     poses2, pts2 = ba.get()
     assert np.array_equal(poses, poses2) and np.array_equal(pts, pts2)
     ba.close()
+
+
+@pytest.mark.parametrize("mode", ["local", "random"])
+def test_c5_full_size_one_iteration_against_numpy_oracle(mode):
+    """BASELINE config 5 at its full size (1000 cameras / 200k landmarks / 1M observations, both visibilities): one LM
+    iteration of the engine -- S, g_red, the step delta_c and the trial cost -- against oracle/ba_numpy.py (sparse
+    algebra + LAPACK Cholesky of the 6000 x 6000 system; the C++ oracle's scalar dense Cholesky is too slow here).
+    `local` runs the substructured banded Cholesky, `random` the block-Jacobi PCG (stopping rule 1e-10 |b|)."""
+    from oracle import ba_numpy
+    from visualodometry_b200 import BAConfig, BundleAdjuster
+    p = synth.make_large(0, mode=mode)
+    assert (p.nc, p.np_, p.no) == (1000, 200_000, 1_000_000)
+    ba = BundleAdjuster(K_of(p), BAConfig(solver="auto"))
+    ba.set_problem(p.poses, p.points, p.obs_cam, p.obs_pt, p.obs_uv, p.fixed_cam)
+    st = ba_numpy.stage(p, mu=1e4)
+    n = st["S"].shape[0]
+    S = ba.dump("S", (n, n))
+    assert rel(S, st["S"]) <= 1e-10
+    assert rel(ba.dump("GRED", (n,)), st["gred"]) <= 1e-10
+    dc = ba.dump("DC", (n,))
+    assert rel(dc, st["dc"]) <= (1e-8 if mode == "local" else 1e-6)
+    # the engine's own linear solve, checked on its own system: |S dc + g_red| / |g_red|
+    res = np.linalg.norm(S @ dc + ba.dump("GRED", (n,))) / np.linalg.norm(st["gred"])
+    assert res <= (1e-10 if mode == "local" else 2e-10)
+    sc = ba.dump("SCALARS", (4,))
+    assert abs(sc[0] - st["cost"]) <= 1e-12 * st["cost"]
+    assert abs(sc[2] - st["trial_cost"]) <= 1e-8 * st["trial_cost"]
+    ba.close()

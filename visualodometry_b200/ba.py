@@ -40,12 +40,14 @@ class BAConfig:
     device: int = 0
     record_history: bool = False
     cluster: bool = True           # few windows: one 8-CTA cluster per window (latency path); False = one CTA per window
+    variant: str = "auto"          # "auto" | "small256" | "cluster8": force a window-kernel instantiation (tests)
 
     def to_options(self) -> _lib.Options:
         return _lib.Options(self.max_iters, {"trivial": 0, "huber": 1}[self.loss], self.loss_scale,
                             self.z_min, self.init_radius, self.ftol, self.gtol, self.ptol,
                             {"auto": 0, "chol": 1, "pcg": 2, "dense": 3}[self.solver], self.pcg_max_iters,
-                            self.pcg_tol, (1 if self.record_history else 0) | (0 if self.cluster else 2), 0)
+                            self.pcg_tol, (1 if self.record_history else 0) | (0 if self.cluster else 2)
+                            | {"auto": 0, "small256": 4, "cluster8": 8}[self.variant], 0)
 
 
 @dataclass
@@ -94,10 +96,10 @@ def _is_cuda_tensor(a):
 class _Arg:
     """Pointer + keep-alive for one array argument, host (numpy) or device (torch CUDA)."""
 
-    def __init__(self, a, np_dtype, torch_dtype, device_mode):
-        if device_mode:
+    def __init__(self, a, np_dtype, torch_dtype, device_mode, device=0):
+        if device_mode:   # on the ADJUSTER's device (config.device), not torch's current one
             t = a if isinstance(a, torch.Tensor) else torch.as_tensor(np.asarray(a))
-            t = t.to(device="cuda", dtype=getattr(torch, torch_dtype)).contiguous()
+            t = t.to(device=torch.device("cuda", device), dtype=getattr(torch, torch_dtype)).contiguous()
             self.keep, self.ptr = t, C.c_void_p(t.data_ptr())
         else:
             if torch is not None and isinstance(a, torch.Tensor):
@@ -161,9 +163,9 @@ class BundleAdjuster:
                     obs_off=None):
         """poses (Nc,12) [R|t] world->camera; batched when the CSR offsets are given."""
         dev = any(_is_cuda_tensor(a) for a in (poses, points, obs_cam, obs_pt, obs_uv))
-        a = [_Arg(poses, np.float64, "float64", dev), _Arg(points, np.float64, "float64", dev),
-             _Arg(obs_cam, np.int32, "int32", dev), _Arg(obs_pt, np.int32, "int32", dev),
-             _Arg(obs_uv, np.float32, "float32", dev), _Arg(fixed_cam, np.uint8, "uint8", dev)]
+        a = [_Arg(poses, np.float64, "float64", dev, self.config.device), _Arg(points, np.float64, "float64", dev, self.config.device),
+             _Arg(obs_cam, np.int32, "int32", dev, self.config.device), _Arg(obs_pt, np.int32, "int32", dev, self.config.device),
+             _Arg(obs_uv, np.float32, "float32", dev, self.config.device), _Arg(fixed_cam, np.uint8, "uint8", dev, self.config.device)]
         nc = int(np.prod(a[0].keep.shape)) // 12
         npts = int(np.prod(a[1].keep.shape)) // 3
         no = int(np.prod(a[2].keep.shape))
@@ -223,8 +225,8 @@ class BundleAdjuster:
             self._check(self._lib.b2ba_get(self._h, poses.ctypes.data, pts.ctypes.data, _lib.MEM_HOST), "b2ba_get")
             return poses, pts
         if device:
-            poses = torch.empty((nc, 12), dtype=torch.float64, device="cuda")
-            pts = torch.empty((npts, 3), dtype=torch.float64, device="cuda")
+            poses = torch.empty((nc, 12), dtype=torch.float64, device=torch.device("cuda", self.config.device))
+            pts = torch.empty((npts, 3), dtype=torch.float64, device=torch.device("cuda", self.config.device))
             self._check(self._lib.b2ba_get(self._h, poses.data_ptr(), pts.data_ptr(), _lib.MEM_DEVICE), "b2ba_get")
         else:
             poses, pts = np.empty((nc, 12)), np.empty((npts, 3))
@@ -241,10 +243,10 @@ class BundleAdjuster:
         P1 = np.ascontiguousarray(K @ np.asarray(T_cw1, np.float64)[:3, :])
         P2 = np.ascontiguousarray(K @ np.asarray(T_cw2, np.float64)[:3, :])
         dev = _is_cuda_tensor(pts1) or _is_cuda_tensor(pts2)
-        a, b = _Arg(pts1, np.float32, "float32", dev), _Arg(pts2, np.float32, "float32", dev)
+        a, b = _Arg(pts1, np.float32, "float32", dev, self.config.device), _Arg(pts2, np.float32, "float32", dev, self.config.device)
         dp = C.POINTER(C.c_double)
         if dev:
-            X = torch.empty((n, 3), dtype=torch.float64, device="cuda"); keep = torch.empty(n, dtype=torch.uint8, device="cuda")
+            X = torch.empty((n, 3), dtype=torch.float64, device=torch.device("cuda", self.config.device)); keep = torch.empty(n, dtype=torch.uint8, device=torch.device("cuda", self.config.device))
             xp, kp = C.c_void_p(X.data_ptr()), C.c_void_p(keep.data_ptr())
         else:
             X = np.empty((n, 3), np.float64); keep = np.empty(n, np.uint8)
@@ -301,12 +303,12 @@ class BundleAdjuster:
             T_cw = T_cw.detach().cpu().numpy()
         poses = poses_from_T(T_cw)
         nb = poses.shape[0]
-        a_pts, a_uv = _Arg(points, np.float64, "float64", dev), _Arg(obs_uv, np.float32, "float32", dev)
+        a_pts, a_uv = _Arg(points, np.float64, "float64", dev, self.config.device), _Arg(obs_uv, np.float32, "float32", dev, self.config.device)
         no = int(np.prod(a_pts.keep.shape)) // 3
         off = np.array([0, no], np.int64) if obs_off is None else np.ascontiguousarray(obs_off, np.int64)
         if off.shape != (nb + 1,) or int(off[-1]) != no or int(np.prod(a_uv.keep.shape)) != 2 * no:
             raise ValueError("refine_poses: obs_off must have B+1 entries ending at the observation count")
-        a_pose = _Arg(poses, np.float64, "float64", dev)
+        a_pose = _Arg(poses, np.float64, "float64", dev, self.config.device)
         sms = (_lib.Summary * max(nb, 1))()
         rc = self._lib.b2ba_refine_poses(self._h, nb, off.ctypes.data, a_pose.ptr, a_pts.ptr, a_uv.ptr,
                                          self.intr.ctypes.data_as(C.POINTER(C.c_double)), int(max_iters), sms,
@@ -330,12 +332,12 @@ class BundleAdjuster:
         ok is False when fewer than 6 inliers remain or the pose is not finite (the caller resets, `vo.py:142-143`)."""
         dev = any(_is_cuda_tensor(a) for a in (points, obs_uv))
         pose = poses_from_T(np.asarray(T_cw_prior, np.float64).reshape(1, 4, 4))
-        a_pts, a_uv = _Arg(points, np.float64, "float64", dev), _Arg(obs_uv, np.float32, "float32", dev)
+        a_pts, a_uv = _Arg(points, np.float64, "float64", dev, self.config.device), _Arg(obs_uv, np.float32, "float32", dev, self.config.device)
         n = int(np.prod(a_pts.keep.shape)) // 3
         if int(np.prod(a_uv.keep.shape)) != 2 * n:
             raise ValueError("track_pose: points (N,3) and obs_uv (N,2) required")
-        a_pose = _Arg(pose, np.float64, "float64", dev)
-        a_inl = _Arg(np.zeros(max(n, 1), np.uint8), np.uint8, "uint8", dev)
+        a_pose = _Arg(pose, np.float64, "float64", dev, self.config.device)
+        a_inl = _Arg(np.zeros(max(n, 1), np.uint8), np.uint8, "uint8", dev, self.config.device)
         cnt, sm = C.c_int32(0), _lib.Summary()
         rc = self._lib.b2ba_track_pose(self._h, n, a_pose.ptr, a_pts.ptr, a_uv.ptr,
                                        self.intr.ctypes.data_as(C.POINTER(C.c_double)), float(reproj_err), int(rounds),
@@ -357,12 +359,12 @@ class BundleAdjuster:
         Returns (ok, T_cw (4,4), inlier indices, BASummary, consensus of the winning hypothesis)."""
         dev = any(_is_cuda_tensor(a) for a in (points, obs_uv))
         pose = poses_from_T(np.asarray(T_cw_prior, np.float64).reshape(1, 4, 4))
-        a_pts, a_uv = _Arg(points, np.float64, "float64", dev), _Arg(obs_uv, np.float32, "float32", dev)
+        a_pts, a_uv = _Arg(points, np.float64, "float64", dev, self.config.device), _Arg(obs_uv, np.float32, "float32", dev, self.config.device)
         n = int(np.prod(a_pts.keep.shape)) // 3
         if int(np.prod(a_uv.keep.shape)) != 2 * n:
             raise ValueError("ransac_pose: points (N,3) and obs_uv (N,2) required")
-        a_pose = _Arg(pose, np.float64, "float64", dev)
-        a_inl = _Arg(np.zeros(max(n, 1), np.uint8), np.uint8, "uint8", dev)
+        a_pose = _Arg(pose, np.float64, "float64", dev, self.config.device)
+        a_inl = _Arg(np.zeros(max(n, 1), np.uint8), np.uint8, "uint8", dev, self.config.device)
         cnt, best, sm = C.c_int32(0), C.c_int32(0), _lib.Summary()
         rc = self._lib.b2ba_ransac_pose(self._h, n, a_pose.ptr, a_pts.ptr, a_uv.ptr,
                                         self.intr.ctypes.data_as(C.POINTER(C.c_double)), float(reproj_err), int(n_hyp),
@@ -385,9 +387,9 @@ class BundleAdjuster:
             sm = self.solve()
             poses_o, pts_o = self.get()
         else:
-            a = [_Arg(batch.poses, np.float64, "float64", False), _Arg(batch.points, np.float64, "float64", False),
-                 _Arg(batch.obs_cam, np.int32, "int32", False), _Arg(batch.obs_pt, np.int32, "int32", False),
-                 _Arg(batch.obs_uv, np.float32, "float32", False), _Arg(batch.fixed_cam, np.uint8, "uint8", False)]
+            a = [_Arg(batch.poses, np.float64, "float64", False, self.config.device), _Arg(batch.points, np.float64, "float64", False, self.config.device),
+                 _Arg(batch.obs_cam, np.int32, "int32", False, self.config.device), _Arg(batch.obs_pt, np.int32, "int32", False, self.config.device),
+                 _Arg(batch.obs_uv, np.float32, "float32", False, self.config.device), _Arg(batch.fixed_cam, np.uint8, "uint8", False, self.config.device)]
             co = np.ascontiguousarray(batch.cam_off, np.int32)
             po = np.ascontiguousarray(batch.pt_off, np.int32)
             oo = np.ascontiguousarray(batch.obs_off, np.int64)

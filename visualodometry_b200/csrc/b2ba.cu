@@ -27,7 +27,7 @@ enum Path { PATH_NONE = 0, PATH_WIN_SMALL, PATH_WIN_BIG, PATH_LARGE };
 }  // namespace
 
 struct b2ba {
-  int device = 0;
+  int device = 0, sms = 148;
   b2ba_options opt;
   std::string err;
   int B = 0, nc_tot = 0, np_tot = 0;
@@ -96,6 +96,18 @@ int cuda_fail(b2ba* h, cudaError_t e, const char* where) {
 }
 #define CU(x, where) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) return cuda_fail(h, e_, where); } while (0)
 
+// Every entry point runs on the handle's device and gives the caller's current device back on return (a torch
+// process keeps its own notion of the current device; the engine must not change it behind its back).
+struct DeviceGuard {
+  int prev = -1, dev;
+  cudaError_t err;
+  explicit DeviceGuard(int d) : dev(d) {
+    err = cudaGetDevice(&prev);
+    if (err == cudaSuccess && prev != dev) err = cudaSetDevice(dev);
+  }
+  ~DeviceGuard() { if (prev >= 0 && prev != dev) cudaSetDevice(prev); }
+};
+
 Params make_params(const b2ba* h, int max_iters) {
   Params P;
   P.fx = h->intr[0]; P.fy = h->intr[1]; P.cx = h->intr[2]; P.cy = h->intr[3];
@@ -136,8 +148,9 @@ WinData make_win(b2ba* h, bool hist, double* dbg) {
 int launch_window_path(const b2ba* h, const WinData& wd, const Params& P, cudaStream_t s) {
   static const bool cluster_on = [] { const char* e = std::getenv("B2BA_CLUSTER"); return !e || std::atoi(e) != 0; }();
   const bool clus = cluster_on && !(h->opt.flags & 2) && h->B <= 18;
-  if (h->path == PATH_WIN_SMALL) return clus ? launch_window_small_cluster(wd, P, s) : launch_window_small(wd, P, s);
-  return clus ? launch_window_big_cluster(wd, P, s) : launch_window_big(wd, P, s);
+  const int variant = ((h->opt.flags & 4) ? kWinSmall256 : 0) | ((h->opt.flags & 8) ? kWinCluster8 : 0);
+  if (h->path == PATH_WIN_SMALL) return clus ? launch_window_small_cluster(wd, P, s, variant) : launch_window_small(wd, P, s, variant);
+  return clus ? launch_window_big_cluster(wd, P, s, variant) : launch_window_big(wd, P, s);
 }
 
 cudaMemcpyKind in_kind(int mem) { return mem == B2BA_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice; }
@@ -188,6 +201,7 @@ LargeData make_large(b2ba* h, bool hist) {
   LargeData d;
   d.nc = h->nc_tot; d.np = h->np_tot; d.nfree = h->lix.nfree; d.n = 6 * h->lix.nfree;
   d.p_lo = h->p_lo; d.p_hi = h->p_hi; d.rank = h->rank; d.nranks = h->nranks;
+  d.sms = h->sms;
   d.pm = h->d_pm.p; d.pt_ptr = h->d_pt_ptr.p; d.cm = h->l_cm.p; d.cam_ptr = h->l_cam_ptr.p;
   d.fidx = h->lix.fidx.p; d.blk_ptr = h->lix.blk_ptr.p; d.blk_col = h->lix.blk_col.p; d.nblk = h->lix.nblk;
   d.frow_ptr = h->lix.frow_ptr.p; d.fcol = h->lix.fcol.p; d.fsrc = h->lix.fsrc.p;
@@ -316,8 +330,8 @@ int b2ba_create(b2ba_t** out, int device, const b2ba_options* opts) {
   int ndev = 0;
   cudaError_t e = cudaGetDeviceCount(&ndev);
   if (e != cudaSuccess || device < 0 || device >= ndev) return B2BA_E_CUDA;   // no CPU fallback
-  e = cudaSetDevice(device);
-  if (e != cudaSuccess) return B2BA_E_CUDA;
+  DeviceGuard dg_(device);
+  if (dg_.err != cudaSuccess) return B2BA_E_CUDA;
   {
     // the index builder's temporaries are stream-ordered allocations: keep them cached in the pool
     // between set_problem calls instead of returning them to the driver at every synchronisation
@@ -329,6 +343,7 @@ int b2ba_create(b2ba_t** out, int device, const b2ba_options* opts) {
   }
   b2ba* h = new b2ba();
   h->device = device;
+  cudaDeviceGetAttribute(&h->sms, cudaDevAttrMultiProcessorCount, device);
   if (opts) h->opt = *opts; else b2ba_default_options(&h->opt);
   *out = h;
   return B2BA_OK;
@@ -336,7 +351,7 @@ int b2ba_create(b2ba_t** out, int device, const b2ba_options* opts) {
 
 void b2ba_destroy(b2ba_t* h) {
   if (!h) return;
-  cudaSetDevice(h->device);
+  DeviceGuard dg_(h->device);
   for (b2ba* k : h->kids) b2ba_destroy(k);
   for (cudaEvent_t e : h->ev_in) cudaEventDestroy(e);
   for (cudaEvent_t e : h->ev_done) cudaEventDestroy(e);
@@ -366,7 +381,7 @@ int b2ba_set_problem_batch(b2ba_t* h, int32_t B, const int32_t* cam_off, const i
   const long long no = obs_off[B];
   if (no > 0 && (!obs_cam || !obs_pt || !obs_uv)) return fail(h, B2BA_E_INVALID, "null observation arrays");
   if (no >= (1ll << 31)) return fail(h, B2BA_E_UNSUPPORTED, "more than 2^31 observations per handle");
-  CU(cudaSetDevice(h->device), "cudaSetDevice");
+  DeviceGuard dg_(h->device); CU(dg_.err, "cudaSetDevice");
   h->B = B; h->nc_tot = cam_off[B]; h->np_tot = pt_off[B]; h->no = no;
   h->solved = false;
   std::memcpy(h->intr, intr, 4 * sizeof(double));
@@ -453,7 +468,7 @@ int b2ba_set_problem(b2ba_t* h, int32_t Nc, int32_t Np, int64_t No, const double
 
 int b2ba_set_state(b2ba_t* h, const double* poses_cw, const double* points, int mem) {
   if (!h || h->path == PATH_NONE) return fail(h, B2BA_E_STATE, "no problem set");
-  CU(cudaSetDevice(h->device), "cudaSetDevice");
+  DeviceGuard dg_(h->device); CU(dg_.err, "cudaSetDevice");
   const cudaMemcpyKind k = in_kind(mem);
   if (poses_cw) {
     CU(cudaMemcpy(h->d_poses.p, poses_cw, (size_t)h->nc_tot * 12 * sizeof(double), k), "copy poses");
@@ -474,7 +489,7 @@ int b2ba_set_state(b2ba_t* h, const double* poses_cw, const double* points, int 
 
 int b2ba_reset(b2ba_t* h) {
   if (!h || h->path == PATH_NONE) return fail(h, B2BA_E_STATE, "no problem set");
-  CU(cudaSetDevice(h->device), "cudaSetDevice");
+  DeviceGuard dg_(h->device); CU(dg_.err, "cudaSetDevice");
   cudaStream_t s = h->last_stream;
   CU(cudaMemcpyAsync(h->d_poses.p, h->d_poses0.p, (size_t)h->nc_tot * 12 * sizeof(double), cudaMemcpyDeviceToDevice, s), "reset poses");
   CU(cudaMemcpyAsync(h->d_pts0.p, h->d_ptsinit.p, (size_t)h->np_tot * 3 * sizeof(double), cudaMemcpyDeviceToDevice, s), "reset points");
@@ -483,7 +498,7 @@ int b2ba_reset(b2ba_t* h) {
 
 int b2ba_get_summaries(b2ba_t* h, b2ba_summary* summaries) {
   if (!h || !h->solved || !summaries) return fail(h, B2BA_E_STATE, "no solve to report");
-  CU(cudaSetDevice(h->device), "cudaSetDevice");
+  DeviceGuard dg_(h->device); CU(dg_.err, "cudaSetDevice");
   CU(cudaMemcpyAsync(summaries, h->d_summ.p, (size_t)h->B * sizeof(b2ba_summary), cudaMemcpyDeviceToHost, h->last_stream), "read summaries");
   CU(cudaStreamSynchronize(h->last_stream), "solve");
   return B2BA_OK;
@@ -491,7 +506,7 @@ int b2ba_get_summaries(b2ba_t* h, b2ba_summary* summaries) {
 
 int b2ba_solve(b2ba_t* h, int32_t max_iters, b2ba_summary* summaries, void* cuda_stream) {
   if (!h || h->path == PATH_NONE) return fail(h, B2BA_E_STATE, "no problem set");
-  CU(cudaSetDevice(h->device), "cudaSetDevice");
+  DeviceGuard dg_(h->device); CU(dg_.err, "cudaSetDevice");
   cudaStream_t s = (cudaStream_t)cuda_stream;
   h->last_stream = s;
   const Params P = make_params(h, max_iters);
@@ -522,7 +537,7 @@ int b2ba_solve(b2ba_t* h, int32_t max_iters, b2ba_summary* summaries, void* cuda
 
 int b2ba_get(b2ba_t* h, double* poses_cw, double* points, int mem) {
   if (!h || h->path == PATH_NONE) return fail(h, B2BA_E_STATE, "no problem set");
-  CU(cudaSetDevice(h->device), "cudaSetDevice");
+  DeviceGuard dg_(h->device); CU(dg_.err, "cudaSetDevice");
   cudaStream_t s = h->last_stream;
   const cudaMemcpyKind k = out_kind(mem);
   if (poses_cw) CU(cudaMemcpyAsync(poses_cw, h->d_poses.p, (size_t)h->nc_tot * 12 * sizeof(double), k, s), "read poses");
@@ -542,7 +557,7 @@ int b2ba_get(b2ba_t* h, double* poses_cw, double* points, int mem) {
 int b2ba_reproj_errors(b2ba_t* h, double* err, int mem) {
   if (!h || h->path == PATH_NONE) return fail(h, B2BA_E_STATE, "no problem set");
   if (!err && h->no > 0) return fail(h, B2BA_E_INVALID, "reproj_errors: null destination");
-  CU(cudaSetDevice(h->device), "cudaSetDevice");
+  DeviceGuard dg_(h->device); CU(dg_.err, "cudaSetDevice");
   cudaStream_t s = h->last_stream;
   if (h->no == 0) return B2BA_OK;
   const double* pts_lm = h->d_pts0.p;
@@ -565,7 +580,7 @@ int b2ba_triangulate(b2ba_t* h, int32_t N, const double P1[12], const double P2[
                      const float* uv2, double min_depth, double max_reproj_err, double* X, uint8_t* keep, int mem) {
   if (!h) return B2BA_E_INVALID;
   if (N < 0 || !P1 || !P2 || (N > 0 && (!uv1 || !uv2 || !X || !keep))) return fail(h, B2BA_E_INVALID, "triangulate: null argument");
-  CU(cudaSetDevice(h->device), "cudaSetDevice");
+  DeviceGuard dg_(h->device); CU(dg_.err, "cudaSetDevice");
   if (N == 0) return B2BA_OK;
   cudaStream_t s = nullptr;
   if (mem == B2BA_MEM_DEVICE) {
@@ -596,7 +611,7 @@ int b2ba_refine_poses(b2ba_t* h, int32_t B, const int64_t* obs_off, double* pose
     if (obs_off[b + 1] < obs_off[b] || obs_off[0] != 0) return fail(h, B2BA_E_INVALID, "refine_poses: obs_off must start at 0 and be non-decreasing");
   const int64_t no = B > 0 ? obs_off[B] : 0;
   if (no > 0 && (!points || !obs_uv)) return fail(h, B2BA_E_INVALID, "refine_poses: null argument");
-  CU(cudaSetDevice(h->device), "cudaSetDevice");
+  DeviceGuard dg_(h->device); CU(dg_.err, "cudaSetDevice");
   h->r_nb = B;
   if (B == 0) return B2BA_OK;
   const cudaMemcpyKind ki = in_kind(mem), ko = out_kind(mem);
@@ -644,7 +659,7 @@ int b2ba_track_pose(b2ba_t* h, int64_t N, double* pose_cw, const double* points,
   if (N < 0 || !pose_cw || !intr || !n_inliers || (N > 0 && (!points || !obs_uv || !inliers)))
     return fail(h, B2BA_E_INVALID, "track_pose: null argument");
   if (!(reproj_err > 0.0) || rounds < 1) return fail(h, B2BA_E_INVALID, "track_pose: reproj_err > 0 and rounds >= 1 required");
-  CU(cudaSetDevice(h->device), "cudaSetDevice");
+  DeviceGuard dg_(h->device); CU(dg_.err, "cudaSetDevice");
   const cudaMemcpyKind ki = in_kind(mem), ko = out_kind(mem);
   cudaStream_t s = nullptr;
   const size_t no = (size_t)N;
@@ -693,7 +708,7 @@ int b2ba_ransac_pose(b2ba_t* h, int64_t N, double* pose_cw, const double* points
     if (N > 0 && mem == B2BA_MEM_HOST) std::memset(inliers, 0, (size_t)N);
     return B2BA_NUMERICAL_FAILURE;
   }
-  CU(cudaSetDevice(h->device), "cudaSetDevice");
+  DeviceGuard dg_(h->device); CU(dg_.err, "cudaSetDevice");
   const cudaMemcpyKind ki = in_kind(mem), ko = out_kind(mem);
   cudaStream_t s = nullptr;
   const size_t no = (size_t)N, nh = (size_t)n_hyp;
@@ -746,11 +761,12 @@ int b2ba_optimize_batch(b2ba_t* h, int32_t B, const int32_t* cam_off, const int3
       !out_points || !summaries)
     return fail(h, B2BA_E_INVALID, "optimize_batch: null argument or B < 1");
   if (h->nranks > 1) return fail(h, B2BA_E_UNSUPPORTED, "optimize_batch is single-GPU (windows shard across ranks on the host side)");
+  if (cam_off[0] != 0 || pt_off[0] != 0 || obs_off[0] != 0) return fail(h, B2BA_E_INVALID, "offsets must start at 0");
   for (int b = 0; b < B; ++b)
     if (cam_off[b + 1] < cam_off[b] || pt_off[b + 1] < pt_off[b] || obs_off[b + 1] < obs_off[b])
       return fail(h, B2BA_E_INVALID, "offsets must be non-decreasing");
   if (obs_off[B] > 0 && (!obs_cam || !obs_pt || !obs_uv)) return fail(h, B2BA_E_INVALID, "null observation arrays");
-  CU(cudaSetDevice(h->device), "cudaSetDevice");
+  DeviceGuard dg_(h->device); CU(dg_.err, "cudaSetDevice");
   if (!h->pipe_copy) {
     CU(cudaStreamCreateWithFlags(&h->pipe_copy, cudaStreamNonBlocking), "stream");
     CU(cudaStreamCreateWithFlags(&h->pipe_solve, cudaStreamNonBlocking), "stream");
@@ -816,6 +832,16 @@ int b2ba_optimize_batch(b2ba_t* h, int32_t B, const int32_t* cam_off, const int3
   int* st_pt = st_cam + B + K;
   const Params P = make_params(h, max_iters);
   h->path = PATH_NONE;                       // results live in the caller's buffers, not in this handle
+  h->solved = false;
+  // From the first enqueue on, copies and kernels of earlier chunks read the caller's inputs and write the caller's
+  // outputs asynchronously: EVERY exit -- errors included -- first waits for all four streams, so that no work of this
+  // call touches a caller buffer after it has returned.
+  auto bail = [&](int rc) {
+    cudaStreamSynchronize(h->pipe_copy); cudaStreamSynchronize(h->pipe_solve);
+    cudaStreamSynchronize(h->pipe_solve2); cudaStreamSynchronize(h->pipe_back);
+    return rc;
+  };
+#define CUB(x, where) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) return bail(cuda_fail(h, e_, where)); } while (0)
   size_t stpos = 0;
   for (int c = 0; c < K; ++c) {
     b2ba* k = h->kids[c];
@@ -824,7 +850,7 @@ int b2ba_optimize_batch(b2ba_t* h, int32_t B, const int32_t* cam_off, const int3
     const int w0 = cut[c], w1 = cut[c + 1], nb = w1 - w0;
     const size_t c0 = cam_off[w0], nc = cam_off[w1] - c0, p0 = pt_off[w0], np = pt_off[w1] - p0;
     const long long o0 = obs_off[w0], no = obs_off[w1] - o0;
-    if (no >= (1ll << 31)) return fail(h, B2BA_E_UNSUPPORTED, "more than 2^31 observations per chunk");
+    if (no >= (1ll << 31)) return bail(fail(h, B2BA_E_UNSUPPORTED, "more than 2^31 observations per chunk"));
     k->B = nb; k->nc_tot = (int)nc; k->np_tot = (int)np; k->no = no; k->path = path;
     std::memcpy(k->intr, intr, 4 * sizeof(double));
     int* sc = st_cam + stpos; int* sp = st_pt + stpos; long long* so = st_obs + stpos;
@@ -832,49 +858,52 @@ int b2ba_optimize_batch(b2ba_t* h, int32_t B, const int32_t* cam_off, const int3
     for (int b = 0; b <= nb; ++b) {
       sc[b] = cam_off[w0 + b] - (int)c0; sp[b] = pt_off[w0 + b] - (int)p0; so[b] = obs_off[w0 + b] - o0;
     }
-    CU(k->d_cam_off.alloc(nb + 1), "alloc"); CU(k->d_pt_off.alloc(nb + 1), "alloc"); CU(k->d_obs_off.alloc(nb + 1), "alloc");
-    CU(k->d_fixed.alloc(nc), "alloc"); CU(k->d_poses.alloc(nc * 12), "alloc");
-    CU(k->d_pts0.alloc(np * 3), "alloc"); CU(k->d_pts1.alloc(np * 3), "alloc"); CU(k->d_scratch.alloc(np * kPtScratch), "alloc");
-    CU(k->d_obs_cam.alloc(no), "alloc"); CU(k->d_obs_pt.alloc(no), "alloc"); CU(k->d_uv.alloc(no), "alloc");
-    CU(k->d_pm.alloc(no), "alloc"); CU(k->d_cm.alloc(no), "alloc");
-    CU(k->d_pt_ptr.alloc(np + 1), "alloc"); CU(k->d_cam_ptr.alloc(nc + 1), "alloc"); CU(k->d_flags.alloc(2), "alloc");
-    CU(k->d_sched.alloc(np), "alloc");
-    CU(k->d_summ.alloc(nb), "alloc");
+    CUB(k->d_cam_off.alloc(nb + 1), "alloc"); CUB(k->d_pt_off.alloc(nb + 1), "alloc"); CUB(k->d_obs_off.alloc(nb + 1), "alloc");
+    CUB(k->d_fixed.alloc(nc), "alloc"); CUB(k->d_poses.alloc(nc * 12), "alloc");
+    CUB(k->d_pts0.alloc(np * 3), "alloc"); CUB(k->d_pts1.alloc(np * 3), "alloc"); CUB(k->d_scratch.alloc(np * kPtScratch), "alloc");
+    CUB(k->d_obs_cam.alloc(no), "alloc"); CUB(k->d_obs_pt.alloc(no), "alloc"); CUB(k->d_uv.alloc(no), "alloc");
+    CUB(k->d_pm.alloc(no), "alloc"); CUB(k->d_cm.alloc(no), "alloc");
+    CUB(k->d_pt_ptr.alloc(np + 1), "alloc"); CUB(k->d_cam_ptr.alloc(nc + 1), "alloc"); CUB(k->d_flags.alloc(2), "alloc");
+    CUB(k->d_sched.alloc(np), "alloc");
+    CUB(k->d_summ.alloc(nb), "alloc");
     cudaStream_t cs = h->pipe_copy, ks = (c & 1) ? h->pipe_solve2 : h->pipe_solve, bs = h->pipe_back;
     const cudaMemcpyKind hd = cudaMemcpyHostToDevice, dh = cudaMemcpyDeviceToHost;
     // nothing of an earlier call is in flight: every call ends with a synchronisation of all streams
-    CU(cudaMemcpyAsync(k->d_cam_off.p, sc, (nb + 1) * sizeof(int), hd, cs), "copy");
-    CU(cudaMemcpyAsync(k->d_pt_off.p, sp, (nb + 1) * sizeof(int), hd, cs), "copy");
-    CU(cudaMemcpyAsync(k->d_obs_off.p, so, (nb + 1) * sizeof(long long), hd, cs), "copy");
-    CU(cudaMemcpyAsync(k->d_fixed.p, fixed_cam + c0, nc, hd, cs), "copy");
-    CU(cudaMemcpyAsync(k->d_poses.p, poses_cw + c0 * 12, nc * 12 * sizeof(double), hd, cs), "copy");
+    CUB(cudaMemcpyAsync(k->d_cam_off.p, sc, (nb + 1) * sizeof(int), hd, cs), "copy");
+    CUB(cudaMemcpyAsync(k->d_pt_off.p, sp, (nb + 1) * sizeof(int), hd, cs), "copy");
+    CUB(cudaMemcpyAsync(k->d_obs_off.p, so, (nb + 1) * sizeof(long long), hd, cs), "copy");
+    CUB(cudaMemcpyAsync(k->d_fixed.p, fixed_cam + c0, nc, hd, cs), "copy");
+    CUB(cudaMemcpyAsync(k->d_poses.p, poses_cw + c0 * 12, nc * 12 * sizeof(double), hd, cs), "copy");
     k->sched_order = np > 0;   // landmarks arrive in the caller's order (pts1) and are put into schedule order (pts0)
-    CU(cudaMemcpyAsync(k->sched_order ? k->d_pts1.p : k->d_pts0.p, points + p0 * 3, np * 3 * sizeof(double), hd, cs), "copy");
+    CUB(cudaMemcpyAsync(k->sched_order ? k->d_pts1.p : k->d_pts0.p, points + p0 * 3, np * 3 * sizeof(double), hd, cs), "copy");
     if (no) {
-      CU(cudaMemcpyAsync(k->d_obs_cam.p, obs_cam + o0, no * sizeof(int), hd, cs), "copy");
-      CU(cudaMemcpyAsync(k->d_obs_pt.p, obs_pt + o0, no * sizeof(int), hd, cs), "copy");
-      CU(cudaMemcpyAsync(k->d_uv.p, obs_uv + 2 * o0, no * sizeof(float2), hd, cs), "copy");
+      CUB(cudaMemcpyAsync(k->d_obs_cam.p, obs_cam + o0, no * sizeof(int), hd, cs), "copy");
+      CUB(cudaMemcpyAsync(k->d_obs_pt.p, obs_pt + o0, no * sizeof(int), hd, cs), "copy");
+      CUB(cudaMemcpyAsync(k->d_uv.p, obs_uv + 2 * o0, no * sizeof(float2), hd, cs), "copy");
     }
-    CU(cudaEventRecord(h->ev_in[c], cs), "event");
-    CU(cudaStreamWaitEvent(ks, h->ev_in[c], 0), "wait");
+    CUB(cudaEventRecord(h->ev_in[c], cs), "event");
+    CUB(cudaStreamWaitEvent(ks, h->ev_in[c], 0), "wait");
     IndexOut io{k->d_pm.p, k->d_pt_ptr.p, k->d_cm.p, k->d_cam_ptr.p, k->d_flags.p, k->sched_order ? k->d_sched.p : nullptr};
     int rc = build_index(make_index_in(k), io, ks);
-    if (rc) return cuda_fail(h, (cudaError_t)rc, "build_index");
-    if (k->sched_order && (rc = permute_pts(k, k->d_pts1.p, k->d_pts0.p, true, ks)) != 0) return cuda_fail(h, (cudaError_t)rc, "permute");
+    if (rc) return bail(cuda_fail(h, (cudaError_t)rc, "build_index"));
+    if (k->sched_order && (rc = permute_pts(k, k->d_pts1.p, k->d_pts0.p, true, ks)) != 0) return bail(cuda_fail(h, (cudaError_t)rc, "permute"));
     rc = launch_window_path(k, make_win(k, false, nullptr), P, ks);
-    if (rc) return cuda_fail(h, (cudaError_t)rc, "launch");
-    if (k->sched_order && (rc = permute_pts(k, k->d_pts0.p, k->d_pts1.p, false, ks)) != 0) return cuda_fail(h, (cudaError_t)rc, "permute");
-    CU(cudaEventRecord(h->ev_done[c], ks), "event");
-    CU(cudaStreamWaitEvent(bs, h->ev_done[c], 0), "wait");
-    CU(cudaMemcpyAsync(out_poses_cw + c0 * 12, k->d_poses.p, nc * 12 * sizeof(double), dh, bs), "read");
-    CU(cudaMemcpyAsync(out_points + p0 * 3, k->sched_order ? k->d_pts1.p : k->d_pts0.p, np * 3 * sizeof(double), dh, bs), "read");
-    CU(cudaMemcpyAsync(st_summ + w0, k->d_summ.p, nb * sizeof(b2ba_summary), dh, bs), "read");
-    CU(cudaMemcpyAsync(h->pinned_flags + 2 * c, k->d_flags.p, 2 * sizeof(int), dh, bs), "read");
+    if (rc) return bail(cuda_fail(h, (cudaError_t)rc, "launch"));
+    if (k->sched_order && (rc = permute_pts(k, k->d_pts0.p, k->d_pts1.p, false, ks)) != 0) return bail(cuda_fail(h, (cudaError_t)rc, "permute"));
+    CUB(cudaEventRecord(h->ev_done[c], ks), "event");
+    CUB(cudaStreamWaitEvent(bs, h->ev_done[c], 0), "wait");
+    CUB(cudaMemcpyAsync(out_poses_cw + c0 * 12, k->d_poses.p, nc * 12 * sizeof(double), dh, bs), "read");
+    CUB(cudaMemcpyAsync(out_points + p0 * 3, k->sched_order ? k->d_pts1.p : k->d_pts0.p, np * 3 * sizeof(double), dh, bs), "read");
+    CUB(cudaMemcpyAsync(st_summ + w0, k->d_summ.p, nb * sizeof(b2ba_summary), dh, bs), "read");
+    CUB(cudaMemcpyAsync(h->pinned_flags + 2 * c, k->d_flags.p, 2 * sizeof(int), dh, bs), "read");
   }
-  CU(cudaStreamSynchronize(h->pipe_copy), "optimize_batch");
-  CU(cudaStreamSynchronize(h->pipe_solve), "optimize_batch");
-  CU(cudaStreamSynchronize(h->pipe_solve2), "optimize_batch");
-  CU(cudaStreamSynchronize(h->pipe_back), "optimize_batch");
+#undef CUB
+  {
+    const cudaError_t e0 = cudaStreamSynchronize(h->pipe_copy), e1 = cudaStreamSynchronize(h->pipe_solve),
+                      e2 = cudaStreamSynchronize(h->pipe_solve2), e3 = cudaStreamSynchronize(h->pipe_back);
+    const cudaError_t ee = e0 != cudaSuccess ? e0 : e1 != cudaSuccess ? e1 : e2 != cudaSuccess ? e2 : e3;
+    if (ee != cudaSuccess) return cuda_fail(h, ee, "optimize_batch");
+  }
   for (int c = 0; c < K; ++c) {
     if (h->pinned_flags[2 * c]) return fail(h, B2BA_E_INVALID, "observation index out of range");
     if (h->pinned_flags[2 * c + 1]) return fail(h, B2BA_E_DUPLICATE, "duplicate (camera, point) observation");
@@ -889,7 +918,7 @@ int b2ba_create_comm(b2ba_t* h, const void* nccl_unique_id, int rank, int nranks
   if (!h || !nccl_unique_id || nranks < 1 || rank < 0 || rank >= nranks) return fail(h, B2BA_E_INVALID, "create_comm: bad arguments");
   NcclApi& api = nccl_api();
   if (!api.ok) return fail(h, B2BA_E_NCCL, "libnccl.so.2 could not be loaded");
-  CU(cudaSetDevice(h->device), "cudaSetDevice");
+  DeviceGuard dg_(h->device); CU(dg_.err, "cudaSetDevice");
   if (h->nccl_comm) { api.CommDestroy(h->nccl_comm); h->nccl_comm = nullptr; }
   NcclApi::UniqueId id;
   std::memcpy(&id, nccl_unique_id, sizeof(id));
@@ -964,7 +993,7 @@ static int canonical_inputs(b2ba* h, bool point_major, std::vector<int>& ptr, st
 int64_t b2ba_dump(b2ba_t* h, int what, void* dst, int64_t bytes) {
   const bool pose_hist = what >= B2BA_D_POSE_HIST_COST && what <= B2BA_D_POSE_HIST_ACCEPT;   // needs no problem
   if (!h || !dst || (h->path == PATH_NONE && !pose_hist)) return fail(h, B2BA_E_STATE, "no problem set");
-  CU(cudaSetDevice(h->device), "cudaSetDevice");
+  DeviceGuard dg_(h->device); CU(dg_.err, "cudaSetDevice");
   CU(cudaDeviceSynchronize(), "sync");
   const size_t no = (size_t)h->no;
   switch (what) {

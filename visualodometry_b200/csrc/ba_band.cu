@@ -543,15 +543,15 @@ int large_band_solve(const LargeData& d, cudaStream_t st) {
     else band_forward_kernel<128><<<chunks, 128, sm, st>>>(d.ctrl, sys, chunks);
   };
   BandSys s{d.band, d.band_ws + pl.off_rhs, d.binv, N, w, pl.nr};
-  band_fill_kernel<<<296, 256, 0, st>>>(d, s, P);
-  band_fill_rhs_kernel<<<296, 256, 0, st>>>(d, s, P);
+  band_fill_kernel<<<2 * d.sms, 256, 0, st>>>(d, s, P);
+  band_fill_rhs_kernel<<<2 * d.sms, 256, 0, st>>>(d, s, P);
   forward(s, P, fwd_smem(w, pl.nr));
   if (P > 1) {
     double* gram = d.band_ws + pl.off_gram;
     BandSys t{d.band_ws + pl.off_tband, d.band_ws + pl.off_trhs, d.band_ws + pl.off_tbinv, pl.Nt, pl.wt, 1};
     double* xsep = d.band_ws + pl.off_xsep;
     band_gram_kernel<<<dim3(P, (pl.nr + 3) / 4), kGramThreads, 0, st>>>(d.ctrl, s, P, gram);
-    band_sep_assemble_kernel<<<148, 256, 0, st>>>(d, s, P, gram, t);
+    band_sep_assemble_kernel<<<d.sms, 256, 0, st>>>(d, s, P, gram, t);
     forward(t, 1, fwd_smem(pl.wt, 1));
     band_backward_kernel<<<1, kBandThreads, bwd_smem(pl.wt), st>>>(d.ctrl, t, 1, nullptr, xsep);
     band_backward_kernel<<<P, kBandThreads, bwd_smem(w), st>>>(d.ctrl, s, P, xsep, d.dc);

@@ -413,7 +413,7 @@ int large_dense_solve(const LargeData& d, cudaStream_t st) {
   static const int mode = getenv("B2BA_DENSE_MODE") ? atoi(getenv("B2BA_DENSE_MODE")) : 2;
   const int npad = d.dense_ld, nb = npad / NB;
   dense_zero_kernel<<<dim3(nb, nb + 1), 256, 0, st>>>(d.ctrl, d.dense, npad);
-  dense_fill_kernel<<<296, 256, 0, st>>>(d);
+  dense_fill_kernel<<<2 * d.sms, 256, 0, st>>>(d);
   if (mode == 0) {
     for (int c0 = 0; c0 < npad; c0 += NB) {
       launch_panel(d, c0, st);

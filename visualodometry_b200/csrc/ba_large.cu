@@ -990,7 +990,8 @@ __global__ void large_control_kernel(LargeData d, Params P, const double* sums) 
   double rho = 0.0;
   if (step_ok && model > 0.0) {
     rho = (c->cost - tc) / model;
-    accept = (isfinite(tc) && rho > kMinRatio) ? 1 : 0;
+    // a step that pushes MORE observations behind the cheirality gate (they cost 0) is rejected like a failed one
+    accept = (isfinite(tc) && rho > kMinRatio && sums[5] <= c->cur_ninv) ? 1 : 0;
   }
   if (P.gtol > 0.0 && c->fresh_lin && gm <= P.gtol) { c->status = B2BA_CONVERGED; c->stop = 1; c->accept = 0; return; }
   if (accept) {
@@ -1077,7 +1078,7 @@ int large_iteration(const LargeData& d, const Params& P, int pcg_max_iters, doub
   if (d.nc > 0) large_cam_kernel<<<d.nc, kCamThreads, 0, s>>>(d, P);
   large_cam_finish_kernel<<<1, 64, 0, s>>>(d);
   if (ar && (rc = ar(ar_user, d.lin_part, d.lin, d.lin_count(), s)) != 0) return rc;
-  large_init_S_kernel<<<296, 256, 0, s>>>(d);
+  large_init_S_kernel<<<2 * d.sms, 256, 0, s>>>(d);
   large_init_diag_kernel<<<(d.nc + 127) / 128 + 1, 128, 0, s>>>(d);
   const int npl = d.p_hi - d.p_lo;
   if (npl > 0) {
@@ -1118,7 +1119,7 @@ int large_iteration(const LargeData& d, const Params& P, int pcg_max_iters, doub
     sums = d.sums_part + 8;
   }
   large_control_kernel<<<1, 32, 0, s>>>(d, P, sums);
-  large_commit_kernel<<<148, 256, 0, s>>>(d);
+  large_commit_kernel<<<d.sms, 256, 0, s>>>(d);
   return (int)cudaGetLastError();
 }
 

@@ -25,6 +25,7 @@ struct LargeData {
   int nc, np, nfree, n;
   int p_lo, p_hi;                  // this rank's landmark range (whole problem on one GPU)
   int rank, nranks;
+  int sms;                         // SM count of the handle's device (grid sizing)
   const ObsRec* pm;                // point-major stream of the WHOLE problem (idx = camera)
   const int* pt_ptr;               // np+1
   const ObsRec* cm;                // camera-major stream of the LOCAL observations (idx = point)

@@ -141,7 +141,8 @@ __device__ void pose_lm_run(const PoseData& d, const Params& P, int b, const uns
     double rho = 0.0;
     if (step_ok && model > 0.0) {
       rho = (cost - tc) / model;
-      accept = (isfinite(tc) && rho > kMinRatio) ? 1 : 0;
+      // a step that pushes MORE observations behind the cheirality gate (they cost 0) is rejected like a failed one
+      accept = (isfinite(tc) && rho > kMinRatio && (int)tri[1] <= ninv) ? 1 : 0;
     }
     if (P.gtol > 0.0 && fresh && gm <= P.gtol) { status = B2BA_CONVERGED; break; }   // before taking the step
     if (accept) {

@@ -19,6 +19,7 @@
 #include <cooperative_groups.h>
 
 #include <cstdlib>
+#include <mutex>
 #include <utility>
 
 namespace b2 {
@@ -850,7 +851,8 @@ window_lm_kernel(const WinData d, const Params P) {
       double rho = 0.0;
       if (step_ok && model > 0.0) {
         rho = (cost - tc) / model;
-        accept = (isfinite(tc) && rho > kMinRatio) ? 1 : 0;
+        // a step that pushes MORE observations behind the cheirality gate (they cost 0) is rejected like a failed one
+        accept = (isfinite(tc) && rho > kMinRatio && (int)ninv <= ninv_cur) ? 1 : 0;
       }
       // gradient test belongs to the linearisation: stop BEFORE taking this step (not counted)
       if (P.gtol > 0.0 && fresh_lin && gm <= P.gtol) { accept = 0; stop = -1; }
@@ -925,19 +927,31 @@ using CfgBigC = WinCfg<16, 16, 16, 32, kMaxCam, 1, kClusterSize>;      // latenc
 using CfgSmallC16 = WinCfg<7, 8, 4, 64, kSmallMaxCam, 1, 16>;          // <= 8 windows: 16 CTAs (non-portable cluster size)
 using CfgBigC16 = WinCfg<16, 16, 16, 32, kMaxCam, 1, 16>;
 
+// cudaFuncSetAttribute applies to the CURRENT device's copy of the kernel: the opt-in (dynamic shared memory above
+// 48 KB, non-portable cluster size) is done once per (instantiation, device), under a mutex -- handles on different
+// devices of one process are independent (include/b2ba.h)
+template <class Cfg, int LOSS>
+static int configure_once() {
+  static std::mutex mtx;
+  static bool configured[64] = {};
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return (int)e;
+  std::lock_guard<std::mutex> lock(mtx);
+  if (dev >= 0 && dev < 64 && configured[dev]) return 0;
+  e = cudaFuncSetAttribute(window_lm_kernel<Cfg, LOSS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM);
+  if (e != cudaSuccess) return (int)e;
+  if (Cfg::CS > 8) {
+    e = cudaFuncSetAttribute(window_lm_kernel<Cfg, LOSS>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+    if (e != cudaSuccess) return (int)e;
+  }
+  if (dev >= 0 && dev < 64) configured[dev] = true;
+  return 0;
+}
+
 template <class Cfg, int LOSS>
 static int launch_l(const WinData& d, const Params& p, cudaStream_t s) {
-  static bool configured = false;
-  if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(window_lm_kernel<Cfg, LOSS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         (int)Cfg::SMEM);
-    if (e != cudaSuccess) return (int)e;
-    if (Cfg::CS > 8) {
-      e = cudaFuncSetAttribute(window_lm_kernel<Cfg, LOSS>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
-      if (e != cudaSuccess) return (int)e;
-    }
-    configured = true;
-  }
+  if (const int rc = configure_once<Cfg, LOSS>()) return rc;
   if constexpr (Cfg::CS > 1) {
     cudaLaunchConfig_t lc = {};
     lc.gridDim = dim3((unsigned)d.nb * Cfg::CS, 1, 1);
@@ -959,31 +973,26 @@ static int launch(const WinData& d, const Params& p, cudaStream_t s) {
   return p.loss == B2BA_LOSS_HUBER ? launch_l<Cfg, 1>(d, p, s) : launch_l<Cfg, 0>(d, p, s);
 }
 
-// B2BA_WIN_VARIANT (developer knob, read once): 1 = 128-thread CTAs, 4 per SM (default), 0 = 256-thread CTAs, 2 per SM
-static int small_variant() {
-  static int v = -1;
-  if (v < 0) {
-    const char* e = std::getenv("B2BA_WIN_VARIANT");
-    v = e ? std::atoi(e) : 1;
-  }
+// variant: kWinAuto, or a forced instantiation (options.flags bits 2 / 3; the parity tests run every one of them).
+// B2BA_WIN_VARIANT=0 (developer knob) makes the 256-thread CTA the default of the batched small path.
+static bool small256_default() {
+  static const bool v = [] { const char* e = std::getenv("B2BA_WIN_VARIANT"); return e && std::atoi(e) == 0; }();
   return v;
 }
-
-int launch_window_small(const WinData& d, const Params& p, cudaStream_t s) {
-  return small_variant() == 1 ? launch<CfgSmall4>(d, p, s) : launch<CfgSmall>(d, p, s);
+int launch_window_small(const WinData& d, const Params& p, cudaStream_t s, int variant) {
+  return (variant & kWinSmall256) || small256_default() ? launch<CfgSmall>(d, p, s) : launch<CfgSmall4>(d, p, s);
 }
 int launch_window_big(const WinData& d, const Params& p, cudaStream_t s) { return launch<CfgBig>(d, p, s); }
 // B2BA_CLUSTER16=0 (developer knob) keeps the portable cluster size for every window count
 static bool cluster16() {
-  static int v = -1;
-  if (v < 0) { const char* e = std::getenv("B2BA_CLUSTER16"); v = (!e || std::atoi(e) != 0) ? 1 : 0; }
-  return v == 1;
+  static const bool v = [] { const char* e = std::getenv("B2BA_CLUSTER16"); return !e || std::atoi(e) != 0; }();
+  return v;
 }
-int launch_window_small_cluster(const WinData& d, const Params& p, cudaStream_t s) {
-  return (d.nb <= 8 && cluster16()) ? launch<CfgSmallC16>(d, p, s) : launch<CfgSmallC>(d, p, s);
+int launch_window_small_cluster(const WinData& d, const Params& p, cudaStream_t s, int variant) {
+  return (d.nb <= 8 && cluster16() && !(variant & kWinCluster8)) ? launch<CfgSmallC16>(d, p, s) : launch<CfgSmallC>(d, p, s);
 }
-int launch_window_big_cluster(const WinData& d, const Params& p, cudaStream_t s) {
-  return (d.nb <= 8 && cluster16()) ? launch<CfgBigC16>(d, p, s) : launch<CfgBigC>(d, p, s);
+int launch_window_big_cluster(const WinData& d, const Params& p, cudaStream_t s, int variant) {
+  return (d.nb <= 8 && cluster16() && !(variant & kWinCluster8)) ? launch<CfgBigC16>(d, p, s) : launch<CfgBigC>(d, p, s);
 }
 
 template <class Cfg>
@@ -1001,8 +1010,8 @@ static int attrs_of(int* regs, int* smem_bytes, int* ctas_per_sm) {
 }
 
 int window_kernel_attrs(int which, int* regs, int* smem_bytes, int* ctas_per_sm) {
-  if (which == 0) return small_variant() == 1 ? attrs_of<CfgSmall4>(regs, smem_bytes, ctas_per_sm)
-                                              : attrs_of<CfgSmall>(regs, smem_bytes, ctas_per_sm);
+  if (which == 0) return small256_default() ? attrs_of<CfgSmall>(regs, smem_bytes, ctas_per_sm)
+                                            : attrs_of<CfgSmall4>(regs, smem_bytes, ctas_per_sm);
   return attrs_of<CfgBig>(regs, smem_bytes, ctas_per_sm);
 }
 

@@ -96,13 +96,16 @@ struct WinCfg {
 constexpr int kSmallMaxCam = 12, kSmallMaxFree = 9;    // window_small: n+1 <= 56
 constexpr int kBigMaxFree = 21;                        // window_big:   n+1 <= 128
 
-// launchers (ba_window.cu). Return cudaError_t as int.
-int launch_window_small(const WinData& d, const Params& p, cudaStream_t s);   // <= 12 cameras, <= 9 free (n+1 <= 56)
+// launchers (ba_window.cu). Return cudaError_t as int.  `variant`: kWinAuto or forced instantiations (options.flags
+// bits 2 / 3), so that every instantiation can be reached -- and parity-tested -- through the C ABI.
+enum { kWinAuto = 0, kWinSmall256 = 1 /* batched small path: 256-thread CTAs, 2 per SM */,
+       kWinCluster8 = 2 /* latency path: the portable 8-CTA cluster even for <= 8 windows */ };
+int launch_window_small(const WinData& d, const Params& p, cudaStream_t s, int variant = kWinAuto);   // <= 12 cameras, <= 9 free (n+1 <= 56)
 int launch_window_big(const WinData& d, const Params& p, cudaStream_t s);     // n+1 <= 128 (<= 21 free cams)
-// Few windows (latency path): one 8-CTA cluster per window.  Same arithmetic per observation; sums are formed
+// Few windows (latency path): one 8- or 16-CTA cluster per window.  Same arithmetic per observation; sums are formed
 // per CTA and then across the cluster in rank order, so results differ from the 1-CTA kernels by rounding only.
-int launch_window_small_cluster(const WinData& d, const Params& p, cudaStream_t s);
-int launch_window_big_cluster(const WinData& d, const Params& p, cudaStream_t s);
+int launch_window_small_cluster(const WinData& d, const Params& p, cudaStream_t s, int variant = kWinAuto);
+int launch_window_big_cluster(const WinData& d, const Params& p, cudaStream_t s, int variant = kWinAuto);
 int window_kernel_attrs(int which, int* regs, int* smem_bytes, int* ctas_per_sm);
 
 }  // namespace b2
