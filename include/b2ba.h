@@ -182,6 +182,10 @@ int b2ba_nccl_unique_id(void* out128);
  * of all ranks must tile [0, Np)).  The host side balances them by observation count. */
 int b2ba_set_point_range(b2ba_t* h, int32_t p_lo, int32_t p_hi);
 
+/* Measurement helper (bench.py roofline denominators; MEASURED_PEAKS.json has no fp64 entry): FP64 peak of `device`
+ * in TFLOP/s with dependent-free DFMA chains and with mma.sync m8n8k4 f64 (DMMA), CUDA-event timed, ~50 ms. */
+int b2ba_peak_flops(int device, double* dfma_tflops, double* dmma_tflops);
+
 int b2ba_version(void);
 
 #ifdef __cplusplus

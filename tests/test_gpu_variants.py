@@ -189,11 +189,11 @@ def test_batch_call_error_exit_leaves_no_work_in_flight():
     torch.cuda.synchronize()
     assert np.array_equal(out[0], snap[0]) and np.array_equal(out[1], snap[1])
     # offsets must start at 0 (same check as set_problem_batch)
-    hb.cam_off = b.cam_off + 1
+    hb.obs_off = b.obs_off + 1
     with pytest.raises(RuntimeError, match="start at 0"):
         ba.optimize_batch(hb, out=out)
     # and the handle is still usable
-    hb.cam_off, hb.obs_cam = b.cam_off, pin(b.obs_cam)
+    hb.obs_off, hb.obs_cam = b.obs_off, pin(b.obs_cam)
     res = ba.optimize_batch(hb, out=out)
     assert all(s.status in (1, 2) for s in res.summaries)
     ba.close()

@@ -20,13 +20,13 @@
 constexpr int kMaxRanks = 8;
 struct Shared {
   cudaIpcMemHandle_t h[kMaxRanks];
-  volatile int arrive[64];
-  double us[kMaxRanks][4];
+  volatile int arrive[256];
+  double us[kMaxRanks][4], us2[kMaxRanks][4];
   int ok[kMaxRanks];
 };
 
 static void host_barrier(Shared* sh, int nranks, int& epoch) {
-  const int slot = epoch % 64;
+  const int slot = epoch % 256;
   __sync_fetch_and_add(&sh->arrive[slot], 1);
   while (sh->arrive[slot] < nranks) usleep(50);
   ++epoch;
@@ -46,13 +46,14 @@ __device__ __forceinline__ long long ld_flag(const long long* p) {
 
 // MODE 0: all-gather of `cnt` doubles per rank; MODE 1: all-reduce of `cnt` doubles.  One CTA.
 template <int MODE>
-__global__ void __launch_bounds__(1024) exch_kernel(Peers P, int rank, int nranks, int cnt, int vec, int iters, double* result) {
+__global__ void __launch_bounds__(1024) exch_kernel(Peers P, int rank, int nranks, int cnt, int vec, int iters, double* result, int fence_all) {
   const int tid = threadIdx.x;
   const size_t slot_doubles = (size_t)vec;
   const size_t data_doubles = 2 * (size_t)nranks * slot_doubles;
   double* mine = P.buf[rank];
   long long* myflags = reinterpret_cast<long long*>(mine + data_doubles);
   double acc = 0.0;
+  int bad = 0;
   for (int it = 1; it <= iters; ++it) {
     const int par = it & 1;
     // produce: value depends on (rank, it, i) so stale data is detected
@@ -60,34 +61,33 @@ __global__ void __launch_bounds__(1024) exch_kernel(Peers P, int rank, int nrank
       double* dst = P.buf[r] + ((size_t)par * nranks + rank) * slot_doubles;
       for (int i = tid; i < cnt; i += blockDim.x) dst[i] = (double)(rank + 1) * 1e-3 * it + i;
     }
+    if (fence_all) __threadfence_system();     // every writer fences its own stores
     __syncthreads();
     if (tid < nranks) {
-      __threadfence_system();
+      if (!fence_all) __threadfence_system();  // one fence after the barrier (cumulativity)
       st_flag(reinterpret_cast<long long*>(P.buf[tid] + data_doubles) + par * nranks + rank, it);
     }
     if (tid < nranks) { while (ld_flag(myflags + par * nranks + tid) < it) {} }
     __syncthreads();
-    // consume
+    // consume (L2 loads: peers wrote the lines, L1 may hold the copy of two iterations ago) and verify exactly
     const double* base = mine + (size_t)par * nranks * slot_doubles;
-    if (MODE == 0) {
-      for (int i = tid; i < cnt * nranks; i += blockDim.x) acc += __ldcg(base + (size_t)(i / cnt) * slot_doubles + i % cnt);
-    } else {
-      for (int i = tid; i < cnt; i += blockDim.x) {
-        double v = 0.0;
-        for (int r = 0; r < nranks; ++r) v += __ldcg(base + (size_t)r * slot_doubles + i);
-        acc += v;
+    for (int i = tid; i < cnt; i += blockDim.x) {
+      double v = 0.0;
+      for (int r = 0; r < nranks; ++r) {
+        const double x = __ldcg(base + (size_t)r * slot_doubles + i);
+        if (x != (double)(r + 1) * 1e-3 * it + i) ++bad;
+        v += x;
       }
+      acc += v;
     }
     __syncthreads();
   }
-  // block sum -> result (for the check)
-  __shared__ double red[1024];
-  for (int i = tid; i < 1024; i += blockDim.x) red[i] = 0.0;
+  __shared__ int sbad;
+  if (tid == 0) sbad = 0;
   __syncthreads();
-  red[tid] = acc;
+  if (bad) atomicAdd(&sbad, bad);
   __syncthreads();
-  for (int s = 512; s > 0; s >>= 1) { if (tid < s) red[tid] += red[tid + s]; __syncthreads(); }
-  if (tid == 0) *result = red[0];
+  if (tid == 0) { result[0] = acc; result[1] = (double)sbad; }
 }
 
 int main(int argc, char** argv) {
@@ -118,40 +118,45 @@ int main(int argc, char** argv) {
     CK(cudaIpcOpenMemHandle(&p, sh->h[r], cudaIpcMemLazyEnablePeerAccess));
     P.buf[r] = (double*)p;
   }
-  double* d_res; CK(cudaMalloc(&d_res, 8));
+  double* d_res; CK(cudaMalloc(&d_res, 16));
   cudaEvent_t e0, e1; CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
   int ok = 1;
   for (int mode = 0; mode < 2; ++mode) {
     const int cnt = mode == 0 ? slice : vec;
-    for (int threads = 256; threads <= 1024; threads *= 4) {
-      CK(cudaMemset(buf, 0, doubles * sizeof(double)));
-      CK(cudaDeviceSynchronize());
-      host_barrier(sh, nranks, epoch);
-      CK(cudaEventRecord(e0));
-      if (mode == 0) exch_kernel<0><<<1, threads>>>(P, rank, nranks, cnt, vec, iters, d_res);
-      else exch_kernel<1><<<1, threads>>>(P, rank, nranks, cnt, vec, iters, d_res);
-      CK(cudaEventRecord(e1));
-      CK(cudaEventSynchronize(e1));
-      float ms; CK(cudaEventElapsedTime(&ms, e0, e1));
-      double res; CK(cudaMemcpy(&res, d_res, 8, cudaMemcpyDeviceToHost));
-      // expected: sum over it, r, i of ((r+1) 1e-3 it + i)
-      double exp = 0.0;
-      for (int it = 1; it <= iters; ++it)
-        for (int r = 0; r < nranks; ++r) exp += (double)cnt * (r + 1) * 1e-3 * it + 0.5 * (double)cnt * (cnt - 1);
-      if (fabs(res - exp) > 1e-9 * fabs(exp)) ok = 0;
-      sh->us[rank][mode * 2 + (threads == 1024)] = ms * 1e3 / iters;
-      host_barrier(sh, nranks, epoch);
+    for (int cfg = 0; cfg < 2; ++cfg) {
+      const int threads = cfg == 0 ? 256 : 1024;
+      for (int fence_all = 0; fence_all < 2; ++fence_all) {
+        CK(cudaMemset(buf, 0, doubles * sizeof(double)));
+        CK(cudaDeviceSynchronize());
+        host_barrier(sh, nranks, epoch);
+        CK(cudaEventRecord(e0));
+        if (mode == 0) exch_kernel<0><<<1, threads>>>(P, rank, nranks, cnt, vec, iters, d_res, fence_all);
+        else exch_kernel<1><<<1, threads>>>(P, rank, nranks, cnt, vec, iters, d_res, fence_all);
+        CK(cudaEventRecord(e1));
+        CK(cudaEventSynchronize(e1));
+        float ms; CK(cudaEventElapsedTime(&ms, e0, e1));
+        double res[2]; CK(cudaMemcpy(res, d_res, 16, cudaMemcpyDeviceToHost));
+        if (res[1] != 0.0) { ok = 0; fprintf(stderr, "rank %d mode %d threads %d fence_all %d: %.0f stale values\n", rank, mode, threads, fence_all, res[1]); }
+        if (fence_all == 0) sh->us[rank][mode * 2 + cfg] = ms * 1e3 / iters;
+        else sh->us2[rank][mode * 2 + cfg] = ms * 1e3 / iters;
+        host_barrier(sh, nranks, epoch);
+      }
     }
   }
   sh->ok[rank] = ok;
   host_barrier(sh, nranks, epoch);
   if (rank == 0) {
-    double mx[4] = {0, 0, 0, 0};
+    double mx[4] = {0, 0, 0, 0}, mx2[4] = {0, 0, 0, 0};
     int all_ok = 1;
-    for (int r = 0; r < nranks; ++r) { all_ok &= sh->ok[r]; for (int k = 0; k < 4; ++k) if (sh->us[r][k] > mx[k]) mx[k] = sh->us[r][k]; }
+    for (int r = 0; r < nranks; ++r) {
+      all_ok &= sh->ok[r];
+      for (int k = 0; k < 4; ++k) { if (sh->us[r][k] > mx[k]) mx[k] = sh->us[r][k]; if (sh->us2[r][k] > mx2[k]) mx2[k] = sh->us2[r][k]; }
+    }
     printf("{\"nranks\": %d, \"allgather_doubles_per_rank\": %d, \"allgather_us_256thr\": %.2f, \"allgather_us_1024thr\": %.2f, "
-           "\"allreduce_doubles\": %d, \"allreduce_us_256thr\": %.2f, \"allreduce_us_1024thr\": %.2f, \"data_ok\": %s}\n",
-           nranks, slice, mx[0], mx[1], vec, mx[2], mx[3], all_ok ? "true" : "false");
+           "\"allreduce_doubles\": %d, \"allreduce_us_256thr\": %.2f, \"allreduce_us_1024thr\": %.2f, "
+           "\"fence_by_every_writer\": {\"allgather_us_256thr\": %.2f, \"allgather_us_1024thr\": %.2f, \"allreduce_us_256thr\": %.2f, \"allreduce_us_1024thr\": %.2f}, "
+           "\"data_ok\": %s}\n",
+           nranks, slice, mx[0], mx[1], vec, mx[2], mx[3], mx2[0], mx2[1], mx2[2], mx2[3], all_ok ? "true" : "false");
     for (int r = 1; r < nranks; ++r) { int st; waitpid(kids[r], &st, 0); }
   }
   for (int r = 0; r < nranks; ++r) if (r != rank) cudaIpcCloseMemHandle(P.buf[r]);

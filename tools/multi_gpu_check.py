@@ -1,5 +1,6 @@
-"""Run under torchrun on >= 2 GPUs: the observation-sharded large path (landmarks split over the ranks, three NCCL
-all-reduces per LM iteration) must give the single-GPU result.  Rank 0 prints one line per case and exits non-zero
+"""Run under torchrun on >= 2 GPUs: the multi-rank large path (S sharded by block row, replicated small state, exchanges
+through peer memory: csrc/ba_large.cuh) must give the single-GPU result for every solver (banded Cholesky, PCG, dense
+DMMA Cholesky).  Rank 0 prints one line per case and exits non-zero
 on a mismatch.   python -m torch.distributed.run --nproc-per-node 2 --master-addr 127.0.0.1 tools/multi_gpu_check.py"""
 import os
 import sys
@@ -19,10 +20,11 @@ def main():
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     rank = dist.get_rank()
     bad = 0
-    for mode, nc, npts in (("local", 120, 12000), ("random", 120, 12000), ("local", 400, 60000)):
+    for mode, nc, npts, solver in (("local", 120, 12000, "auto"), ("random", 120, 12000, "pcg"), ("local", 400, 60000, "auto"),
+                                   ("random", 300, 40000, "pcg"), ("random", 120, 12000, "dense")):
         p = synth.make_large(7, n_cams=nc, n_pts=npts, mode=mode)
         K = np.array([[p.intr[0], 0, p.intr[2]], [0, p.intr[1], p.intr[3]], [0, 0, 1.0]])
-        cfg = BAConfig(max_iters=6, solver="pcg" if mode == "random" else "auto", device=local)
+        cfg = BAConfig(max_iters=6, solver=solver, device=local)
         single = BundleAdjuster(K, cfg)
         single.set_problem(p.poses, p.points, p.obs_cam, p.obs_pt, p.obs_uv, p.fixed_cam)
         s1 = single.solve()[0]
@@ -38,7 +40,7 @@ def main():
         dc = abs(s1.final_cost - s2.final_cost) / s1.final_cost
         ok = dp < 1e-7 and dx < 1e-7 and dc < 1e-9 and (s1.accepted, s1.rejected) == (s2.accepted, s2.rejected)
         if rank == 0:
-            print(f"{mode} nc={nc} np={npts}: ranks={dist.get_world_size()} |dpose|={dp:.2e} |dX|rel={dx:.2e} dcost={dc:.2e} "
+            print(f"{mode} nc={nc} np={npts} solver={solver}: ranks={dist.get_world_size()} |dpose|={dp:.2e} |dX|rel={dx:.2e} dcost={dc:.2e} "
                   f"accepted {s1.accepted}/{s2.accepted} pcg {s1.pcg_iters}/{s2.pcg_iters} -> {'OK' if ok else 'MISMATCH'}", flush=True)
         bad += 0 if ok else 1
     dist.barrier()

@@ -49,7 +49,7 @@ struct b2ba {
   LargeIndex lix;
   DevBuf<ObsRec> l_cm;
   DevBuf<int> l_cam_ptr;
-  DevBuf<double> l_poses_tri, l_lin_part, l_lin, l_Dc, l_Sg, l_dc, l_r, l_z, l_q, l_Minv, l_part, l_sums, l_band, l_binv, l_band_ws, l_zbuf, l_dense, l_dense_winv, l_dense_x, l_tbuf;
+  DevBuf<double> l_poses_tri, l_lin_part, l_Dc, l_Sg, l_dc, l_r, l_z, l_q, l_Minv, l_part, l_sums, l_band, l_binv, l_band_ws, l_zbuf, l_dense, l_dense_winv, l_dense_x, l_tbuf;
   DevBuf<int> l_dense_flags;
   int l_dense_ld = 0;
   // motion-only BA (b2ba_refine_poses): own buffers, independent of the problem set with b2ba_set_problem
@@ -75,6 +75,9 @@ struct b2ba {
   // multi-GPU
   int rank = 0, nranks = 1;
   void* nccl_comm = nullptr;
+  DevBuf<double> l_arena, l_Sl;        // peer-exchange arena (mapped into every rank), owned rows of S
+  void* peer_arena[kMaxRanks] = {};    // every rank's arena as mapped into this process
+  Peer peer = {};
   // pipelined batch call (b2ba_optimize_batch): child engines (one per chunk) and their streams / events
   std::vector<b2ba*> kids;
   cudaStream_t pipe_copy = nullptr, pipe_solve = nullptr, pipe_solve2 = nullptr, pipe_back = nullptr;
@@ -165,6 +168,7 @@ struct NcclApi {
   int (*GetUniqueId)(UniqueId*) = nullptr;
   int (*CommInitRank)(void**, int, UniqueId, int) = nullptr;
   int (*AllReduce)(const void*, void*, size_t, int, int, void*, cudaStream_t) = nullptr;
+  int (*AllGather)(const void*, void*, size_t, int, void*, cudaStream_t) = nullptr;
   int (*CommDestroy)(void*) = nullptr;
   const char* (*GetErrorString)(int) = nullptr;
   bool ok = false;
@@ -182,19 +186,86 @@ NcclApi& nccl_api() {
       api.AllReduce = (int (*)(const void*, void*, size_t, int, int, void*, cudaStream_t))dlsym(lib, "ncclAllReduce");
       api.CommDestroy = (int (*)(void*))dlsym(lib, "ncclCommDestroy");
       api.GetErrorString = (const char* (*)(int))dlsym(lib, "ncclGetErrorString");
-      api.ok = api.GetUniqueId && api.CommInitRank && api.AllReduce && api.CommDestroy;
+      api.AllGather = (int (*)(const void*, void*, size_t, int, void*, cudaStream_t))dlsym(lib, "ncclAllGather");
+      api.ok = api.GetUniqueId && api.CommInitRank && api.AllReduce && api.AllGather && api.CommDestroy;
     }
   }
   return api;
 }
-int nccl_allreduce_f64(void* user, const double* send, double* recv, size_t count, cudaStream_t s) {
-  b2ba* h = (b2ba*)user;
-  const int rc = nccl_api().AllReduce(send, recv, count, /*ncclFloat64*/ 8, /*ncclSum*/ 0, h->nccl_comm, s);
+// Bootstrap collectives (set-up only; the LM loop exchanges through peer memory, see ba_large.cuh):
+// all-gather of `bytes` per rank (device buffers) and a barrier.
+int nccl_allgather_bytes(b2ba* h, const void* send, void* recv, size_t bytes) {
+  int rc = nccl_api().AllGather(send, recv, bytes, /*ncclChar*/ 0, h->nccl_comm, nullptr);
+  if (rc == 0 && cudaStreamSynchronize(nullptr) != cudaSuccess) rc = -1;
   if (rc != 0) {
-    h->err = std::string("ncclAllReduce: ") + (nccl_api().GetErrorString ? nccl_api().GetErrorString(rc) : "error");
+    h->err = std::string("ncclAllGather: ") + (rc > 0 && nccl_api().GetErrorString ? nccl_api().GetErrorString(rc) : "error");
     return B2BA_E_NCCL;
   }
   return 0;
+}
+int nccl_barrier(b2ba* h) {
+  DevBuf<double> one;
+  if (one.alloc(1) != cudaSuccess) return fail(h, B2BA_E_CUDA, "alloc");
+  cudaMemset(one.p, 0, sizeof(double));
+  int rc = nccl_api().AllReduce(one.p, one.p, 1, /*ncclFloat64*/ 8, /*ncclSum*/ 0, h->nccl_comm, nullptr);
+  if (rc == 0 && cudaStreamSynchronize(nullptr) != cudaSuccess) rc = -1;
+  if (rc != 0) return fail(h, B2BA_E_NCCL, "ncclAllReduce (barrier) failed");
+  return 0;
+}
+
+// unmap the peers' arenas (own entry is not a mapping)
+void close_peers(b2ba* h) {
+  for (int r = 0; r < kMaxRanks; ++r) {
+    if (h->peer_arena[r] && r != h->rank) cudaIpcCloseMemHandle(h->peer_arena[r]);
+    h->peer_arena[r] = nullptr;
+  }
+}
+
+// nranks > 1: one exchange arena per rank, same layout everywhere, mapped into every rank with CUDA IPC
+int setup_arena(b2ba* h) {
+  const size_t n = 6 * (size_t)h->lix.nfree, nblk = h->lix.nblk, np = h->np_tot;
+  auto up = [](size_t v) { return (v + 15) / 16 * 16; };   // 128-byte alignment of every region
+  Peer& x = h->peer;
+  size_t off = 0;
+  x.off_flags = off; off += up(kMaxRanks);
+  x.off_sums = off; off += up(kMaxRanks * 8);
+  x.off_qx = off; off += up(2 * n);
+  x.off_minv = off; off += up((size_t)h->lix.nfree * 37);
+  x.off_r = off; off += up(n);
+  x.off_sg = off; off += up(nblk * 36 + n);
+  x.off_pts_tri = off; off += up(np * 3);
+  x.rank = h->rank; x.nranks = h->nranks;
+  if (off > h->l_arena.n || !h->l_arena.p) {
+    // (re)allocation: every rank takes this branch together (the layout depends on the problem only)
+    if (h->l_arena.p) {
+      close_peers(h);
+      int rc = nccl_barrier(h);                    // nobody still maps the old arena
+      if (rc) return rc;
+    }
+    CU(h->l_arena.alloc(off), "alloc arena");
+    CU(cudaMemset(h->l_arena.p, 0, off * sizeof(double)), "memset arena");
+    CU(cudaDeviceSynchronize(), "arena");
+    cudaIpcMemHandle_t mine;
+    CU(cudaIpcGetMemHandle(&mine, h->l_arena.p), "cudaIpcGetMemHandle");
+    DevBuf<cudaIpcMemHandle_t> snd, rcv;
+    CU(snd.alloc(1), "alloc"); CU(rcv.alloc(h->nranks), "alloc");
+    CU(cudaMemcpy(snd.p, &mine, sizeof(mine), cudaMemcpyHostToDevice), "copy handle");
+    int rc = nccl_allgather_bytes(h, snd.p, rcv.p, sizeof(mine));
+    if (rc) return rc;
+    std::vector<cudaIpcMemHandle_t> all(h->nranks);
+    CU(cudaMemcpy(all.data(), rcv.p, sizeof(mine) * h->nranks, cudaMemcpyDeviceToHost), "read handles");
+    for (int r = 0; r < h->nranks; ++r) {
+      if (r == h->rank) { h->peer_arena[r] = h->l_arena.p; continue; }
+      void* ptr = nullptr;
+      const cudaError_t e = cudaIpcOpenMemHandle(&ptr, all[r], cudaIpcMemLazyEnablePeerAccess);
+      if (e != cudaSuccess) return cuda_fail(h, e, "cudaIpcOpenMemHandle (peer arenas need peer access between the GPUs of one box)");
+      h->peer_arena[r] = ptr;
+    }
+    rc = nccl_barrier(h);                          // every arena is zeroed and mapped before anyone stores into it
+    if (rc) return rc;
+  }
+  for (int r = 0; r < kMaxRanks; ++r) x.arena[r] = (double*)h->peer_arena[r];
+  return B2BA_OK;
 }
 
 LargeData make_large(b2ba* h, bool hist) {
@@ -202,11 +273,15 @@ LargeData make_large(b2ba* h, bool hist) {
   d.nc = h->nc_tot; d.np = h->np_tot; d.nfree = h->lix.nfree; d.n = 6 * h->lix.nfree;
   d.p_lo = h->p_lo; d.p_hi = h->p_hi; d.rank = h->rank; d.nranks = h->nranks;
   d.sms = h->sms;
+  d.peer = h->peer;
+  d.f_lo = h->lix.f_lo; d.f_hi = h->lix.f_hi; d.nlocal = h->lix.nlocal;
+  d.lrow_ptr = h->lix.lrow_ptr.p; d.lcol = h->lix.lcol.p; d.lsrc = h->lix.lsrc.p; d.ldiag = h->lix.ldiag.p;
+  d.Sl = h->l_Sl.p;
   d.pm = h->d_pm.p; d.pt_ptr = h->d_pt_ptr.p; d.cm = h->l_cm.p; d.cam_ptr = h->l_cam_ptr.p;
   d.fidx = h->lix.fidx.p; d.blk_ptr = h->lix.blk_ptr.p; d.blk_col = h->lix.blk_col.p; d.nblk = h->lix.nblk;
   d.frow_ptr = h->lix.frow_ptr.p; d.fcol = h->lix.fcol.p; d.fsrc = h->lix.fsrc.p;
   d.poses = h->d_poses.p; d.poses_tri = h->l_poses_tri.p; d.pts = h->d_pts0.p; d.pts_tri = h->d_pts1.p;
-  d.lin_part = h->l_lin_part.p; d.lin = h->nranks > 1 ? h->l_lin.p : h->l_lin_part.p;
+  d.lin_part = h->l_lin_part.p; d.lin = h->l_lin_part.p;     // the camera pass is replicated on nranks > 1
   d.Dc = h->l_Dc.p; d.pt_scratch = h->d_scratch.p; d.Sg = h->l_Sg.p; d.dc = h->l_dc.p;
   d.r = h->l_r.p; d.z = h->l_z.p; d.q = h->l_q.p; d.Minv = h->l_Minv.p; d.tbuf = h->l_tbuf.p; d.part = h->l_part.p;
   d.pair_ptr = h->lix.pair_ptr.p; d.pair_ab = h->lix.pair_ab.p; d.blk_row = h->lix.blk_row.p; d.zbuf = h->l_zbuf.p;
@@ -214,7 +289,7 @@ LargeData make_large(b2ba* h, bool hist) {
   {
     // average pair-list length of the off-diagonal blocks (a diagonal list = the camera's observations)
     const long long noff = h->lix.nblk - h->lix.nfree;
-    const long long per = noff > 0 ? (h->lix.npairs - (h->p_hi > h->p_lo ? h->lix.a_hi - h->lix.a_lo : 0)) / noff : 1000;
+    const long long per = noff > 0 ? (h->lix.npairs - (h->lix.a_hi - h->lix.a_lo)) / noff : 1000;
     d.pair_lanes = per < 10 ? 1 : per < 48 ? 8 : 32;
   }
   d.bw = h->l_bw; d.band = h->l_band.p; d.binv = h->l_binv.p; d.band_P = h->l_band_P; d.band_ws = h->l_band_ws.p;
@@ -223,6 +298,10 @@ LargeData make_large(b2ba* h, bool hist) {
   d.sums_part = h->l_sums.p; d.ctrl = h->l_ctrl.p; d.summary = h->d_summ.p;
   d.hist_cost = hist ? h->d_hist_cost.p : nullptr; d.hist_mu = hist ? h->d_hist_mu.p : nullptr;
   d.hist_accept = hist ? h->d_hist_accept.p : nullptr;
+  if (h->nranks > 1) {      // what peers store into lives in the exchange arena
+    d.Sg = h->peer.at(h->rank, h->peer.off_sg);
+    d.pts_tri = h->peer.at(h->rank, h->peer.off_pts_tri);
+  }
   return d;
 }
 
@@ -236,25 +315,37 @@ int setup_large(b2ba* h) {
   if (rc) return cuda_fail(h, (cudaError_t)rc, "large_build_structure");
   const size_t nc = h->nc_tot, n = 6 * (size_t)h->lix.nfree, nblk = h->lix.nblk;
   if (n * sizeof(double) > 200 * 1024) return fail(h, B2BA_E_UNSUPPORTED, "PCG keeps the search direction in shared memory: at most 4266 free cameras");
+  // camera-major stream, Schur pair lists and Z records cover ALL landmarks on every rank (on nranks > 1 the passes
+  // over the observations are replicated work; what is sharded is S by block row and the back-substitution by landmark)
   CU(h->l_cm.alloc(h->no), "alloc"); CU(h->l_cam_ptr.alloc(nc + 1), "alloc");
-  rc = large_build_cm_slice(h->nc_tot, h->p_lo, h->p_hi, h->d_pm.p, h->d_pt_ptr.p, h->l_cm.p, h->l_cam_ptr.p, nullptr);
+  rc = large_build_cm_slice(h->nc_tot, 0, h->np_tot, h->d_pm.p, h->d_pt_ptr.p, h->l_cm.p, h->l_cam_ptr.p, nullptr);
   if (rc) return cuda_fail(h, (cudaError_t)rc, "large_build_cm_slice");
-  rc = large_build_pairs(h->p_lo, h->p_hi, h->no, h->d_pm.p, h->d_pt_ptr.p, h->lix, nullptr);
+  rc = large_build_pairs(0, h->np_tot, h->no, h->d_pm.p, h->d_pt_ptr.p, h->lix, nullptr);
   if (rc) return cuda_fail(h, (cudaError_t)rc, "large_build_pairs");
   CU(h->l_zbuf.alloc((size_t)h->no * 24), "alloc");
   int blocks = 0;
   size_t smem = 0;
-  rc = large_pcg_grid((int)n, &blocks, &smem);
+  rc = h->nranks > 1 ? large_pcg_dist_grid((int)n, &blocks, &smem) : large_pcg_grid((int)n, &blocks, &smem);
   if (rc) return cuda_fail(h, (cudaError_t)rc, "large_pcg_grid");
+  if (h->nranks > 1) {
+    rc = large_build_rows(h->rank, h->nranks, h->lix, nullptr);
+    if (rc) return cuda_fail(h, (cudaError_t)rc, "large_build_rows");
+    CU(h->l_Sl.alloc((size_t)(h->lix.nlocal > 0 ? h->lix.nlocal : 1) * 36), "alloc");
+    if ((rc = setup_arena(h)) != 0) return rc;
+  }
   const size_t nparts = ((size_t)(h->p_hi - h->p_lo) + 127) / 128;
   size_t part = 2 * nc;
   if ((size_t)blocks * 4 > part) part = (size_t)blocks * 4;
   if (nparts * 8 > part) part = nparts * 8;
   CU(h->l_poses_tri.alloc(nc * 12), "alloc"); CU(h->l_lin_part.alloc(nc * 27 + 2), "alloc");
-  CU(h->l_lin.alloc(nc * 27 + 2), "alloc"); CU(h->l_Dc.alloc(nc * 6), "alloc");
+  CU(h->l_Dc.alloc(nc * 6), "alloc");
   CU(h->l_Sg.alloc(nblk * 36 + n), "alloc"); CU(h->l_dc.alloc(n), "alloc"); CU(h->l_r.alloc(n), "alloc");
   CU(h->l_z.alloc(n), "alloc"); CU(h->l_q.alloc(n), "alloc"); CU(h->l_Minv.alloc(6 * n), "alloc"); CU(h->l_tbuf.alloc(nblk * 6), "alloc");
-  CU(h->l_part.alloc(part + 8), "alloc"); CU(h->l_sums.alloc(16), "alloc"); CU(h->l_ctrl.alloc(1), "alloc");
+  CU(h->l_part.alloc(part + 8), "alloc"); CU(h->l_sums.alloc(16), "alloc");
+  if (!h->l_ctrl.p) {       // the exchange epoch lives in the control block and only grows: zero it once
+    CU(h->l_ctrl.alloc(1), "alloc");
+    CU(cudaMemset(h->l_ctrl.p, 0, sizeof(LargeCtrl)), "memset");
+  }
   // solver choice on the large path: S block-banded (half-bandwidth <= kBandMaxBw camera blocks) -> exact banded
   // Cholesky, unless PCG was asked for explicitly; otherwise block-Jacobi PCG
   h->l_bw = -1;
@@ -287,29 +378,17 @@ int setup_large(b2ba* h) {
   return B2BA_OK;
 }
 
-__global__ void zero_outside_range(double* pts, int np, int p_lo, int p_hi) {
-  const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
-  if (i < (size_t)np * 3 && (i < (size_t)p_lo * 3 || i >= (size_t)p_hi * 3)) pts[i] = 0.0;
-}
-
 int solve_large(b2ba* h, const Params& P, bool hist, cudaStream_t s) {
   const LargeData d = make_large(h, hist);
-  AllReduceFn ar = h->nranks > 1 ? nccl_allreduce_f64 : nullptr;
   int rc = large_init_ctrl(d, P, s);
   if (rc) return cuda_fail(h, (cudaError_t)rc, "large_init_ctrl");
   for (int it = 0; it < P.max_iters; ++it) {
-    rc = large_iteration(d, P, h->opt.pcg_max_iters, h->opt.pcg_tol, ar, h, s);
-    if (rc == B2BA_E_NCCL) return rc;
+    rc = large_iteration(d, P, h->opt.pcg_max_iters, h->opt.pcg_tol, s);
     if (rc) return cuda_fail(h, (cudaError_t)rc, "large_iteration");
   }
   rc = large_finish(d, s);
   if (rc) return cuda_fail(h, (cudaError_t)rc, "large_finish");
-  if (h->nranks > 1) {   // every rank ends with all landmarks: sum of range-masked copies
-    zero_outside_range<<<(h->np_tot * 3 + 255) / 256, 256, 0, s>>>(h->d_pts0.p, h->np_tot, h->p_lo, h->p_hi);
-    rc = nccl_allreduce_f64(h, h->d_pts0.p, h->d_pts0.p, (size_t)h->np_tot * 3, s);
-    if (rc) return rc;
-  }
-  return B2BA_OK;
+  return B2BA_OK;        // nranks > 1: poses and landmarks are replicated state, every rank ends with all of them
 }
 
 }  // namespace
@@ -361,6 +440,7 @@ void b2ba_destroy(b2ba_t* h) {
   if (h->pinned_stage) cudaFreeHost(h->pinned_stage);
   if (h->pipe_back) cudaStreamDestroy(h->pipe_back);
   if (h->pinned_flags) cudaFreeHost(h->pinned_flags);
+  close_peers(h);
   if (h->nccl_comm && nccl_api().ok) nccl_api().CommDestroy(h->nccl_comm);
   delete h;
 }
@@ -501,6 +581,11 @@ int b2ba_get_summaries(b2ba_t* h, b2ba_summary* summaries) {
   DeviceGuard dg_(h->device); CU(dg_.err, "cudaSetDevice");
   CU(cudaMemcpyAsync(summaries, h->d_summ.p, (size_t)h->B * sizeof(b2ba_summary), cudaMemcpyDeviceToHost, h->last_stream), "read summaries");
   CU(cudaStreamSynchronize(h->last_stream), "solve");
+  if (h->path == PATH_LARGE && h->nranks > 1) {
+    LargeCtrl c;
+    CU(cudaMemcpy(&c, h->l_ctrl.p, sizeof(c), cudaMemcpyDeviceToHost), "read control");
+    if (c.xerr) return fail(h, B2BA_E_NCCL, "peer-memory exchange timed out (a rank did not arrive): solve abandoned");
+  }
   return B2BA_OK;
 }
 

@@ -6,6 +6,7 @@
 #include <cub/device/device_scan.cuh>
 #include <cub/device/device_select.cuh>
 
+#include <algorithm>
 #include <vector>
 
 namespace cg = cooperative_groups;
@@ -348,6 +349,44 @@ done:
   return (int)e;
 }
 
+// nranks > 1: the block rows this rank owns -- a contiguous range [f_lo, f_hi), the ranges of all ranks balanced by
+// FULL-row entries (both triangles: a rank multiplies whole rows of S) -- and their local CSR.  Host side: the
+// structure is small (<= 2 * nblk ints) and is built once per problem.
+int large_build_rows(int rank, int nranks, LargeIndex& ix, cudaStream_t s) {
+  const int nfree = ix.nfree;
+  std::vector<int> rp(nfree + 1), col(ix.nfull), src(ix.nfull);
+  cudaError_t e = cudaMemcpyAsync(rp.data(), ix.frow_ptr.p, rp.size() * 4, cudaMemcpyDeviceToHost, s);
+  if (e == cudaSuccess && ix.nfull) e = cudaMemcpyAsync(col.data(), ix.fcol.p, (size_t)ix.nfull * 4, cudaMemcpyDeviceToHost, s);
+  if (e == cudaSuccess && ix.nfull) e = cudaMemcpyAsync(src.data(), ix.fsrc.p, (size_t)ix.nfull * 4, cudaMemcpyDeviceToHost, s);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+  if (e != cudaSuccess) return (int)e;
+  // cut r: the first row whose prefix of entries reaches r/nranks of the total (identical on every rank)
+  auto cut = [&](int r) {
+    if (r <= 0) return 0;
+    if (r >= nranks) return nfree;
+    const long long target = (long long)ix.nfull * r / nranks;
+    int f = (int)(std::lower_bound(rp.begin(), rp.end(), (int)target) - rp.begin());
+    return f > nfree ? nfree : f;
+  };
+  ix.f_lo = cut(rank); ix.f_hi = cut(rank + 1);
+  const int nrows = ix.f_hi - ix.f_lo, e0 = rp[ix.f_lo], e1 = rp[ix.f_hi];
+  ix.nlocal = e1 - e0;
+  std::vector<int> lrp(nrows + 1), ldiag(nrows > 0 ? nrows : 1, 0);
+  for (int i = 0; i <= nrows; ++i) lrp[i] = rp[ix.f_lo + i] - e0;
+  for (int i = 0; i < nrows; ++i)
+    for (int q = rp[ix.f_lo + i]; q < rp[ix.f_lo + i + 1]; ++q)
+      if (col[q] == ix.f_lo + i) ldiag[i] = q - e0;
+  if ((e = ix.lrow_ptr.alloc(nrows + 1)) != cudaSuccess) return (int)e;
+  if ((e = ix.ldiag.alloc(nrows > 0 ? nrows : 1)) != cudaSuccess) return (int)e;
+  if ((e = ix.lcol.alloc(ix.nlocal > 0 ? ix.nlocal : 1)) != cudaSuccess) return (int)e;
+  if ((e = ix.lsrc.alloc(ix.nlocal > 0 ? ix.nlocal : 1)) != cudaSuccess) return (int)e;
+  e = cudaMemcpy(ix.lrow_ptr.p, lrp.data(), lrp.size() * 4, cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) e = cudaMemcpy(ix.ldiag.p, ldiag.data(), ldiag.size() * 4, cudaMemcpyHostToDevice);
+  if (e == cudaSuccess && ix.nlocal) e = cudaMemcpy(ix.lcol.p, col.data() + e0, (size_t)ix.nlocal * 4, cudaMemcpyHostToDevice);
+  if (e == cudaSuccess && ix.nlocal) e = cudaMemcpy(ix.lsrc.p, src.data() + e0, (size_t)ix.nlocal * 4, cudaMemcpyHostToDevice);
+  return (int)e;
+}
+
 }  // namespace b2
 
 // =============================================================================================
@@ -435,6 +474,7 @@ __global__ void large_init_S_kernel(LargeData d) {
   const size_t gid = blockIdx.x * (size_t)blockDim.x + threadIdx.x, gsz = (size_t)gridDim.x * blockDim.x;
   const double* B = d.lin;
   for (size_t i = gid; i < (size_t)d.nc * 6; i += gsz) d.Dc[i] = clampd(B[(i / 6) * 21 + packed21((int)(i % 6), (int)(i % 6))]);
+  if (d.nranks > 1) return;                        // every entry of S is written by the owner of its row
   for (size_t i = gid; i < d.sg_count(); i += gsz) d.Sg[i] = 0.0;
   // the grid-wide zero fill must finish before the diagonal blocks are written: second kernel below
 }
@@ -454,7 +494,7 @@ __global__ void large_init_diag_kernel(LargeData d) {
     ctrl->step_bad = 0;
     ctrl->sums[6] = 0.0;
   }
-  if (c >= d.nc || d.rank != 0) return;
+  if (c >= d.nc || d.nranks > 1) return;           // nranks > 1: large_sblock_rows_kernel forms the owned rows, B' included
   const int f = d.fidx[c];
   if (f < 0) return;
   const double imu = 1.0 / ctrl->mu;
@@ -484,9 +524,9 @@ __device__ __forceinline__ void atomic_max_pos(double* addr, double v) {   // v 
 __global__ void __launch_bounds__(128) large_pt_kernel(LargeData d, Params P) {
   LargeCtrl* ctrl = d.ctrl;
   if (ctrl->stop) return;
-  const int pi = d.p_lo + blockIdx.x * blockDim.x + threadIdx.x;
-  const bool live = pi < d.p_hi;                  // (no early exit: warp-wide max below)
-  const int p = live ? pi : d.p_lo;
+  const int pi = blockIdx.x * blockDim.x + threadIdx.x;
+  const bool live = pi < d.np;                    // (no early exit: warp-wide max below)
+  const int p = live ? pi : 0;
   const double imu = 1.0 / ctrl->mu;
   const int a0 = d.pt_ptr[p], a1 = live ? d.pt_ptr[p + 1] : a0;
   const double X0 = d.pts[3 * (size_t)p], X1 = d.pts[3 * (size_t)p + 1], X2 = d.pts[3 * (size_t)p + 2];
@@ -625,6 +665,173 @@ __global__ void __launch_bounds__(128) large_sblock_kernel(LargeData d) {
     for (int k = 0; k < 6; ++k)
       if (k % G == gl) gred[6 * f + k] -= ag[k];
   }
+}
+
+}  // namespace
+}  // namespace b2
+
+// =============================================================================================
+// Peer-memory exchange (nranks > 1).  A rank publishes epoch e by storing e into slot [its rank] of every rank's flag
+// array with a system-scope release AFTER its data stores (which went to the peers' arenas over NVLink); a rank that
+// has seen all flags >= e may read what the others stored for epoch e.  Epochs only grow, and every rank takes part
+// in every exchange, so a rank can run at most one exchange ahead of the slowest one: buffers that are written for
+// epoch e + 2 are never still being read for epoch e (the q buffer, written every CG iteration, alternates by parity).
+namespace b2 {
+namespace {
+
+__device__ __forceinline__ void st_release_sys(long long* p, long long v) {
+  asm volatile("st.release.sys.global.s64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ long long ld_acquire_sys(const long long* p) {
+  long long v;
+  asm volatile("ld.acquire.sys.global.s64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ unsigned long long global_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+constexpr unsigned long long kXchgTimeoutNs = 4000000000ull;   // a rank that is 4 s late is lost: give up, do not hang
+
+// Called by ONE thread per peer (threads 0..nranks-1 of a CTA) after the CTA's / grid's data stores are complete and
+// every storing thread has executed __threadfence_system().
+__device__ __forceinline__ void xchg_publish(const Peer& x, int peer, long long epoch) {
+  __threadfence_system();
+  st_release_sys(reinterpret_cast<long long*>(x.at(peer, x.off_flags)) + x.rank, epoch);
+}
+// Thread `src` waits for rank `src`.  false on timeout.
+__device__ __forceinline__ bool xchg_wait(const Peer& x, int src, long long epoch) {
+  const long long* f = reinterpret_cast<const long long*>(x.at(x.rank, x.off_flags)) + src;
+  if (ld_acquire_sys(f) >= epoch) return true;
+  const unsigned long long t0 = global_ns();
+  while (ld_acquire_sys(f) < epoch) {
+    if (global_ns() - t0 > kXchgTimeoutNs) return false;
+    __nanosleep(64);
+  }
+  return true;
+}
+
+// a stand-alone exchange between two ordinary kernels: publish (everything the previous kernels of this stream
+// stored into the peers is complete: kernel boundaries order it), wait, bump the epoch.  One CTA, 32 threads.
+__global__ void large_xchg_kernel(LargeData d) {
+  LargeCtrl* ctrl = d.ctrl;
+  if (ctrl->stop) return;
+  const Peer& x = d.peer;
+  const long long e = ctrl->xepoch + 1;
+  bool ok = true;
+  if ((int)threadIdx.x < x.nranks) {
+    xchg_publish(x, threadIdx.x, e);
+    ok = xchg_wait(x, threadIdx.x, e);
+  }
+  ok = __all_sync(0xffffffffu, ok);
+  if (threadIdx.x == 0) {
+    ctrl->xepoch = e;
+    if (!ok) { ctrl->xerr = 1; ctrl->stop = 1; ctrl->status = B2BA_NUMERICAL_FAILURE; }
+  }
+}
+
+// nranks > 1, a1-a4: the owned FULL rows of S.  One group of G lanes per local entry (f, c):
+//   S(f, c) = [f == c] B'_f  -  sum over the pair list of the upper block {f, c} of  Z_a Z_b^T  (transposed for c < f)
+// and, on diagonal entries,  g_red(f) = g_c(f) - sum zy_a.  MODE 1: diagonal entries only (long lists: the camera's
+// observations), MODE 2: off-diagonal entries only.  Fixed summation order (pair list order, fixed shuffle tree).
+template <int G, int MODE>
+__global__ void __launch_bounds__(128) large_sblock_rows_kernel(LargeData d) {
+  const LargeCtrl* ctrl = d.ctrl;
+  if (ctrl->stop) return;
+  const int gi = (blockIdx.x * blockDim.x + threadIdx.x) / G, gl = threadIdx.x % G;
+  const int nrows = d.f_hi - d.f_lo;
+  bool live = gi < (MODE == 1 ? nrows : d.nlocal);      // (no early exit: the shuffles below name the full warp)
+  const int e = !live ? 0 : MODE == 1 ? d.ldiag[gi] : gi;
+  const int srcw = live ? d.lsrc[e] : 0;
+  const int src = srcw & 0x7fffffff;
+  const bool tr = srcw < 0;
+  const bool isdiag = live && d.blk_row[src] == d.blk_col[src];
+  if (MODE == 2 && isdiag) live = false;
+  const int q0 = live ? d.pair_ptr[src] : 0, q1 = live ? d.pair_ptr[src + 1] : 0;
+  double acc[36], ag[6];
+#pragma unroll
+  for (int k = 0; k < 36; ++k) acc[k] = 0.0;
+#pragma unroll
+  for (int k = 0; k < 6; ++k) ag[k] = 0.0;
+  for (int q = q0 + gl; q < q1; q += G) {
+    const int2 ab = d.pair_ab[q];
+    const double2* za = reinterpret_cast<const double2*>(d.zbuf + (size_t)ab.x * 24);
+    double A[18], B[18];
+#pragma unroll
+    for (int k = 0; k < 9; ++k) { const double2 t = za[k]; A[2 * k] = t.x; A[2 * k + 1] = t.y; }
+    if (ab.x == ab.y) {
+#pragma unroll
+      for (int k = 0; k < 18; ++k) B[k] = A[k];
+#pragma unroll
+      for (int k = 0; k < 3; ++k) { const double2 t = za[9 + k]; ag[2 * k] += t.x; ag[2 * k + 1] += t.y; }
+    } else {
+      const double2* zb = reinterpret_cast<const double2*>(d.zbuf + (size_t)ab.y * 24);
+#pragma unroll
+      for (int k = 0; k < 9; ++k) { const double2 t = zb[k]; B[2 * k] = t.x; B[2 * k + 1] = t.y; }
+    }
+#pragma unroll
+    for (int r = 0; r < 6; ++r)
+#pragma unroll
+      for (int c = 0; c < 6; ++c)
+        acc[6 * r + c] = fma(A[3 * r], B[3 * c], fma(A[3 * r + 1], B[3 * c + 1], fma(A[3 * r + 2], B[3 * c + 2], acc[6 * r + c])));
+  }
+#pragma unroll
+  for (int m = G >> 1; m > 0; m >>= 1) {
+#pragma unroll
+    for (int k = 0; k < 36; ++k) acc[k] += __shfl_xor_sync(0xffffffffu, acc[k], m);
+#pragma unroll
+    for (int k = 0; k < 6; ++k) ag[k] += __shfl_xor_sync(0xffffffffu, ag[k], m);
+  }
+  if (!live) return;
+  double* S = d.Sl + (size_t)e * 36;
+  if (isdiag) {
+    const int f = d.blk_row[src];
+    // camera of free index f: fidx is monotone, so search upwards from f
+    int c = f;
+    while (d.fidx[c] != f) ++c;
+    const double imu = 1.0 / ctrl->mu;
+    const double* B = d.lin + (size_t)c * 21;
+#pragma unroll
+    for (int k = 0; k < 36; ++k)
+      if (k % G == gl) {
+        const int r = k / 6, s2 = k % 6;
+        double v = B[packed21(min(r, s2), max(r, s2))];
+        if (r == s2) v += clampd(v) * imu;
+        S[k] = v - acc[k];
+      }
+    double* gred = d.Sg + (size_t)d.nblk * 36;
+#pragma unroll
+    for (int k = 0; k < 6; ++k)
+      if (k % G == gl) gred[6 * f + k] = d.lin[(size_t)d.nc * 21 + (size_t)c * 6 + k] - ag[k];
+  } else {
+#pragma unroll
+    for (int k = 0; k < 36; ++k)
+      if (k % G == gl) S[tr ? (k % 6) * 6 + k / 6 : k] = -acc[k];
+  }
+}
+
+// nranks > 1, banded / dense solvers: the upper blocks of the owned rows and their g_red rows go into EVERY rank's
+// S array (the factorisation runs replicated).  Followed by large_xchg_kernel.
+__global__ void large_push_rows_kernel(LargeData d) {
+  const LargeCtrl* ctrl = d.ctrl;
+  if (ctrl->stop) return;
+  const Peer& x = d.peer;
+  const size_t gid = blockIdx.x * (size_t)blockDim.x + threadIdx.x, gsz = (size_t)gridDim.x * blockDim.x;
+  for (size_t i = gid; i < (size_t)d.nlocal * 36; i += gsz) {
+    const int e = (int)(i / 36), k = (int)(i % 36);
+    const int srcw = d.lsrc[e];
+    if (srcw < 0) continue;                               // lower-triangle entry: its transpose is pushed by its owner
+    const double v = d.Sl[i];
+    for (int r = 0; r < x.nranks; ++r) x.at(r, x.off_sg)[(size_t)srcw * 36 + k] = v;
+  }
+  const double* gred = d.Sg + (size_t)d.nblk * 36;
+  for (size_t i = (size_t)d.f_lo * 6 + gid; i < (size_t)d.f_hi * 6; i += gsz) {
+    const double v = gred[i];
+    for (int r = 0; r < x.nranks; ++r)
+      if (r != x.rank) x.at(r, x.off_sg)[(size_t)d.nblk * 36 + i] = v;
+  }
+  __threadfence_system();
 }
 
 }  // namespace
@@ -855,6 +1062,195 @@ __global__ void __launch_bounds__(kPcgThreads) large_pcg_kernel(LargeData d, int
 }  // namespace
 }  // namespace b2
 
+// =============================================================================================
+// a6 on nranks > 1 GPUs: block-Jacobi PCG with S sharded by block row, ONE cooperative launch per rank, all ranks in
+// lockstep.  Vectors (x, r, z, p) are replicated and stay bit-identical on every rank (same arithmetic on the same
+// data in the same order; the grid size is the same on every rank); S exists only as the owned full rows (d.Sl).
+//   set-up : a rank inverts the diagonal blocks of its rows and stores M_f^-1 and r_f = -g_red(f) into EVERY rank
+//            (exchange 1); then z = M^-1 r, r.z and b.b everywhere.
+//   per CG iteration: p = z + beta p (whole vector in shared memory, every CTA);  q_f = S(f,:) p for the owned rows,
+//            stored into every rank's q buffer of this parity (exchange: the all-gather of q, 6 doubles per owned row);
+//            p.q from the gathered q (every CTA, whole vector);  x, r, z and the partial r.z / r.r by CTA-strided rows;
+//            ordered sums.  Two grid syncs and one peer exchange per iteration.
+// Same stopping rule and the same operations as large_pcg_kernel / the oracle's PCG; the dot products are summed in a
+// different (fixed) order, so iterates agree to rounding.
+namespace b2 {
+namespace {
+
+__global__ void __launch_bounds__(kPcgThreads) large_pcg_dist_kernel(LargeData d, int max_it, double tol) {
+  cg::grid_group grid = cg::this_grid();
+  LargeCtrl* ctrl = d.ctrl;
+  if (ctrl->stop || ctrl->step_bad) return;       // replicated state: uniform across the grid AND across the ranks
+  extern __shared__ double psh[];                  // p (n doubles)
+  __shared__ double red[kPcgThreads / 32][4];
+  __shared__ double rowred[kPcgThreads / 32][6];
+  __shared__ double bcast[4];
+  __shared__ int xok;
+  const Peer& X = d.peer;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  constexpr int nwarp_cta = kPcgThreads / 32;
+  const int G_ = (int)gridDim.x;
+  const int n = d.n, nfree = d.nfree, nrows = d.f_hi - d.f_lo;
+  double* part = d.part;                           // [gridDim.x * 4]
+  double* Minv = X.at(X.rank, X.off_minv);         // nfree x 37 (36 + ok marker), filled by the owners
+  double* rvec = X.at(X.rank, X.off_r);            // n
+  const int bl = lane / 6, rr = lane % 6;          // lanes 0..29: (block slot, row); 30, 31 idle
+  long long epoch = ctrl->xepoch;
+
+  // all CTAs wait for exchange `e` (CTA 0 publishes after a grid sync: every CTA's stores are done and fenced)
+  auto exchange = [&](long long e) -> bool {
+    __threadfence_system();
+    grid.sync();
+    if (blockIdx.x == 0 && tid < X.nranks) xchg_publish(X, tid, e);
+    if (tid == 0) xok = 1;
+    __syncthreads();
+    if (tid < X.nranks && !xchg_wait(X, tid, e)) xok = 0;
+    __syncthreads();
+    return xok != 0;
+  };
+  auto fail_exchange = [&]() {
+    if (blockIdx.x == 0 && tid == 0) { ctrl->xerr = 1; ctrl->stop = 1; ctrl->status = B2BA_NUMERICAL_FAILURE; ctrl->xepoch = epoch; }
+  };
+
+  // ---- set-up: owned rows -> M^-1, r = -g_red into every rank
+  {
+    const double* gred = d.Sg + (size_t)d.nblk * 36;
+    for (int i = blockIdx.x * kPcgThreads + tid; i < nrows; i += G_ * kPcgThreads) {
+      const int f = d.f_lo + i;
+      double Inv[36];
+      const bool ok = inv6_spd(d.Sl + (size_t)d.ldiag[i] * 36, Inv);
+      for (int r_ = 0; r_ < X.nranks; ++r_) {
+        double* M = X.at(r_, X.off_minv) + (size_t)f * 37;
+        for (int k = 0; k < 36; ++k) M[k] = ok ? Inv[k] : 0.0;
+        M[36] = ok ? 1.0 : 0.0;
+        double* rv = X.at(r_, X.off_r) + 6 * (size_t)f;
+        for (int k = 0; k < 6; ++k) rv[k] = -gred[6 * f + k];
+      }
+    }
+  }
+  if (!exchange(++epoch)) { fail_exchange(); return; }
+  // every rank now holds M^-1 and r of every row: x = 0, z = M^-1 r, r.z, b.b (CTA-strided rows, ordered sums)
+  double s_rz = 0.0, s_bb = 0.0, s_bad = 0.0;
+  for (int f = blockIdx.x * kPcgThreads + tid; f < nfree; f += G_ * kPcgThreads) {
+    const double* M = Minv + (size_t)f * 37;
+    if (__ldcg(M + 36) == 0.0) s_bad = 1.0;
+    double rv[6];
+    for (int k = 0; k < 6; ++k) { rv[k] = __ldcg(rvec + 6 * f + k); d.r[6 * f + k] = rv[k]; d.dc[6 * f + k] = 0.0; }
+    for (int r_ = 0; r_ < 6; ++r_) {
+      double v = 0.0;
+      for (int s_ = 0; s_ < 6; ++s_) v += __ldcg(M + 6 * r_ + s_) * rv[s_];
+      d.z[6 * f + r_] = v;
+      s_rz += rv[r_] * v;
+      s_bb += rv[r_] * rv[r_];
+    }
+  }
+  s_rz = warp_sum(s_rz); s_bb = warp_sum(s_bb); s_bad = warp_sum(s_bad);
+  if (lane == 0) { red[warp][0] = s_rz; red[warp][1] = s_bb; red[warp][2] = s_bad; }
+  __syncthreads();
+  if (tid == 0) {
+    double a = 0, b = 0, c = 0;
+    for (int w = 0; w < nwarp_cta; ++w) { a += red[w][0]; b += red[w][1]; c += red[w][2]; }
+    part[blockIdx.x * 4] = a; part[blockIdx.x * 4 + 1] = b; part[blockIdx.x * 4 + 2] = c;
+  }
+  grid.sync();
+  double rz = ordered_sum(part, G_, 4, &bcast[0]);
+  const double bb = ordered_sum(part + 1, G_, 4, &bcast[1]);
+  const double nbad = ordered_sum(part + 2, G_, 4, &bcast[2]);
+  grid.sync();                                     // partials are reused below
+  if (nbad > 0.0) {                                // a diagonal block of S is not SPD (on some rank): the step fails
+    if (blockIdx.x == 0 && tid == 0) { ctrl->step_bad = 1; ctrl->xepoch = epoch; }
+    return;
+  }
+  double rnorm2 = bb, beta = 0.0;
+  int it = 0;
+  for (int i = tid; i < n; i += kPcgThreads) psh[i] = 0.0;
+  __syncthreads();
+  bool bad_pq = false;
+  if (bb > 0.0) {
+    for (; it < max_it; ++it) {
+      if (rnorm2 <= tol * tol * bb) break;
+      // ---- p = z + beta p (whole vector, every CTA)
+      for (int i = tid; i < n; i += kPcgThreads) psh[i] = d.z[i] + beta * psh[i];
+      __syncthreads();
+      // ---- q_f = S(f,:) p for the owned rows (one CTA per row, warps stride over the row's blocks, fixed order) -> all ranks
+      const size_t qoff = X.off_qx + (size_t)((epoch + 1) & 1) * n;
+      for (int i = blockIdx.x; i < nrows; i += G_) {
+        const int f = d.f_lo + i;
+        double v = 0.0;
+        if (lane < 30) {
+          for (int e = d.lrow_ptr[i] + warp * 5 + bl; e < d.lrow_ptr[i + 1]; e += 5 * nwarp_cta) {
+            const double* M = d.Sl + (size_t)e * 36;
+            const double* x = psh + 6 * d.lcol[e];
+#pragma unroll
+            for (int s_ = 0; s_ < 6; ++s_) v += M[6 * rr + s_] * x[s_];
+          }
+        }
+        v += __shfl_down_sync(0xffffffffu, v, 6) + __shfl_down_sync(0xffffffffu, v, 12) +
+             __shfl_down_sync(0xffffffffu, v, 18) + __shfl_down_sync(0xffffffffu, v, 24);
+        if (lane < 6) rowred[warp][lane] = v;
+        __syncthreads();
+        if (warp == 0 && lane < 6) {
+          double t = 0.0;
+#pragma unroll
+          for (int w = 0; w < nwarp_cta; ++w) t += rowred[w][lane];    // fixed order
+          for (int r_ = 0; r_ < X.nranks; ++r_) X.at(r_, qoff)[6 * f + lane] = t;
+        }
+        __syncthreads();
+      }
+      if (!exchange(++epoch)) { fail_exchange(); return; }
+      // ---- p.q from the gathered q: every CTA, whole vector, fixed order
+      const double* q = X.at(X.rank, qoff);
+      double s_pq = 0.0;
+      for (int i = tid; i < n; i += kPcgThreads) s_pq += psh[i] * __ldcg(q + i);
+      s_pq = warp_sum(s_pq);
+      if (lane == 0) red[warp][0] = s_pq;
+      __syncthreads();
+      if (tid == 0) { double a = 0; for (int w = 0; w < nwarp_cta; ++w) a += red[w][0]; bcast[0] = a; }
+      __syncthreads();
+      const double pq = bcast[0];
+      if (!(pq > 0.0) || !isfinite(pq)) { bad_pq = true; break; }     // identical on every CTA and rank
+      const double alpha = rz / pq;
+      // ---- x += alpha p, r -= alpha q, z = M^-1 r by CTA-strided rows; partial r.z, r.r
+      double s_a = 0.0, s_b = 0.0;
+      for (int f = blockIdx.x * nwarp_cta + warp; f < nfree; f += G_ * nwarp_cta) {
+        double rn = 0.0;
+        if (lane < 6) {
+          d.dc[6 * f + lane] += alpha * psh[6 * f + lane];
+          rn = d.r[6 * f + lane] - alpha * __ldcg(q + 6 * f + lane);
+          d.r[6 * f + lane] = rn;
+        }
+        double zv = 0.0;
+#pragma unroll
+        for (int s_ = 0; s_ < 6; ++s_) {
+          const double rs = __shfl_sync(0xffffffffu, rn, s_);
+          if (lane < 6) zv += __ldcg(Minv + (size_t)f * 37 + 6 * lane + s_) * rs;
+        }
+        if (lane < 6) { d.z[6 * f + lane] = zv; s_a += rn * zv; s_b += rn * rn; }
+      }
+      s_a = warp_sum(s_a); s_b = warp_sum(s_b);
+      if (lane == 0) { red[warp][2] = s_a; red[warp][3] = s_b; }
+      __syncthreads();
+      if (tid == 0) {
+        double a = 0, b = 0;
+        for (int w = 0; w < nwarp_cta; ++w) { a += red[w][2]; b += red[w][3]; }
+        part[blockIdx.x * 4 + 2] = a; part[blockIdx.x * 4 + 3] = b;
+      }
+      grid.sync();
+      const double rz2 = ordered_sum(part + 2, G_, 4, &bcast[2]);
+      rnorm2 = ordered_sum(part + 3, G_, 4, &bcast[3]);
+      beta = rz2 / rz;
+      rz = rz2;
+    }
+  }
+  if (blockIdx.x == 0 && tid == 0) {
+    if (bad_pq) ctrl->step_bad = 1;
+    ctrl->pcg_last = it; ctrl->pcg_iters += it; ctrl->xepoch = epoch;
+  }
+}
+
+}  // namespace
+}  // namespace b2
+
 namespace b2 {
 namespace {
 
@@ -933,7 +1329,14 @@ __global__ void __launch_bounds__(kBsThreads) large_backsub_kernel(LargeData d, 
     const double u0 = F0 * t0, u1 = F1 * t0 + F3 * t1, u2 = F2 * t0 + F4 * t1 + F5 * t2;
     const double d0 = -(F0 * u0 + F1 * u1 + F2 * u2), d1 = -(F3 * u1 + F4 * u2), d2 = -(F5 * u2);
     const double Xn0 = X0 + d0, Xn1 = X1 + d1, Xn2 = X2 + d2;
-    d.pts_tri[3 * (size_t)p] = Xn0; d.pts_tri[3 * (size_t)p + 1] = Xn1; d.pts_tri[3 * (size_t)p + 2] = Xn2;
+    if (d.nranks > 1) {      // the trial landmark goes into EVERY rank's copy (landmarks are replicated state)
+      for (int r_ = 0; r_ < d.nranks; ++r_) {
+        double* pt = d.peer.at(r_, d.peer.off_pts_tri) + 3 * (size_t)p;
+        pt[0] = Xn0; pt[1] = Xn1; pt[2] = Xn2;
+      }
+    } else {
+      d.pts_tri[3 * (size_t)p] = Xn0; d.pts_tri[3 * (size_t)p + 1] = Xn1; d.pts_tri[3 * (size_t)p + 2] = Xn2;
+    }
     s[1] = d0 * d0 * sc[9] + d1 * d1 * sc[10] + d2 * d2 * sc[11];
     s[2] = d0 * g0 + d1 * g1 + d2 * g2;
     s[3] = d0 * d0 + d1 * d1 + d2 * d2;
@@ -956,6 +1359,7 @@ __global__ void __launch_bounds__(kBsThreads) large_backsub_kernel(LargeData d, 
     for (int w = 0; w < kBsThreads / 32; ++w) v += red[w][tid];
     d.part[(size_t)blockIdx.x * 8 + tid] = v;
   }
+  if (d.nranks > 1) __threadfence_system();     // peer stores of this CTA are ordered before the exchange kernel's flag
 }
 
 // ordered sum of the back-substitution partials -> sums_part[0..5] (+ local gmax in [6])
@@ -972,7 +1376,41 @@ __global__ void large_reduce_kernel(LargeData d, int nparts) {
   if (threadIdx.x == 0) { d.sums_part[6] = ctrl->sums[6]; d.sums_part[7] = ctrl->step_bad ? 1.0 : 0.0; }
 }
 
-// LM control (Spec a0), one thread; identical on every rank (inputs are allreduced)
+// nranks > 1: the 8 partial sums of every rank's landmark range -> every rank; summed in RANK ORDER (identical
+// everywhere), gmax / step-bad by max.  One CTA of 32 threads; the trial landmarks stored by large_backsub_kernel are
+// covered by the same flag (kernel boundary + system fence order them before it).
+__global__ void large_xchg_sums_kernel(LargeData d) {
+  LargeCtrl* ctrl = d.ctrl;
+  if (ctrl->stop) return;
+  const Peer& x = d.peer;
+  const int t = threadIdx.x;
+  const long long e = ctrl->xepoch + 1;
+  if (t < 8)
+    for (int r = 0; r < x.nranks; ++r) x.at(r, x.off_sums)[x.rank * 8 + t] = d.sums_part[t];
+  __threadfence_system();
+  __syncwarp();
+  bool ok = true;
+  if (t < x.nranks) {
+    xchg_publish(x, t, e);
+    ok = xchg_wait(x, t, e);
+  }
+  ok = __all_sync(0xffffffffu, ok);
+  if (t < 8 && ok) {
+    const double* sl = x.at(x.rank, x.off_sums);
+    double v = 0.0;
+    for (int r = 0; r < x.nranks; ++r) {
+      const double a = __ldcg(sl + r * 8 + t);
+      v = (t >= 6) ? fmax(v, a) : v + a;
+    }
+    d.sums_part[8 + t] = v;
+  }
+  if (t == 0) {
+    ctrl->xepoch = e;
+    if (!ok) { ctrl->xerr = 1; ctrl->stop = 1; ctrl->status = B2BA_NUMERICAL_FAILURE; }
+  }
+}
+
+// LM control (Spec a0), one thread; identical on every rank (replicated inputs, rank-ordered sums)
 __global__ void large_control_kernel(LargeData d, Params P, const double* sums) {
   LargeCtrl* c = d.ctrl;
   if (c->stop || threadIdx.x != 0) return;
@@ -1026,13 +1464,14 @@ __global__ void large_commit_kernel(LargeData d) {
   if (!c->accept) return;
   const size_t gid = blockIdx.x * (size_t)blockDim.x + threadIdx.x, gsz = (size_t)gridDim.x * blockDim.x;
   for (size_t i = gid; i < (size_t)d.nc * 12; i += gsz) d.poses[i] = d.poses_tri[i];
-  for (size_t i = (size_t)d.p_lo * 3 + gid; i < (size_t)d.p_hi * 3; i += gsz) d.pts[i] = d.pts_tri[i];
+  for (size_t i = gid; i < (size_t)d.np * 3; i += gsz) d.pts[i] = d.pts_tri[i];    // landmarks are replicated state
 }
 
 __global__ void large_clear_accept_kernel(LargeData d) { d.ctrl->accept = 0; }
 
 __global__ void large_init_ctrl_kernel(LargeData d, Params P) {
   LargeCtrl* c = d.ctrl;
+  c->xerr = 0;              // (xepoch is NOT reset: peer flags only grow over the life of the communicator)
   c->mu = P.init_mu; c->nu = 2.0; c->cost = 0.0; c->initial_cost = 0.0;
   for (int k = 0; k < 8; ++k) c->sums[k] = 0.0;
   for (int k = 0; k < 4; ++k) c->cam_sums[k] = 0.0;
@@ -1071,19 +1510,42 @@ int large_init_ctrl(const LargeData& d, const Params& P, cudaStream_t s) {
   return (int)cudaGetLastError();
 }
 
-int large_iteration(const LargeData& d, const Params& P, int pcg_max_iters, double pcg_tol,
-                    AllReduceFn ar, void* ar_user, cudaStream_t s) {
+int large_pcg_dist_grid(int n, int* blocks, size_t* smem) {
+  *smem = (size_t)n * sizeof(double);
+  cudaError_t e = cudaFuncSetAttribute(large_pcg_dist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)*smem);
+  if (e != cudaSuccess) return (int)e;
+  int per_sm = 0, dev = 0, sms = 0;
+  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, large_pcg_dist_kernel, kPcgThreads, *smem);
+  if (e != cudaSuccess) return (int)e;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  if (per_sm < 1) return (int)cudaErrorInvalidConfiguration;
+  *blocks = sms;            // one CTA per SM: the grid size fixes the summation order, it must be the same on every rank
+  return 0;
+}
+
+int large_iteration(const LargeData& d, const Params& P, int pcg_max_iters, double pcg_tol, cudaStream_t s) {
   int rc;
+  const bool mr = d.nranks > 1;
   large_clear_accept_kernel<<<1, 1, 0, s>>>(d);
   if (d.nc > 0) large_cam_kernel<<<d.nc, kCamThreads, 0, s>>>(d, P);
   large_cam_finish_kernel<<<1, 64, 0, s>>>(d);
-  if (ar && (rc = ar(ar_user, d.lin_part, d.lin, d.lin_count(), s)) != 0) return rc;
   large_init_S_kernel<<<2 * d.sms, 256, 0, s>>>(d);
   large_init_diag_kernel<<<(d.nc + 127) / 128 + 1, 128, 0, s>>>(d);
-  const int npl = d.p_hi - d.p_lo;
-  if (npl > 0) {
-    large_pt_kernel<<<(npl + 127) / 128, 128, 0, s>>>(d, P);
+  if (d.np > 0) {
+    large_pt_kernel<<<(d.np + 127) / 128, 128, 0, s>>>(d, P);
     if (d.a_hi > d.a_lo) large_z_kernel<<<(d.a_hi - d.a_lo + 255) / 256, 256, 0, s>>>(d, P, d.a_lo, d.a_hi);
+  }
+  if (mr) {
+    // S sharded by block row: the owned full rows (diagonal entries carry B' and g_red), nothing to reduce
+    const int nrows = d.f_hi - d.f_lo;
+    if (nrows > 0) large_sblock_rows_kernel<32, 1><<<(int)(((size_t)nrows * 32 + 127) / 128), 128, 0, s>>>(d);
+    if (d.nlocal > 0) {
+      if (d.pair_lanes == 1) large_sblock_rows_kernel<1, 2><<<(d.nlocal + 127) / 128, 128, 0, s>>>(d);
+      else if (d.pair_lanes == 8) large_sblock_rows_kernel<8, 2><<<(int)(((size_t)d.nlocal * 8 + 127) / 128), 128, 0, s>>>(d);
+      else large_sblock_rows_kernel<32, 2><<<(int)(((size_t)d.nlocal * 32 + 127) / 128), 128, 0, s>>>(d);
+    }
+  } else if (d.np > 0) {
     // lanes per S block: dense visibility gives many blocks with a handful of pairs each
     if (d.pair_lanes == 32) {
       large_sblock_kernel<32, 0><<<(int)(((size_t)d.nblk * 32 + 127) / 128), 128, 0, s>>>(d);
@@ -1093,7 +1555,11 @@ int large_iteration(const LargeData& d, const Params& P, int pcg_max_iters, doub
       else large_sblock_kernel<8, 2><<<(int)(((size_t)d.nblk * 8 + 127) / 128), 128, 0, s>>>(d);
     }
   }
-  if (ar && (rc = ar(ar_user, d.Sg, d.Sg, d.sg_count(), s)) != 0) return rc;
+  if (mr && (d.dense || d.bw >= 0)) {
+    // factorisations run replicated: the owned rows go into every rank's S (small when S is banded)
+    large_push_rows_kernel<<<2 * d.sms, 256, 0, s>>>(d);
+    large_xchg_kernel<<<1, 32, 0, s>>>(d);
+  }
   if (d.dense) {
     if ((rc = large_dense_solve(d, s)) != 0) return rc;
   } else if (d.bw >= 0) {
@@ -1101,21 +1567,23 @@ int large_iteration(const LargeData& d, const Params& P, int pcg_max_iters, doub
   } else {
     int blocks = 0;
     size_t smem = 0;
-    if ((rc = large_pcg_grid(d.n, &blocks, &smem)) != 0) return rc;
+    if ((rc = mr ? large_pcg_dist_grid(d.n, &blocks, &smem) : large_pcg_grid(d.n, &blocks, &smem)) != 0) return rc;
     LargeData dd = d;
     int mi = pcg_max_iters;
     double tol = pcg_tol;
     void* args[] = {&dd, &mi, &tol};
-    cudaError_t e = cudaLaunchCooperativeKernel((void*)large_pcg_kernel, dim3(blocks), dim3(kPcgThreads), args, smem, s);
+    cudaError_t e = cudaLaunchCooperativeKernel(mr ? (void*)large_pcg_dist_kernel : (void*)large_pcg_kernel, dim3(blocks),
+                                                dim3(kPcgThreads), args, smem, s);
     if (e != cudaSuccess) return (int)e;
   }
   large_cam_update_kernel<<<1, 1024, 0, s>>>(d);
+  const int npl = d.p_hi - d.p_lo;
   const int nparts = (npl + kBsThreads - 1) / kBsThreads;
   if (nparts > 0) large_backsub_kernel<<<nparts, kBsThreads, 0, s>>>(d, P);
   large_reduce_kernel<<<1, 192, 0, s>>>(d, nparts);
   const double* sums = d.sums_part;
-  if (ar) {
-    if ((rc = ar(ar_user, d.sums_part, d.sums_part + 8, 8, s)) != 0) return rc;
+  if (mr) {
+    large_xchg_sums_kernel<<<1, 32, 0, s>>>(d);
     sums = d.sums_part + 8;
   }
   large_control_kernel<<<1, 32, 0, s>>>(d, P, sums);

@@ -2,10 +2,20 @@
 // block-sparse reduced camera system and block-Jacobi PCG, all control on the device (the host
 // only enqueues a fixed kernel sequence per LM iteration; no host synchronisation in the loop).
 //
-// Multi-GPU (SURVEY §8 row e): landmarks are sharded by contiguous point ranges balanced by
-// observation count; poses are replicated; per LM iteration three ncclAllReduce(sum, f64):
-//   {B_c, g_c, cost}  ->  {S blocks, g_red}  ->  {trial cost, model-decrease terms}
-// and the PCG + LM control run replicated (bit-identical inputs on every rank).
+// Multi-GPU (SURVEY §8 row e), one process per GPU.  The small state (poses, landmarks, LM control) is REPLICATED and
+// kept bit-identical on every rank; what is big is sharded and exchanged by the engine's own kernels through PEER
+// MEMORY (every rank's exchange arena is mapped into every other rank with CUDA IPC; stores over NVLink / NVSwitch
+// followed by a system-scope release of an epoch flag; no collective library call inside the LM loop):
+//   * the reduced camera system S is sharded by BLOCK ROW: a rank forms the full rows it owns (Schur pair lists of
+//     ALL landmarks, restricted to its rows) -- S is born sharded, it is never reduced or gathered for PCG;
+//   * PCG runs on every rank in lockstep with replicated vectors; a rank multiplies its rows and stores its slice of
+//     q = S p into every rank's q buffer: ONE all-gather of 6 doubles per owned row per CG iteration, inside the
+//     kernel (dense C5: 18 MB of S per rank at 8 GPUs, L2-resident, instead of 144 MB streamed from HBM);
+//   * banded / dense solvers: the owned rows are pushed into every rank's copy of S (small when S is banded) and the
+//     factorisation runs replicated;
+//   * back-substitution is sharded by landmark range; a rank stores its trial landmarks and its 8 partial sums into
+//     every rank, which adds the partial sums in rank order (deterministic, identical everywhere).
+// NCCL is only the bootstrap (unique id, exchange of the IPC handles, barriers at set-up).
 #pragma once
 #include "ba_math.cuh"
 #include "devbuf.cuh"
@@ -13,7 +23,21 @@
 
 namespace b2 {
 
+constexpr int kMaxRanks = 8;
+
+// Peer-memory exchange state (nranks > 1).  Every rank allocates one arena with the SAME layout; arena[r] is rank r's
+// arena as mapped into this process.  flags: kMaxRanks int64 per rank, flags[src] = last epoch rank `src` has
+// published; epochs only grow (LargeCtrl::xepoch, identical on every rank because every rank runs the same exchanges).
+struct Peer {
+  double* arena[kMaxRanks];
+  int rank, nranks;
+  size_t off_flags, off_sums, off_qx, off_minv, off_r, off_sg, off_pts_tri;   // in doubles
+  __host__ __device__ double* at(int r, size_t off) const { return arena[r] + off; }
+};
+
 struct LargeCtrl {          // device-resident LM state
+  long long xepoch;         // peer exchanges completed so far (replicated)
+  int xerr, xpad;           // a peer exchange timed out (the solve is abandoned, b2ba_solve reports it)
   double mu, nu, cost, initial_cost;
   double sums[8];           // reduced: trial cost, dDd, gd, dn2, xn2, n_invalid(trial), gmax, -
   double cam_sums[4];       // camera part of dDd, gd, dn2
@@ -26,6 +50,14 @@ struct LargeData {
   int p_lo, p_hi;                  // this rank's landmark range (whole problem on one GPU)
   int rank, nranks;
   int sms;                         // SM count of the handle's device (grid sizing)
+  Peer peer;                       // nranks > 1: exchange arenas of all ranks
+  int f_lo, f_hi;                  // nranks > 1: block rows of S this rank owns
+  const int* lrow_ptr;             // (f_hi - f_lo + 1): the owned FULL rows (both triangles), local entry offsets
+  const int* lcol;                 // column block of each local entry
+  const int* lsrc;                 // upper block the entry is (or is the transpose of): id | (transposed << 31)
+  const int* ldiag;                // (f_hi - f_lo): local entry index of each owned row's diagonal block
+  int nlocal;                      // local entries
+  double* Sl;                      // nlocal x 36: the owned rows of S, block (f, c) row-major
   const ObsRec* pm;                // point-major stream of the WHOLE problem (idx = camera)
   const int* pt_ptr;               // np+1
   const ObsRec* cm;                // camera-major stream of the LOCAL observations (idx = point)
@@ -76,11 +108,11 @@ struct LargeData {
   __host__ __device__ size_t sg_count() const { return (size_t)nblk * 36 + n; }
 };
 
-typedef int (*AllReduceFn)(void* user, const double* send, double* recv, size_t count, cudaStream_t s);
-
 // S block structure from the point-major stream (a8, device). Fills the DevBufs; returns cudaError.
 struct LargeIndex {
   DevBuf<int> fidx, blk_ptr, blk_col, frow_ptr, fcol, fsrc, pair_ptr, blk_row, pm_pt;
+  DevBuf<int> lrow_ptr, lcol, lsrc, ldiag;   // nranks > 1: the owned full rows (large_build_rows)
+  int f_lo = 0, f_hi = 0, nlocal = 0;
   int a_lo = 0, a_hi = 0;
   DevBuf<int2> pair_ab;
   long long npairs = 0;
@@ -90,14 +122,16 @@ int large_build_structure(int nc, int np, long long no, const ObsRec* pm, const 
                           const unsigned char* h_fixed, LargeIndex& ix, cudaStream_t s);
 // Schur pair list of the landmarks [p_lo, p_hi) (needs the structure): ix.pair_ptr / pair_ab / blk_row
 int large_build_pairs(int p_lo, int p_hi, long long no, const ObsRec* pm, const int* pt_ptr, LargeIndex& ix, cudaStream_t s);
+// nranks > 1: block rows [f_lo, f_hi) owned by `rank` (contiguous, balanced by full-row entries) and their local CSR
+int large_build_rows(int rank, int nranks, LargeIndex& ix, cudaStream_t s);
 // camera-major stream of the observations of landmarks [p_lo, p_hi)
 int large_build_cm_slice(int nc, int p_lo, int p_hi, const ObsRec* pm, const int* pt_ptr, ObsRec* cm,
                          int* cam_ptr, cudaStream_t s);
 
 int large_init_ctrl(const LargeData& d, const Params& P, cudaStream_t s);
-// enqueue one LM iteration (all kernels + the three allreduces when ar != null)
-int large_iteration(const LargeData& d, const Params& P, int pcg_max_iters, double pcg_tol,
-                    AllReduceFn ar, void* ar_user, cudaStream_t s);
+// enqueue one LM iteration (nranks > 1: the peer-memory exchanges are part of the kernels)
+int large_iteration(const LargeData& d, const Params& P, int pcg_max_iters, double pcg_tol, cudaStream_t s);
+int large_pcg_dist_grid(int n, int* blocks, size_t* smem);   // cooperative launch geometry of the distributed PCG
 int large_finish(const LargeData& d, cudaStream_t s);
 int large_pcg_grid(int n, int* blocks, size_t* smem);   // cooperative launch geometry
 // exact banded Cholesky solve of S dc = -g_red (ba_band.cu); needs d.bw >= 0
