@@ -50,7 +50,8 @@ typedef struct b2ba_options {
                              handle are otherwise solved by one 8- or 16-CTA cluster each: the latency path);
                              bit2 / bit3 force kernel instantiations that the engine would not pick by itself
                              (256-thread CTAs on the batched small path / the portable 8-CTA cluster for <= 8
-                             windows): same results up to summation order; used by the parity tests */
+                             windows): same results up to summation order; used by the parity tests;
+                             bit4: time the phases of the next solves with CUDA events (b2ba_get_timings) */
   int32_t pad_;
 } b2ba_options;
 
@@ -58,6 +59,24 @@ typedef struct b2ba_summary {
   int32_t status, iterations, accepted, rejected, n_invalid, pcg_iters;
   double initial_cost, final_cost, final_mu;
 } b2ba_summary;
+
+/* Device times of the last set_problem / solve (SURVEY §5 "Metrics": per-phase ms).  Filled when options.flags bit 4
+ * is set; phases are recorded with CUDA events on the solve's stream between the kernel groups of an LM iteration and
+ * summed over the iterations (large path; the window path is ONE kernel, so only setup_ms / solve_ms apply there).
+ * Host ranges of the same phases are emitted as NVTX ranges ("b2ba:<phase>") in every mode. */
+enum { B2BA_T_LINEARISE = 0,   /* camera pass + landmark blocks + Z records (a1-a3) */
+       B2BA_T_SCHUR = 1,       /* S blocks / owned block rows from the pair lists (a4) */
+       B2BA_T_EXCHANGE = 2,    /* multi-GPU, banded / dense solvers: owned rows pushed into every rank's S + flags */
+       B2BA_T_SOLVE = 3,       /* reduced camera system: PCG (incl. its in-kernel all-gathers) / banded / dense (a5-a6) */
+       B2BA_T_BACKSUB = 4,     /* camera update, back-substitution, trial cost (a7) */
+       B2BA_T_CONTROL = 5,     /* partial sums (multi-GPU: + their peer exchange), LM control, commit */
+       B2BA_T_PHASES = 8 };
+typedef struct b2ba_timings {
+  double setup_ms;                 /* index build + structure (a8), device time of the last set_problem */
+  double solve_ms;                 /* last b2ba_solve, first to last kernel */
+  double phase_ms[B2BA_T_PHASES];  /* per phase, summed over the LM iterations */
+  int32_t iterations_enqueued, pad_;
+} b2ba_timings;
 
 void b2ba_default_options(b2ba_options* o);
 
@@ -90,6 +109,8 @@ int b2ba_reset(b2ba_t* h);
  * enqueues work (no synchronisation); otherwise it synchronises the stream and fills them. */
 int b2ba_solve(b2ba_t* h, int32_t max_iters, b2ba_summary* summaries, void* cuda_stream);
 int b2ba_get_summaries(b2ba_t* h, b2ba_summary* summaries);
+/* Synchronises the last solve's stream; B2BA_E_STATE unless options.flags bit 4 was set for it. */
+int b2ba_get_timings(b2ba_t* h, b2ba_timings* out);
 
 int b2ba_get(b2ba_t* h, double* poses_cw, double* points, int mem);
 

@@ -75,7 +75,7 @@ __global__ void __launch_bounds__(1024) exch_kernel(Peers P, int rank, int nrank
       double v = 0.0;
       for (int r = 0; r < nranks; ++r) {
         const double x = __ldcg(base + (size_t)r * slot_doubles + i);
-        if (x != (double)(r + 1) * 1e-3 * it + i) ++bad;
+        if (fabs(x - ((double)(r + 1) * 1e-3 * it + i)) > 1e-7) ++bad;   // a stale value (iteration it - 2) is off by >= 2e-3
         v += x;
       }
       acc += v;

@@ -17,7 +17,7 @@ D = dict(PM_PERM=1, PT_PTR=2, CM_PERM=3, CAM_PTR=4, FIDX=5, BLK_PTR=6, BLK_COL=7
          HIST_COST=64, HIST_MU=65, HIST_ACCEPT=66, POSE_HIST_COST=80, POSE_HIST_MU=81, POSE_HIST_ACCEPT=82)
 # every symbol include/b2ba.h declares
 SYMBOLS = ["b2ba_default_options", "b2ba_create", "b2ba_destroy", "b2ba_last_error", "b2ba_set_problem",
-           "b2ba_set_problem_batch", "b2ba_set_state", "b2ba_reset", "b2ba_solve", "b2ba_get_summaries",
+           "b2ba_set_problem_batch", "b2ba_set_state", "b2ba_reset", "b2ba_solve", "b2ba_get_summaries", "b2ba_get_timings",
            "b2ba_get", "b2ba_optimize_batch", "b2ba_refine_poses", "b2ba_track_pose", "b2ba_ransac_pose", "b2ba_triangulate", "b2ba_reproj_errors", "b2ba_dump", "b2ba_create_comm", "b2ba_nccl_unique_id", "b2ba_set_point_range",
            "b2ba_peak_flops", "b2ba_version"]
 
@@ -35,6 +35,13 @@ class Summary(C.Structure):
                 ("rejected", C.c_int32), ("n_invalid", C.c_int32), ("pcg_iters", C.c_int32),
                 ("initial_cost", C.c_double), ("final_cost", C.c_double), ("final_mu", C.c_double)]
 
+
+class Timings(C.Structure):
+    _fields_ = [("setup_ms", C.c_double), ("solve_ms", C.c_double), ("phase_ms", C.c_double * 8),
+                ("iterations_enqueued", C.c_int32), ("pad_", C.c_int32)]
+
+
+PHASES = ("linearise", "schur", "exchange", "solve", "backsub", "control")
 
 _lib = None
 
@@ -62,6 +69,7 @@ def load():
     lib.b2ba_reset.argtypes = [vp]
     lib.b2ba_solve.argtypes = [vp, i32, vp, vp]
     lib.b2ba_get_summaries.argtypes = [vp, vp]
+    lib.b2ba_get_timings.argtypes = [vp, C.POINTER(Timings)]
     lib.b2ba_get.argtypes = [vp, vp, vp, C.c_int]
     lib.b2ba_optimize_batch.argtypes = [vp, i32, vp, vp, vp, vp, vp, vp, vp, vp, vp, dp, i32, vp, vp, vp, i32]
     lib.b2ba_refine_poses.argtypes = [vp, i32, vp, vp, vp, vp, dp, i32, vp, i32]

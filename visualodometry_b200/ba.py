@@ -41,13 +41,14 @@ class BAConfig:
     record_history: bool = False
     cluster: bool = True           # few windows: one 8-CTA cluster per window (latency path); False = one CTA per window
     variant: str = "auto"          # "auto" | "small256" | "cluster8": force a window-kernel instantiation (tests)
+    time_phases: bool = False      # CUDA-event timing of set-up / solve / LM phases (BundleAdjuster.timings())
 
     def to_options(self) -> _lib.Options:
         return _lib.Options(self.max_iters, {"trivial": 0, "huber": 1}[self.loss], self.loss_scale,
                             self.z_min, self.init_radius, self.ftol, self.gtol, self.ptol,
                             {"auto": 0, "chol": 1, "pcg": 2, "dense": 3}[self.solver], self.pcg_max_iters,
                             self.pcg_tol, (1 if self.record_history else 0) | (0 if self.cluster else 2)
-                            | {"auto": 0, "small256": 4, "cluster8": 8}[self.variant], 0)
+                            | {"auto": 0, "small256": 4, "cluster8": 8}[self.variant] | (16 if self.time_phases else 0), 0)
 
 
 @dataclass
@@ -207,6 +208,13 @@ class BundleAdjuster:
         sm = (_lib.Summary * self._nb)()
         self._check(self._lib.b2ba_get_summaries(self._h, sm), "b2ba_get_summaries")
         return [self._summary(s) for s in sm]
+
+    def timings(self) -> dict:
+        """Device times of the last set_problem / solve (config.time_phases): {"setup_ms", "solve_ms", "phases": {...}}."""
+        t = _lib.Timings()
+        self._check(self._lib.b2ba_get_timings(self._h, C.byref(t)), "b2ba_get_timings")
+        return {"setup_ms": t.setup_ms, "solve_ms": t.solve_ms, "iterations": t.iterations_enqueued,
+                "phases": {k: t.phase_ms[i] for i, k in enumerate(_lib.PHASES)}}
 
     @staticmethod
     def _summary(s):

@@ -12,6 +12,8 @@
 #include <utility>
 #include <vector>
 
+#include <nvtx3/nvToolsExt.h>
+
 #include "ba_index.cuh"
 #include "devbuf.cuh"
 #include "ba_large.cuh"
@@ -72,6 +74,11 @@ struct b2ba {
   bool range_set = false;
   cudaStream_t last_stream = nullptr;
   bool solved = false;
+  // timings (options.flags bit 4)
+  std::vector<cudaEvent_t> t_ev;       // 7 per LM iteration (large path) or 2 (window path)
+  cudaEvent_t t_setup[2] = {nullptr, nullptr};
+  int t_iters = 0;
+  bool t_valid = false, t_setup_valid = false;
   // multi-GPU
   int rank = 0, nranks = 1;
   void* nccl_comm = nullptr;
@@ -238,7 +245,9 @@ int setup_arena(b2ba* h) {
   if (off > h->l_arena.n || !h->l_arena.p) {
     // (re)allocation: every rank takes this branch together (the layout depends on the problem only)
     if (h->l_arena.p) {
-      close_peers(h);
+      for (cudaEvent_t e : h->t_ev) cudaEventDestroy(e);
+  if (h->t_setup[0]) { cudaEventDestroy(h->t_setup[0]); cudaEventDestroy(h->t_setup[1]); }
+  close_peers(h);
       int rc = nccl_barrier(h);                    // nobody still maps the old arena
       if (rc) return rc;
     }
@@ -380,14 +389,24 @@ int setup_large(b2ba* h) {
 
 int solve_large(b2ba* h, const Params& P, bool hist, cudaStream_t s) {
   const LargeData d = make_large(h, hist);
+  const bool timed = (h->opt.flags & 16) != 0;
+  if (timed) {
+    while (h->t_ev.size() < (size_t)P.max_iters * 7) {
+      cudaEvent_t e;
+      CU(cudaEventCreate(&e), "event");
+      h->t_ev.push_back(e);
+    }
+  }
+  h->t_valid = false;
   int rc = large_init_ctrl(d, P, s);
   if (rc) return cuda_fail(h, (cudaError_t)rc, "large_init_ctrl");
   for (int it = 0; it < P.max_iters; ++it) {
-    rc = large_iteration(d, P, h->opt.pcg_max_iters, h->opt.pcg_tol, s);
+    rc = large_iteration(d, P, h->opt.pcg_max_iters, h->opt.pcg_tol, s, timed ? h->t_ev.data() + 7 * (size_t)it : nullptr);
     if (rc) return cuda_fail(h, (cudaError_t)rc, "large_iteration");
   }
   rc = large_finish(d, s);
   if (rc) return cuda_fail(h, (cudaError_t)rc, "large_finish");
+  h->t_iters = P.max_iters; h->t_valid = timed;
   return B2BA_OK;        // nranks > 1: poses and landmarks are replicated state, every rank ends with all of them
 }
 
@@ -440,6 +459,8 @@ void b2ba_destroy(b2ba_t* h) {
   if (h->pinned_stage) cudaFreeHost(h->pinned_stage);
   if (h->pipe_back) cudaStreamDestroy(h->pipe_back);
   if (h->pinned_flags) cudaFreeHost(h->pinned_flags);
+  for (cudaEvent_t e : h->t_ev) cudaEventDestroy(e);
+  if (h->t_setup[0]) { cudaEventDestroy(h->t_setup[0]); cudaEventDestroy(h->t_setup[1]); }
   close_peers(h);
   if (h->nccl_comm && nccl_api().ok) nccl_api().CommDestroy(h->nccl_comm);
   delete h;
@@ -512,7 +533,14 @@ int b2ba_set_problem_batch(b2ba_t* h, int32_t B, const int32_t* cam_off, const i
   const bool want_pcg = h->opt.solver == B2BA_SOLVER_PCG || h->opt.solver == B2BA_SOLVER_DENSE;   // = the large path
   h->sched_order = !want_pcg && h->max_nc <= kMaxCam && h->max_nfree <= kBigMaxFree && np > 0;
   IndexOut io{h->d_pm.p, h->d_pt_ptr.p, h->d_cm.p, h->d_cam_ptr.p, h->d_flags.p, h->sched_order ? h->d_sched.p : nullptr};
+  h->t_setup_valid = false;
+  if (h->opt.flags & 16) {
+    if (!h->t_setup[0]) { CU(cudaEventCreate(&h->t_setup[0]), "event"); CU(cudaEventCreate(&h->t_setup[1]), "event"); }
+    CU(cudaEventRecord(h->t_setup[0], nullptr), "event");
+  }
+  nvtxRangePushA("b2ba:index_build");
   int rc = build_index(make_index_in(h), io, nullptr);
+  nvtxRangePop();
   if (rc) { cudaDeviceSynchronize(); return cuda_fail(h, (cudaError_t)rc, "build_index"); }   // copies above are done with the caller's buffers
   int flags[2] = {0, 0};
   CU(cudaMemcpy(flags, h->d_flags.p, sizeof(flags), cudaMemcpyDeviceToHost), "read index flags");
@@ -531,9 +559,12 @@ int b2ba_set_problem_batch(b2ba_t* h, int32_t B, const int32_t* cam_off, const i
   if (h->nranks > 1 && h->path != PATH_LARGE)
     return fail(h, B2BA_E_UNSUPPORTED, "observation sharding (nranks > 1) needs solver = B2BA_SOLVER_PCG");
   if (h->path == PATH_LARGE) {
+    nvtxRangePushA("b2ba:large_structure");
     const int rc2 = setup_large(h);
+    nvtxRangePop();
     if (rc2) { h->path = PATH_NONE; return rc2; }
   }
+  if (h->opt.flags & 16) { CU(cudaEventRecord(h->t_setup[1], nullptr), "event"); h->t_setup_valid = true; }
   return B2BA_OK;
 }
 
@@ -589,6 +620,30 @@ int b2ba_get_summaries(b2ba_t* h, b2ba_summary* summaries) {
   return B2BA_OK;
 }
 
+int b2ba_get_timings(b2ba_t* h, b2ba_timings* out) {
+  if (!h || !out) return B2BA_E_INVALID;
+  if (!h->solved || !h->t_valid) return fail(h, B2BA_E_STATE, "no timed solve (options.flags bit 4)");
+  DeviceGuard dg_(h->device); CU(dg_.err, "cudaSetDevice");
+  CU(cudaStreamSynchronize(h->last_stream), "solve");
+  std::memset(out, 0, sizeof(*out));
+  float ms = 0.f;
+  if (h->t_setup_valid && cudaEventElapsedTime(&ms, h->t_setup[0], h->t_setup[1]) == cudaSuccess) out->setup_ms = ms;
+  out->iterations_enqueued = h->t_iters;
+  if (h->t_iters == 0) {          // window path: one kernel
+    CU(cudaEventElapsedTime(&ms, h->t_ev[0], h->t_ev[1]), "elapsed");
+    out->solve_ms = ms;
+    return B2BA_OK;
+  }
+  for (int it = 0; it < h->t_iters; ++it)
+    for (int p = 0; p < 6; ++p) {
+      CU(cudaEventElapsedTime(&ms, h->t_ev[7 * (size_t)it + p], h->t_ev[7 * (size_t)it + p + 1]), "elapsed");
+      out->phase_ms[p] += ms;
+    }
+  CU(cudaEventElapsedTime(&ms, h->t_ev[0], h->t_ev[7 * (size_t)(h->t_iters - 1) + 6]), "elapsed");
+  out->solve_ms = ms;
+  return B2BA_OK;
+}
+
 int b2ba_solve(b2ba_t* h, int32_t max_iters, b2ba_summary* summaries, void* cuda_stream) {
   if (!h || h->path == PATH_NONE) return fail(h, B2BA_E_STATE, "no problem set");
   DeviceGuard dg_(h->device); CU(dg_.err, "cudaSetDevice");
@@ -604,7 +659,18 @@ int b2ba_solve(b2ba_t* h, int32_t max_iters, b2ba_summary* summaries, void* cuda
     CU(cudaMemsetAsync(h->d_hist_accept.p, 0, (size_t)h->B * kHist * 4, s), "memset");
   }
   int rc = 0;
-  if (h->path == PATH_WIN_SMALL || h->path == PATH_WIN_BIG) rc = launch_window_path(h, make_win(h, hist, nullptr), P, s);
+  if (h->path == PATH_WIN_SMALL || h->path == PATH_WIN_BIG) {
+    const bool timed = (h->opt.flags & 16) != 0;
+    if (timed) {
+      while (h->t_ev.size() < 2) { cudaEvent_t e; CU(cudaEventCreate(&e), "event"); h->t_ev.push_back(e); }
+      CU(cudaEventRecord(h->t_ev[0], s), "event");
+    }
+    nvtxRangePushA("b2ba:window_lm_kernel");
+    rc = launch_window_path(h, make_win(h, hist, nullptr), P, s);
+    nvtxRangePop();
+    if (timed) CU(cudaEventRecord(h->t_ev[1], s), "event");
+    h->t_iters = 0; h->t_valid = timed;
+  }
   else if (h->path == PATH_LARGE) {
     if (hist) { CU(h->d_hist_cost.alloc(kHist), "alloc"); }
     rc = solve_large(h, P, hist, s);

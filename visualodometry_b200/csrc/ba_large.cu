@@ -5,6 +5,7 @@
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
 #include <cub/device/device_select.cuh>
+#include <nvtx3/nvToolsExt.h>
 
 #include <algorithm>
 #include <vector>
@@ -1524,9 +1525,18 @@ int large_pcg_dist_grid(int n, int* blocks, size_t* smem) {
   return 0;
 }
 
-int large_iteration(const LargeData& d, const Params& P, int pcg_max_iters, double pcg_tol, cudaStream_t s) {
+int large_iteration(const LargeData& d, const Params& P, int pcg_max_iters, double pcg_tol, cudaStream_t s, cudaEvent_t* ev) {
   int rc;
   const bool mr = d.nranks > 1;
+  int phase = 0;
+  // phase boundary: NVTX range of the host enqueue + (profiling mode) an event on the stream
+  auto mark = [&](const char* next) {
+    if (phase > 0) nvtxRangePop();
+    if (ev) cudaEventRecord(ev[phase], s);
+    if (next) nvtxRangePushA(next);
+    ++phase;
+  };
+  mark("b2ba:linearise");
   large_clear_accept_kernel<<<1, 1, 0, s>>>(d);
   if (d.nc > 0) large_cam_kernel<<<d.nc, kCamThreads, 0, s>>>(d, P);
   large_cam_finish_kernel<<<1, 64, 0, s>>>(d);
@@ -1536,6 +1546,7 @@ int large_iteration(const LargeData& d, const Params& P, int pcg_max_iters, doub
     large_pt_kernel<<<(d.np + 127) / 128, 128, 0, s>>>(d, P);
     if (d.a_hi > d.a_lo) large_z_kernel<<<(d.a_hi - d.a_lo + 255) / 256, 256, 0, s>>>(d, P, d.a_lo, d.a_hi);
   }
+  mark("b2ba:schur");
   if (mr) {
     // S sharded by block row: the owned full rows (diagonal entries carry B' and g_red), nothing to reduce
     const int nrows = d.f_hi - d.f_lo;
@@ -1555,31 +1566,35 @@ int large_iteration(const LargeData& d, const Params& P, int pcg_max_iters, doub
       else large_sblock_kernel<8, 2><<<(int)(((size_t)d.nblk * 8 + 127) / 128), 128, 0, s>>>(d);
     }
   }
+  mark("b2ba:exchange");
   if (mr && (d.dense || d.bw >= 0)) {
     // factorisations run replicated: the owned rows go into every rank's S (small when S is banded)
     large_push_rows_kernel<<<2 * d.sms, 256, 0, s>>>(d);
     large_xchg_kernel<<<1, 32, 0, s>>>(d);
   }
+  mark("b2ba:solve");
   if (d.dense) {
-    if ((rc = large_dense_solve(d, s)) != 0) return rc;
+    if ((rc = large_dense_solve(d, s)) != 0) { nvtxRangePop(); return rc; }
   } else if (d.bw >= 0) {
-    if ((rc = large_band_solve(d, s)) != 0) return rc;
+    if ((rc = large_band_solve(d, s)) != 0) { nvtxRangePop(); return rc; }
   } else {
     int blocks = 0;
     size_t smem = 0;
-    if ((rc = mr ? large_pcg_dist_grid(d.n, &blocks, &smem) : large_pcg_grid(d.n, &blocks, &smem)) != 0) return rc;
+    if ((rc = mr ? large_pcg_dist_grid(d.n, &blocks, &smem) : large_pcg_grid(d.n, &blocks, &smem)) != 0) { nvtxRangePop(); return rc; }
     LargeData dd = d;
     int mi = pcg_max_iters;
     double tol = pcg_tol;
     void* args[] = {&dd, &mi, &tol};
     cudaError_t e = cudaLaunchCooperativeKernel(mr ? (void*)large_pcg_dist_kernel : (void*)large_pcg_kernel, dim3(blocks),
                                                 dim3(kPcgThreads), args, smem, s);
-    if (e != cudaSuccess) return (int)e;
+    if (e != cudaSuccess) { nvtxRangePop(); return (int)e; }
   }
+  mark("b2ba:backsub");
   large_cam_update_kernel<<<1, 1024, 0, s>>>(d);
   const int npl = d.p_hi - d.p_lo;
   const int nparts = (npl + kBsThreads - 1) / kBsThreads;
   if (nparts > 0) large_backsub_kernel<<<nparts, kBsThreads, 0, s>>>(d, P);
+  mark("b2ba:control");
   large_reduce_kernel<<<1, 192, 0, s>>>(d, nparts);
   const double* sums = d.sums_part;
   if (mr) {
@@ -1588,6 +1603,7 @@ int large_iteration(const LargeData& d, const Params& P, int pcg_max_iters, doub
   }
   large_control_kernel<<<1, 32, 0, s>>>(d, P, sums);
   large_commit_kernel<<<d.sms, 256, 0, s>>>(d);
+  mark(nullptr);
   return (int)cudaGetLastError();
 }
 
