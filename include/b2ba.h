@@ -203,6 +203,27 @@ int b2ba_nccl_unique_id(void* out128);
  * of all ranks must tile [0, Np)).  The host side balances them by observation count. */
 int b2ba_set_point_range(b2ba_t* h, int32_t p_lo, int32_t p_hi);
 
+/* NO COUNTERPART IN THE REFERENCE: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid allocation).
+ * The window solve (window_lm_kernel, the kernel b2ba_solve launches for problems of <= 24 cameras per window) with ALL
+ * of its scratch -- the landmark ping-pong buffers and the per-landmark rows F | g_p | D_p -- in one file-scope
+ * `static __device__` array of the library: the call allocates NOTHING (no cudaMalloc / cudaFree / stream-ordered
+ * allocation, no events) and does not synchronise; it enqueues two memory operations and three kernels on `cuda_stream`.
+ *   Set-up (may allocate, do it once, outside the no-allocation region): b2ba_create + b2ba_set_problem / _batch build the
+ * index arrays the kernel walks; this call reads them and nothing else of the handle.
+ *   poses_cw (Nc x 12 [R | t]) and points (Np x 3, the caller's landmark order) are DEVICE buffers of the caller, in: the
+ * initial state, out: the refined one; summaries: DEVICE array of B entries (out).  max_iters <= 0: options.max_iters.
+ *   Limit: the handle's problem may hold at most B2BA_NOALLOC_MAX_POINTS landmarks in total (144 bytes of scratch each: a
+ * 4.5 MiB array that every GPU which loads the library holds until exit); more -> B2BA_E_UNSUPPORTED, use b2ba_solve.
+ *   The array is shared by every call on a device and keeps the last call's contents (what must start at zero is cleared
+ * by the call itself): calls that OVERLAP on the GPU -- two streams, two handles, two threads -- race; serialise them.
+ *   The first call on a device resolves the array's device address (cudaGetSymbolAddress: no allocation, but make that
+ * one call before a graph capture begins).  Results are those of b2ba_set_state + b2ba_solve + b2ba_get on the same
+ * inputs (same kernel, same data); no history / timing options apply. */
+#define B2BA_NOALLOC_MAX_POINTS 32768
+int b2ba_solve_window_noalloc(b2ba_t* h, double* poses_cw, double* points, b2ba_summary* summaries, int32_t max_iters,
+                              void* cuda_stream);
+
 /* Measurement helper (bench.py roofline denominators; MEASURED_PEAKS.json has no fp64 entry): FP64 peak of `device`
  * in TFLOP/s with dependent-free DFMA chains and with mma.sync m8n8k4 f64 (DMMA), CUDA-event timed, ~50 ms. */
 int b2ba_peak_flops(int device, double* dfma_tflops, double* dmma_tflops);

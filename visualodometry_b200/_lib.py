@@ -11,6 +11,7 @@ LIB_PATH = os.path.join(HERE, "libb2ba.so")
 OK, E_INVALID, E_CUDA, E_NCCL, E_DUPLICATE, E_STATE, E_UNSUPPORTED = 0, -1, -2, -3, -4, -5, -6
 MAX_ITERS, CONVERGED, NUMERICAL_FAILURE = 1, 2, 3
 MEM_HOST, MEM_DEVICE = 0, 1
+NOALLOC_MAX_POINTS = 32768     # include/b2ba.h B2BA_NOALLOC_MAX_POINTS
 D = dict(PM_PERM=1, PT_PTR=2, CM_PERM=3, CAM_PTR=4, FIDX=5, BLK_PTR=6, BLK_COL=7, SCHED=8,
          RESIDUALS=16, WEIGHTS=17, JC=18, JP=19,
          B=32, GC=33, C=34, GP=35, S=36, GRED=37, DC=38, DP=39, SCALARS=40,
@@ -19,7 +20,7 @@ D = dict(PM_PERM=1, PT_PTR=2, CM_PERM=3, CAM_PTR=4, FIDX=5, BLK_PTR=6, BLK_COL=7
 SYMBOLS = ["b2ba_default_options", "b2ba_create", "b2ba_destroy", "b2ba_last_error", "b2ba_set_problem",
            "b2ba_set_problem_batch", "b2ba_set_state", "b2ba_reset", "b2ba_solve", "b2ba_get_summaries", "b2ba_get_timings",
            "b2ba_get", "b2ba_optimize_batch", "b2ba_refine_poses", "b2ba_track_pose", "b2ba_ransac_pose", "b2ba_triangulate", "b2ba_reproj_errors", "b2ba_dump", "b2ba_create_comm", "b2ba_nccl_unique_id", "b2ba_set_point_range",
-           "b2ba_peak_flops", "b2ba_version"]
+           "b2ba_peak_flops", "b2ba_solve_window_noalloc", "b2ba_version"]
 
 
 class Options(C.Structure):
@@ -83,6 +84,7 @@ def load():
     lib.b2ba_nccl_unique_id.argtypes = [vp]
     lib.b2ba_set_point_range.argtypes = [vp, i32, i32]
     lib.b2ba_peak_flops.argtypes = [C.c_int, dp, dp]
+    lib.b2ba_solve_window_noalloc.argtypes = [vp, vp, vp, vp, i32, vp]
     lib.b2ba_version.restype = C.c_int
     _lib = lib
     return lib

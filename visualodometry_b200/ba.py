@@ -209,6 +209,21 @@ class BundleAdjuster:
         self._check(self._lib.b2ba_get_summaries(self._h, sm), "b2ba_get_summaries")
         return [self._summary(s) for s in sm]
 
+    def solve_noalloc(self, poses, points, summaries, max_iters=0, stream=None):
+        """`b2ba_solve_window_noalloc` (no counterpart in the reference; added for callers that cannot call cudaMalloc):
+        the window solve of the problem set with set_problem, scratch in the library's static device array, nothing
+        allocated, nothing synchronised.  poses (Nc,12) / points (Np,3): CUDA float64 tensors, refined in place;
+        summaries: CUDA uint8 tensor of >= 48 * B bytes (b2ba_summary per window).  At most
+        `_lib.NOALLOC_MAX_POINTS` landmarks; overlapping calls on one GPU race (one shared scratch array)."""
+        for t, n in ((poses, self._shape[0] * 12), (points, self._shape[1] * 3)):
+            if not _is_cuda_tensor(t) or t.dtype != torch.float64 or t.numel() != n or not t.is_contiguous():
+                raise ValueError("solve_noalloc: contiguous CUDA float64 tensors of the problem's size required")
+        if not _is_cuda_tensor(summaries) or summaries.numel() * summaries.element_size() < 48 * self._nb:
+            raise ValueError("solve_noalloc: summaries must be a CUDA buffer of 48 bytes per window")
+        rc = self._lib.b2ba_solve_window_noalloc(self._h, poses.data_ptr(), points.data_ptr(), summaries.data_ptr(),
+                                                 max_iters, C.c_void_p(stream) if stream else None)
+        self._check(rc, "b2ba_solve_window_noalloc")
+
     def timings(self) -> dict:
         """Device times of the last set_problem / solve (config.time_phases): {"setup_ms", "solve_ms", "phases": {...}}."""
         t = _lib.Timings()

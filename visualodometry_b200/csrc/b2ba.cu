@@ -7,6 +7,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <dlfcn.h>
+#include <mutex>
 #include <cstring>
 #include <string>
 #include <utility>
@@ -1339,6 +1340,75 @@ int64_t b2ba_dump(b2ba_t* h, int what, void* dst, int64_t bytes) {
     default:
       return fail(h, B2BA_E_UNSUPPORTED, "dump: unknown or unavailable array");
   }
+}
+
+// ---------------------------------------------------------------------------------------------
+// b2ba_solve_window_noalloc: the window kernel with its scratch in a file-scope device array (include/b2ba.h).
+// No counterpart in the reference; added for callers that cannot call
+// cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).
+//
+// Scratch layout, per landmark of the handle's problem (schedule order), 18 doubles:
+//   [0, 3 Np)  landmarks, current      [3 Np, 6 Np)  landmarks, trial (ping-pong)      [6 Np, 18 Np)  F | g_p | D_p rows
+// Every device that loads the library holds the array (kNoAllocMaxPoints * 18 * 8 bytes = 4.5 MiB) until exit.
+// In HOST code `g_noalloc_scratch` is a host-side stand-in for the symbol, not a device address: the address a kernel
+// may use comes from cudaGetSymbolAddress, looked up once per device with that device current.
+constexpr int kNoAllocMaxPoints = B2BA_NOALLOC_MAX_POINTS;
+constexpr size_t kNoAllocDoublesPerPoint = 6 + kPtScratch;
+static __device__ __align__(256) double g_noalloc_scratch[(size_t)kNoAllocMaxPoints * kNoAllocDoublesPerPoint];
+
+namespace {
+// device address of g_noalloc_scratch on the CURRENT device (resolved once per device, under a mutex)
+int noalloc_scratch_ptr(b2ba* h, double** out) {
+  static std::mutex mtx;
+  static double* cache[64] = {};
+  int dev = -1;
+  CU(cudaGetDevice(&dev), "cudaGetDevice");
+  if (dev < 0 || dev >= 64) return fail(h, B2BA_E_UNSUPPORTED, "solve_window_noalloc: device index above 63");
+  std::lock_guard<std::mutex> lock(mtx);
+  if (!cache[dev]) {
+    double* ptr = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress((void**)&ptr, g_noalloc_scratch);
+    if (e != cudaSuccess || !ptr) return cuda_fail(h, e, "cudaGetSymbolAddress(g_noalloc_scratch)");
+    cache[dev] = ptr;
+  }
+  *out = cache[dev];
+  return B2BA_OK;
+}
+}  // namespace
+
+int b2ba_solve_window_noalloc(b2ba_t* h, double* poses_cw, double* points, b2ba_summary* summaries, int32_t max_iters,
+                              void* cuda_stream) {
+  if (!h) return B2BA_E_INVALID;
+  if (h->path != PATH_WIN_SMALL && h->path != PATH_WIN_BIG)
+    return fail(h, B2BA_E_STATE, "solve_window_noalloc: set a window problem first (b2ba_set_problem / _batch; <= 24 cameras per window)");
+  if (!poses_cw || !points || !summaries) return fail(h, B2BA_E_INVALID, "solve_window_noalloc: null argument (device pointers required)");
+  if (h->np_tot > kNoAllocMaxPoints)
+    return fail(h, B2BA_E_UNSUPPORTED, "solve_window_noalloc: " + std::to_string(h->np_tot) + " landmarks exceed the static scratch (B2BA_NOALLOC_MAX_POINTS = " +
+                                       std::to_string(kNoAllocMaxPoints) + "); use b2ba_solve");
+  DeviceGuard dg_(h->device); CU(dg_.err, "cudaSetDevice");
+  double* scr = nullptr;
+  if (const int rc = noalloc_scratch_ptr(h, &scr)) return rc;
+  cudaStream_t s = (cudaStream_t)cuda_stream;
+  const size_t np = (size_t)h->np_tot;
+  // the handle's index arrays (built by set_problem) + the caller's buffers + the static scratch; nothing of the
+  // handle's own state (d_poses, d_pts*, d_scratch, summaries, history) is read or written
+  WinData d = make_win(h, false, nullptr);
+  d.poses = poses_cw;
+  d.pts[0] = scr; d.pts[1] = scr + 3 * np; d.pt_scratch = scr + 6 * np;
+  d.summaries = summaries;
+  // the array keeps the last call's contents.  Every word the kernel reads is written first in the same call (landmarks by
+  // the permutation below, trial landmarks and scratch rows by the kernel before it reads them); the scratch rows are
+  // cleared all the same, so that a call never depends on what an earlier one left behind
+  CU(cudaMemsetAsync(scr + 3 * np, 0, (size_t)(3 + kPtScratch) * np * sizeof(double), s), "clear scratch");
+  int rc = h->sched_order ? permute_pts(h, points, d.pts[0], true, s)
+                          : (int)cudaMemcpyAsync(d.pts[0], points, 3 * np * sizeof(double), cudaMemcpyDeviceToDevice, s);
+  if (rc) return cuda_fail(h, (cudaError_t)rc, "solve_window_noalloc: landmarks in");
+  rc = launch_window_path(h, d, make_params(h, max_iters), s);
+  if (rc) return cuda_fail(h, (cudaError_t)rc, "solve_window_noalloc: launch");
+  rc = h->sched_order ? permute_pts(h, d.pts[0], points, false, s)
+                      : (int)cudaMemcpyAsync(points, d.pts[0], 3 * np * sizeof(double), cudaMemcpyDeviceToDevice, s);
+  if (rc) return cuda_fail(h, (cudaError_t)rc, "solve_window_noalloc: landmarks out");
+  return B2BA_OK;      // enqueued on `cuda_stream`; no synchronisation, no allocation
 }
 
 }  // extern "C"
