@@ -1,0 +1,9 @@
+#!/bin/bash
+# on the GPU box: bench every build_exp/libb2ba_*.so (C4 value, frac, e2e)
+cp visualodometry_b200/libb2ba.so /tmp/libb2ba_keep.so
+for f in build_exp/libb2ba_*.so; do
+  cp $f visualodometry_b200/libb2ba.so
+  echo -n "$f: "
+  timeout 200 python bench.py --no-cpu --no-c5 ${EXP_ARGS} 2>/dev/null | python -c "import json,sys; d=json.loads(sys.stdin.read()); print(d['ms_per_step'], round(d['roofline']['frac'],4), d['e2e']['ms_per_step'])"
+done
+cp /tmp/libb2ba_keep.so visualodometry_b200/libb2ba.so

@@ -26,6 +26,23 @@ namespace b2 {
 
 namespace cg = cooperative_groups;
 
+// experiment switches of the window kernel (defaults = the shipped configuration)
+#ifndef WX_STASH
+#define WX_STASH 0      // loop 2 reads w J_p / J_c parked by loop 1 in the Z slot instead of re-projecting
+#endif
+#ifndef WX_RECPIPE_PT
+#define WX_RECPIPE_PT 1 // point pass: first two records of the next batch loaded into registers during the DMMA
+#endif
+#ifndef WX_RECPIPE_BS
+#define WX_RECPIPE_BS 1 // back-substitution: same register pipeline
+#endif
+#ifndef WX_SPARSECLR
+#define WX_SPARSECLR 1  // Z tile cleared once per iteration; per batch only rows of cameras that left the slot are zeroed
+#endif
+#ifndef WX_SCHOIST
+#define WX_SCHOIST 0    // back-substitution: scratch row loaded at the top of the batch
+#endif
+
 __device__ __forceinline__ int packed21(int r, int s) { return r * 6 - r * (r - 1) / 2 + (s - r); }
 
 // ---- compile-time loop: f(integral_constant<int, I>) for I in [0, N)
@@ -83,11 +100,12 @@ __global__ void __launch_bounds__(Cfg::NTHREADS, Cfg::MINB)
 window_lm_kernel(const WinData d, const Params P) {
   constexpr int NTHREADS = Cfg::NTHREADS, NWARPS = Cfg::NWARPS, G = Cfg::G, KS = Cfg::KS, NT = Cfg::NT;
   constexpr int TPW = Cfg::TPW, TPP = Cfg::TPP, PB = Cfg::PB, LDT = Cfg::LDT, LDS = Cfg::LDS, MAXCAM = Cfg::MAXCAM;
+  constexpr int PS = Cfg::PS;               // pose stride in shared memory (doubles)
   constexpr int CS = Cfg::CS, BS = Cfg::CS * Cfg::PB;   // CTAs per window; landmark stride between this CTA's batches
   extern __shared__ __align__(16) double smem[];
   double* pose_cur = smem;
-  double* pose_tri = pose_cur + MAXCAM * 12;
-  double* Bc = pose_tri + MAXCAM * 12;      // MAXCAM x 21 (upper, packed)
+  double* pose_tri = pose_cur + MAXCAM * PS;
+  double* Bc = pose_tri + MAXCAM * PS;      // MAXCAM x 21 (upper, packed)
   double* gc = Bc + MAXCAM * 21;            // MAXCAM x 6
   double* Dc = gc + MAXCAM * 6;
   double* dvec = Dc + MAXCAM * 6;           // delta_c (6*nfree)
@@ -107,7 +125,7 @@ window_lm_kernel(const WinData d, const Params P) {
   const int c0 = d.cam_off[win], nc = d.cam_off[win + 1] - c0;
   const int p0 = d.pt_off[win], npw = d.pt_off[win + 1] - p0;
 
-  for (int i = tid; i < nc * 12; i += NTHREADS) pose_cur[i] = d.poses[(size_t)c0 * 12 + i];
+  for (int i = tid; i < nc * 12; i += NTHREADS) pose_cur[(i / 12) * PS + i % 12] = d.poses[(size_t)c0 * 12 + i];
   if (tid == 0) {
     int nf = 0;
     for (int c = 0; c < nc; ++c) {
@@ -189,7 +207,7 @@ window_lm_kernel(const WinData d, const Params P) {
           e = b + (int)(((long long)len * (crank + 1)) / CS);
           b = b + (int)(((long long)len * crank) / CS);
           Pose12 q;
-          load_pose(pose_cur + 12 * c, q);
+          load_pose(pose_cur + PS * c, q);
           const bool isfree = fidx[c] >= 0;
           double acc[29];
 #pragma unroll
@@ -217,7 +235,7 @@ window_lm_kernel(const WinData d, const Params P) {
       for (int c = 0; c < nc; ++c) {
         const int b = d.cam_ptr[c0 + c], e = d.cam_ptr[c0 + c + 1];
         Pose12 q;
-        load_pose(pose_cur + 12 * c, q);
+        load_pose(pose_cur + PS * c, q);
         const bool isfree = fidx[c] >= 0;
         double acc[29];
 #pragma unroll
@@ -290,8 +308,19 @@ window_lm_kernel(const WinData d, const Params P) {
     const double imu = 1.0 / mu;
     const double* zf = Z + (lane & 3) * LDT + (lane >> 2);   // DMMA fragment base of this lane
     double* const zcol = Z + (size_t)3 * slot * LDT;          // this landmark's 3 columns: 3*LDT contiguous doubles
-    int a0n = 0, a1n = 0;
+    const ObsRec zrec{0.f, 0.f, 0, 0};
+    unsigned prev_rows = 0;                   // free cameras (+ bit nfree: the y row) this slot wrote in the previous batch
+    if constexpr (WX_SPARSECLR) {
+      // the tile memory held S and the Cholesky factor: clear it once; afterwards a slot only zeroes the rows of cameras
+      // that saw its previous landmark but do not see the present one
+      double2* z2 = reinterpret_cast<double2*>(Z);
+      const double2 zz = make_double2(0.0, 0.0);
+      for (int i = tid; i < Cfg::NCOL * LDT / 2; i += NTHREADS) z2[i] = zz;
+      __syncthreads();
+    }
+    int a0n = 0, a1n = 0, a0nn = 0, a1nn = 0;
     double Xn0 = 0, Xn1 = 0, Xn2 = 0;
+    ObsRec rn0 = zrec, rn1 = zrec;            // this lane's first two records of the NEXT batch (registers)
     const int bfirst = crank * PB;            // this CTA takes batches bfirst, bfirst + BS, ...
     // landmark slots are in schedule order (decreasing observation count, set up by the index builder), so the
     // landmarks sharing a warp do the same number of rounds and all per-landmark arrays are contiguous
@@ -299,32 +328,49 @@ window_lm_kernel(const WinData d, const Params P) {
       const int pf = bfirst + slot;
       a0n = d.pt_ptr[p0 + pf]; a1n = d.pt_ptr[p0 + pf + 1];
       Xn0 = X[3 * pf]; Xn1 = X[3 * pf + 1]; Xn2 = X[3 * pf + 2];
+      if (a0n + sub < a1n) rn0 = d.pm[a0n + sub];
+      if (a0n + sub + TPP < a1n) rn1 = d.pm[a0n + sub + TPP];
     }
-    // record range of the batch AFTER the current one: L1-prefetched while the current batch's DMMA runs; the
-    // range itself is loaded one batch earlier
-    int pf_s = d.pt_ptr[p0 + min(bfirst + BS, npw)], pf_e = d.pt_ptr[p0 + min(bfirst + BS + PB, npw)];
+    if (bfirst + BS + slot < npw) { a0nn = d.pt_ptr[p0 + bfirst + BS + slot]; a1nn = d.pt_ptr[p0 + bfirst + BS + slot + 1]; }
+    // software pipeline of the record stream: while batch b runs its DMMA, the records of batch b + 1 are loaded into
+    // registers (they are L1 hits: their lines were prefetched during batch b - 1) and the lines of batch b + 2 are
+    // L1-prefetched; the landmark offsets are loaded one batch before they are needed as addresses
+    {
+      const int rs = d.pt_ptr[p0 + min(bfirst + BS, npw)], re = d.pt_ptr[p0 + min(bfirst + BS + PB, npw)];
+      for (int a = (rs & ~7) + tid * 8; a < re; a += NTHREADS * 8) prefetch_l1(d.pm + a);
+    }
+    int pf_s = d.pt_ptr[p0 + min(bfirst + 2 * BS, npw)], pf_e = d.pt_ptr[p0 + min(bfirst + 2 * BS + PB, npw)];
 
     for (int b0 = bfirst; b0 < npw; b0 += BS) {
       const int p = b0 + slot;
       const bool act = p < npw;
       const int a0 = a0n, a1 = a1n;
       const double X0 = Xn0, X1 = Xn1, X2 = Xn2;
+      ObsRec rec0 = rn0, rec1 = rn1;
+      if constexpr (!WX_RECPIPE_PT) {
+        rec0 = zrec; rec1 = zrec;
+        if (a0 + sub < a1) rec0 = d.pm[a0 + sub];
+        if (a0 + sub + TPP < a1) rec1 = d.pm[a0 + sub + TPP];
+      }
       // clear the column block (rows of cameras that do not see the landmark must be zero; the
       // block is contiguous, so this is TPP lanes x STS.128)
-      {
+      if constexpr (!WX_SPARSECLR || WX_STASH) {
         double2* zc2 = reinterpret_cast<double2*>(zcol);
         const double2 zz = make_double2(0.0, 0.0);
 #pragma unroll 4
         for (int i = sub; i < 3 * LDT / 2; i += TPP) zc2[i] = zz;
+        __syncwarp();   // column block cleared by all TPP lanes before anyone writes into it
       }
       // loop 1: C_p, g_p.  A lane takes observations a0+sub, a0+sub+TPP, ...; they are handled two at a
-      // time in one basic block (independent dependency chains interleave); `rounds` is warp-uniform.
+      // time in one basic block (independent dependency chains interleave); `rounds` is warp-uniform.  What loop 2
+      // needs of a free camera's observation -- w J_p (2x3) and the 10 non-zero entries of J_c -- is parked in the 18
+      // doubles of the column block that will hold this observation's Z rows, so loop 2 projects nothing.
       const int rounds = (int)((__reduce_max_sync(0xffffffffu, (unsigned)(a1 - a0)) + TPP - 1) / TPP);
-      const ObsRec zrec{0.f, 0.f, 0, 0};
       double C[6] = {0, 0, 0, 0, 0, 0}, g[3] = {0, 0, 0};
-      auto accum = [&](const ObsRec& rec, bool lv) {
+      auto accum = [&](const ObsRec& rec, bool lv) -> int {
+        const int f = lv ? fidx[rec.idx] : -1;
         Pose12 q;
-        load_pose(pose_cur + 12 * rec.idx, q);
+        load_pose(pose_cur + PS * rec.idx, q);
         Geo o;
         geo_project<LOSS>(P, q, X0, X1, X2, rec.u, rec.v, o);
         const double w = lv ? o.w : 0.0;
@@ -338,19 +384,64 @@ window_lm_kernel(const WinData d, const Params P) {
         g[0] = fma(u0, o.r0, fma(v0, o.r1, g[0]));
         g[1] = fma(u1, o.r0, fma(v1, o.r1, g[1]));
         g[2] = fma(u2, o.r0, fma(v2, o.r1, g[2]));
+        if constexpr (WX_STASH) {
+        double j0[6], j1[6];
+        geo_jc(o, j0, j1);
+        if (f >= 0) {
+          double* zr = zcol + 6 * f;
+          double2* c0 = reinterpret_cast<double2*>(zr);
+          double2* c1 = reinterpret_cast<double2*>(zr + LDT);
+          double2* c2 = reinterpret_cast<double2*>(zr + 2 * LDT);
+          c0[0] = make_double2(u0, u1); c0[1] = make_double2(u2, v0); c0[2] = make_double2(v1, v2);
+          c1[0] = make_double2(j0[0], j0[1]); c1[1] = make_double2(j0[2], j0[3]); c1[2] = make_double2(j0[5], j1[0]);
+          c2[0] = make_double2(j1[1], j1[2]); c2[1] = make_double2(j1[4], j1[5]);
+        }
+        }
+        return f;
       };
-      for (int r = 0; r < rounds; r += 2) {
+      int f0 = -1, f1 = -1;
+      if (rounds > 1) {
+        f0 = accum(rec0, a0 + sub < a1);
+        f1 = accum(rec1, a0 + sub + TPP < a1);
+      } else if (rounds == 1) {
+        f0 = accum(rec0, a0 + sub < a1);
+      }
+      unsigned rows = (f0 >= 0 ? 1u << f0 : 0u) | (f1 >= 0 ? 1u << f1 : 0u);
+      for (int r = 2; r < rounds; r += 2) {
         const int aA = a0 + sub + r * TPP, aB = aA + TPP;
         const bool lvA = aA < a1, lvB = aB < a1;
         ObsRec recA = zrec, recB = zrec;
         if (lvA) recA = d.pm[aA];
         if (r + 1 < rounds) {
           if (lvB) recB = d.pm[aB];
-          accum(recA, lvA);
-          accum(recB, lvB);
+          const int fa = accum(recA, lvA);
+          const int fb = accum(recB, lvB);
+          rows |= (fa >= 0 ? 1u << fa : 0u) | (fb >= 0 ? 1u << fb : 0u);
         } else {
-          accum(recA, lvA);
+          const int fa = accum(recA, lvA);
+          rows |= (fa >= 0 ? 1u << fa : 0u);
         }
+      }
+      if constexpr (WX_SPARSECLR && !WX_STASH) {
+        if (act) rows |= 1u << nfree;           // the y row (rows n ...)
+#pragma unroll
+        for (int m = TPP >> 1; m > 0; m >>= 1) rows |= __shfl_xor_sync(0xffffffffu, rows, m);
+        unsigned cl = prev_rows & ~rows;
+        prev_rows = rows;
+        const double2 zz = make_double2(0.0, 0.0);
+        for (int k = 0; cl; ++k) {
+          const int f = __ffs(cl) - 1;
+          cl &= cl - 1;
+          if ((k & (TPP - 1)) == sub) {
+            double* zr = zcol + 6 * f;
+#pragma unroll
+            for (int j = 0; j < 3; ++j) {
+              double2* dst = reinterpret_cast<double2*>(zr + j * LDT);
+              dst[0] = zz; dst[1] = zz; dst[2] = zz;
+            }
+          }
+        }
+        __syncwarp();   // rows zeroed before another lane of the landmark writes them
       }
 #pragma unroll
       for (int m = TPP >> 1; m > 0; m >>= 1) {
@@ -370,7 +461,6 @@ window_lm_kernel(const WinData d, const Params P) {
         }
       }
       gmax = fmax(gmax, fmax(fabs(g[0]), fmax(fabs(g[1]), fabs(g[2]))));
-      __syncwarp();   // column block cleared by all TPP lanes before anyone writes into it
       if (sub == 0 && act) {
         zcol[n] = F[0] * g[0];
         zcol[LDT + n] = fma(F[1], g[0], F[3] * g[1]);
@@ -385,17 +475,40 @@ window_lm_kernel(const WinData d, const Params P) {
           for (int k = 0; k < 3; ++k) d.dbg[dbgL.off_gp() + (size_t)p * 3 + k] = g[k];
         }
       }
-      // loop 2: Z rows of camera k = E_k F = w J_c^T (J_p F), 6 x 3, into the column block
-      auto emit = [&](const ObsRec& rec, bool lv) {
-        const int f = fidx[rec.idx];
-        const bool st = lv && f >= 0;
+      // loop 2: Z rows of free camera f = E_k F = J_c^T ((w J_p) F), 6 x 3, from the parked values, in place
+      auto emit = [&](int f) {
+        const bool st = f >= 0;
+        double* zr = zcol + 6 * (st ? f : 0);
+        double2* c0 = reinterpret_cast<double2*>(zr);
+        double2* c1 = reinterpret_cast<double2*>(zr + LDT);
+        double2* c2 = reinterpret_cast<double2*>(zr + 2 * LDT);
+        const double2 wa = c0[0], wb = c0[1], wc = c0[2];
+        const double2 ja = c1[0], jb = c1[1], jc_ = c1[2];
+        const double2 jd = c2[0], je = c2[1];
+        const double w0 = wa.x, w1 = wa.y, w2 = wb.x, w3 = wb.y, w4 = wc.x, w5 = wc.y;
+        // G = (w J_p) F  (2 x 3; F upper triangular)
+        const double G0[3] = {w0 * F[0], fma(w0, F[1], w1 * F[3]), fma(w0, F[2], fma(w1, F[4], w2 * F[5]))};
+        const double G1[3] = {w3 * F[0], fma(w3, F[1], w4 * F[3]), fma(w3, F[2], fma(w4, F[4], w5 * F[5]))};
+        // J_c rows: j0 = (ja.x ja.y jb.x jb.y 0 jc.x), j1 = (jc.y jd.x jd.y 0 je.x je.y)
+        if (st) {
+          double2* dst[3] = {c0, c1, c2};
+#pragma unroll
+          for (int j = 0; j < 3; ++j) {
+            dst[j][0] = make_double2(fma(ja.x, G0[j], jc_.y * G1[j]), fma(ja.y, G0[j], jd.x * G1[j]));
+            dst[j][1] = make_double2(fma(jb.x, G0[j], jd.y * G1[j]), jb.y * G0[j]);
+            dst[j][2] = make_double2(je.x * G1[j], fma(jc_.x, G0[j], je.y * G1[j]));
+          }
+        }
+      };
+      // (WX_STASH == 0: re-project instead)
+      auto emit_rec = [&](const ObsRec& rec, int f) {
+        const bool st = f >= 0;
         Pose12 q;
-        load_pose(pose_cur + 12 * rec.idx, q);
+        load_pose(pose_cur + PS * rec.idx, q);
         Geo o;
         geo_project<LOSS>(P, q, X0, X1, X2, rec.u, rec.v, o);
         double jp[6];
         geo_jp(q, o, jp);
-        // G = w J_p F  (2 x 3; F upper triangular)
         const double w0 = o.w * jp[0], w1 = o.w * jp[1], w2 = o.w * jp[2];
         const double w3 = o.w * jp[3], w4 = o.w * jp[4], w5 = o.w * jp[5];
         const double G0[3] = {w0 * F[0], fma(w0, F[1], w1 * F[3]), fma(w0, F[2], fma(w1, F[4], w2 * F[5]))};
@@ -413,32 +526,45 @@ window_lm_kernel(const WinData d, const Params P) {
           }
         }
       };
-      for (int r = 0; r < rounds; r += 2) {
-        const int aA = a0 + sub + r * TPP, aB = aA + TPP;
-        const bool lvA = aA < a1, lvB = aB < a1;
-        ObsRec recA = zrec, recB = zrec;
-        if (lvA) recA = d.pm[aA];
-        if (r + 1 < rounds) {
-          if (lvB) recB = d.pm[aB];
-          emit(recA, lvA);
-          emit(recB, lvB);
-        } else {
-          emit(recA, lvA);
+      if constexpr (WX_STASH) {
+        if (rounds > 1) {
+          emit(f0);
+          emit(f1);
+        } else if (rounds == 1) {
+          emit(f0);
+        }
+      } else {
+        if (rounds > 1) {
+          emit_rec(rec0, f0);
+          emit_rec(rec1, f1);
+        } else if (rounds == 1) {
+          emit_rec(rec0, f0);
         }
       }
+      for (int r = 2; r < rounds; ++r) {
+        const int a = a0 + sub + r * TPP;
+        int f = -1;
+        ObsRec rec = zrec;
+        if (a < a1) { rec = d.pm[a]; f = fidx[rec.idx]; }
+        if constexpr (WX_STASH) emit(f); else emit_rec(rec, f);
+      }
       __syncthreads();
-      // the next batch's landmark (registers) and records (L1 prefetch: a landmark's records are one
-      // contiguous run of <= 2-3 lines) are fetched while the tensor pipe works
+      // the next batch's landmark and first two records (registers) and the lines of the batch after it (L1
+      // prefetch: a landmark's records are one contiguous run of <= 2-3 lines) are fetched while the tensor pipe works
       {
         const int pn = p + BS;
-        a0n = 0; a1n = 0;
-        if (pn < npw) {
-          a0n = d.pt_ptr[p0 + pn]; a1n = d.pt_ptr[p0 + pn + 1];
-          Xn0 = X[3 * pn]; Xn1 = X[3 * pn + 1]; Xn2 = X[3 * pn + 2];
+        a0n = a0nn; a1n = a1nn;
+        if constexpr (WX_RECPIPE_PT) {
+          rn0 = zrec; rn1 = zrec;
+          if (a0n + sub < a1n) rn0 = d.pm[a0n + sub];
+          if (a0n + sub + TPP < a1n) rn1 = d.pm[a0n + sub + TPP];
         }
+        if (pn < npw) { Xn0 = X[3 * pn]; Xn1 = X[3 * pn + 1]; Xn2 = X[3 * pn + 2]; }
+        a0nn = 0; a1nn = 0;
+        if (pn + BS < npw) { a0nn = d.pt_ptr[p0 + pn + BS]; a1nn = d.pt_ptr[p0 + pn + BS + 1]; }
         for (int a = (pf_s & ~7) + tid * 8; a < pf_e; a += NTHREADS * 8) prefetch_l1(d.pm + a);
-        pf_s = d.pt_ptr[p0 + min(b0 + 2 * BS, npw)];
-        pf_e = d.pt_ptr[p0 + min(b0 + 2 * BS + PB, npw)];
+        pf_s = d.pt_ptr[p0 + min(b0 + 3 * BS, npw)];
+        pf_e = d.pt_ptr[p0 + min(b0 + 3 * BS + PB, npw)];
       }
       // Z Z^T accumulate: DMMA over this batch's 3*PB columns (this warp's k-slice)
       syrk_dispatch<Cfg>(grp, zf, ksp * (Cfg::KSTEPS / KS), acc);
@@ -669,9 +795,9 @@ window_lm_kernel(const WinData d, const Params P) {
     // trial cameras + camera part of the model decrease
     if (tid < nc) {
       const int f = fidx[tid];
-      if (f >= 0) retract_pose(pose_cur + 12 * tid, dvec + 6 * f, pose_tri + 12 * tid);
+      if (f >= 0) retract_pose(pose_cur + PS * tid, dvec + 6 * f, pose_tri + PS * tid);
       else
-        for (int k = 0; k < 12; ++k) pose_tri[12 * tid + k] = pose_cur[12 * tid + k];
+        for (int k = 0; k < 12; ++k) pose_tri[PS * tid + k] = pose_cur[PS * tid + k];
     }
     if (tid == 0) {
       double dDd = 0.0, gd = 0.0, dn2 = 0.0;
@@ -699,35 +825,62 @@ window_lm_kernel(const WinData d, const Params P) {
     // ------------------------------------------------------------------ back-substitution + trial cost (a7)
     double s_tc = 0.0, s_dDd = 0.0, s_gd = 0.0, s_dn2 = 0.0, s_xn2 = 0.0, s_inv = 0.0;
     if (step_ok) {
-      const int qfirst = crank * PB + slot;
-      int a0n = 0, a1n = 0;
-      if (qfirst < npw) { a0n = d.pt_ptr[p0 + qfirst]; a1n = d.pt_ptr[p0 + qfirst + 1]; }
+      const int qfirst = crank * PB + slot, bq = crank * PB;
+      const ObsRec zrec{0.f, 0.f, 0, 0};
+      int a0n = 0, a1n = 0, a0nn = 0, a1nn = 0;
+      ObsRec rn0 = zrec, rn1 = zrec;          // this lane's first two records of the NEXT batch (registers)
+      if (qfirst < npw) {
+        a0n = d.pt_ptr[p0 + qfirst]; a1n = d.pt_ptr[p0 + qfirst + 1];
+        if (a0n + sub < a1n) rn0 = d.pm[a0n + sub];
+        if (a0n + sub + TPP < a1n) rn1 = d.pm[a0n + sub + TPP];
+      }
+      if (qfirst + BS < npw) { a0nn = d.pt_ptr[p0 + qfirst + BS]; a1nn = d.pt_ptr[p0 + qfirst + BS + 1]; }
+      // record lines of the batch after the next one (L1 prefetch); its range is loaded one batch earlier
+      int pf_s = d.pt_ptr[p0 + min(bq + 2 * BS, npw)], pf_e = d.pt_ptr[p0 + min(bq + 2 * BS + PB, npw)];
       for (int p = qfirst; p < np_round; p += BS) {
         const bool act = p < npw;
         const int a0 = a0n, a1 = a1n;
+        ObsRec rec0 = rn0, rec1 = rn1;
+        if constexpr (!WX_RECPIPE_BS) {
+          rec0 = zrec; rec1 = zrec;
+          if (a0 + sub < a1) rec0 = d.pm[a0 + sub];
+          if (a0 + sub + TPP < a1) rec1 = d.pm[a0 + sub + TPP];
+        }
         double X0 = 0, X1 = 0, X2 = 0;
-        if (act) { X0 = X[3 * p]; X1 = X[3 * p + 1]; X2 = X[3 * p + 2]; }
-        a0n = 0; a1n = 0;
-        if (p + BS < npw) { a0n = d.pt_ptr[p0 + p + BS]; a1n = d.pt_ptr[p0 + p + BS + 1]; }   // used next round
-        {   // L1-prefetch the next batch: landmark offsets, landmarks, scratch rows, records
-          const int bn = p - slot + BS, bnn = min(bn + PB, npw);
-          if (bn < npw) {
-            const int* pp = d.pt_ptr + p0 + bn;
-            if (tid * 32 <= bnn - bn) prefetch_l1(pp + tid * 32);
-            if (tid * 16 < 3 * (bnn - bn)) prefetch_l1(X + 3 * bn + tid * 16);
-            if (tid * 16 < kPtScratch * (bnn - bn)) prefetch_l1(scratch + (size_t)bn * kPtScratch + tid * 16);
-            const int rs = d.pt_ptr[p0 + bn], re = d.pt_ptr[p0 + bnn];
-            for (int a = (rs & ~7) + tid * 8; a < re; a += NTHREADS * 8) prefetch_l1(d.pm + a);
+        double2 s0 = make_double2(0, 0), s1 = s0, s2 = s0, s3 = s0, s4 = s0, s5 = s0;
+        if (act) {
+          X0 = X[3 * p]; X1 = X[3 * p + 1]; X2 = X[3 * p + 2];
+          if constexpr (WX_SCHOIST) {
+            const double2* sc = reinterpret_cast<const double2*>(scratch + (size_t)p * kPtScratch);
+            s0 = sc[0]; s1 = sc[1]; s2 = sc[2]; s3 = sc[3]; s4 = sc[4]; s5 = sc[5];
           }
         }
+        // next batch: offsets from registers, first two records into registers (L1 hits); offsets of the batch after it
+        a0n = a0nn; a1n = a1nn;
+        if constexpr (WX_RECPIPE_BS) {
+          rn0 = zrec; rn1 = zrec;
+          if (a0n + sub < a1n) rn0 = d.pm[a0n + sub];
+          if (a0n + sub + TPP < a1n) rn1 = d.pm[a0n + sub + TPP];
+        }
+        a0nn = 0; a1nn = 0;
+        if (p + 2 * BS < npw) { a0nn = d.pt_ptr[p0 + p + 2 * BS]; a1nn = d.pt_ptr[p0 + p + 2 * BS + 1]; }
+        {   // L1 prefetch: landmarks and scratch rows of the next batch, record lines of the batch after it
+          const int bn = p - slot + BS, bnn = min(bn + PB, npw);
+          if (bn < npw) {
+            if (tid * 16 < 3 * (bnn - bn)) prefetch_l1(X + 3 * bn + tid * 16);
+            if (tid * 16 < kPtScratch * (bnn - bn)) prefetch_l1(scratch + (size_t)bn * kPtScratch + tid * 16);
+          }
+          for (int a = (pf_s & ~7) + tid * 8; a < pf_e; a += NTHREADS * 8) prefetch_l1(d.pm + a);
+          pf_s = d.pt_ptr[p0 + min(bn + 2 * BS, npw)];
+          pf_e = d.pt_ptr[p0 + min(bn + 2 * BS + PB, npw)];
+        }
         const int rounds = (int)((__reduce_max_sync(0xffffffffu, (unsigned)(a1 - a0)) + TPP - 1) / TPP);
-        const ObsRec zrec{0.f, 0.f, 0, 0};
         double v[3] = {0, 0, 0};
         auto etd = [&](const ObsRec& rec, bool lv) {
           const int f = fidx[rec.idx];
           const bool use = lv && f >= 0;
           Pose12 q;
-          load_pose(pose_cur + 12 * rec.idx, q);
+          load_pose(pose_cur + PS * rec.idx, q);
           Geo o;
           geo_project<LOSS>(P, q, X0, X1, X2, rec.u, rec.v, o);
           double jp[6], j0[6], j1[6];
@@ -741,7 +894,13 @@ window_lm_kernel(const WinData d, const Params P) {
 #pragma unroll
           for (int j = 0; j < 3; ++j) v[j] = fma(jp[j], t0, fma(jp[3 + j], t1, v[j]));
         };
-        for (int r = 0; r < rounds; r += 2) {
+        if (rounds > 1) {
+          etd(rec0, a0 + sub < a1);
+          etd(rec1, a0 + sub + TPP < a1);
+        } else if (rounds == 1) {
+          etd(rec0, a0 + sub < a1);
+        }
+        for (int r = 2; r < rounds; r += 2) {
           const int aA = a0 + sub + r * TPP, aB = aA + TPP;
           const bool lvA = aA < a1, lvB = aB < a1;
           ObsRec recA = zrec, recB = zrec;
@@ -761,8 +920,10 @@ window_lm_kernel(const WinData d, const Params P) {
         }
         double Xn0 = X0, Xn1 = X1, Xn2 = X2;
         if (act) {
-          const double2* sc = reinterpret_cast<const double2*>(scratch + (size_t)p * kPtScratch);
-          const double2 s0 = sc[0], s1 = sc[1], s2 = sc[2], s3 = sc[3], s4 = sc[4], s5 = sc[5];
+          if constexpr (!WX_SCHOIST) {
+            const double2* sc = reinterpret_cast<const double2*>(scratch + (size_t)p * kPtScratch);
+            s0 = sc[0]; s1 = sc[1]; s2 = sc[2]; s3 = sc[3]; s4 = sc[4]; s5 = sc[5];
+          }
           const double F0 = s0.x, F1 = s0.y, F2 = s1.x, F3 = s1.y, F4 = s2.x, F5 = s2.y;
           const double g0 = s3.x, g1 = s3.y, g2 = s4.x;
           const double t0 = g0 + v[0], t1 = g1 + v[1], t2 = g2 + v[2];
@@ -781,13 +942,19 @@ window_lm_kernel(const WinData d, const Params P) {
         }
         auto trial = [&](const ObsRec& rec, bool lv) {
           Pose12 q;
-          load_pose(pose_tri + 12 * rec.idx, q);
+          load_pose(pose_tri + PS * rec.idx, q);
           Geo o;
           geo_project<LOSS>(P, q, Xn0, Xn1, Xn2, rec.u, rec.v, o);
           s_tc = fma(0.5, lv ? o.rho : 0.0, s_tc);
           s_inv += (lv && !o.valid) ? 1.0 : 0.0;
         };
-        for (int r = 0; r < rounds; r += 2) {
+        if (rounds > 1) {
+          trial(rec0, a0 + sub < a1);
+          trial(rec1, a0 + sub + TPP < a1);
+        } else if (rounds == 1) {
+          trial(rec0, a0 + sub < a1);
+        }
+        for (int r = 2; r < rounds; r += 2) {
           const int aA = a0 + sub + r * TPP, aB = aA + TPP;
           const bool lvA = aA < a1, lvB = aB < a1;
           ObsRec recA = zrec, recB = zrec;
@@ -882,7 +1049,7 @@ window_lm_kernel(const WinData d, const Params P) {
       nu = 2.0;
       cost = scal[5];
       ninv_cur = (int)scal[7];
-      for (int i = tid; i < nc * 12; i += NTHREADS) pose_cur[i] = pose_tri[i];
+      for (int i = tid; i < nc * PS; i += NTHREADS) pose_cur[i] = pose_tri[i];
       cur ^= 1;
       have_lin = 0;
       ++n_acc;
@@ -908,7 +1075,7 @@ window_lm_kernel(const WinData d, const Params P) {
     for (int i = crank * NTHREADS + tid; i < npw * 3; i += CS * NTHREADS) dst[i] = src[i];
   }
   if (crank != 0) return;                  // poses and the summary are identical in every CTA of the cluster
-  for (int i = tid; i < nc * 12; i += NTHREADS) d.poses[(size_t)c0 * 12 + i] = pose_cur[i];
+  for (int i = tid; i < nc * 12; i += NTHREADS) d.poses[(size_t)c0 * 12 + i] = pose_cur[(i / 12) * PS + i % 12];
   if (tid == 0) {
     b2ba_summary s;
     s.status = status; s.iterations = it; s.accepted = n_acc; s.rejected = n_rej;
@@ -919,7 +1086,10 @@ window_lm_kernel(const WinData d, const Params P) {
 }
 
 using CfgSmall = WinCfg<7, 8, 4, 64, kSmallMaxCam, 2>;    // 256 threads, 2 CTAs / SM
-using CfgSmall4 = WinCfg<7, 4, 4, 32, kSmallMaxCam, 4>;   // 128 threads, 4 CTAs / SM
+#ifndef WX_G
+#define WX_G 4
+#endif
+using CfgSmall4 = WinCfg<7, 4, WX_G, 32, kSmallMaxCam, 4>;   // 128 threads, 4 CTAs / SM
 using CfgBig = WinCfg<16, 16, 16, 32, kMaxCam, 1>;        // n+1 <= 128: up to 21 free cameras (C3)
 constexpr int kClusterSize = 8;                           // portable cluster size
 using CfgSmallC = WinCfg<7, 8, 4, 64, kSmallMaxCam, 1, kClusterSize>;   // latency path: 8 CTAs x 256 threads per window

@@ -63,6 +63,12 @@ template <int NT_, int NWARPS_, int G_, int PB_, int MAXCAM_, int MINB_, int CS_
 struct WinCfg {
   static constexpr int NT = NT_, NWARPS = NWARPS_, G = G_, PB = PB_, MAXCAM = MAXCAM_, MINB = MINB_, CS = CS_;
   static constexpr int NTHREADS = NWARPS * 32;
+#ifndef WX_POSE_STRIDE
+#define WX_POSE_STRIDE 14
+#endif
+  // poses in shared memory: 12 doubles padded to 14, so that the LDS.128 of lanes holding up to 8 different cameras
+  // fall into different banks (stride 12: cameras c and c + 4 collide)
+  static constexpr int PS = WX_POSE_STRIDE;
   static constexpr int KS = NWARPS / G;            // k-splits of the SYRK
   static constexpr int T = NT * (NT + 1) / 2;      // upper 8x8 tiles
   static constexpr int TPW = (T + G - 1) / G;      // tiles per warp
@@ -84,7 +90,7 @@ struct WinCfg {
   static constexpr int XDATA = ((MAXCAM * 27 + 2 > XCHUNK ? MAXCAM * 27 + 2 : XCHUNK) + 1) / 2 * 2;
   static constexpr int XBUF = CS > 1 ? XDATA + 16 : 0;
   // doubles: pose_cur, pose_tri, B(21), gc, Dc, dvec, gred, red, scal, xbuf, Zt/S
-  static constexpr int SM_DOUBLES = MAXCAM * (12 + 12 + 21 + 6 + 6) + 128 + 128 + NRED + 16 + XBUF + ZS;
+  static constexpr int SM_DOUBLES = MAXCAM * (PS + PS + 21 + 6 + 6) + 128 + 128 + NRED + 16 + XBUF + ZS;
   static constexpr size_t SMEM = (size_t)SM_DOUBLES * 8 + (2 * MAXCAM + 8) * 4;
   static_assert(KS * G == NWARPS, "warps = groups x k-splits");
   static_assert(KSTEPS % KS == 0, "k-steps split evenly");
