@@ -57,8 +57,9 @@ __device__ __forceinline__ void static_for(F&& f) {
 template <class Cfg, int GRP, int R>
 constexpr bool row_used() {
   for (int q = 0; q < Cfg::TPW; ++q) {
-    const int t = GRP * Cfg::TPW + q;
-    if (t < Cfg::T && (Tri<Cfg::NT>::mi(t) == R || Tri<Cfg::NT>::ni(t) == R)) return true;
+    if (GRP * Cfg::TPW + q >= Cfg::T) continue;
+    const int t = Cfg::tile_of(GRP, q);
+    if (Tri<Cfg::NT>::mi(t) == R || Tri<Cfg::NT>::ni(t) == R) return true;
   }
   return false;
 }
@@ -79,8 +80,10 @@ __device__ __forceinline__ void syrk_group(const double* __restrict__ zf, int kb
     });
     static_for<0, Cfg::TPW>([&](auto q) {
       constexpr int Q = decltype(q)::value;
-      constexpr int t = GRP * Cfg::TPW + Q;
-      if constexpr (t < Cfg::T) dmma884(acc[Q][0], acc[Q][1], fr[Tri<Cfg::NT>::mi(t)], fr[Tri<Cfg::NT>::ni(t)]);
+      if constexpr (GRP * Cfg::TPW + Q < Cfg::T) {
+        constexpr int t = Cfg::tile_of(GRP, Q);
+        dmma884(acc[Q][0], acc[Q][1], fr[Tri<Cfg::NT>::mi(t)], fr[Tri<Cfg::NT>::ni(t)]);
+      }
     });
     zk += 4 * Cfg::LDT;
   }
@@ -240,16 +243,22 @@ window_lm_kernel(const WinData d, const Params P) {
         double acc[29];
 #pragma unroll
         for (int k = 0; k < 29; ++k) acc[k] = 0.0;
-        // records two iterations ahead in registers; the landmark of the next iteration is L1-prefetched
+        // records three iterations ahead in registers.  The landmark gather comes from L2 (the L1 left beside 4 x 55 KB
+        // of shared memory is small), so it is prefetched TWO iterations ahead: for a record that was itself loaded one
+        // iteration earlier (its index is in a register by now -- no wait on the record load)
         const ObsRec zrec{0.f, 0.f, 0, 0};
-        ObsRec rec_n = zrec, rec_nn = zrec;
+        ObsRec rec_n = zrec, rec_nn = zrec, rec_n3 = zrec;
         if (b + tid < e) rec_n = d.cm[b + tid];
         if (b + tid + NTHREADS < e) rec_nn = d.cm[b + tid + NTHREADS];
+        if (b + tid + 2 * NTHREADS < e) rec_n3 = d.cm[b + tid + 2 * NTHREADS];
+        if (b + tid < e) { prefetch_l1(X + 3 * rec_n.idx); prefetch_l1(X + 3 * rec_n.idx + 2); }
+        if (b + tid + NTHREADS < e) { prefetch_l1(X + 3 * rec_nn.idx); prefetch_l1(X + 3 * rec_nn.idx + 2); }
         for (int a = b + tid; a < e; a += NTHREADS) {
           const ObsRec rec = rec_n;
           rec_n = rec_nn;
-          if (a + 2 * NTHREADS < e) rec_nn = d.cm[a + 2 * NTHREADS];
-          if (a + NTHREADS < e) { prefetch_l1(X + 3 * rec_n.idx); prefetch_l1(X + 3 * rec_n.idx + 2); }
+          rec_nn = rec_n3;
+          if (a + 3 * NTHREADS < e) rec_n3 = d.cm[a + 3 * NTHREADS];
+          if (a + 2 * NTHREADS < e) { prefetch_l1(X + 3 * rec_nn.idx); prefetch_l1(X + 3 * rec_nn.idx + 2); }
           cam_accum(rec, q, isfree, acc);
         }
         red[warp * 32 + lane] = warp_totals(acc);
@@ -332,14 +341,17 @@ window_lm_kernel(const WinData d, const Params P) {
       if (a0n + sub + TPP < a1n) rn1 = d.pm[a0n + sub + TPP];
     }
     if (bfirst + BS + slot < npw) { a0nn = d.pt_ptr[p0 + bfirst + BS + slot]; a1nn = d.pt_ptr[p0 + bfirst + BS + slot + 1]; }
+    int a0n3 = 0, a1n3 = 0;
+    if (bfirst + 2 * BS + slot < npw) { a0n3 = d.pt_ptr[p0 + bfirst + 2 * BS + slot]; a1n3 = d.pt_ptr[p0 + bfirst + 2 * BS + slot + 1]; }
     // software pipeline of the record stream: while batch b runs its DMMA, the records of batch b + 1 are loaded into
-    // registers (they are L1 hits: their lines were prefetched during batch b - 1) and the lines of batch b + 2 are
-    // L1-prefetched; the landmark offsets are loaded one batch before they are needed as addresses
-    {
-      const int rs = d.pt_ptr[p0 + min(bfirst + BS, npw)], re = d.pt_ptr[p0 + min(bfirst + BS + PB, npw)];
-      for (int a = (rs & ~7) + tid * 8; a < re; a += NTHREADS * 8) prefetch_l1(d.pm + a);
-    }
-    int pf_s = d.pt_ptr[p0 + min(bfirst + 2 * BS, npw)], pf_e = d.pt_ptr[p0 + min(bfirst + 2 * BS + PB, npw)];
+    // registers (L1 hits: their lines were prefetched during batch b - 1), the lines of batch b + 2 are L1-prefetched
+    // by the landmark's own lanes (a landmark's records are one contiguous run of <= 3 lines), and the landmark
+    // offsets of batch b + 3 are loaded -- every address is in a register one batch before it is needed
+    auto prefetch_records = [&](int s0_, int s1_) {
+      const int a = (s0_ & ~7) + 8 * sub;
+      if (a < s1_) prefetch_l1(d.pm + a);
+    };
+    prefetch_records(a0nn, a1nn);
 
     for (int b0 = bfirst; b0 < npw; b0 += BS) {
       const int p = b0 + slot;
@@ -560,11 +572,10 @@ window_lm_kernel(const WinData d, const Params P) {
           if (a0n + sub + TPP < a1n) rn1 = d.pm[a0n + sub + TPP];
         }
         if (pn < npw) { Xn0 = X[3 * pn]; Xn1 = X[3 * pn + 1]; Xn2 = X[3 * pn + 2]; }
-        a0nn = 0; a1nn = 0;
-        if (pn + BS < npw) { a0nn = d.pt_ptr[p0 + pn + BS]; a1nn = d.pt_ptr[p0 + pn + BS + 1]; }
-        for (int a = (pf_s & ~7) + tid * 8; a < pf_e; a += NTHREADS * 8) prefetch_l1(d.pm + a);
-        pf_s = d.pt_ptr[p0 + min(b0 + 3 * BS, npw)];
-        pf_e = d.pt_ptr[p0 + min(b0 + 3 * BS + PB, npw)];
+        a0nn = a0n3; a1nn = a1n3;
+        prefetch_records(a0nn, a1nn);
+        a0n3 = 0; a1n3 = 0;
+        if (pn + 2 * BS < npw) { a0n3 = d.pt_ptr[p0 + pn + 2 * BS]; a1n3 = d.pt_ptr[p0 + pn + 2 * BS + 1]; }
       }
       // Z Z^T accumulate: DMMA over this batch's 3*PB columns (this warp's k-slice)
       syrk_dispatch<Cfg>(grp, zf, ksp * (Cfg::KSTEPS / KS), acc);
@@ -579,15 +590,20 @@ window_lm_kernel(const WinData d, const Params P) {
 #pragma unroll
     for (int s = 0; s < KS; ++s) {
       if (ksp == s) {
-#pragma unroll
-        for (int q = 0; q < TPW; ++q) {
-          const int t = grp * TPW + q;
-          if (t < Cfg::T) {
-            double* dst = SP + t * 64 + (lane >> 2) * 8 + 2 * (lane & 3);
-            if (s == 0) { dst[0] = acc[q][0]; dst[1] = acc[q][1]; }
-            else { dst[0] += acc[q][0]; dst[1] += acc[q][1]; }
+        static_for<0, G>([&](auto gg) {
+          constexpr int GG = decltype(gg)::value;
+          if (grp == GG) {
+            static_for<0, TPW>([&](auto qq) {
+              constexpr int Q = decltype(qq)::value;
+              if constexpr (GG * TPW + Q < Cfg::T) {
+                constexpr int t = Cfg::tile_of(GG, Q);
+                double* dst = SP + t * 64 + (lane >> 2) * 8 + 2 * (lane & 3);
+                if (s == 0) { dst[0] = acc[Q][0]; dst[1] = acc[Q][1]; }
+                else { dst[0] += acc[Q][0]; dst[1] += acc[Q][1]; }
+              }
+            });
           }
-        }
+        });
       }
       __syncthreads();
     }
@@ -835,8 +851,15 @@ window_lm_kernel(const WinData d, const Params P) {
         if (a0n + sub + TPP < a1n) rn1 = d.pm[a0n + sub + TPP];
       }
       if (qfirst + BS < npw) { a0nn = d.pt_ptr[p0 + qfirst + BS]; a1nn = d.pt_ptr[p0 + qfirst + BS + 1]; }
-      // record lines of the batch after the next one (L1 prefetch); its range is loaded one batch earlier
-      int pf_s = d.pt_ptr[p0 + min(bq + 2 * BS, npw)], pf_e = d.pt_ptr[p0 + min(bq + 2 * BS + PB, npw)];
+      int a0n3 = 0, a1n3 = 0;
+      if (qfirst + 2 * BS < npw) { a0n3 = d.pt_ptr[p0 + qfirst + 2 * BS]; a1n3 = d.pt_ptr[p0 + qfirst + 2 * BS + 1]; }
+      // same pipeline as the point pass: records one batch ahead in registers, their lines two batches ahead in L1
+      // (prefetched by the landmark's own lanes), the landmark offsets three batches ahead
+      auto prefetch_records = [&](int s0_, int s1_) {
+        const int a = (s0_ & ~7) + 8 * sub;
+        if (a < s1_) prefetch_l1(d.pm + a);
+      };
+      prefetch_records(a0nn, a1nn);
       for (int p = qfirst; p < np_round; p += BS) {
         const bool act = p < npw;
         const int a0 = a0n, a1 = a1n;
@@ -862,17 +885,16 @@ window_lm_kernel(const WinData d, const Params P) {
           if (a0n + sub < a1n) rn0 = d.pm[a0n + sub];
           if (a0n + sub + TPP < a1n) rn1 = d.pm[a0n + sub + TPP];
         }
-        a0nn = 0; a1nn = 0;
-        if (p + 2 * BS < npw) { a0nn = d.pt_ptr[p0 + p + 2 * BS]; a1nn = d.pt_ptr[p0 + p + 2 * BS + 1]; }
-        {   // L1 prefetch: landmarks and scratch rows of the next batch, record lines of the batch after it
+        a0nn = a0n3; a1nn = a1n3;
+        prefetch_records(a0nn, a1nn);
+        a0n3 = 0; a1n3 = 0;
+        if (p + 3 * BS < npw) { a0n3 = d.pt_ptr[p0 + p + 3 * BS]; a1n3 = d.pt_ptr[p0 + p + 3 * BS + 1]; }
+        {   // L1 prefetch: landmarks and scratch rows of the next batch
           const int bn = p - slot + BS, bnn = min(bn + PB, npw);
           if (bn < npw) {
             if (tid * 16 < 3 * (bnn - bn)) prefetch_l1(X + 3 * bn + tid * 16);
             if (tid * 16 < kPtScratch * (bnn - bn)) prefetch_l1(scratch + (size_t)bn * kPtScratch + tid * 16);
           }
-          for (int a = (pf_s & ~7) + tid * 8; a < pf_e; a += NTHREADS * 8) prefetch_l1(d.pm + a);
-          pf_s = d.pt_ptr[p0 + min(bn + 2 * BS, npw)];
-          pf_e = d.pt_ptr[p0 + min(bn + 2 * BS + PB, npw)];
         }
         const int rounds = (int)((__reduce_max_sync(0xffffffffu, (unsigned)(a1 - a0)) + TPP - 1) / TPP);
         double v[3] = {0, 0, 0};

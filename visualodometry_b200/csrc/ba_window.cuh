@@ -63,6 +63,9 @@ template <int NT_, int NWARPS_, int G_, int PB_, int MAXCAM_, int MINB_, int CS_
 struct WinCfg {
   static constexpr int NT = NT_, NWARPS = NWARPS_, G = G_, PB = PB_, MAXCAM = MAXCAM_, MINB = MINB_, CS = CS_;
   static constexpr int NTHREADS = NWARPS * 32;
+#ifndef WX_TILEPERM
+#define WX_TILEPERM 1
+#endif
 #ifndef WX_POSE_STRIDE
 #define WX_POSE_STRIDE 14
 #endif
@@ -73,6 +76,19 @@ struct WinCfg {
   static constexpr int T = NT * (NT + 1) / 2;      // upper 8x8 tiles
   static constexpr int TPW = (T + G - 1) / G;      // tiles per warp
   static constexpr int TPP = NTHREADS / PB;        // lanes per point
+  // canonical tile (upper triangle, row-major) computed by warp group `grp` as its q-th tile.  For the 7 x 7 / 4-group
+  // shape of the batched small path the partition is chosen so that a group touches few distinct tile rows (17 row
+  // fragments per k-step over the 4 groups instead of 22 with consecutive tiles): a fragment is loaded from shared
+  // memory once per group and k-step, and the shared-memory pipe is one of the two resources that bound the kernel.
+  static constexpr __host__ __device__ int tile_of(int grp, int q) {
+    if (NT == 7 && G == 4 && WX_TILEPERM) {
+      // groups: rows {0,1,4,5,6}, {1,2,3,4}, {0,2,3,6}, {2,3,4,5}
+      constexpr int tab[4][7] = {{1, 4, 5, 11, 12, 24, 26}, {7, 8, 9, 10, 13, 14, 15},
+                                 {0, 2, 3, 6, 17, 21, 27}, {16, 18, 19, 20, 22, 23, 25}};
+      return tab[grp][q];
+    }
+    return grp * TPW + q;
+  }
   static constexpr int NR = 8 * NT;                // rows of Z (6*nfree + 1, padded)
   static constexpr int NCOL = 3 * PB;              // columns of Z per batch (3 per landmark)
   static constexpr int LDT = NR + 4;               // Z is stored TRANSPOSED: Zt[col * LDT + row];
