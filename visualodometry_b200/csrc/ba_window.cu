@@ -43,6 +43,11 @@ namespace cg = cooperative_groups;
 #define WX_SCHOIST 0    // back-substitution: scratch row loaded at the top of the batch
 #endif
 
+// A 16-byte record is loaded with one LDG.128; its `orig` word is not used by the solve, and a dead destination register
+// is recycled at once -- the next write to it then waits for the load (write-after-write on the long scoreboard).
+// Naming the word where the record is consumed keeps the register allocated while the load is in flight.
+__device__ __forceinline__ void keep_alive(const ObsRec& r) { asm volatile("" ::"r"(r.orig)); }
+
 __device__ __forceinline__ int packed21(int r, int s) { return r * 6 - r * (r - 1) / 2 + (s - r); }
 
 // ---- compile-time loop: f(integral_constant<int, I>) for I in [0, N)
@@ -140,6 +145,9 @@ window_lm_kernel(const WinData d, const Params P) {
   }
   __syncthreads();
   const int nfree = lo[nc];
+  // first / last record of the window: unconditional record loads are clamped into the window's own stream (a record of
+  // this window names one of its cameras, so whatever an idle lane computes from it stays finite and is weighted 0)
+  const int rec_lo = d.pt_ptr[p0], rec_hi = max(d.pt_ptr[p0 + npw] - 1, rec_lo);
   const int n = 6 * nfree;              // reduced system size; row n of Z is the y row
   const int grp = warp % G, ksp = warp / G;
 
@@ -159,10 +167,9 @@ window_lm_kernel(const WinData d, const Params P) {
     const int fresh_lin = !have_lin;
     if (!have_lin) {
       // one observation of camera pose q into the 21 + 6 + 2 sums (structural zeros of J_c skipped)
-      auto cam_accum = [&](const ObsRec& rec, const Pose12& q, bool isfree, double* acc) {
-        const double* Xp = X + 3 * rec.idx;
+      auto cam_accum = [&](const ObsRec& rec, double x0, double x1, double x2, const Pose12& q, bool isfree, double* acc) {
         Geo o;
-        geo_project<LOSS>(P, q, Xp[0], Xp[1], Xp[2], rec.u, rec.v, o);
+        geo_project<LOSS>(P, q, x0, x1, x2, rec.u, rec.v, o);
         if (!o.valid) { acc[28] += 1.0; return; }
         acc[27] = fma(0.5, o.rho, acc[27]);
         if (isfree) {
@@ -221,7 +228,8 @@ window_lm_kernel(const WinData d, const Params P) {
           for (int a = b + lane; a < e; a += 32) {
             const ObsRec rec = rec_n;
             if (a + 32 < e) { rec_n = d.cm[a + 32]; prefetch_l1(X + 3 * rec_n.idx); prefetch_l1(X + 3 * rec_n.idx + 2); }
-            cam_accum(rec, q, isfree, acc);
+            const double* Xp = X + 3 * rec.idx;
+            cam_accum(rec, Xp[0], Xp[1], Xp[2], q, isfree, acc);
           }
           const double v = warp_totals(acc);
           if (lane < 21) Bc[c * 21 + lane] = v;
@@ -243,23 +251,26 @@ window_lm_kernel(const WinData d, const Params P) {
         double acc[29];
 #pragma unroll
         for (int k = 0; k < 29; ++k) acc[k] = 0.0;
-        // records three iterations ahead in registers.  The landmark gather comes from L2 (the L1 left beside 4 x 55 KB
-        // of shared memory is small), so it is prefetched TWO iterations ahead: for a record that was itself loaded one
-        // iteration earlier (its index is in a register by now -- no wait on the record load)
-        const ObsRec zrec{0.f, 0.f, 0, 0};
-        ObsRec rec_n = zrec, rec_nn = zrec, rec_n3 = zrec;
-        if (b + tid < e) rec_n = d.cm[b + tid];
-        if (b + tid + NTHREADS < e) rec_nn = d.cm[b + tid + NTHREADS];
-        if (b + tid + 2 * NTHREADS < e) rec_n3 = d.cm[b + tid + 2 * NTHREADS];
-        if (b + tid < e) { prefetch_l1(X + 3 * rec_n.idx); prefetch_l1(X + 3 * rec_n.idx + 2); }
-        if (b + tid + NTHREADS < e) { prefetch_l1(X + 3 * rec_nn.idx); prefetch_l1(X + 3 * rec_nn.idx + 2); }
-        for (int a = b + tid; a < e; a += NTHREADS) {
-          const ObsRec rec = rec_n;
-          rec_n = rec_nn;
-          rec_nn = rec_n3;
-          if (a + 3 * NTHREADS < e) rec_n3 = d.cm[a + 3 * NTHREADS];
-          if (a + 2 * NTHREADS < e) { prefetch_l1(X + 3 * rec_nn.idx); prefetch_l1(X + 3 * rec_nn.idx + 2); }
-          cam_accum(rec, q, isfree, acc);
+        // software pipeline: records three iterations ahead in registers (unconditional loads, clamped into the
+        // camera's run); the landmark a record names comes from L2 (the L1 left beside 4 x 55 KB of shared memory is
+        // small), so it is L1-prefetched two iterations ahead and loaded into registers one iteration ahead
+        if (b < e) {
+          const int last = e - 1;
+          ObsRec rec_n = d.cm[min(b + tid, last)], rec_nn = d.cm[min(b + tid + NTHREADS, last)];
+          ObsRec rec_n3 = d.cm[min(b + tid + 2 * NTHREADS, last)];
+          double xn0 = X[3 * rec_n.idx], xn1 = X[3 * rec_n.idx + 1], xn2 = X[3 * rec_n.idx + 2];
+          prefetch_l1(X + 3 * rec_nn.idx); prefetch_l1(X + 3 * rec_nn.idx + 2);
+          for (int a = b + tid; a < e; a += NTHREADS) {
+            const ObsRec rec = rec_n;
+            const double x0 = xn0, x1 = xn1, x2 = xn2;
+            keep_alive(rec);
+            rec_n = rec_nn;
+            rec_nn = rec_n3;
+            rec_n3 = d.cm[min(a + 3 * NTHREADS, last)];
+            xn0 = X[3 * rec_n.idx]; xn1 = X[3 * rec_n.idx + 1]; xn2 = X[3 * rec_n.idx + 2];
+            prefetch_l1(X + 3 * rec_nn.idx); prefetch_l1(X + 3 * rec_nn.idx + 2);
+            cam_accum(rec, x0, x1, x2, q, isfree, acc);
+          }
         }
         red[warp * 32 + lane] = warp_totals(acc);
         __syncthreads();
@@ -337,8 +348,8 @@ window_lm_kernel(const WinData d, const Params P) {
       const int pf = bfirst + slot;
       a0n = d.pt_ptr[p0 + pf]; a1n = d.pt_ptr[p0 + pf + 1];
       Xn0 = X[3 * pf]; Xn1 = X[3 * pf + 1]; Xn2 = X[3 * pf + 2];
-      if (a0n + sub < a1n) rn0 = d.pm[a0n + sub];
-      if (a0n + sub + TPP < a1n) rn1 = d.pm[a0n + sub + TPP];
+      rn0 = d.pm[min(max(a0n, rec_lo) + sub, rec_hi)];
+      rn1 = d.pm[min(max(a0n, rec_lo) + sub + TPP, rec_hi)];
     }
     if (bfirst + BS + slot < npw) { a0nn = d.pt_ptr[p0 + bfirst + BS + slot]; a1nn = d.pt_ptr[p0 + bfirst + BS + slot + 1]; }
     int a0n3 = 0, a1n3 = 0;
@@ -359,6 +370,7 @@ window_lm_kernel(const WinData d, const Params P) {
       const int a0 = a0n, a1 = a1n;
       const double X0 = Xn0, X1 = Xn1, X2 = Xn2;
       ObsRec rec0 = rn0, rec1 = rn1;
+      keep_alive(rec0); keep_alive(rec1);
       if constexpr (!WX_RECPIPE_PT) {
         rec0 = zrec; rec1 = zrec;
         if (a0 + sub < a1) rec0 = d.pm[a0 + sub];
@@ -567,9 +579,10 @@ window_lm_kernel(const WinData d, const Params P) {
         const int pn = p + BS;
         a0n = a0nn; a1n = a1nn;
         if constexpr (WX_RECPIPE_PT) {
-          rn0 = zrec; rn1 = zrec;
-          if (a0n + sub < a1n) rn0 = d.pm[a0n + sub];
-          if (a0n + sub + TPP < a1n) rn1 = d.pm[a0n + sub + TPP];
+          // unconditional loads from clamped addresses (no zero-fill of the destination, which would have to wait for
+          // the previous load into the same registers); validity is decided by the offsets when the record is used
+          rn0 = d.pm[min(max(a0n, rec_lo) + sub, rec_hi)];
+          rn1 = d.pm[min(max(a0n, rec_lo) + sub + TPP, rec_hi)];
         }
         if (pn < npw) { Xn0 = X[3 * pn]; Xn1 = X[3 * pn + 1]; Xn2 = X[3 * pn + 2]; }
         a0nn = a0n3; a1nn = a1n3;
@@ -847,8 +860,8 @@ window_lm_kernel(const WinData d, const Params P) {
       ObsRec rn0 = zrec, rn1 = zrec;          // this lane's first two records of the NEXT batch (registers)
       if (qfirst < npw) {
         a0n = d.pt_ptr[p0 + qfirst]; a1n = d.pt_ptr[p0 + qfirst + 1];
-        if (a0n + sub < a1n) rn0 = d.pm[a0n + sub];
-        if (a0n + sub + TPP < a1n) rn1 = d.pm[a0n + sub + TPP];
+        rn0 = d.pm[min(max(a0n, rec_lo) + sub, rec_hi)];
+        rn1 = d.pm[min(max(a0n, rec_lo) + sub + TPP, rec_hi)];
       }
       if (qfirst + BS < npw) { a0nn = d.pt_ptr[p0 + qfirst + BS]; a1nn = d.pt_ptr[p0 + qfirst + BS + 1]; }
       int a0n3 = 0, a1n3 = 0;
@@ -864,6 +877,7 @@ window_lm_kernel(const WinData d, const Params P) {
         const bool act = p < npw;
         const int a0 = a0n, a1 = a1n;
         ObsRec rec0 = rn0, rec1 = rn1;
+        keep_alive(rec0); keep_alive(rec1);
         if constexpr (!WX_RECPIPE_BS) {
           rec0 = zrec; rec1 = zrec;
           if (a0 + sub < a1) rec0 = d.pm[a0 + sub];
@@ -881,9 +895,8 @@ window_lm_kernel(const WinData d, const Params P) {
         // next batch: offsets from registers, first two records into registers (L1 hits); offsets of the batch after it
         a0n = a0nn; a1n = a1nn;
         if constexpr (WX_RECPIPE_BS) {
-          rn0 = zrec; rn1 = zrec;
-          if (a0n + sub < a1n) rn0 = d.pm[a0n + sub];
-          if (a0n + sub + TPP < a1n) rn1 = d.pm[a0n + sub + TPP];
+          rn0 = d.pm[min(max(a0n, rec_lo) + sub, rec_hi)];
+          rn1 = d.pm[min(max(a0n, rec_lo) + sub + TPP, rec_hi)];
         }
         a0nn = a0n3; a1nn = a1n3;
         prefetch_records(a0nn, a1nn);
