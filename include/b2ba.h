@@ -120,6 +120,20 @@ int b2ba_get(b2ba_t* h, double* poses_cw, double* points, int mem);
  * here as the input of outlier culling after BA.  err: No doubles, HOST or DEVICE per `mem`. */
 int b2ba_reproj_errors(b2ba_t* h, double* err, int mem);
 
+/* Outlier culling after BA, on the device.  ONE kernel evaluates the reprojection error of every
+ * observation at the current state, keeps it iff 0 <= err <= max_err -- the gate the reference applies to new landmarks
+ * (`src/modules/frontend.py:139-142`, `src/config/config.py:31-32`; an observation that fails it corresponds to the
+ * reference's "untracked" id -1, `src/modules/vo.py:53`, a landmark with no surviving observation to an entry
+ * `_prune_map` would drop, `vo.py:35-47`) -- compacts the observation arrays in the caller's order (stable, single-pass
+ * scan) and counts the survivors per landmark.  Outputs, any of which may be NULL: keep (No bytes, 1 = kept), live
+ * (Np_tot int32: surviving observations per landmark), kept_index (the original index of every kept observation,
+ * ascending; capacity No) -- HOST or DEVICE per `mem`; n_kept: ONE int64 on the HOST.
+ * apply != 0: the handle's problem BECOMES the culled one -- compacted observation arrays, index rebuilt on the device,
+ * state (and the state b2ba_reset restores) = the present one -- so optimise -> cull -> optimise needs no host round
+ * trip of the observation arrays.  Landmarks keep their slots (one with live == 0 stays, unobserved). */
+int b2ba_cull(b2ba_t* h, double max_err, uint8_t* keep, int32_t* live, int32_t* kept_index, int64_t* n_kept,
+              int apply, int mem);
+
 /* Batched two-view triangulation + gating: `triangulate_points` of the reference
  * (`src/modules/frontend.py:115-148`, called at `vo.py:262-270`).  P1, P2: K [R|t] of the two views (3 x 4 row-major,
  * HOST, the arguments of cv2.triangulatePoints at frontend.py:128-131); uv1, uv2: N x 2 float32 matched keypoints;

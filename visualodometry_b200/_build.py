@@ -15,7 +15,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "libb2ba.so")
-SOURCES = ["b2ba.cu", "ba_index.cu", "ba_window.cu", "ba_large.cu", "ba_band.cu", "ba_dense.cu", "ba_pose.cu", "ba_peak.cu"]
+SOURCES = ["b2ba.cu", "ba_index.cu", "ba_cull.cu", "ba_window.cu", "ba_large.cu", "ba_band.cu", "ba_dense.cu", "ba_pose.cu", "ba_peak.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr"]
 

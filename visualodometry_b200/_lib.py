@@ -19,7 +19,7 @@ D = dict(PM_PERM=1, PT_PTR=2, CM_PERM=3, CAM_PTR=4, FIDX=5, BLK_PTR=6, BLK_COL=7
 # every symbol include/b2ba.h declares
 SYMBOLS = ["b2ba_default_options", "b2ba_create", "b2ba_destroy", "b2ba_last_error", "b2ba_set_problem",
            "b2ba_set_problem_batch", "b2ba_set_state", "b2ba_reset", "b2ba_solve", "b2ba_get_summaries", "b2ba_get_timings",
-           "b2ba_get", "b2ba_optimize_batch", "b2ba_refine_poses", "b2ba_track_pose", "b2ba_ransac_pose", "b2ba_triangulate", "b2ba_reproj_errors", "b2ba_dump", "b2ba_create_comm", "b2ba_nccl_unique_id", "b2ba_set_point_range",
+           "b2ba_get", "b2ba_optimize_batch", "b2ba_refine_poses", "b2ba_track_pose", "b2ba_ransac_pose", "b2ba_triangulate", "b2ba_reproj_errors", "b2ba_cull", "b2ba_dump", "b2ba_create_comm", "b2ba_nccl_unique_id", "b2ba_set_point_range",
            "b2ba_peak_flops", "b2ba_solve_window_noalloc", "b2ba_version"]
 
 
@@ -78,6 +78,7 @@ def load():
     lib.b2ba_ransac_pose.argtypes = [vp, i64, vp, vp, vp, dp, C.c_double, i32, i32, C.c_uint64, i32, vp, vp, vp, vp, i32]
     lib.b2ba_triangulate.argtypes = [vp, i32, dp, dp, vp, vp, C.c_double, C.c_double, vp, vp, i32]
     lib.b2ba_reproj_errors.argtypes = [vp, vp, i32]
+    lib.b2ba_cull.argtypes = [vp, C.c_double, vp, vp, vp, C.POINTER(i64), i32, i32]
     lib.b2ba_dump.argtypes = [vp, C.c_int, vp, i64]
     lib.b2ba_dump.restype = i64
     lib.b2ba_create_comm.argtypes = [vp, vp, C.c_int, C.c_int]

@@ -150,6 +150,23 @@ def cull_window(vo, window, packed: PackedWindow, err: np.ndarray, max_err: floa
     return int(bad.sum())
 
 
+def cull_window_device(vo, window, packed: PackedWindow, ba, max_err: float) -> int:
+    """`cull_window` with the decision made on the device (`b2ba_cull`: error, gate, per-landmark survivor counts in
+    one kernel); the host only edits the reference's own structures (keyframe id arrays, the landmark dict).  Same
+    result as `cull_window(vo, window, packed, ba.reproj_errors(), max_err)`, bit for bit (tests/test_cull.py)."""
+    keep, live, _ = ba.cull(max_err)
+    bad = ~keep
+    if not bad.any():
+        return 0
+    kfs = list(window)
+    for j in np.unique(packed.obs_cam[bad]).tolist():
+        m = bad & (packed.obs_cam == j)
+        kfs[j]["ids"][packed.obs_kp[m]] = -1
+    for p in packed.pids[live == 0].tolist():
+        vo.map_points.pop(int(p), None)
+    return int(bad.sum())
+
+
 def refine_window(vo, window, ba: BundleAdjuster, n_fixed: int = 2, cull_px: float | None = None):
     """Pack -> BundleAdjuster.optimize -> write back (-> cull).  Returns the BASummary (or None if skipped)."""
     packed = pack_window(window, vo.map_points, n_fixed=n_fixed)
@@ -159,7 +176,9 @@ def refine_window(vo, window, ba: BundleAdjuster, n_fixed: int = 2, cull_px: flo
     if not res.summary.ok or not np.isfinite(res.T_cw).all() or not np.isfinite(res.points).all():
         return res.summary                        # numerical failure: keep the reference's state
     write_back(vo, window, packed, res.T_cw, res.points)
-    if cull_px is not None and hasattr(ba, "reproj_errors"):
+    if cull_px is not None and hasattr(ba, "cull"):
+        cull_window_device(vo, window, packed, ba, cull_px)
+    elif cull_px is not None and hasattr(ba, "reproj_errors"):
         cull_window(vo, window, packed, ba.reproj_errors(), cull_px)
     return res.summary
 

@@ -293,6 +293,25 @@ class BundleAdjuster:
         self._check(self._lib.b2ba_reproj_errors(self._h, out.ctypes.data, _lib.MEM_HOST), "b2ba_reproj_errors")
         return out
 
+    def cull(self, max_err: float, apply: bool = False):
+        """Outlier culling after BA on the device (`b2ba_cull`): the reference's landmark gate
+        (`frontend.py:139-142`, `config.py:31-32`) applied to every observation at the current (refined) state.
+        Returns (keep (No,) bool, live (Np,) int32 = surviving observations per landmark, kept_index (n_kept,) int32).
+        `apply=True` makes the culled problem the handle's problem (compacted on the device, index rebuilt), so the
+        next `solve()` runs on it without passing the observation arrays through the host again."""
+        if self._shape is None:
+            raise RuntimeError("cull: no problem set")
+        nc, npts, no = self._shape
+        keep = np.empty(no, np.uint8)
+        live = np.empty(npts, np.int32)
+        idx = np.empty(no, np.int32)
+        n = C.c_int64(0)
+        self._check(self._lib.b2ba_cull(self._h, float(max_err), keep.ctypes.data, live.ctypes.data, idx.ctypes.data,
+                                        C.byref(n), 1 if apply else 0, _lib.MEM_HOST), "b2ba_cull")
+        if apply:
+            self._shape = (nc, npts, int(n.value))
+        return keep.astype(bool), live, idx[: int(n.value)].copy()
+
     def dump(self, what: str, shape, dtype=np.float64):
         out = np.zeros(shape, dtype)
         n = self._lib.b2ba_dump(self._h, _lib.D[what], out.ctypes.data, out.nbytes)

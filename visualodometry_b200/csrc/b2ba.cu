@@ -728,6 +728,67 @@ int b2ba_reproj_errors(b2ba_t* h, double* err, int mem) {
   return B2BA_OK;
 }
 
+int b2ba_cull(b2ba_t* h, double max_err, uint8_t* keep, int32_t* live, int32_t* kept_index, int64_t* n_kept,
+              int apply, int mem) {
+  if (!h || h->path == PATH_NONE) return fail(h, B2BA_E_STATE, "no problem set");
+  if (!(max_err >= 0.0)) return fail(h, B2BA_E_INVALID, "cull: max_err must be >= 0");
+  if (apply && h->nranks > 1) return fail(h, B2BA_E_UNSUPPORTED, "cull: apply is not available on a sharded (multi-rank) problem");
+  DeviceGuard dg_(h->device); CU(dg_.err, "cudaSetDevice");
+  cudaStream_t s = h->last_stream;
+  const size_t no = (size_t)h->no, np = (size_t)h->np_tot, nc = (size_t)h->nc_tot;
+  const bool dev = mem == B2BA_MEM_DEVICE;
+  // the observation arrays index landmarks in the caller's order
+  const double* pts_lm = h->d_pts0.p;
+  if (h->sched_order) {
+    const int rcp = permute_pts(h, h->d_pts0.p, h->d_pts1.p, false, s);
+    if (rcp) return cuda_fail(h, (cudaError_t)rcp, "permute points");
+    pts_lm = h->d_pts1.p;
+  }
+  DevBuf<unsigned char> t_keep, t_work;
+  DevBuf<int> t_live, t_idx, t_cam, t_pt;
+  DevBuf<float2> t_uv;
+  DevBuf<long long> t_cnt;                       // [0] n_kept, [1 .. B] kept per window
+  CU(t_cnt.alloc((size_t)h->B + 1), "alloc"); CU(t_work.alloc(cull_work_bytes(h->no)), "alloc");
+  unsigned char* d_keep = nullptr;
+  int *d_live = nullptr, *d_idx = nullptr;
+  if (keep) { if (dev) d_keep = keep; else { CU(t_keep.alloc(no), "alloc"); d_keep = t_keep.p; } }
+  if (live) { if (dev) d_live = live; else { CU(t_live.alloc(np), "alloc"); d_live = t_live.p; } }
+  if (kept_index) { if (dev) d_idx = kept_index; else { CU(t_idx.alloc(no), "alloc"); d_idx = t_idx.p; } }
+  if (apply) { CU(t_cam.alloc(no), "alloc"); CU(t_pt.alloc(no), "alloc"); CU(t_uv.alloc(no), "alloc"); }
+  const int rc = cull_observations(make_index_in(h), make_params(h, 1), h->d_poses.p, pts_lm, max_err, d_keep, d_live,
+                                   t_cnt.p + 1, apply ? t_cam.p : nullptr, apply ? t_pt.p : nullptr,
+                                   apply ? t_uv.p : nullptr, d_idx, t_cnt.p, t_work.p, s);
+  if (rc) return cuda_fail(h, (cudaError_t)rc, "cull_kernel");
+  std::vector<long long> cnt((size_t)h->B + 1);
+  CU(cudaMemcpyAsync(cnt.data(), t_cnt.p, cnt.size() * sizeof(long long), cudaMemcpyDeviceToHost, s), "read counts");
+  CU(cudaStreamSynchronize(s), "cull");
+  if (n_kept) *n_kept = cnt[0];
+  if (!dev) {
+    if (keep && no) CU(cudaMemcpyAsync(keep, d_keep, no, cudaMemcpyDeviceToHost, s), "read keep");
+    if (live && np) CU(cudaMemcpyAsync(live, d_live, np * sizeof(int), cudaMemcpyDeviceToHost, s), "read live");
+    if (kept_index && cnt[0]) CU(cudaMemcpyAsync(kept_index, d_idx, (size_t)cnt[0] * sizeof(int), cudaMemcpyDeviceToHost, s), "read index");
+    CU(cudaStreamSynchronize(s), "cull");
+  }
+  if (!apply) return B2BA_OK;
+  // the culled problem replaces the handle's: compacted observation arrays (device), state = the present one
+  DevBuf<double> t_poses, t_pts;
+  DevBuf<unsigned char> t_fixed;
+  CU(t_poses.alloc(nc * 12), "alloc"); CU(t_pts.alloc(np * 3), "alloc"); CU(t_fixed.alloc(nc), "alloc");
+  CU(cudaMemcpyAsync(t_poses.p, h->d_poses.p, nc * 12 * sizeof(double), cudaMemcpyDeviceToDevice, s), "copy poses");
+  CU(cudaMemcpyAsync(t_pts.p, pts_lm, np * 3 * sizeof(double), cudaMemcpyDeviceToDevice, s), "copy points");
+  CU(cudaMemcpyAsync(t_fixed.p, h->d_fixed.p, nc, cudaMemcpyDeviceToDevice, s), "copy fixed");
+  CU(cudaStreamSynchronize(s), "cull");
+  const std::vector<int> cam_off = h->h_cam_off, pt_off = h->h_pt_off;
+  std::vector<long long> obs_off((size_t)h->B + 1, 0);
+  for (int b = 0; b < h->B; ++b) obs_off[b + 1] = obs_off[b] + cnt[1 + b];
+  double intr[4];
+  std::memcpy(intr, h->intr, sizeof(intr));
+  static_assert(sizeof(long long) == sizeof(int64_t), "obs_off");
+  return b2ba_set_problem_batch(h, h->B, cam_off.data(), pt_off.data(), reinterpret_cast<const int64_t*>(obs_off.data()),
+                                t_poses.p, t_pts.p, t_cam.p, t_pt.p, reinterpret_cast<const float*>(t_uv.p), t_fixed.p,
+                                intr, B2BA_MEM_DEVICE);
+}
+
 int b2ba_triangulate(b2ba_t* h, int32_t N, const double P1[12], const double P2[12], const float* uv1,
                      const float* uv2, double min_depth, double max_reproj_err, double* X, uint8_t* keep, int mem) {
   if (!h) return B2BA_E_INVALID;

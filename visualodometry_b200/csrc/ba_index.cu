@@ -8,14 +8,6 @@ namespace b2 {
 
 namespace {
 
-__device__ __forceinline__ int find_window(const long long* __restrict__ obs_off, int nb, long long i) {
-  int lo = 0, hi = nb;   // obs_off[lo] <= i < obs_off[hi]
-  while (hi - lo > 1) {
-    const int mid = (lo + hi) >> 1;
-    if (obs_off[mid] <= i) lo = mid; else hi = mid;
-  }
-  return lo;
-}
 
 // pos_of (or null): global landmark -> global schedule position; the point-major stream is then laid out in
 // schedule order (the canonical order is by landmark id)

@@ -18,6 +18,16 @@ struct IndexIn {
   const float2* obs_uv;      // device
 };
 
+// window of observation i: obs_off[b] <= i < obs_off[b + 1]
+__device__ __forceinline__ int find_window(const long long* __restrict__ obs_off, int nb, long long i) {
+  int lo = 0, hi = nb;
+  while (hi - lo > 1) {
+    const int mid = (lo + hi) >> 1;
+    if (obs_off[mid] <= i) lo = mid; else hi = mid;
+  }
+  return lo;
+}
+
 struct IndexOut {
   ObsRec* pm;      // no
   int* pt_ptr;     // np_tot+1
@@ -43,6 +53,16 @@ int permute_points(int nb, int np_tot, const int* pt_off, const int* sched, cons
 // -1 where the landmark is behind the cheirality gate (the input of outlier culling)
 int obs_errors(const IndexIn& in, const Params& P, const double* poses, const double* pts, double* err,
                cudaStream_t s);
+
+// SURVEY §8 row f-4, outlier culling after BA, in ONE kernel (ba_cull.cu): reprojection error of every observation at
+// the given state -> keep = (0 <= err <= max_err), the reference's landmark gate (frontend.py:139-142, config.py:31-32)
+// -> stable compaction of the observation arrays (single-pass scan with decoupled look-back) + surviving observations
+// per landmark (`live`, np_tot) and per window (`win_kept`, nb) + the total (`n_kept`).  Any output may be null.
+// `work`: device scratch of cull_work_bytes(no) bytes.  Asynchronous on `s`.
+size_t cull_work_bytes(long long no);
+int cull_observations(const IndexIn& in, const Params& P, const double* poses, const double* pts, double max_err,
+                      unsigned char* keep, int* live, long long* win_kept, int* out_cam, int* out_pt, float2* out_uv,
+                      int* kept_index, long long* n_kept, void* work, cudaStream_t s);
 
 // a1 dump in ORIGINAL observation order (parity tests): r (no x 2), w (no), Jc (no x 12), Jp (no x 6)
 int dump_obs_terms(const IndexIn& in, const Params& P, const double* poses, const double* pts,
