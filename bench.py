@@ -194,6 +194,9 @@ def run_c2(args, impl):
         cv2.setRNGSeed(0)
         lcfg = vo_loop.LoopConfig()
         vo = vo_loop.VOLoop(seq.K, lcfg, vo_synth.SynthFrontend(seq))
+        # the GPU arms keep the map in the dense id -> slot table (landmark_table.py); results are
+        # bit-identical to the dict scans of the reference (tests/test_landmark_table.py)
+        vo.dense_map = kind == "gpu"
         ad, t_ba, n_obs, nbytes = None, [0.0], [0], [0, 0]
         if gpu_tracker:
             # SURVEY 8 row f-2 widened: the tracker's cv2.solvePnPRansac call (vo.py:135-141) replaced by the
@@ -269,7 +272,8 @@ def run_c2(args, impl):
             "note": "PnP consensus / triangulation on the GPU: behaviourally pinned to cv2.solvePnPRansac / triangulate_points "
                     "(tests/test_pose.py, tests/test_triangulate.py), not result-identical; trajectories differ from the pinned loop",
             "gpu_tracker_sampling_free": r_trk, "gpu_ransac": r_rsc, "gpu_ransac_and_gpu_triangulation": r_all}
-        out["config"]["gpu_stages_of_the_headline"] = "window BA (b2ba_optimize) once per keyframe; everything else as in the reference"
+        out["config"]["gpu_stages_of_the_headline"] = ("window BA (b2ba_optimize) once per keyframe; landmark look-ups through the dense "
+                                                       "id -> slot table (same results as the dict scans); everything else as in the reference")
     if impl == "reference":
         from oracle import ba_cpu
         out["impl"] = "reference"

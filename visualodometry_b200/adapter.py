@@ -100,7 +100,11 @@ def pack_window(window, map_points, n_fixed: int = 2, min_obs: int = 2) -> Packe
     cand = np.flatnonzero(keep_pt)                  # only landmarks that can enter the problem are looked up
     if cand.size == 0:
         return None
-    keep_pt[cand] = np.fromiter((p in map_points for p in upid[cand].tolist()), bool, cand.size)
+    dense = hasattr(map_points, "lookup")           # LandmarkTable: array gathers instead of per-id dict look-ups
+    if dense:
+        keep_pt[cand], _ = map_points.lookup(upid[cand])
+    else:
+        keep_pt[cand] = np.fromiter((p in map_points for p in upid[cand].tolist()), bool, cand.size)
     if not keep_pt.any():
         return None
     slot = np.cumsum(keep_pt) - 1
@@ -109,7 +113,10 @@ def pack_window(window, map_points, n_fixed: int = 2, min_obs: int = 2) -> Packe
     obs_cam = cam[keep_obs]
     obs_uv = np.ascontiguousarray(uv[keep_obs])
     upid = upid[keep_pt]
-    points = np.array([map_points[p] for p in upid.tolist()], np.float64).reshape(-1, 3)
+    if dense:
+        points = np.ascontiguousarray(map_points.lookup(upid)[1])
+    else:
+        points = np.array([map_points[p] for p in upid.tolist()], np.float64).reshape(-1, 3)
     T_cw = np.stack([np.linalg.inv(np.asarray(kf["T_wc"], np.float64)) for kf in kfs])
     fixed = np.zeros(nc, bool)
     fixed[:max(1, min(n_fixed, nc - 1))] = True
@@ -126,6 +133,9 @@ def write_back(vo, window, packed: PackedWindow, T_cw: np.ndarray, points: np.nd
     vo.T_wc = newest["T_wc"].copy()
     vo.last_pos = vo.T_wc[:3, 3].copy()          # vo.py:204
     mp = vo.map_points
+    if hasattr(mp, "update_rows"):
+        mp.update_rows(packed.pids, points)
+        return
     rows = np.array(points, np.float64)             # one copy; every landmark gets its own row (an ndarray(3,) view)
     mp.update((p, x) for p, x in zip(packed.pids.tolist(), rows) if p in mp)
 

@@ -88,9 +88,22 @@ class VOLoop:
         # where the reference would not.  None = cv2.solvePnPRansac only, as the reference does (the pinned loop).
         self.pnp_solver = None
         self.pnp_fallbacks = 0
+        # NOT in the reference: `dense_map = True` keeps `map_points` in a LandmarkTable (a dict with a dense id -> slot
+        # mirror, landmark_table.py) and answers the matched-id look-ups of vo.py:121-130 and the pruning of
+        # vo.py:41-47 with array operations; results are identical to the dict scans (tests/test_landmark_table.py).
+        self.dense_map = False
+
+    def _new_map(self):
+        if self.dense_map:
+            from .landmark_table import LandmarkTable
+            return LandmarkTable()
+        return {}
 
     # ------------------------------------------------------------------ vo.py:49-250
     def process_frame(self, img) -> None:
+        if self.dense_map and not hasattr(self.map_points, "lookup"):
+            from .landmark_table import LandmarkTable
+            self.map_points = LandmarkTable(self.map_points)
         feats = self.frontend.process_image(img)
         ids = np.full(feats["keypoints"].shape[1], -1, dtype=int)
         if self.keyframe is None:                                          # vo.py:56-61
@@ -135,11 +148,15 @@ class VOLoop:
     def _track(self, feats, ids, ref_idx, cur_idx):
         cfg, mp = self.cfg, self.map_points
         kf_ids = self.keyframe["ids"][ref_idx]
-        valid = np.array([(p != -1 and p in mp) for p in kf_ids])
+        if self.dense_map and hasattr(mp, "lookup"):
+            valid, X = mp.lookup(kf_ids)
+        else:
+            valid = np.array([(p != -1 and p in mp) for p in kf_ids])
         if not np.sum(valid) > cfg.min_inliers:
             self._reset_system()
             return
-        X = np.array([mp[p] for p in kf_ids[valid]])
+        if not (self.dense_map and hasattr(mp, "lookup")):
+            X = np.array([mp[p] for p in kf_ids[valid]])
         uv = _kp(feats)[cur_idx[valid]]
         ok = False
         if self.pnp_solver is not None:
@@ -207,13 +224,16 @@ class VOLoop:
         self.keyframe = {"feats": curr_feats, "ids": curr_ids, "T_wc": self.T_wc.copy()}
         floor = self.next_pt_id - self.MAX_MAP_POINTS                         # vo.py:35-47
         if floor > 0:
-            for pid in [p for p in self.map_points if p < floor]:
-                del self.map_points[pid]
+            if self.dense_map and hasattr(self.map_points, "prune_below"):
+                self.map_points.prune_below(floor)
+            else:
+                for pid in [p for p in self.map_points if p < floor]:
+                    del self.map_points[pid]
 
     # ------------------------------------------------------------------ vo.py:290-299
     def _reset_system(self):
         self.initialized = False
-        self.map_points = {}
+        self.map_points = self._new_map()
         self.keyframe = None
         self.trajectory = []
         self.last_pos = np.zeros(3)
