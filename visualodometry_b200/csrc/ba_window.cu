@@ -152,20 +152,20 @@ window_lm_kernel(const WinData d, const Params P) {
   const int grp = warp % G, ksp = warp / G;
 
   double mu = P.init_mu, nu = 2.0, cost = 0.0, initial_cost = 0.0;
-  int cur = 0, have_lin = 0, it = 0, n_acc = 0, n_rej = 0, status = B2BA_MAX_ITERS, ninv_cur = 0;
+  int cur = 0, it = 0, n_acc = 0, n_rej = 0, status = B2BA_MAX_ITERS, ninv_cur = 0;
   double* const scratch = d.pt_scratch + (size_t)p0 * kPtScratch;
   const int slot = tid / TPP, sub = tid % TPP;
   const int np_round = ((npw + PB - 1) / PB) * PB;
   WinDbg dbgL{nc, npw, n};
 
-  for (; it < P.max_iters; ++it) {
-    const double* X = d.pts[cur] + (size_t)p0 * 3;
-    double* Xt = d.pts[cur ^ 1] + (size_t)p0 * 3;
-    const bool dbg = (d.dbg != nullptr) && it == 0;
-
-    // ------------------------------------------------------------------ camera pass (a1+a2)
-    const int fresh_lin = !have_lin;
-    if (!have_lin) {
+  // ------------------------------------------------------------------ camera pass (a1+a2)
+  // Linearisation of the camera side at the state (pose_sm, X): B_c (21) and g_c (6) of every camera into Bd / Bd +
+  // MAXCAM * 21, cost and invalid count into scal[0] / scal[1] (cluster: summed over the CTAs in rank order).  It runs
+  // once before the loop and then as the TRIAL EVALUATION of every step: the trial cost of a step is the cost of the
+  // next linearisation point, so an accepted step (the common case) already holds its B_c, g_c and no separate
+  // point-major trial pass re-projects the observations.
+  auto camera_pass = [&](const double* pose_sm, const double* X, double* Bd) {
+    double* gd = Bd + MAXCAM * 21;
       // one observation of camera pose q into the 21 + 6 + 2 sums (structural zeros of J_c skipped)
       auto cam_accum = [&](const ObsRec& rec, double x0, double x1, double x2, const Pose12& q, bool isfree, double* acc) {
         Geo o;
@@ -217,7 +217,7 @@ window_lm_kernel(const WinData d, const Params P) {
           e = b + (int)(((long long)len * (crank + 1)) / CS);
           b = b + (int)(((long long)len * crank) / CS);
           Pose12 q;
-          load_pose(pose_cur + PS * c, q);
+          load_pose(pose_sm + PS * c, q);
           const bool isfree = fidx[c] >= 0;
           double acc[29];
 #pragma unroll
@@ -232,8 +232,8 @@ window_lm_kernel(const WinData d, const Params P) {
             cam_accum(rec, Xp[0], Xp[1], Xp[2], q, isfree, acc);
           }
           const double v = warp_totals(acc);
-          if (lane < 21) Bc[c * 21 + lane] = v;
-          else if (lane < 27) gc[c * 6 + lane - 21] = v;
+          if (lane < 21) Bd[c * 21 + lane] = v;
+          else if (lane < 27) gd[c * 6 + lane - 21] = v;
           else if (lane == 27) cst_w += v;
           else if (lane == 28) ninv_w += v;
         }
@@ -246,7 +246,7 @@ window_lm_kernel(const WinData d, const Params P) {
       for (int c = 0; c < nc; ++c) {
         const int b = d.cam_ptr[c0 + c], e = d.cam_ptr[c0 + c + 1];
         Pose12 q;
-        load_pose(pose_cur + PS * c, q);
+        load_pose(pose_sm + PS * c, q);
         const bool isfree = fidx[c] >= 0;
         double acc[29];
 #pragma unroll
@@ -277,8 +277,8 @@ window_lm_kernel(const WinData d, const Params P) {
         if (tid < 29) {
           double v = 0.0;
           for (int w = 0; w < NWARPS; ++w) v += red[w * 32 + tid];
-          if (tid < 21) Bc[c * 21 + tid] = v;
-          else if (tid < 27) gc[c * 6 + tid - 21] = v;
+          if (tid < 21) Bd[c * 21 + tid] = v;
+          else if (tid < 27) gd[c * 6 + tid - 21] = v;
           else if (tid == 27) cst_tot += v;
           else ninv_tot += v;
         }
@@ -291,8 +291,8 @@ window_lm_kernel(const WinData d, const Params P) {
         // all-reduce {B_c, g_c, cost, n_invalid} over the cluster: partials go to xbuf, every CTA sums the
         // CS remote copies in rank order (deterministic and identical on all CTAs)
         __syncthreads();
-        constexpr int NB = MAXCAM * 27;          // Bc and gc are contiguous in shared memory
-        for (int i = tid; i < NB; i += NTHREADS) xbuf[i] = Bc[i];
+        constexpr int NB = MAXCAM * 27;          // B and g are contiguous (Bc | gc, and their trial copies alike)
+        for (int i = tid; i < NB; i += NTHREADS) xbuf[i] = Bd[i];
         if (tid < 2) xbuf[NB + tid] = scal[tid];
         cg::cluster_group cl = cg::this_cluster();
         cl.sync();
@@ -300,18 +300,26 @@ window_lm_kernel(const WinData d, const Params P) {
           double v = 0.0;
 #pragma unroll
           for (int r = 0; r < CS; ++r) v += cl.map_shared_rank(xbuf, r)[i];
-          if (i < NB) Bc[i] = v; else scal[i - NB] = v;
+          if (i < NB) Bd[i] = v; else scal[i - NB] = v;
         }
         cl.sync();                               // xbuf may be overwritten again
       }
-      __syncthreads();
-      for (int i = tid; i < nc * 6; i += NTHREADS) Dc[i] = clampd(Bc[(i / 6) * 21 + packed21(i % 6, i % 6)]);
-      __syncthreads();
-      cost = scal[0];
-      ninv_cur = (int)scal[1];
-      if (it == 0) initial_cost = cost;
-      have_lin = 1;
-    }
+    __syncthreads();
+  };
+  double* const Bt = Z;                       // trial B_c | g_c (the tile memory is free between the solve and the next point pass)
+  int fresh_lin = 1;                          // the linearisation at hand has not been solved with yet
+  camera_pass(pose_cur, d.pts[0] + (size_t)p0 * 3, Bc);
+  for (int i = tid; i < nc * 6; i += NTHREADS) Dc[i] = clampd(Bc[(i / 6) * 21 + packed21(i % 6, i % 6)]);
+  cost = scal[0];
+  ninv_cur = (int)scal[1];
+  initial_cost = cost;
+  __syncthreads();
+
+  for (; it < P.max_iters; ++it) {
+    const double* X = d.pts[cur] + (size_t)p0 * 3;
+    double* Xt = d.pts[cur ^ 1] + (size_t)p0 * 3;
+    const bool dbg = (d.dbg != nullptr) && it == 0;
+
     if (dbg) {
       for (int i = tid; i < nc * 36; i += NTHREADS) {
         int c = i / 36, r = (i % 36) / 6, s = i % 6;
@@ -852,9 +860,9 @@ window_lm_kernel(const WinData d, const Params P) {
 
 
     // ------------------------------------------------------------------ back-substitution + trial cost (a7)
-    double s_tc = 0.0, s_dDd = 0.0, s_gd = 0.0, s_dn2 = 0.0, s_xn2 = 0.0, s_inv = 0.0;
+    double s_dDd = 0.0, s_gd = 0.0, s_dn2 = 0.0, s_xn2 = 0.0;
     if (step_ok) {
-      const int qfirst = crank * PB + slot, bq = crank * PB;
+      const int qfirst = crank * PB + slot;
       const ObsRec zrec{0.f, 0.f, 0, 0};
       int a0n = 0, a1n = 0, a0nn = 0, a1nn = 0;
       ObsRec rn0 = zrec, rn1 = zrec;          // this lane's first two records of the NEXT batch (registers)
@@ -953,7 +961,6 @@ window_lm_kernel(const WinData d, const Params P) {
 #pragma unroll
           for (int k = 0; k < 3; ++k) v[k] += __shfl_xor_sync(0xffffffffu, v[k], m);
         }
-        double Xn0 = X0, Xn1 = X1, Xn2 = X2;
         if (act) {
           if constexpr (!WX_SCHOIST) {
             const double2* sc = reinterpret_cast<const double2*>(scratch + (size_t)p * kPtScratch);
@@ -965,9 +972,8 @@ window_lm_kernel(const WinData d, const Params P) {
           // delta_p = -F F^T t
           const double u0 = F0 * t0, u1 = fma(F1, t0, F3 * t1), u2 = fma(F2, t0, fma(F4, t1, F5 * t2));
           const double d0 = -fma(F0, u0, fma(F1, u1, F2 * u2)), d1 = -fma(F3, u1, F4 * u2), d2 = -(F5 * u2);
-          Xn0 = X0 + d0; Xn1 = X1 + d1; Xn2 = X2 + d2;
           if (sub == 0) {
-            Xt[3 * p] = Xn0; Xt[3 * p + 1] = Xn1; Xt[3 * p + 2] = Xn2;
+            Xt[3 * p] = X0 + d0; Xt[3 * p + 1] = X1 + d1; Xt[3 * p + 2] = X2 + d2;
             s_dDd += d0 * d0 * s4.y + d1 * d1 * s5.x + d2 * d2 * s5.y;
             s_gd += d0 * g0 + d1 * g1 + d2 * g2;
             s_dn2 += d0 * d0 + d1 * d1 + d2 * d2;
@@ -975,77 +981,56 @@ window_lm_kernel(const WinData d, const Params P) {
             if (dbg) { double* dp = d.dbg + dbgL.off_dp() + (size_t)p * 3; dp[0] = d0; dp[1] = d1; dp[2] = d2; }
           }
         }
-        auto trial = [&](const ObsRec& rec, bool lv) {
-          Pose12 q;
-          load_pose(pose_tri + PS * rec.idx, q);
-          Geo o;
-          geo_project<LOSS>(P, q, Xn0, Xn1, Xn2, rec.u, rec.v, o);
-          s_tc = fma(0.5, lv ? o.rho : 0.0, s_tc);
-          s_inv += (lv && !o.valid) ? 1.0 : 0.0;
-        };
-        if (rounds > 1) {
-          trial(rec0, a0 + sub < a1);
-          trial(rec1, a0 + sub + TPP < a1);
-        } else if (rounds == 1) {
-          trial(rec0, a0 + sub < a1);
-        }
-        for (int r = 2; r < rounds; r += 2) {
-          const int aA = a0 + sub + r * TPP, aB = aA + TPP;
-          const bool lvA = aA < a1, lvB = aB < a1;
-          ObsRec recA = zrec, recB = zrec;
-          if (lvA) recA = d.pm[aA];
-          if (r + 1 < rounds) {
-            if (lvB) recB = d.pm[aB];
-            trial(recA, lvA);
-            trial(recB, lvB);
-          } else {
-            trial(recA, lvA);
-          }
-        }
       }
     }
     {
-      double vals[7] = {s_tc, s_dDd, s_gd, s_dn2, s_xn2, s_inv, gmax};
+      double vals[4] = {s_dDd, s_gd, s_dn2, s_xn2};
 #pragma unroll
-      for (int k = 0; k < 6; ++k) {
+      for (int k = 0; k < 4; ++k) {
         const double v = warp_sum(vals[k]);
         if (lane == 0) red[warp * 32 + k] = v;
       }
-      double gm = vals[6];
+      double gm = gmax;
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) gm = fmax(gm, __shfl_xor_sync(0xffffffffu, gm, o));
-      if (lane == 0) red[warp * 32 + 6] = gm;
+      if (lane == 0) red[warp * 32 + 4] = gm;
     }
-    __syncthreads();
+    __syncthreads();                             // the sums; the trial landmarks are visible to the whole CTA
+    // landmark-part sums of this CTA (fixed order over the warps) -> scal[9..13]; in a cluster also -> xbuf: the barrier
+    // that makes every CTA's trial landmarks visible to the cluster publishes them, and every CTA adds the CS copies in
+    // rank order after the trial evaluation
+    if (tid == 0) {
+      double t[5] = {0, 0, 0, 0, 0};
+      for (int w = 0; w < NWARPS; ++w) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) t[k] += red[w * 32 + k];
+        t[4] = fmax(t[4], red[w * 32 + 4]);
+      }
+#pragma unroll
+      for (int k = 0; k < 5; ++k) {
+        scal[9 + k] = t[k];
+        if constexpr (CS > 1) xbuf[Cfg::XDATA + k] = t[k];
+      }
+    }
+    if constexpr (CS > 1) cg::this_cluster().sync();
+    else __syncthreads();                        // `red` is the camera pass's scratch from here on
+
+    // ------------------------------------------------------------------ trial evaluation = next linearisation (a1+a2, a7)
+    if (step_ok) camera_pass(pose_tri, Xt, Bt);
 
     // ------------------------------------------------------------------ LM control (Spec a0)
-    if constexpr (CS > 1) {
-      // landmark-part sums of this CTA -> xbuf; every CTA then adds the CS copies in rank order
-      if (tid == 0) {
-        double t[7] = {0, 0, 0, 0, 0, 0, 0};
-        for (int w = 0; w < NWARPS; ++w) {
-#pragma unroll
-          for (int k = 0; k < 6; ++k) t[k] += red[w * 32 + k];
-          t[6] = fmax(t[6], red[w * 32 + 6]);
-        }
-#pragma unroll
-        for (int k = 0; k < 7; ++k) xbuf[Cfg::XDATA + k] = t[k];
-      }
-      cg::this_cluster().sync();
-    }
     if (tid == 0) {
-      double tc = 0, dDd = scal[2], gd = scal[3], dn2 = scal[4], xn2 = 0, ninv = 0, gm = 0;
+      // trial cost and invalid count: the camera pass at the trial state (already summed over the cluster)
+      const double tc = step_ok ? scal[0] : 0.0, ninv = step_ok ? scal[1] : 0.0;
+      double dDd = scal[2], gd = scal[3], dn2 = scal[4], xn2 = 0, gm = 0;
       if constexpr (CS > 1) {
         cg::cluster_group cl = cg::this_cluster();
         for (int r = 0; r < CS; ++r) {
           const double* xr = cl.map_shared_rank(xbuf, r) + Cfg::XDATA;
-          tc += xr[0]; dDd += xr[1]; gd += xr[2]; dn2 += xr[3]; xn2 += xr[4]; ninv += xr[5]; gm = fmax(gm, xr[6]);
+          dDd += xr[0]; gd += xr[1]; dn2 += xr[2]; xn2 += xr[3]; gm = fmax(gm, xr[4]);
         }
       } else {
-        for (int w = 0; w < NWARPS; ++w) {
-          tc += red[w * 32]; dDd += red[w * 32 + 1]; gd += red[w * 32 + 2]; dn2 += red[w * 32 + 3];
-          xn2 += red[w * 32 + 4]; ninv += red[w * 32 + 5]; gm = fmax(gm, red[w * 32 + 6]);
-        }
+        dDd += scal[9]; gd += scal[10]; dn2 += scal[11]; xn2 = scal[12]; gm = scal[13];
       }
       for (int i = 0; i < nc * 6; ++i) if (fidx[i / 6] >= 0) gm = fmax(gm, fabs(gc[i]));
       const double model = 0.5 * (dDd * imu - gd);
@@ -1072,7 +1057,7 @@ window_lm_kernel(const WinData d, const Params P) {
       }
       iflag[1] = accept; iflag[2] = stop; iflag[0] = 0;
     }
-    if constexpr (CS > 1) cg::this_cluster().sync();   // every CTA has read the xbufs; trial landmarks are visible
+    if constexpr (CS > 1) cg::this_cluster().sync();   // every CTA has read the xbufs
     else __syncthreads();
     const int accept = iflag[1];
     int stop = iflag[2];
@@ -1085,12 +1070,16 @@ window_lm_kernel(const WinData d, const Params P) {
       cost = scal[5];
       ninv_cur = (int)scal[7];
       for (int i = tid; i < nc * PS; i += NTHREADS) pose_cur[i] = pose_tri[i];
+      // the trial evaluation is the linearisation of the accepted state
+      for (int i = tid; i < MAXCAM * 27; i += NTHREADS) Bc[i] = Bt[i];
+      for (int i = tid; i < nc * 6; i += NTHREADS) Dc[i] = clampd(Bt[(i / 6) * 21 + packed21(i % 6, i % 6)]);
       cur ^= 1;
-      have_lin = 0;
+      fresh_lin = 1;
       ++n_acc;
     } else {
       mu = mu / nu;
       nu *= 2.0;
+      fresh_lin = 0;
       ++n_rej;
     }
     if (tid == 0 && crank == 0 && d.hist_cost != nullptr && it < kHist) {
