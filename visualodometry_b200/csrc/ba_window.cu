@@ -43,10 +43,13 @@ namespace cg = cooperative_groups;
 #define WX_SCHOIST 0    // back-substitution: scratch row loaded at the top of the batch
 #endif
 
-// A 16-byte record is loaded with one LDG.128; its `orig` word is not used by the solve, and a dead destination register
-// is recycled at once -- the next write to it then waits for the load (write-after-write on the long scoreboard).
-// Naming the word where the record is consumed keeps the register allocated while the load is in flight.
-__device__ __forceinline__ void keep_alive(const ObsRec& r) { asm volatile("" ::"r"(r.orig)); }
+// A 16-byte record is loaded with one LDG.128; its `orig` word is not used by the solve, and ptxas recycles a dead
+// destination register at once -- the next write to it (a loop counter of the DMMA loop) then waits for the load
+// (write-after-write on the long scoreboard).  A real, never-taken use where the record is consumed keeps the register
+// allocated while the load is in flight: `orig` is an observation index, < 2^31 - 1 by the ABI's size limit.
+__device__ __forceinline__ void keep_alive(const ObsRec& r) {
+  asm volatile("{\n\t.reg .pred p;\n\tsetp.eq.s32 p, %0, 0x7fffffff;\n\t@p trap;\n\t}" ::"r"(r.orig));
+}
 
 __device__ __forceinline__ int packed21(int r, int s) { return r * 6 - r * (r - 1) / 2 + (s - r); }
 
