@@ -133,6 +133,12 @@ IndexIn make_index_in(const b2ba* h) {
   in.nb = h->B; in.nc_tot = h->nc_tot; in.np_tot = h->np_tot; in.no = h->no;
   in.cam_off = h->d_cam_off.p; in.pt_off = h->d_pt_off.p; in.obs_off = h->d_obs_off.p;
   in.obs_cam = h->d_obs_cam.p; in.obs_pt = h->d_obs_pt.p; in.obs_uv = h->d_uv.p;
+  if ((int)h->h_pt_off.size() == h->B + 1 && (int)h->h_cam_off.size() == h->B + 1) {
+    for (int b = 0; b < h->B; ++b) {
+      in.max_np = std::max(in.max_np, h->h_pt_off[b + 1] - h->h_pt_off[b]);
+      in.max_nc = std::max(in.max_nc, h->h_cam_off[b + 1] - h->h_cam_off[b]);
+    }
+  }
   return in;
 }
 
@@ -1097,7 +1103,9 @@ int b2ba_optimize_batch(b2ba_t* h, int32_t B, const int32_t* cam_off, const int3
     CUB(cudaEventRecord(h->ev_in[c], cs), "event");
     CUB(cudaStreamWaitEvent(ks, h->ev_in[c], 0), "wait");
     IndexOut io{k->d_pm.p, k->d_pt_ptr.p, k->d_cm.p, k->d_cam_ptr.p, k->d_flags.p, k->sched_order ? k->d_sched.p : nullptr};
-    int rc = build_index(make_index_in(k), io, ks);
+    IndexIn kin = make_index_in(k);
+    for (int b = 0; b < nb; ++b) { kin.max_np = std::max(kin.max_np, sp[b + 1] - sp[b]); kin.max_nc = std::max(kin.max_nc, sc[b + 1] - sc[b]); }
+    int rc = build_index(kin, io, ks);
     if (rc) return bail(cuda_fail(h, (cudaError_t)rc, "build_index"));
     if (k->sched_order && (rc = permute_pts(k, k->d_pts1.p, k->d_pts0.p, true, ks)) != 0) return bail(cuda_fail(h, (cudaError_t)rc, "permute"));
     rc = launch_window_path(k, make_win(k, false, nullptr), P, ks);

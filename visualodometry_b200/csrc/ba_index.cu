@@ -4,6 +4,9 @@
 
 #include <cub/device/device_radix_sort.cuh>
 
+#include <cstdlib>
+#include <mutex>
+
 namespace b2 {
 
 namespace {
@@ -153,11 +156,200 @@ int permute_points(int nb, int np_tot, const int* pt_off, const int* sched, cons
   return (int)cudaGetLastError();
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Window path: the whole index of ONE window built by ONE CTA in shared memory -- no global sort.  A window's landmark
+// has every camera at most once, so the point-major order (slot, camera, original index) and the camera-major order
+// (camera, slot) follow from one 32-bit camera mask per landmark: position inside a landmark's run = number of lower
+// cameras that see it (popc), position inside a camera's run = number of lower slots it sees (per-camera bit vectors
+// over the slots + prefix counts per 32 slots).  The landmark schedule (decreasing observation count, stable) is a
+// stable counting sort over 32 buckets.  Output is bit-identical to the global radix-sort builder below (and to the
+// oracle's std::stable_sort): tests/test_gpu_parity.py::test_index_bit_exact, ::test_landmark_schedule_is_stable_count_sort.
+// HBM traffic: the observation arrays twice in (8 + 16 B), both streams once out (32 B) per observation, against
+// ~10 passes over 12-byte key/value pairs for the two device-wide sorts; one launch instead of ~20.
+constexpr int kWinIdxThreads = 512;
+
+struct WinIdxSmem {   // layout of the dynamic shared memory (ints), for a window with <= max_np landmarks, <= 32 cameras
+  int max_np, nchunk;
+  __host__ __device__ size_t mask() const { return 0; }
+  __host__ __device__ size_t sched() const { return mask() + max_np; }
+  __host__ __device__ size_t pos_of() const { return sched() + max_np; }
+  __host__ __device__ size_t ptr() const { return pos_of() + max_np; }                 // max_np + 1
+  __host__ __device__ size_t bv() const { return ptr() + max_np + 1; }                 // 32 x nchunk
+  __host__ __device__ size_t cp() const { return bv() + (size_t)32 * nchunk; }         // 32 x nchunk
+  __host__ __device__ size_t wc() const { return cp() + (size_t)32 * nchunk; }         // (threads / 32) x 32
+  __host__ __device__ size_t run() const { return wc() + (kWinIdxThreads / 32) * 32; } // 32 bucket cursors
+  __host__ __device__ size_t cam() const { return run() + 32; }                        // 33 camera run starts
+  __host__ __device__ size_t total() const { return cam() + 33 + 3; }
+};
+
+__global__ void __launch_bounds__(kWinIdxThreads) window_index_kernel(IndexIn in, IndexOut out, WinIdxSmem L) {
+  extern __shared__ int sm[];
+  unsigned* mask = reinterpret_cast<unsigned*>(sm + L.mask());
+  int* sched = sm + L.sched();
+  int* pos_of = sm + L.pos_of();
+  int* ptr = sm + L.ptr();
+  unsigned* bv = reinterpret_cast<unsigned*>(sm + L.bv());
+  int* cp = sm + L.cp();
+  int* wc = sm + L.wc();
+  int* run = sm + L.run();
+  int* cam = sm + L.cam();
+  int* carry = cam + 33;
+  constexpr int T = kWinIdxThreads, NW = T / 32;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int b = blockIdx.x;
+  const int c0 = in.cam_off[b], nc = in.cam_off[b + 1] - c0;
+  const int p0 = in.pt_off[b], np = in.pt_off[b + 1] - p0;
+  const long long o0 = in.obs_off[b], o1 = in.obs_off[b + 1];
+  const int nchunk = (np + 31) >> 5;
+
+  for (int p = tid; p < np; p += T) mask[p] = 0u;
+  if (tid < 32) run[tid] = 0;
+  __syncthreads();
+  // 1. camera mask per landmark; duplicate (camera, landmark) pairs and out-of-range indices are flagged
+  for (long long i = o0 + tid; i < o1; i += T) {
+    int c = in.obs_cam[i], p = in.obs_pt[i];
+    if (c < 0 || c >= nc || p < 0 || p >= np) { out.flags[0] = 1; c = 0; p = 0; }
+    if (np > 0) {
+      const unsigned bit = 1u << c;
+      if (atomicOr(&mask[p], bit) & bit) out.flags[1] = 1;
+    }
+  }
+  __syncthreads();
+  // 2. landmark schedule: stable counting sort by bucket 31 - min(observation count, 31) (landmark id order inside a
+  //    bucket).  run[k]: landmarks of bucket k seen so far; first the bucket sizes, then their starts, then a pass in
+  //    id order, T landmarks at a time: rank inside the warp by match_any, over the warps by a small table.
+  for (int p = tid; p < np; p += T) atomicAdd(&run[31 - min(__popc(mask[p]), 31)], 1);
+  __syncthreads();
+  if (tid == 0) {
+    int acc = 0;
+    for (int k = 0; k < 32; ++k) { const int n = run[k]; run[k] = acc; acc += n; }
+  }
+  __syncthreads();
+  for (int base = 0; base < np; base += T) {
+    const int p = base + tid;
+    const bool live = p < np;
+    const int k = live ? 31 - min(__popc(mask[p]), 31) : 32 + lane;        // idle lanes match nobody
+    const unsigned same = __match_any_sync(0xffffffffu, k);
+    const int rank_w = __popc(same & ((1u << lane) - 1u));
+    wc[warp * 32 + lane] = 0;
+    __syncwarp();
+    if (live && rank_w == 0) wc[warp * 32 + k] = __popc(same);            // one leader per key and warp
+    __syncthreads();
+    if (live) {
+      int off = run[k] + rank_w;
+      for (int w = 0; w < warp; ++w) off += wc[w * 32 + k];
+      sched[off] = p;
+      pos_of[p] = off;
+    }
+    __syncthreads();
+    if (tid < 32) {
+      int n = 0;
+      for (int w = 0; w < NW; ++w) n += wc[w * 32 + tid];
+      run[tid] += n;
+    }
+    __syncthreads();
+  }
+  // 3. pt_ptr: exclusive scan of the observation counts in schedule order
+  if (tid == 0) carry[0] = 0;
+  __syncthreads();
+  for (int base = 0; base < np; base += T) {
+    const int q = base + tid;
+    const int v = q < np ? __popc(mask[sched[q]]) : 0;
+    int incl = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int u = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += u;
+    }
+    if (lane == 31) wc[warp] = incl;
+    __syncthreads();
+    int before = carry[0];
+    for (int w = 0; w < warp; ++w) before += wc[w];
+    if (q < np) ptr[q] = before + incl - v;
+    __syncthreads();
+    if (tid == T - 1) carry[0] = before + incl;
+    __syncthreads();
+  }
+  if (tid == 0) ptr[np] = carry[0];
+  // 4. per camera: bit vector over the slots, observation count in front of every 32 slots, run starts
+  for (int j = warp; j < nchunk; j += NW) {
+    const int q = 32 * j + lane;
+    const unsigned m = q < np ? mask[sched[q]] : 0u;
+    for (int c = 0; c < nc; ++c) {
+      const unsigned bits = __ballot_sync(0xffffffffu, (m >> c) & 1u);
+      if (lane == c) bv[c * nchunk + j] = bits;
+    }
+  }
+  __syncthreads();
+  if (tid < nc) {
+    int acc = 0;
+    for (int j = 0; j < nchunk; ++j) { cp[tid * nchunk + j] = acc; acc += __popc(bv[tid * nchunk + j]); }
+    cam[tid + 1] = acc;                    // observations of camera tid
+  }
+  __syncthreads();
+  if (tid == 0) {
+    cam[0] = 0;
+    for (int c = 0; c < nc; ++c) cam[c + 1] += cam[c];
+  }
+  __syncthreads();
+  // 5. offsets and the schedule out (absolute offsets; a window's last entry is its successor's first: same value)
+  for (int q = tid; q <= np; q += T) out.pt_ptr[p0 + q] = (int)o0 + ptr[q];
+  for (int c = tid; c <= nc; c += T) out.cam_ptr[c0 + c] = (int)o0 + cam[c];
+  if (out.sched)
+    for (int q = tid; q < np; q += T) out.sched[p0 + q] = sched[q];
+  // 6. both streams
+  if (np > 0) {
+    for (long long i = o0 + tid; i < o1; i += T) {
+      int c = in.obs_cam[i], p = in.obs_pt[i];
+      if (c < 0 || c >= nc || p < 0 || p >= np) { c = 0; p = 0; }
+      const float2 uv = in.obs_uv[i];
+      const int s_ = pos_of[p];
+      const unsigned m = mask[p];
+      const long long a_pm = o0 + ptr[s_] + __popc(m & ((1u << c) - 1u));
+      const long long a_cm = o0 + cam[c] + cp[c * nchunk + (s_ >> 5)] + __popc(bv[c * nchunk + (s_ >> 5)] & ((1u << (s_ & 31)) - 1u));
+      ObsRec r; r.u = uv.x; r.v = uv.y; r.orig = (int)i;
+      r.idx = c; out.pm[a_pm] = r;
+      r.idx = s_; out.cm[a_cm] = r;
+    }
+  }
+}
+
+// the per-window builder applies when the streams are schedule-ordered (window path), every window has <= 32 cameras
+// and its tables fit into shared memory
+static bool window_index_fits(const IndexIn& in, const IndexOut& out, WinIdxSmem* L, size_t* bytes) {
+  if (!out.sched || in.max_nc <= 0 || in.max_nc > 32 || in.max_np <= 0) return false;
+  static const bool off = [] { const char* e = std::getenv("B2BA_INDEX_SORT"); return e && std::atoi(e) != 0; }();
+  if (off) return false;                   // developer knob: force the global-sort builder (parity of the two builders)
+  L->max_np = in.max_np; L->nchunk = (in.max_np + 31) / 32;
+  *bytes = L->total() * sizeof(int);
+  return *bytes <= 200 * 1024;
+}
+
 int build_index(const IndexIn& in, const IndexOut& out, cudaStream_t s) {
   cudaError_t e;
   e = cudaMemsetAsync(out.flags, 0, 2 * sizeof(int), s);
   if (e != cudaSuccess) return (int)e;
   const long long no = in.no;
+  {
+    WinIdxSmem L;
+    size_t bytes = 0;
+    if (window_index_fits(in, out, &L, &bytes)) {
+      static std::mutex mtx;
+      static bool configured[64] = {};
+      int dev = 0;
+      if ((e = cudaGetDevice(&dev)) != cudaSuccess) return (int)e;
+      {
+        std::lock_guard<std::mutex> lock(mtx);
+        if (dev < 0 || dev >= 64 || !configured[dev]) {
+          e = cudaFuncSetAttribute(window_index_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+          if (e != cudaSuccess) return (int)e;
+          if (dev >= 0 && dev < 64) configured[dev] = true;
+        }
+      }
+      window_index_kernel<<<in.nb, kWinIdxThreads, bytes, s>>>(in, out, L);
+      return (int)cudaGetLastError();
+    }
+  }
   if (no == 0) {
     fill_ptr<<<(in.np_tot + 256) / 256, 256, 0, s>>>(out.pt_ptr, in.np_tot + 1, 0);
     fill_ptr<<<(in.nc_tot + 256) / 256, 256, 0, s>>>(out.cam_ptr, in.nc_tot + 1, 0);

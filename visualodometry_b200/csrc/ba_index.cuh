@@ -16,6 +16,7 @@ struct IndexIn {
   const int* obs_cam;        // device, window-local
   const int* obs_pt;         // device, window-local
   const float2* obs_uv;      // device
+  int max_np = 0, max_nc = 0;   // host-known maxima over the windows (0 = unknown: the global-sort builder is used)
 };
 
 // window of observation i: obs_off[b] <= i < obs_off[b + 1]
