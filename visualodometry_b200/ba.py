@@ -68,12 +68,49 @@ class BASummary:
         return self.status in (_lib.MAX_ITERS, _lib.CONVERGED)
 
 
-@dataclass
 class BAResult:
-    T_cw: np.ndarray            # (Nc,4,4) f64
-    points: np.ndarray          # (Np,3) f64
-    summary: BASummary
-    summaries: list = field(default_factory=list)   # per window (batched problems)
+    """T_cw (Nc,4,4) f64, points (Np,3) f64, summary (the worst of the batch), summaries (per window).  The 4 x 4
+    matrices are built from the engine's [R|t] rows on first access (a 4096-window batch has 40960 of them)."""
+
+    def __init__(self, T_cw, points, summary, summaries=None, poses=None):
+        self._T, self._poses = T_cw, poses
+        self.points, self.summary = points, summary
+        self.summaries = summaries if summaries is not None else []
+
+    @property
+    def T_cw(self) -> np.ndarray:
+        if self._T is None:
+            self._T = T_from_poses(self._poses)
+        return self._T
+
+    @property
+    def poses(self) -> np.ndarray:
+        return self._poses if self._poses is not None else poses_from_T(self._T)
+
+
+class SummaryList:
+    """Per-window summaries of a batch call: a sequence of BASummary over the C array the call filled, converted on
+    access (4096 Python objects per call are not free); `.array` is the structured numpy view of the same memory."""
+    DTYPE = np.dtype([("status", "<i4"), ("iterations", "<i4"), ("accepted", "<i4"), ("rejected", "<i4"), ("n_invalid", "<i4"),
+                      ("pcg_iters", "<i4"), ("initial_cost", "<f8"), ("final_cost", "<f8"), ("final_mu", "<f8")])
+
+    def __init__(self, carray):
+        self._c = carray
+        self.array = np.frombuffer(carray, dtype=self.DTYPE) if len(carray) else np.empty(0, self.DTYPE)
+
+    def __len__(self):
+        return len(self._c)
+
+    def __getitem__(self, i):
+        if isinstance(i, slice):
+            return [self[j] for j in range(*i.indices(len(self)))]
+        return BundleAdjuster._summary(self._c[i])
+
+    def __iter__(self):
+        return (BundleAdjuster._summary(x) for x in self._c)
+
+    def worst(self):
+        return self[int(np.argmax(self.array["status"]))]
 
 
 def poses_from_T(T_cw) -> np.ndarray:
@@ -445,7 +482,9 @@ class BundleAdjuster:
                                                *[x.ptr for x in a], self.intr.ctypes.data_as(C.POINTER(C.c_double)), 0,
                                                poses_o.ctypes.data, pts_o.ctypes.data, sms, chunks)
             self._check(rc, "b2ba_optimize_batch")
-            sm = [self._summary(x) for x in sms]
+            assert C.sizeof(_lib.Summary) == SummaryList.DTYPE.itemsize
+            sm = SummaryList(sms)
             self._nb, self._shape = 0, None
+            return BAResult(None, pts_o, sm.worst(), sm, poses=poses_o)
         worst = max(sm, key=lambda s: s.status)
-        return BAResult(T_from_poses(poses_o), pts_o, worst, sm)
+        return BAResult(None, pts_o, worst, sm, poses=poses_o)

@@ -1008,18 +1008,19 @@ int b2ba_optimize_batch(b2ba_t* h, int32_t B, const int32_t* cam_off, const int3
   if (max_nc <= kSmallMaxCam && max_nfree <= kSmallMaxFree) path = PATH_WIN_SMALL;
   else if (max_nc <= kMaxCam && max_nfree <= kBigMaxFree) path = PATH_WIN_BIG;
   else return fail(h, B2BA_E_UNSUPPORTED, "optimize_batch takes window problems (<= 24 cameras, <= 21 free per window)");
-  // chunk boundaries: with chunks <= 0 they fall on multiples of one launch wave (no partial waves inside the
-  // batch): a first chunk of one wave (the solve starts early), then two waves per chunk; few windows -> one
-  // chunk on the cluster (latency) path
+  // chunk boundaries: with chunks <= 0 they fall on multiples of half a launch wave: a first chunk of half a wave (its
+  // upload is the only one the solve cannot hide), then one wave per chunk (the last, short chunk keeps the final
+  // read-back short); few windows -> one chunk on the cluster (latency) path
   std::vector<int> cut{0};
   const int wave = path == PATH_WIN_SMALL ? h->wave_small : h->wave_big;
   if (B <= 18) cut.push_back(B);
   else if (chunks > 0) { const int K = chunks > B ? B : chunks; for (int c = 1; c <= K; ++c) cut.push_back((int)((long long)B * c / K)); }
   else if (wave <= 0 || B <= 2 * wave) cut.push_back(B);
   else {
-    // B2BA_CHUNK_PLAN="first,step" in quarter waves (default 4,8: one wave, then two waves per chunk)
-    int q_first = 4, q_step = 8;
-    if (const char* e = getenv("B2BA_CHUNK_PLAN")) { if (sscanf(e, "%d,%d", &q_first, &q_step) != 2 || q_first < 1 || q_step < 1) { q_first = 4; q_step = 8; } }
+    // B2BA_CHUNK_PLAN="first,step" in quarter waves (default 2,4: half a wave, then one wave per chunk; measured with
+    // tools/e2e_chunks.py: 65.7 ms against 67.1 ms for 4,8 on the C4 batch)
+    int q_first = 2, q_step = 4;
+    if (const char* e = getenv("B2BA_CHUNK_PLAN")) { if (sscanf(e, "%d,%d", &q_first, &q_step) != 2 || q_first < 1 || q_step < 1) { q_first = 2; q_step = 4; } }
     int w = wave * q_first / 4;
     while (w < B) { cut.push_back(w); w += wave * q_step / 4; }
     cut.push_back(B);
@@ -1055,6 +1056,11 @@ int b2ba_optimize_batch(b2ba_t* h, int32_t B, const int32_t* cam_off, const int3
   // From the first enqueue on, copies and kernels of earlier chunks read the caller's inputs and write the caller's
   // outputs asynchronously: EVERY exit -- errors included -- first waits for all four streams, so that no work of this
   // call touches a caller buffer after it has returned.
+  // B2BA_E2E_TRACE=1 (developer knob): timing events per chunk, printed to stderr after the call
+  static const bool trace = [] { const char* e = getenv("B2BA_E2E_TRACE"); return e && atoi(e) != 0; }();
+  std::vector<cudaEvent_t> tev;
+  auto mark = [&](cudaStream_t st) { if (!trace) return; cudaEvent_t e; cudaEventCreate(&e); cudaEventRecord(e, st); tev.push_back(e); };
+  mark(h->pipe_copy);
   auto bail = [&](int rc) {
     cudaStreamSynchronize(h->pipe_copy); cudaStreamSynchronize(h->pipe_solve);
     cudaStreamSynchronize(h->pipe_solve2); cudaStreamSynchronize(h->pipe_back);
@@ -1101,22 +1107,27 @@ int b2ba_optimize_batch(b2ba_t* h, int32_t B, const int32_t* cam_off, const int3
       CUB(cudaMemcpyAsync(k->d_uv.p, obs_uv + 2 * o0, no * sizeof(float2), hd, cs), "copy");
     }
     CUB(cudaEventRecord(h->ev_in[c], cs), "event");
+    mark(cs);
     CUB(cudaStreamWaitEvent(ks, h->ev_in[c], 0), "wait");
+    mark(ks);
     IndexOut io{k->d_pm.p, k->d_pt_ptr.p, k->d_cm.p, k->d_cam_ptr.p, k->d_flags.p, k->sched_order ? k->d_sched.p : nullptr};
     IndexIn kin = make_index_in(k);
     for (int b = 0; b < nb; ++b) { kin.max_np = std::max(kin.max_np, sp[b + 1] - sp[b]); kin.max_nc = std::max(kin.max_nc, sc[b + 1] - sc[b]); }
     int rc = build_index(kin, io, ks);
     if (rc) return bail(cuda_fail(h, (cudaError_t)rc, "build_index"));
     if (k->sched_order && (rc = permute_pts(k, k->d_pts1.p, k->d_pts0.p, true, ks)) != 0) return bail(cuda_fail(h, (cudaError_t)rc, "permute"));
+    mark(ks);
     rc = launch_window_path(k, make_win(k, false, nullptr), P, ks);
     if (rc) return bail(cuda_fail(h, (cudaError_t)rc, "launch"));
     if (k->sched_order && (rc = permute_pts(k, k->d_pts0.p, k->d_pts1.p, false, ks)) != 0) return bail(cuda_fail(h, (cudaError_t)rc, "permute"));
     CUB(cudaEventRecord(h->ev_done[c], ks), "event");
+    mark(ks);
     CUB(cudaStreamWaitEvent(bs, h->ev_done[c], 0), "wait");
     CUB(cudaMemcpyAsync(out_poses_cw + c0 * 12, k->d_poses.p, nc * 12 * sizeof(double), dh, bs), "read");
     CUB(cudaMemcpyAsync(out_points + p0 * 3, k->sched_order ? k->d_pts1.p : k->d_pts0.p, np * 3 * sizeof(double), dh, bs), "read");
     CUB(cudaMemcpyAsync(st_summ + w0, k->d_summ.p, nb * sizeof(b2ba_summary), dh, bs), "read");
     CUB(cudaMemcpyAsync(h->pinned_flags + 2 * c, k->d_flags.p, 2 * sizeof(int), dh, bs), "read");
+    mark(bs);
   }
 #undef CUB
   {
@@ -1125,6 +1136,15 @@ int b2ba_optimize_batch(b2ba_t* h, int32_t B, const int32_t* cam_off, const int3
     const cudaError_t ee = e0 != cudaSuccess ? e0 : e1 != cudaSuccess ? e1 : e2 != cudaSuccess ? e2 : e3;
     if (ee != cudaSuccess) return cuda_fail(h, ee, "optimize_batch");
   }
+  if (trace && tev.size() == (size_t)(1 + 5 * K)) {
+    for (int c = 0; c < K; ++c) {
+      float t[5];
+      for (int j = 0; j < 5; ++j) cudaEventElapsedTime(&t[j], tev[0], tev[1 + 5 * c + j]);
+      fprintf(stderr, "chunk %d (%d windows): copied %.2f  solve stream free %.2f  index+permute done %.2f  solved %.2f  read back %.2f ms\n",
+              c, cut[c + 1] - cut[c], t[0], t[1], t[2], t[3], t[4]);
+    }
+  }
+  for (cudaEvent_t e : tev) cudaEventDestroy(e);
   for (int c = 0; c < K; ++c) {
     if (h->pinned_flags[2 * c]) return fail(h, B2BA_E_INVALID, "observation index out of range");
     if (h->pinned_flags[2 * c + 1]) return fail(h, B2BA_E_DUPLICATE, "duplicate (camera, point) observation");
