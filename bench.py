@@ -440,6 +440,32 @@ def run_reference(args, rank, world):
                       "e2e": {"value": v, "unit": "obs*iter/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
 
 
+def bind_to_gpu_numa_node(local):
+    """Multi-rank runs: keep a rank's threads -- and with them the pinned host buffers it allocates next (first touch) --
+    on the NUMA node its GPU hangs off, so that the ranks' H2D / D2H streams do not all cross one socket's memory
+    controller (the end-to-end number decayed from 1 to 8 ranks).  Best effort: returns what it did."""
+    try:
+        import torch
+        bus = torch.cuda.get_device_properties(local).pci_bus_id
+        dom = torch.cuda.get_device_properties(local).pci_domain_id
+        dev = torch.cuda.get_device_properties(local).pci_device_id
+        path = f"/sys/bus/pci/devices/{dom:04x}:{bus:02x}:{dev:02x}.0/numa_node"
+        node = int(open(path).read().strip())
+        if node < 0:
+            return {"node": node, "bound": False}
+        cpus = []
+        for part in open(f"/sys/devices/system/node/node{node}/cpulist").read().strip().split(","):
+            lo, _, hi = part.partition("-")
+            cpus += list(range(int(lo), int(hi or lo) + 1))
+        allowed = sorted(set(cpus) & os.sched_getaffinity(0))
+        if not allowed:
+            return {"node": node, "bound": False}
+        os.sched_setaffinity(0, allowed)
+        return {"node": node, "bound": True, "cpus": len(allowed)}
+    except Exception as e:   # no sysfs entry, no permission: run unbound
+        return {"bound": False, "why": type(e).__name__}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -477,6 +503,7 @@ def main():
     if args.workload == "pnp":
         return run_pnp(args) if rank == 0 else None
     torch.cuda.set_device(local)
+    numa = bind_to_gpu_numa_node(local) if world > 1 else {"bound": False, "why": "single rank"}
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
@@ -607,7 +634,7 @@ def main():
                "clocks": clocks, "gpu_launches": args.steps,
                "e2e": {"value": units_all / (ms_e2e * 1e-3), "unit": "obs*iter/s", "h2d_bytes_per_step": int(h2d),
                        "d2h_bytes_per_step": int(d2h), "ms_per_step": ms_e2e},
-               "wall_s_timed_region": t_wall}
+               "wall_s_timed_region": t_wall, "numa_binding_rank0": numa}
         if c5:
             # dominant kernel: the cooperative PCG (block-sparse mat-vec, HBM/L2 bound).  Algorithmic bytes of
             # the step: 46.4 B per observation*iteration + 288 B per STORED (upper) S block per CG iteration
