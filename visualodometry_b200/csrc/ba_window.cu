@@ -1116,7 +1116,10 @@ using CfgSmall = WinCfg<7, 8, 4, 64, kSmallMaxCam, 2>;    // 256 threads, 2 CTAs
 #ifndef WX_G
 #define WX_G 4
 #endif
-using CfgSmall4 = WinCfg<7, 4, WX_G, 32, kSmallMaxCam, 4>;   // 128 threads, 4 CTAs / SM
+#ifndef WX_MINB
+#define WX_MINB 4
+#endif
+using CfgSmall4 = WinCfg<7, 4, WX_G, 32, kSmallMaxCam, WX_MINB>;   // 128 threads, 4 CTAs / SM
 using CfgBig = WinCfg<16, 16, 16, 32, kMaxCam, 1>;        // n+1 <= 128: up to 21 free cameras (C3)
 constexpr int kClusterSize = 8;                           // portable cluster size
 using CfgSmallC = WinCfg<7, 8, 4, 64, kSmallMaxCam, 1, kClusterSize>;   // latency path: 8 CTAs x 256 threads per window
