@@ -356,7 +356,7 @@ int setup_large(b2ba* h) {
   CU(h->l_poses_tri.alloc(nc * 12), "alloc"); CU(h->l_lin_part.alloc(nc * 27 + 2), "alloc");
   CU(h->l_Dc.alloc(nc * 6), "alloc");
   CU(h->l_Sg.alloc(nblk * 36 + n), "alloc"); CU(h->l_dc.alloc(n), "alloc"); CU(h->l_r.alloc(n), "alloc");
-  CU(h->l_z.alloc(n), "alloc"); CU(h->l_q.alloc(n), "alloc"); CU(h->l_Minv.alloc(6 * n), "alloc"); CU(h->l_tbuf.alloc(nblk * 6), "alloc");
+  CU(h->l_z.alloc(n), "alloc"); CU(h->l_q.alloc(n), "alloc"); CU(h->l_Minv.alloc(6 * n), "alloc"); CU(h->l_tbuf.alloc(std::max((size_t)nblk * 6, (size_t)blocks * n)), "alloc");   // tbuf, or one n-vector per PCG CTA
   CU(h->l_part.alloc(part + 8), "alloc"); CU(h->l_sums.alloc(16), "alloc");
   if (!h->l_ctrl.p) {       // the exchange epoch lives in the control block and only grows: zero it once
     CU(h->l_ctrl.alloc(1), "alloc");

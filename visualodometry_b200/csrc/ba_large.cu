@@ -1,6 +1,8 @@
 // Large path kernels -- see ba_large.cuh.
 #include "ba_large.cuh"
 
+#include <cstdlib>
+
 #include <cooperative_groups.h>
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
@@ -897,14 +899,23 @@ __global__ void __launch_bounds__(kPcgThreads) large_pcg_kernel(LargeData d, int
   cg::grid_group grid = cg::this_grid();
   LargeCtrl* ctrl = d.ctrl;
   if (ctrl->stop || ctrl->step_bad) return;       // uniform across the grid
-  extern __shared__ double psh[];                  // p (n doubles)
+  extern __shared__ double psh[];                  // p (n doubles) [+ qT (n doubles), see below]
   __shared__ double red[kPcgThreads / 32][4];
   __shared__ double rowred[kPcgThreads / 32][6];
+  __shared__ double red2[kPcgThreads / 32][32];
   __shared__ double bcast[4];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int nwarp_cta = kPcgThreads / 32;
   const int gwarp = blockIdx.x * nwarp_cta + warp, nwarps = gridDim.x * nwarp_cta;
   const int n = d.n, nfree = d.nfree;
+  // Transposed half of the symmetric mat-vec.  When a second n-vector fits into shared memory (the launch then asks for
+  // 2 n doubles), a CTA adds the products S(f,c)^T p_f of its rows into qT[c] there (one row at a time, every block of a
+  // row has its own c: plain read-modify-write, fixed order) and publishes qT as ONE coalesced n-vector; the vectors of
+  // all CTAs are then added in CTA order.  Otherwise (large n) every product goes to tbuf and is gathered back.
+  unsigned dyn_smem;
+  asm("mov.u32 %0, %%dynamic_smem_size;" : "=r"(dyn_smem));
+  const bool use_qt = dyn_smem >= 2u * (unsigned)n * (unsigned)sizeof(double);
+  double* qT = psh + n;
   const double* S = d.Sg;
   const double* gred = d.Sg + (size_t)d.nblk * 36;
   double* part = d.part;                           // [gridDim.x * 4]
@@ -960,6 +971,10 @@ __global__ void __launch_bounds__(kPcgThreads) large_pcg_kernel(LargeData d, int
       // lists longer.
       // Odd CG iterations walk the passes backwards: what the previous iteration read last is still in L2.
       const int G_ = (int)gridDim.x, J_ = (nfree + G_ - 1) / G_;
+      if (use_qt) {
+        for (int i = tid; i < n; i += kPcgThreads) qT[i] = 0.0;
+        __syncthreads();
+      }
       for (int jj = 0; jj < J_; ++jj) {
         const int j = (it & 1) ? J_ - 1 - jj : jj;
         const int f = j * G_ + ((j & 1) ? G_ - 1 - (int)blockIdx.x : (int)blockIdx.x);
@@ -977,7 +992,10 @@ __global__ void __launch_bounds__(kPcgThreads) large_pcg_kernel(LargeData d, int
               v += M[6 * rr + s_] * x[s_];
               t += M[6 * s_ + rr] * pf[s_];
             }
-            if (c != f) d.tbuf[(size_t)b * 6 + rr] = t;
+            if (c != f) {
+              if (use_qt) qT[6 * c + rr] += t;          // (c, rr) is this lane's alone within the row
+              else d.tbuf[(size_t)b * 6 + rr] = t;
+            }
           }
         }
         v += __shfl_down_sync(0xffffffffu, v, 6) + __shfl_down_sync(0xffffffffu, v, 12) +
@@ -992,8 +1010,33 @@ __global__ void __launch_bounds__(kPcgThreads) large_pcg_kernel(LargeData d, int
         }
         __syncthreads();
       }
+      if (use_qt) {
+        double* mine = d.tbuf + (size_t)blockIdx.x * n;
+        for (int i = tid; i < n; i += kPcgThreads) mine[i] = qT[i];
+      }
       grid.sync();
       double s_pq = 0.0;
+      if (use_qt) {
+        // q_i = own part + the transposed parts of all CTAs in CTA order: a CTA finishes a contiguous slice of q, 32
+        // elements at a time; warp w adds the vectors of CTAs w, w + 8, ... (coalesced), warp 0 the 8 partial sums
+        const int E = (n + G_ - 1) / G_, lo = (int)blockIdx.x * E, hi = min(n, lo + E);
+        for (int i0 = lo; i0 < hi; i0 += 32) {
+          const int i = i0 + lane;
+          double a = 0.0;
+          if (i < hi)
+            for (int g = warp; g < G_; g += nwarp_cta) a += d.tbuf[(size_t)g * n + i];
+          red2[warp][lane] = a;
+          __syncthreads();
+          if (warp == 0 && i < hi) {
+            double t = d.q[i];
+#pragma unroll
+            for (int w = 0; w < nwarp_cta; ++w) t += red2[w][lane];      // fixed order
+            d.q[i] = t;
+            s_pq += t * psh[i];
+          }
+          __syncthreads();
+        }
+      } else {
       for (int j = 0; j * G_ < nfree; ++j) {
         const int f = nfree - 1 - (j * G_ + ((j & 1) ? G_ - 1 - (int)blockIdx.x : (int)blockIdx.x));   // long lists first
         if (f < 0) continue;
@@ -1016,6 +1059,7 @@ __global__ void __launch_bounds__(kPcgThreads) large_pcg_kernel(LargeData d, int
           s_pq += t * psh[6 * f + lane];
         }
         __syncthreads();
+      }
       }
       s_pq = warp_sum(s_pq);
       if (lane == 0) red[warp][0] = s_pq;
@@ -1493,7 +1537,11 @@ __global__ void large_finish_kernel(LargeData d) {
 }  // namespace
 
 int large_pcg_grid(int n, int* blocks, size_t* smem) {
+  // p, and (when it fits: n <= 12800) the CTA's transposed-product vector qT: see large_pcg_kernel.  B2BA_PCG_QT=0
+  // (developer knob) keeps the tbuf gather.
+  static const bool qt_off = [] { const char* e = std::getenv("B2BA_PCG_QT"); return e && std::atoi(e) == 0; }();
   *smem = (size_t)n * sizeof(double);
+  if (!qt_off && 2 * *smem <= 200 * 1024) *smem *= 2;
   cudaError_t e = cudaFuncSetAttribute(large_pcg_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)*smem);
   if (e != cudaSuccess) return (int)e;
   int per_sm = 0, dev = 0, sms = 0;
@@ -1502,7 +1550,8 @@ int large_pcg_grid(int n, int* blocks, size_t* smem) {
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   if (per_sm < 1) return (int)cudaErrorInvalidConfiguration;
-  *blocks = sms * (per_sm > 2 ? 2 : per_sm);
+  static const int cap = [] { const char* e = std::getenv("B2BA_PCG_CTAS_PER_SM"); return e ? std::atoi(e) : 2; }();
+  *blocks = sms * (per_sm > cap ? (cap < 1 ? 1 : cap) : per_sm);
   return 0;
 }
 
