@@ -305,7 +305,8 @@ window_lm_kernel(const WinData d, const Params P) {
           for (int r = 0; r < CS; ++r) v += cl.map_shared_rank(xbuf, r)[i];
           if (i < NB) Bd[i] = v; else scal[i - NB] = v;
         }
-        cl.sync();                               // xbuf may be overwritten again
+        // no second barrier: the next writes into xbuf[0, NB + 2) are the reduce-scattered tiles of the next point
+        // pass, and those come after that pass's first cluster barrier, which every CTA reaches after these reads
       }
     __syncthreads();
   };
@@ -1060,8 +1061,10 @@ window_lm_kernel(const WinData d, const Params P) {
       }
       iflag[1] = accept; iflag[2] = stop; iflag[0] = 0;
     }
-    if constexpr (CS > 1) cg::this_cluster().sync();   // every CTA has read the xbufs
-    else __syncthreads();
+    // (cluster: the step scalars in the peers' xbufs are next overwritten after two more cluster barriers, so a CTA
+    // barrier is enough here; one cluster barrier after the loop keeps every CTA's shared memory alive until all
+    // remote reads are done)
+    __syncthreads();
     const int accept = iflag[1];
     int stop = iflag[2];
     if (stop < 0) { status = B2BA_CONVERGED; break; }
@@ -1096,6 +1099,7 @@ window_lm_kernel(const WinData d, const Params P) {
   }
 
   // ------------------------------------------------------------------ write back
+  if constexpr (CS > 1) cg::this_cluster().sync();   // no CTA leaves while a peer may still read its shared memory
   if (cur == 1) {
     const double* src = d.pts[1] + (size_t)p0 * 3;
     double* dst = d.pts[0] + (size_t)p0 * 3;
