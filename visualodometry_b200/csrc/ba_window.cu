@@ -695,7 +695,11 @@ window_lm_kernel(const WinData d, const Params P) {
     }
 
     // ------------------------------------------------------------------ Cholesky + solve (a5)
-    // right-looking Cholesky in 6-column (camera) blocks, lower triangle of S, 2 barriers per block
+    // right-looking Cholesky in 6-column (camera) blocks, lower triangle of S, 2 barriers per block.  The right-hand side
+    // -g_red rides along as row n of S: panel solves and trailing updates treat it like any other row, so the forward
+    // substitution y = L^-1 b falls out of the factorisation in parallel and only the backward solve stays serial
+    for (int k = tid; k < n; k += NTHREADS) S[n * LDS + k] = -gred[k];
+    __syncthreads();
     for (int j0 = 0; j0 < n; j0 += 6) {
       // every thread factors the 6x6 diagonal block redundantly in registers: L (packed lower, row-major)
       double L[6][6], inv[6];
@@ -727,8 +731,8 @@ window_lm_kernel(const WinData d, const Params P) {
       }
       if (bad && tid == 0) iflag[0] = 1;
       const int m = n - j0 - 6;
-      // panel: row i of L21 = A21 row * L11^-T, one thread per row
-      for (int t = tid; t < m; t += NTHREADS) {
+      // panel: row i of L21 = A21 row * L11^-T, one thread per row (row m = the right-hand side)
+      for (int t = tid; t <= m; t += NTHREADS) {
         double* row = S + (j0 + 6 + t) * LDS + j0;
         double x[6];
 #pragma unroll
@@ -753,9 +757,9 @@ window_lm_kernel(const WinData d, const Params P) {
         }
       }
       // trailing update A22 -= L21 L21^T (lower triangle), work items = (row, 6-column block) pairs
-      const int npairs = (m / 6) * (m + 6) / 2;      // sum over column blocks cb of (m - cb)
+      const int npairs = (m / 6) * (m + 6) / 2 + m / 6;   // sum over column blocks cb of (m - cb + 1): rows cb .. m
       for (int id = tid; id < npairs; id += NTHREADS) {
-        int cb = 0, rem = id, len = m;
+        int cb = 0, rem = id, len = m + 1;
         while (rem >= len) { rem -= len; len -= 6; cb += 6; }
         const int ii = cb + rem;
         double* ri = S + (j0 + 6 + ii) * LDS + j0;
@@ -778,37 +782,16 @@ window_lm_kernel(const WinData d, const Params P) {
     }
     __syncthreads();
     if (warp == 0) {
-      // L y = -g_red, L^T x = y with the vector in registers (row k of lane k % 32), one shuffle per step.  Every
-      // lane keeps its unknowns pre-scaled by its own 1 / L_kk (x_k = d_k b_k - sum (d_k L_ki) y_i), so the dependent
-      // chain of a step is shuffle + FMA only; the coefficients of step i + 1 are loaded before step i is consumed.
+      // L^T x = y (y = row n of S, see above) with the vector in registers (row k of lane k % 32), one shuffle per step.
+      // Every lane keeps its unknowns pre-scaled by its own 1 / L_kk (x_k = d_k y_k - sum (d_k L_ik) x_i), so the
+      // dependent chain of a step is shuffle + FMA only; the coefficients of step i - 1 are loaded before step i is consumed.
       constexpr int RPL = Cfg::NR / 32 + (Cfg::NR % 32 ? 1 : 0);
       double x[RPL], di[RPL], cn[RPL];
 #pragma unroll
       for (int q = 0; q < RPL; ++q) {
         const int k = lane + 32 * q;
         di[q] = k < n ? red[k] : 0.0;
-        x[q] = k < n ? -gred[k] * di[q] : 0.0;
-        cn[q] = (k > 0 && k < n) ? S[k * LDS] * di[q] : 0.0;
-      }
-      for (int i = 0; i < n; ++i) {
-        double c[RPL];
-#pragma unroll
-        for (int q = 0; q < RPL; ++q) {
-          const int k = lane + 32 * q;
-          c[q] = cn[q];
-          cn[q] = (k > i + 1 && k < n) ? S[k * LDS + i + 1] * di[q] : 0.0;
-        }
-        double xi = 0.0;
-#pragma unroll
-        for (int q = 0; q < RPL; ++q)
-          if ((i >> 5) == q) xi = __shfl_sync(0xffffffffu, x[q], i & 31);
-#pragma unroll
-        for (int q = 0; q < RPL; ++q) x[q] = fma(-c[q], xi, x[q]);
-      }
-#pragma unroll
-      for (int q = 0; q < RPL; ++q) {
-        const int k = lane + 32 * q;
-        x[q] *= di[q];
+        x[q] = k < n ? S[n * LDS + k] * di[q] : 0.0;
         cn[q] = (k < n - 1) ? S[(n - 1) * LDS + k] * di[q] : 0.0;
       }
       for (int i = n - 1; i >= 0; --i) {
