@@ -652,17 +652,17 @@ window_lm_kernel(const WinData d, const Params P) {
         }
         xbuf[e] = v;
       }
-      cl.sync();                                 // ... and every CTA then gathers the sums from their owners
+      cl.sync();                                 // ... and every CTA then gathers the sums from their owners:
+      // independent remote loads, a few per thread, into its own tile memory (no peer reads that any more), so the
+      // assembly below works on local shared memory in every variant
+      for (int e = tid; e < Cfg::SPART; e += NTHREADS) SP[e] = cl.map_shared_rank(xbuf, e / Cfg::XCHUNK)[e % Cfg::XCHUNK];
+      __syncthreads();
     }
-    // (Z Z^T)[i][j] for i <= j: one tile entry, summed over the cluster's CTAs in rank order
+    // (Z Z^T)[i][j] for i <= j: one tile entry (cluster: summed over the CTAs in rank order)
     auto zzt = [&](int i, int j) -> double {
       const int mi = i >> 3, ni = j >> 3;
       const int off = (mi * NT - mi * (mi - 1) / 2 + (ni - mi)) * 64 + (i & 7) * 8 + (j & 7);
-      if constexpr (CS > 1) {
-        return cg::this_cluster().map_shared_rank(xbuf, off / Cfg::XCHUNK)[off % Cfg::XCHUNK];
-      } else {
-        return SP[off];
-      }
+      return SP[off];
     };
     for (int idx = tid; idx < n * n; idx += NTHREADS) {
       const int i = idx / n, j = idx - i * n;
