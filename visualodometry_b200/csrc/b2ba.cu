@@ -341,7 +341,7 @@ int setup_large(b2ba* h) {
   CU(h->l_zbuf.alloc((size_t)h->no * 24), "alloc");
   int blocks = 0;
   size_t smem = 0;
-  rc = h->nranks > 1 ? large_pcg_dist_grid((int)n, &blocks, &smem) : large_pcg_grid((int)n, &blocks, &smem);
+  rc = h->nranks > 1 ? large_pcg_dist_grid((int)n, h->nranks, &blocks, &smem) : large_pcg_grid((int)n, &blocks, &smem);
   if (rc) return cuda_fail(h, (cudaError_t)rc, "large_pcg_grid");
   if (h->nranks > 1) {
     rc = large_build_rows(h->rank, h->nranks, h->lix, nullptr);

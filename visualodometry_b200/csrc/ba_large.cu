@@ -850,13 +850,15 @@ namespace b2 {
 namespace {
 
 constexpr int kPcgThreads = 256;
-// The distributed PCG runs ONE CTA per SM (the grid size fixes the summation order on every rank) and, at 8 ranks, a
-// rank has fewer rows than SMs: a row (up to 288 KB of blocks) is then streamed by a single CTA, so its memory-level
-// parallelism -- not the grid -- sets the mat-vec time.  Twice the warps per CTA.
-#ifndef B2_PCG_DIST_THREADS
-#define B2_PCG_DIST_THREADS 512
-#endif
-constexpr int kPcgDistThreads = B2_PCG_DIST_THREADS;
+// The distributed PCG runs ONE CTA per SM (the grid size fixes the summation order on every rank).  Threads per CTA:
+// at 2 ranks a CTA streams several 288-KB rows per CG iteration and more warps mean more loads in flight (512 threads:
+// 57.8 -> 54.2 us per CG iteration); from 4 ranks on a CG iteration is barriers and exchanges, and the lighter CTA
+// wins (256 threads: 30.1 / 25.9 us at 4 / 8 ranks against 34.2 / 30.3 us with 512).  B2BA_PCG_DIST_THREADS overrides.
+inline int pcg_dist_threads(int nranks) {
+  static const int forced = [] { const char* e = std::getenv("B2BA_PCG_DIST_THREADS"); return e ? std::atoi(e) : 0; }();
+  if (forced == 256 || forced == 512) return forced;
+  return nranks <= 2 ? 512 : 256;
+}
 
 __device__ __forceinline__ bool inv6_spd(const double* M, double* Inv) {   // M row-major, upper used
   double L[21];   // packed lower: L[i*(i+1)/2 + j]
@@ -1129,18 +1131,19 @@ __global__ void __launch_bounds__(kPcgThreads) large_pcg_kernel(LargeData d, int
 namespace b2 {
 namespace {
 
-__global__ void __launch_bounds__(kPcgDistThreads) large_pcg_dist_kernel(LargeData d, int max_it, double tol) {
+template <int NT>
+__global__ void __launch_bounds__(NT) large_pcg_dist_kernel(LargeData d, int max_it, double tol) {
   cg::grid_group grid = cg::this_grid();
   LargeCtrl* ctrl = d.ctrl;
   if (ctrl->stop || ctrl->step_bad) return;       // replicated state: uniform across the grid AND across the ranks
   extern __shared__ double psh[];                  // p (n doubles)
-  __shared__ double red[kPcgDistThreads / 32][4];
-  __shared__ double rowred[kPcgDistThreads / 32][6];
+  __shared__ double red[NT / 32][4];
+  __shared__ double rowred[NT / 32][6];
   __shared__ double bcast[4];
   __shared__ int xok;
   const Peer& X = d.peer;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  constexpr int nwarp_cta = kPcgDistThreads / 32;
+  constexpr int nwarp_cta = NT / 32;
   const int G_ = (int)gridDim.x;
   const int n = d.n, nfree = d.nfree, nrows = d.f_hi - d.f_lo;
   double* part = d.part;                           // [gridDim.x * 4]
@@ -1167,7 +1170,7 @@ __global__ void __launch_bounds__(kPcgDistThreads) large_pcg_dist_kernel(LargeDa
   // ---- set-up: owned rows -> M^-1, r = -g_red into every rank
   {
     const double* gred = d.Sg + (size_t)d.nblk * 36;
-    for (int i = blockIdx.x * kPcgDistThreads + tid; i < nrows; i += G_ * kPcgDistThreads) {
+    for (int i = blockIdx.x * NT + tid; i < nrows; i += G_ * NT) {
       const int f = d.f_lo + i;
       double Inv[36];
       const bool ok = inv6_spd(d.Sl + (size_t)d.ldiag[i] * 36, Inv);
@@ -1183,7 +1186,7 @@ __global__ void __launch_bounds__(kPcgDistThreads) large_pcg_dist_kernel(LargeDa
   if (!exchange(++epoch)) { fail_exchange(); return; }
   // every rank now holds M^-1 and r of every row: x = 0, z = M^-1 r, r.z, b.b (CTA-strided rows, ordered sums)
   double s_rz = 0.0, s_bb = 0.0, s_bad = 0.0;
-  for (int f = blockIdx.x * kPcgDistThreads + tid; f < nfree; f += G_ * kPcgDistThreads) {
+  for (int f = blockIdx.x * NT + tid; f < nfree; f += G_ * NT) {
     const double* M = Minv + (size_t)f * 37;
     if (__ldcg(M + 36) == 0.0) s_bad = 1.0;
     double rv[6];
@@ -1215,14 +1218,14 @@ __global__ void __launch_bounds__(kPcgDistThreads) large_pcg_dist_kernel(LargeDa
   }
   double rnorm2 = bb, beta = 0.0;
   int it = 0;
-  for (int i = tid; i < n; i += kPcgDistThreads) psh[i] = 0.0;
+  for (int i = tid; i < n; i += NT) psh[i] = 0.0;
   __syncthreads();
   bool bad_pq = false;
   if (bb > 0.0) {
     for (; it < max_it; ++it) {
       if (rnorm2 <= tol * tol * bb) break;
       // ---- p = z + beta p (whole vector, every CTA)
-      for (int i = tid; i < n; i += kPcgDistThreads) psh[i] = d.z[i] + beta * psh[i];
+      for (int i = tid; i < n; i += NT) psh[i] = d.z[i] + beta * psh[i];
       __syncthreads();
       // ---- q_f = S(f,:) p for the owned rows (one CTA per row, warps stride over the row's blocks, fixed order) -> all ranks
       const size_t qoff = X.off_qx + (size_t)((epoch + 1) & 1) * n;
@@ -1253,7 +1256,7 @@ __global__ void __launch_bounds__(kPcgDistThreads) large_pcg_dist_kernel(LargeDa
       // ---- p.q from the gathered q: every CTA, whole vector, fixed order
       const double* q = X.at(X.rank, qoff);
       double s_pq = 0.0;
-      for (int i = tid; i < n; i += kPcgDistThreads) s_pq += psh[i] * __ldcg(q + i);
+      for (int i = tid; i < n; i += NT) s_pq += psh[i] * __ldcg(q + i);
       s_pq = warp_sum(s_pq);
       if (lane == 0) red[warp][0] = s_pq;
       __syncthreads();
@@ -1567,12 +1570,15 @@ int large_init_ctrl(const LargeData& d, const Params& P, cudaStream_t s) {
   return (int)cudaGetLastError();
 }
 
-int large_pcg_dist_grid(int n, int* blocks, size_t* smem) {
+int large_pcg_dist_grid(int n, int nranks, int* blocks, size_t* smem) {
   *smem = (size_t)n * sizeof(double);
-  cudaError_t e = cudaFuncSetAttribute(large_pcg_dist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)*smem);
+  const int nt = pcg_dist_threads(nranks);
+  const void* fn = nt == 512 ? (const void*)large_pcg_dist_kernel<512> : (const void*)large_pcg_dist_kernel<256>;
+  cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)*smem);
   if (e != cudaSuccess) return (int)e;
   int per_sm = 0, dev = 0, sms = 0;
-  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, large_pcg_dist_kernel, kPcgDistThreads, *smem);
+  e = nt == 512 ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, large_pcg_dist_kernel<512>, 512, *smem)
+                : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, large_pcg_dist_kernel<256>, 256, *smem);
   if (e != cudaSuccess) return (int)e;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
@@ -1636,13 +1642,14 @@ int large_iteration(const LargeData& d, const Params& P, int pcg_max_iters, doub
   } else {
     int blocks = 0;
     size_t smem = 0;
-    if ((rc = mr ? large_pcg_dist_grid(d.n, &blocks, &smem) : large_pcg_grid(d.n, &blocks, &smem)) != 0) { nvtxRangePop(); return rc; }
+    if ((rc = mr ? large_pcg_dist_grid(d.n, d.nranks, &blocks, &smem) : large_pcg_grid(d.n, &blocks, &smem)) != 0) { nvtxRangePop(); return rc; }
     LargeData dd = d;
     int mi = pcg_max_iters;
     double tol = pcg_tol;
     void* args[] = {&dd, &mi, &tol};
-    cudaError_t e = cudaLaunchCooperativeKernel(mr ? (void*)large_pcg_dist_kernel : (void*)large_pcg_kernel, dim3(blocks),
-                                                dim3(mr ? kPcgDistThreads : kPcgThreads), args, smem, s);
+    const int nt = mr ? pcg_dist_threads(d.nranks) : kPcgThreads;
+    void* fn = !mr ? (void*)large_pcg_kernel : nt == 512 ? (void*)large_pcg_dist_kernel<512> : (void*)large_pcg_dist_kernel<256>;
+    cudaError_t e = cudaLaunchCooperativeKernel(fn, dim3(blocks), dim3(nt), args, smem, s);
     if (e != cudaSuccess) { nvtxRangePop(); return (int)e; }
   }
   mark("b2ba:backsub");

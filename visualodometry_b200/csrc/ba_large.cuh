@@ -132,7 +132,7 @@ int large_init_ctrl(const LargeData& d, const Params& P, cudaStream_t s);
 // enqueue one LM iteration (nranks > 1: the peer-memory exchanges are part of the kernels)
 // ev: null, or 7 events recorded at the phase boundaries (include/b2ba.h B2BA_T_*)
 int large_iteration(const LargeData& d, const Params& P, int pcg_max_iters, double pcg_tol, cudaStream_t s, cudaEvent_t* ev = nullptr);
-int large_pcg_dist_grid(int n, int* blocks, size_t* smem);   // cooperative launch geometry of the distributed PCG
+int large_pcg_dist_grid(int n, int nranks, int* blocks, size_t* smem);   // cooperative launch geometry of the distributed PCG
 int large_finish(const LargeData& d, cudaStream_t s);
 int large_pcg_grid(int n, int* blocks, size_t* smem);   // cooperative launch geometry
 // exact banded Cholesky solve of S dc = -g_red (ba_band.cu); needs d.bw >= 0
