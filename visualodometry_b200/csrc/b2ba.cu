@@ -1064,6 +1064,8 @@ int b2ba_optimize_batch(b2ba_t* h, int32_t B, const int32_t* cam_off, const int3
   auto bail = [&](int rc) {
     cudaStreamSynchronize(h->pipe_copy); cudaStreamSynchronize(h->pipe_solve);
     cudaStreamSynchronize(h->pipe_solve2); cudaStreamSynchronize(h->pipe_back);
+    for (cudaEvent_t e : tev) cudaEventDestroy(e);
+    tev.clear();
     return rc;
   };
 #define CUB(x, where) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) return bail(cuda_fail(h, e_, where)); } while (0)
